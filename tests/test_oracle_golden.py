@@ -1,0 +1,106 @@
+"""Pin the CPU oracle (oracle/goalnet_oracle.py) against vectors produced by the reference's own code
+(tests/golden/*.npz, made by oracle/gen_golden.py from /root/reference/utils.py)."""
+import numpy as np
+import pytest
+
+from oracle import goalnet_oracle as O
+from cvml_goalnet_b200 import synthetic as syn
+
+
+def test_preprocess_matches_reference_arithmetic(golden):
+    g = golden("preprocess")
+    for name in ("down", "down2", "up", "flat"):
+        fr, ref = g[f"{name}_frames"], g[f"{name}_out"]
+        lit = O.extract_condensed_frame_tensor_array(fr, 40, literal=True)
+        np.testing.assert_array_equal(lit, ref)                  # same cv2 call -> bit-exact
+        closed = O.extract_condensed_frame_tensor_array(fr, 40)
+        assert closed.shape == ref.shape and closed.dtype == np.float32
+        assert np.abs(closed - ref).max() <= 5e-7, name           # closed form vs cv2: <= 5e-7 abs
+
+
+def test_preprocess_matches_reference_function_on_file(golden):
+    g = golden("preprocess")
+    if "file_out" not in g.files:
+        pytest.skip("video-file golden not generated")
+    skip = int(g["file_skip_frames"])
+    dec = g["file_decoded_frames"]
+    assert int(g["file_full_n_frames"]) == len(dec)             # count-1 == number of decoded frames
+    out = O.extract_condensed_frame_tensor_array(dec[::skip], 40)
+    assert np.abs(out - g["file_out"]).max() <= 5e-7
+
+
+def test_model_forward_matches_reference_avm(golden):
+    g = golden("model")
+    for tag, audio_included, gain in (("av", True, 1.0), ("v", False, 1.0), ("av_gain", True, 100.0)):
+        w = syn.make_weights(seed=0, audio_included=audio_included, score_gain=gain)
+        assert sorted(w.keys()) == list(g[f"{tag}_keys"])        # state_dict contract
+        y, feats = O.avm_forward(w, g["audio_input"], g["visual_input"], audio_included, return_features=True)
+        np.testing.assert_allclose(y.numpy(), g[f"{tag}_scores"], rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(feats["visual_features"].numpy(), g[f"{tag}_visual_features"], rtol=1e-4, atol=1e-5)
+        for k in ("vis1", "vis2", "vis3"):
+            np.testing.assert_allclose(feats[k].numpy()[:2], g[f"{tag}_{k}"], rtol=1e-4, atol=1e-5)
+        if audio_included:
+            np.testing.assert_allclose(feats["audio_features"].numpy(), g[f"{tag}_audio_features"], rtol=1e-4, atol=1e-4)
+    # the gain variant must actually spread the scores, otherwise rounding tests are vacuous
+    assert g["av_gain_scores"].std() > 0.05
+
+
+def test_expand_array(golden):
+    g = golden("integer_path")
+    for name in ("trunc", "pad", "ident", "exact"):
+        rate, length = g[f"expand_{name}_args"]
+        out = O.expand_array(g[f"expand_{name}_in"].tolist(), int(rate), int(length))
+        assert list(out) == g[f"expand_{name}_out"].tolist()
+
+
+def test_knapsack_literal_and_rows(golden):
+    g = golden("integer_path")
+    for i in range(int(g["knap_n"])):
+        v, w, c = g[f"knap_{i}_values"].tolist(), g[f"knap_{i}_weights"].tolist(), int(g[f"knap_{i}_cap"])
+        ref = g[f"knap_{i}_sel"].tolist()
+        assert O.knapsack(v, w, c) == ref, i
+        assert O.knapsack_rows(v, w, c) == ref, i
+
+
+def test_clip_information(golden):
+    g = golden("integer_path")
+    v, l, _ = O.get_clip_information(g["clip_cps"].tolist(), g["clip_imp"].tolist())
+    assert v == g["clip_values"].tolist() and l == g["clip_lengths"].tolist()
+
+
+def test_fscore(golden):
+    g = golden("integer_path")
+    fa, fm = O.get_fscore(g["fs_G"], g["fs_S"])
+    assert [fa, fm] == g["fs_avg_max"].tolist()                  # bit-exact float64
+    fa0, fm0 = O.get_fscore(g["fs_G"], np.zeros_like(g["fs_S"]))
+    assert [fa0, fm0] == g["fs_empty_avg_max"].tolist()
+
+
+def test_postprocess(golden):
+    g = golden("postprocess")
+    for name in ("a", "b", "c"):
+        skip, n_raw = (int(x) for x in g[f"{name}_args"])
+        for fast in (True, False):
+            _, ind = O.postprocess_array(g[f"{name}_scores"], skip, n_raw, g[f"{name}_cps"], fast=fast)
+            np.testing.assert_array_equal(ind, g[f"{name}_indicator"])
+        assert 0 < ind.sum() < n_raw
+
+
+def test_audio_features_literal_loop(golden):
+    g = golden("audio")
+    for name in ("int", "ragged", "b16"):
+        sr, n_frames, B = (int(x) for x in g[f"{name}_args"])
+        out = O.extract_audio_features_array(g[f"{name}_y"], sr, n_frames, B)
+        assert out.shape == (n_frames, 30, B) and out.dtype == np.float64
+        np.testing.assert_array_equal(out, g[f"{name}_features"])
+    np.testing.assert_array_equal(O.mfcc(g["mfcc_y"], 16000), g["mfcc_out"])
+
+
+def test_cubic_resample_is_linear_operator(golden):
+    g = golden("audio")
+    sr, n_frames, B = (int(x) for x in g["int_args"])
+    y = g["int_y"]
+    for i, (s, e) in enumerate(O.segment_bounds(len(y), n_frames)):
+        m = O.mfcc(y[s:e], sr).astype(np.float64)
+        W = O.cubic_resample_matrix(m.shape[1], B)
+        np.testing.assert_allclose(m @ W.T, g["int_features"][i], rtol=1e-10, atol=1e-9)
