@@ -165,10 +165,10 @@ def gen_postprocess(R):
     """utils.py:606-643 executed literally with an in-memory stand-in for the two HDF5 files."""
     import torch
     out = {}
-    cases = {"a": (120, 15, 1800), "b": (77, 30, 2290), "c": (50, 1, 50)}
-    for name, (N, skip, n_raw) in cases.items():
+    cases = {"a": (120, 15, 1800, 20, 200), "b": (77, 30, 2290, 20, 200), "c": (50, 1, 50, 2, 8)}
+    for name, (N, skip, n_raw, lo, hi) in cases.items():
         scores = syn.make_scores(N, seed=len(out))
-        cps = syn.make_change_points(n_raw, seed=len(out) + 1, lo=20, hi=200)
+        cps = syn.make_change_points(n_raw, seed=len(out) + 1, lo=lo, hi=hi)
 
         class FakeFile(dict):
             def __enter__(self):
