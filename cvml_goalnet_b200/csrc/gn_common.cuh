@@ -1,0 +1,78 @@
+// Shared declarations for the goalnet_b200 CUDA sources (sm_100a only).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/goalnet_b200.h"
+
+struct gn_handle {
+    int device;
+    int num_sms;
+    int64_t launches;
+    // cuTensorMapEncodeTiled, resolved through cudaGetDriverEntryPoint so that the library does not
+    // link against libcuda (it must load, and export its symbols, on a box without a driver).
+    void* encode_tiled;
+};
+
+#define GN_CUDA(expr)                                   \
+    do {                                                \
+        cudaError_t _e = (expr);                        \
+        if (_e != cudaSuccess) return (int)_e;          \
+    } while (0)
+
+#define GN_LAUNCHED(h)                                  \
+    do {                                                \
+        (h)->launches++;                                \
+        cudaError_t _e = cudaGetLastError();            \
+        if (_e != cudaSuccess) return (int)_e;          \
+    } while (0)
+
+static inline cudaStream_t gn_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---- model object ------------------------------------------------------------------------------
+// Geometry of VisBl at S=40 (reference utils.py:151-164): conv1 k3 s3 p3 -> 15x15, pool -> 13x13,
+// conv2 p1 -> 13x13, pool -> 11x11, conv3 p1 -> 11x11, pool -> 9x9, flatten 512*81 = 41472.
+struct gn_model {
+    gn_handle* h;
+    int audio_included, S, B;
+    int C1, P1, P2, P3;          // 15, 13, 11, 9
+    int L1, L2;                  // AudBl lengths 15, 8
+    int fin;                     // 640 or 512
+    // fp32 (CUDA-core layers)
+    float *conv1_w, *conv1_b;    // [27][64] (k-major: (ky,kx,ci) x co), [64]
+    float *bn_scale[3], *bn_shift[3];   // gamma/sqrt(var+eps), beta - mean*scale
+    float *conv2_b, *conv3_b, *linear5_b;
+    float *aconv1_w, *aconv1_b, *aconv2_w, *aconv2_b, *alinear3_w, *alinear3_b;
+    float *f_b[4];               // fusion.0/3/6/9 biases
+    float *f12_w, *f12_b;        // [128], [1]
+    // bf16 K-major GEMM operands: [N_out][K]
+    __nv_bfloat16 *conv2_wk;     // [256][9*64]    k = (ky*3+kx)*64 + ci
+    __nv_bfloat16 *conv3_wk;     // [512][9*256]
+    __nv_bfloat16 *linear5_wk;   // [512][81*512]  k = p*512 + c   (reference flatten is c*81 + p)
+    __nv_bfloat16 *f_wk[4];      // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
+    void* arena;                 // one allocation backing everything above
+};
+
+// Workspace layout for n frames (all bf16 unless noted); offsets are computed by gn_ws_layout().
+struct gn_ws {
+    __nv_bfloat16* a1p;   // [n][15][15][64]   block-1 output, zero border (conv2 input)
+    __nv_bfloat16* a2p;   // [n][13][13][256]  block-2 output, zero border (conv3 input)
+    __nv_bfloat16* a3;    // [n][81][512]      block-3 output, (p, c) order (linear5 input)
+    __nv_bfloat16* h0;    // [n][fin]          [audio128 | visual512]
+    __nv_bfloat16* h1;    // [n][512]
+    __nv_bfloat16* h2;    // [n][512]
+    __nv_bfloat16* h3;    // [n][256]
+    int64_t bytes;
+};
+gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
+
+// ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
+int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);
+int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st);
+int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
+                          cudaStream_t st);
+int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
+                            cudaStream_t st);

@@ -1,0 +1,183 @@
+// (a2) audio features: per frame-slot STFT(2048/512, hann, centred) -> |.|^2 -> 128 Slaney mels ->
+// 10 log10 with an 80 dB floor under the segment max -> DCT-II ortho (30 rows) -> cubic time
+// resampling W (B x q).  Replaces reference utils.py:322-349 (librosa.feature.mfcc + interp1d loop).
+//
+// One CTA per slot.  Two STFT columns share one complex 2048-point FFT (column j in the real part,
+// column j+1 in the imaginary part), radix-2 DIF in shared memory; mel sums and the segment max are
+// warp-shuffle reductions.  HBM traffic is the slot's samples in and 30*B floats out.
+#include "gn_common.cuh"
+
+namespace {
+
+constexpr int kFFT = 2048;
+constexpr int kLog2FFT = 11;
+constexpr int kHop = 512;
+constexpr int kMels = 128;
+constexpr int kMfcc = 30;
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads)
+mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, const int32_t* __restrict__ seg_len,
+            const int32_t* __restrict__ w_offset, const float* __restrict__ w_all, int64_t n, int B, int max_q,
+            const int32_t* __restrict__ mel_start, const int32_t* __restrict__ mel_count,
+            const int32_t* __restrict__ mel_offset, const float* __restrict__ mel_w,
+            const float* __restrict__ dct, const float2* __restrict__ twiddle, const float* __restrict__ hann,
+            float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* z = reinterpret_cast<float2*>(smem_raw);            // [2048] FFT buffer
+    float2* tw = z + kFFT;                                       // [1024] twiddles
+    float* pw0 = reinterpret_cast<float*>(tw + kFFT / 2);        // [1025] power of column j
+    float* pw1 = pw0 + (kFFT / 2 + 1);                           // [1025] power of column j+1
+    float* mel = pw1 + (kFFT / 2 + 1);                           // [128][max_q] log-mel
+    float* cep = mel + kMels * max_q;                            // [30][max_q]
+    __shared__ float red[kThreads / 32];
+    __shared__ float s_max;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < kFFT / 2; i += kThreads) tw[i] = twiddle[i];
+
+    for (int64_t slot = blockIdx.x; slot < n; slot += gridDim.x) {
+        const int64_t s0 = seg_start[slot];
+        const int L = seg_len[slot];
+        const int q = 1 + L / kHop;
+        const float* seg = y + s0;
+        __syncthreads();
+        for (int j = 0; j < q; j += 2) {
+            const bool two = (j + 1 < q);
+            // windowed columns j (re) and j+1 (im); samples outside [0,L) are the centre zero padding
+            for (int t = tid; t < kFFT; t += kThreads) {
+                const float w = hann[t];
+                const int i0 = j * kHop - kFFT / 2 + t;
+                const int i1 = i0 + kHop;
+                float a = (i0 >= 0 && i0 < L) ? seg[i0] * w : 0.f;
+                float b = (two && i1 >= 0 && i1 < L) ? seg[i1] * w : 0.f;
+                z[t] = make_float2(a, b);
+            }
+            __syncthreads();
+            // radix-2 decimation-in-frequency, in place; output index is bit-reversed
+#pragma unroll 1
+            for (int s = 0; s < kLog2FFT; ++s) {
+                const int m = kFFT >> (s + 1);
+                for (int bfly = tid; bfly < kFFT / 2; bfly += kThreads) {
+                    const int pos = bfly & (m - 1);
+                    const int i = ((bfly - pos) << 1) + pos;
+                    const float2 a = z[i], c = z[i + m];
+                    const float2 wv = tw[pos << s];
+                    const float dx = a.x - c.x, dy = a.y - c.y;
+                    z[i] = make_float2(a.x + c.x, a.y + c.y);
+                    z[i + m] = make_float2(dx * wv.x - dy * wv.y, dx * wv.y + dy * wv.x);
+                }
+                __syncthreads();
+            }
+            // split the two real spectra: X1[k] = (Z[k] + conj Z[N-k])/2, X2[k] = (Z[k] - conj Z[N-k])/(2i)
+            for (int k = tid; k <= kFFT / 2; k += kThreads) {
+                const float2 zk = z[__brev((unsigned)k) >> (32 - kLog2FFT)];
+                const float2 zn = z[__brev((unsigned)((kFFT - k) & (kFFT - 1))) >> (32 - kLog2FFT)];
+                const float x1r = 0.5f * (zk.x + zn.x), x1i = 0.5f * (zk.y - zn.y);
+                const float x2r = 0.5f * (zk.y + zn.y), x2i = -0.5f * (zk.x - zn.x);
+                pw0[k] = x1r * x1r + x1i * x1i;
+                pw1[k] = x2r * x2r + x2i * x2i;
+            }
+            __syncthreads();
+            // mel filterbank: one warp per mel band, lanes stride over the band's bins
+            for (int mband = warp; mband < kMels; mband += kThreads / 32) {
+                const int st = mel_start[mband], cnt = mel_count[mband];
+                const float* wv = mel_w + mel_offset[mband];
+                float a0 = 0.f, a1 = 0.f;
+                for (int i = lane; i < cnt; i += 32) {
+                    const float w = wv[i];
+                    a0 = fmaf(w, pw0[st + i], a0);
+                    a1 = fmaf(w, pw1[st + i], a1);
+                }
+                a0 = warp_sum(a0);
+                a1 = warp_sum(a1);
+                if (lane == 0) {
+                    mel[mband * max_q + j] = a0;
+                    if (two) mel[mband * max_q + j + 1] = a1;
+                }
+            }
+            __syncthreads();
+        }
+        // power_to_db: 10 log10(max(1e-10, S)), floored at (segment max - 80 dB)
+        float lmax = -INFINITY;
+        for (int i = tid; i < kMels * q; i += kThreads) {
+            const int mband = i / q, j = i - mband * q;
+            const float v = 10.f * log10f(fmaxf(1e-10f, mel[mband * max_q + j]));
+            mel[mband * max_q + j] = v;
+            lmax = fmaxf(lmax, v);
+        }
+        lmax = warp_max(lmax);
+        if (lane == 0) red[warp] = lmax;
+        __syncthreads();
+        if (warp == 0) {
+            float v = lane < kThreads / 32 ? red[lane] : -INFINITY;
+            v = warp_max(v);
+            if (lane == 0) s_max = v;
+        }
+        __syncthreads();
+        const float floor_db = s_max - 80.f;
+        // DCT-II ortho over the mel axis: cep[c][j] = sum_m dct[c][m] * max(logmel[m][j], floor)
+        for (int i = tid; i < kMfcc * q; i += kThreads) {
+            const int c = i / q, j = i - c * q;
+            const float* d = dct + c * kMels;
+            float acc = 0.f;
+#pragma unroll 8
+            for (int mband = 0; mband < kMels; ++mband)
+                acc = fmaf(d[mband], fmaxf(mel[mband * max_q + j], floor_db), acc);
+            cep[c * max_q + j] = acc;
+        }
+        __syncthreads();
+        // cubic time resampling (utils.py:336-343) as the linear operator W (B x q)
+        const float* W = w_all + w_offset[slot];
+        float* o = out + slot * (int64_t)(kMfcc * B);
+        for (int i = tid; i < kMfcc * B; i += kThreads) {
+            const int c = i / B, b = i - c * B;
+            float acc = 0.f;
+            for (int j = 0; j < q; ++j) acc = fmaf(W[b * q + j], cep[c * max_q + j], acc);
+            o[i] = acc;
+        }
+    }
+}
+
+}  // namespace
+
+struct gn_mfcc_tables { const float2* twiddle; const float* hann; };
+gn_mfcc_tables gn_get_mfcc_tables(gn_handle* h);   // gn_api.cu
+
+extern "C" int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_samples, const int64_t* d_seg_start,
+                                 const int32_t* d_seg_len, const int32_t* d_w_offset, const float* d_w, int64_t n,
+                                 int B, int max_q, const int32_t* d_mel_start, const int32_t* d_mel_count,
+                                 const int32_t* d_mel_offset, const float* d_mel_w, const float* d_dct,
+                                 float* d_out, void* stream) {
+    if (!h || n < 0 || n_samples < 0 || B <= 0) return GN_E_ARG;
+    if (max_q < 1 || max_q > GN_MFCC_MAX_Q || B > 4096) return GN_E_SHAPE;
+    if (n == 0) return GN_OK;
+    if (!d_y || !d_seg_start || !d_seg_len || !d_w_offset || !d_w || !d_mel_start || !d_mel_count ||
+        !d_mel_offset || !d_mel_w || !d_dct || !d_out) return GN_E_ARG;
+    const gn_mfcc_tables t = gn_get_mfcc_tables(h);
+    const size_t smem = sizeof(float2) * (kFFT + kFFT / 2) + sizeof(float) * (2 * (kFFT / 2 + 1)) +
+                        sizeof(float) * (size_t)(kMels + kMfcc) * max_q + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_set = true;
+    }
+    const int64_t max_grid = (int64_t)h->num_sms * 4;
+    const int grid = (int)(n < max_grid ? n : max_grid);
+    mfcc_kernel<<<grid, kThreads, smem, gn_stream(stream)>>>(
+        d_y, d_seg_start, d_seg_len, d_w_offset, d_w, n, B, max_q, d_mel_start, d_mel_count, d_mel_offset,
+        d_mel_w, d_dct, t.twiddle, t.hann, d_out);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}

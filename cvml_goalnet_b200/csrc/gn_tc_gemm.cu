@@ -1,0 +1,430 @@
+// Tensor-core layers of the AVM forward (reference utils.py:179-191 and 242-258) as persistent,
+// warp-specialised tcgen05 kernels:
+//   * implicit-GEMM 3x3/s1/p1 convolution (conv2, conv3) with the bias + ReLU + MaxPool(3,1) +
+//     BatchNorm(eval) block fused into the epilogue;
+//   * K-major GEMM  C = relu(A . W^T + b)  (linear5, fusion.0/3/6), and the same with the last
+//     layer (fusion.12), the sigmoid and 4y+1 folded in (fusion.9 -> scores).
+// Operands are bf16, staged by TMA into 128B-swizzled shared memory, multiplied by
+// tcgen05.mma (cta_group::1, M=128) into fp32 accumulators in TMEM (two 256-column buffers so that
+// the epilogue of tile i overlaps the MMAs of tile i+1), and read back with tcgen05.ld.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).
+#include "gn_common.cuh"
+#include "gn_tc_ptx.cuh"
+
+namespace {
+
+using namespace tcx;
+
+constexpr int kThreads = 192;
+constexpr int kBK = 64;                  // bf16 elements per k-step = one 128-byte swizzle row
+constexpr int kTmemCols = 512;
+constexpr int kAccCols = 256;            // columns per accumulator buffer (MT * BN)
+
+enum Mode { kConv = 0, kLinear = 1, kScore = 2 };
+
+struct ConvGeom {
+    int OH, OW;        // conv output == input interior (k3 s1 p1)
+    int P;             // pooled size OH-2
+    int out_pad;       // 1: write into a (P+2)x(P+2) zero-bordered buffer; 0: dense PxP
+    int cin_blocks;    // Cin / 64
+    int cout;          // total output channels
+};
+
+struct GemmArgs {
+    int64_t M;               // rows (frames) for linear modes; frames for conv
+    int N, K;                // N = total output features, K = reduction length
+    const float* bias;       // [N]
+    const float* bn_scale;   // conv: [N]
+    const float* bn_shift;   // conv: [N]
+    __nv_bfloat16* out;      // conv: activation buffer; linear: [M][ld_out]
+    int ld_out, col_off;     // linear: leading dimension and first column of the output
+    float* out_f32;          // linear: optional fp32 copy [M][N]
+    const float* w_last;     // score: fusion.12 weight [128]
+    const float* b_last;     // score: fusion.12 bias [1]
+    float* scores;           // score: [M]
+    ConvGeom g;
+};
+
+template <int MT, int BN, int STAGES, int MODE>
+struct Cfg {
+    static constexpr int kABytes = MT * 128 * 128;          // MT x 128 rows x 128 B
+    static constexpr int kBBytes = BN * 128;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStgStride = BN * 2 + 16;          // padded bf16 row of the pooling stage
+    static constexpr int kStgBytes = (MODE == kConv) ? (MT * 128 * kStgStride) : 0;
+    static constexpr int kSmemBytes = 1024 /*align slack*/ + STAGES * kStageBytes + kStgBytes + 256 /*barriers*/;
+    static_assert(MT * BN <= kAccCols, "an accumulator buffer is at most 256 TMEM columns");
+    static_assert(MODE == kConv || MT == 1, "linear modes use one 128-row M tile");
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int MT, int BN, int STAGES, int MODE>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmArgs args) {
+    using C = Cfg<MT, BN, STAGES, MODE>;
+    extern __shared__ unsigned char smem_raw[];
+    // 1024-byte alignment: SWIZZLE_128B atoms are 8 rows x 128 B and the swizzle is address based.
+    unsigned char* smem = reinterpret_cast<unsigned char*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    unsigned char* stage_base = smem;
+    unsigned char* stg = smem + STAGES * C::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stg + C::kStgBytes);
+    uint64_t* full_bar = bars;                    // [STAGES]
+    uint64_t* empty_bar = bars + STAGES;          // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int n_blocks = args.N / BN;
+    const int64_t m_blocks = (MODE == kConv) ? args.M : (args.M + 127) / 128;
+    const int64_t num_tiles = m_blocks * n_blocks;
+    const int k_iters = args.K / kBK;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_a);
+        prefetch_tmap(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(smem_u32(&full_bar[s]), 1);
+            mbar_init(smem_u32(&empty_bar[s]), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(&tfull_bar[b]), 1);
+            mbar_init(smem_u32(&tempty_bar[b]), 4);   // one arrive per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int64_t m_blk = tile / n_blocks;
+                const int n_blk = (int)(tile - m_blk * n_blocks);
+                for (int kt = 0; kt < k_iters; ++kt) {
+                    mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+                    const uint32_t fb = smem_u32(&full_bar[stage]);
+                    const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                    const uint32_t sb = sa + C::kABytes;
+                    if (MODE == kConv) {
+                        const int tap = kt / args.g.cin_blocks;
+                        const int cb = kt - tap * args.g.cin_blocks;
+                        const int ky = tap / 3, kx = tap - ky * 3;
+                        mbar_expect_tx(fb, (uint32_t)(args.g.OH * args.g.OW * 128 + C::kBBytes));
+                        // box (64 ch, OW, OH, 1 frame) of the zero-bordered NHWC input, shifted by the tap
+                        tma_load_4d(sa, &tmap_a, fb, cb * kBK, kx, ky, (int)m_blk);
+                    } else {
+                        mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
+                        tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
+                    }
+                    tma_load_2d(sb, &tmap_b, fb, kt * kBK, n_blk * BN);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+        int stage = 0;
+        uint32_t phase = 0;
+        int ab = 0;
+        uint32_t aphase = 0;
+        for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            mbar_wait(smem_u32(&tempty_bar[ab]), aphase ^ 1);     // epilogue drained this buffer
+            tc_fence_after();
+            for (int kt = 0; kt < k_iters; ++kt) {
+                mbar_wait(smem_u32(&full_bar[stage]), phase);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                    const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) {
+                        const uint32_t d = tmem_base + (uint32_t)(ab * kAccCols + mt * BN);
+#pragma unroll
+                        for (int k4 = 0; k4 < kBK / 16; ++k4) {
+                            const uint64_t ad = make_desc_sw128(sa + mt * (128 * 128) + k4 * 32);
+                            const uint64_t bd = make_desc_sw128(sb + k4 * 32);
+                            umma_bf16(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(smem_u32(&empty_bar[stage]));              // smem slot free when MMAs retire
+                    if (kt == k_iters - 1) umma_commit(smem_u32(&tfull_bar[ab]));  // accumulator ready
+                }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            if (++ab == 2) { ab = 0; aphase ^= 1; }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int q = warp & 3;                     // TMEM lane quarter this warp may read
+        const int row = q * 32 + lane;              // accumulator row owned by this thread
+        const int et = (warp - 2) * 32 + lane;      // 0..127 among epilogue threads
+        int ab = 0;
+        uint32_t aphase = 0;
+        for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int64_t m_blk = tile / n_blocks;
+            const int n_blk = (int)(tile - m_blk * n_blocks);
+            const int n0 = n_blk * BN;
+            mbar_wait(smem_u32(&tfull_bar[ab]), aphase);
+            tc_fence_after();
+            const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * kAccCols);
+
+            if (MODE == kConv) {
+                const int npix = args.g.OH * args.g.OW;
+#pragma unroll 1
+                for (int mt = 0; mt < MT; ++mt) {
+                    const int pix = mt * 128 + row;
+#pragma unroll 1
+                    for (int c = 0; c < BN / 32; ++c) {
+                        uint32_t r[32];
+                        tmem_ld32(tbase + (uint32_t)(mt * BN + c * 32), r);
+                        tmem_ld_wait();
+                        if (pix < npix) {
+                            const float* bp = args.bias + n0 + c * 32;
+                            uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)pix * C::kStgStride + c * 64);
+#pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                uint32_t w[4];
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    const int i = v * 8 + e * 2;
+                                    const float x0 = fmaxf(__uint_as_float(r[i]) + __ldg(bp + i), 0.f);
+                                    const float x1 = fmaxf(__uint_as_float(r[i + 1]) + __ldg(bp + i + 1), 0.f);
+                                    w[e] = pack_bf16(x0, x1);
+                                }
+                                dst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));      // TMEM buffer may be overwritten
+                asm volatile("bar.sync 1, 128;" ::: "memory");               // staging tile complete
+                // MaxPool(3, stride 1) over the ReLU'd tile, then BatchNorm affine, bf16 store.
+                const int P = args.g.P, OW = args.g.OW;
+                const int PW = P + 2 * args.g.out_pad;
+                constexpr int kPairs = BN / 2;
+                __nv_bfloat16* obase = args.out + (size_t)m_blk * PW * PW * args.g.cout + n0;
+                for (int item = et; item < P * P * kPairs; item += 128) {
+                    const int op = item / kPairs, cp = item - op * kPairs;
+                    const int oy = op / P, ox = op - oy * P;
+                    const unsigned char* s0 = stg + (size_t)(oy * OW + ox) * C::kStgStride + cp * 4;
+                    __nv_bfloat162 m = *reinterpret_cast<const __nv_bfloat162*>(s0);
+#pragma unroll
+                    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) {
+                            if (dy == 0 && dx == 0) continue;
+                            m = __hmax2(m, *reinterpret_cast<const __nv_bfloat162*>(
+                                               s0 + (size_t)(dy * OW + dx) * C::kStgStride));
+                        }
+                    const float2 sc = __ldg(reinterpret_cast<const float2*>(args.bn_scale + n0) + cp);
+                    const float2 sh = __ldg(reinterpret_cast<const float2*>(args.bn_shift + n0) + cp);
+                    const float2 mf = __bfloat1622float2(m);
+                    const uint32_t o = pack_bf16(fmaf(mf.x, sc.x, sh.x), fmaf(mf.y, sc.y, sh.y));
+                    const int opix = (oy + args.g.out_pad) * PW + ox + args.g.out_pad;
+                    *reinterpret_cast<uint32_t*>(obase + (size_t)opix * args.g.cout + cp * 2) = o;
+                }
+                if (args.g.out_pad) {   // zero border of the next conv's input (padding = 1)
+                    const int nborder = 4 * PW - 4;
+                    for (int item = et; item < nborder * kPairs; item += 128) {
+                        const int bi = item / kPairs, cp = item - bi * kPairs;
+                        int by, bx;
+                        if (bi < PW) { by = 0; bx = bi; }
+                        else if (bi < 2 * PW) { by = PW - 1; bx = bi - PW; }
+                        else { const int t = bi - 2 * PW; by = 1 + (t >> 1); bx = (t & 1) ? PW - 1 : 0; }
+                        *reinterpret_cast<uint32_t*>(obase + (size_t)(by * PW + bx) * args.g.cout + cp * 2) = 0u;
+                    }
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");               // staging tile may be reused
+            } else {
+                const int64_t grow = m_blk * 128 + row;
+                float dot = 0.f;
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld32(tbase + (uint32_t)(c * 32), r);
+                    tmem_ld_wait();
+                    const float* bp = args.bias + n0 + c * 32;
+                    float x[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) x[i] = fmaxf(__uint_as_float(r[i]) + __ldg(bp + i), 0.f);
+                    if (MODE == kScore) {
+                        const float* wl = args.w_last + n0 + c * 32;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) dot = fmaf(x[i], __ldg(wl + i), dot);
+                    } else if (grow < args.M) {
+                        uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
+                                                              n0 + c * 32);
+#pragma unroll
+                        for (int v = 0; v < 4; ++v)
+                            dst[v] = make_uint4(pack_bf16(x[v * 8], x[v * 8 + 1]), pack_bf16(x[v * 8 + 2], x[v * 8 + 3]),
+                                                pack_bf16(x[v * 8 + 4], x[v * 8 + 5]), pack_bf16(x[v * 8 + 6], x[v * 8 + 7]));
+                        if (args.out_f32) {
+                            float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)grow * args.N + n0 + c * 32);
+#pragma unroll
+                            for (int v = 0; v < 8; ++v) {
+                                // the fp32 copy carries the bf16-rounded values the next layer consumes
+                                df[v] = make_float4(__bfloat162float(__float2bfloat16(x[v * 4])),
+                                                    __bfloat162float(__float2bfloat16(x[v * 4 + 1])),
+                                                    __bfloat162float(__float2bfloat16(x[v * 4 + 2])),
+                                                    __bfloat162float(__float2bfloat16(x[v * 4 + 3])));
+                            }
+                        }
+                    }
+                }
+                if (MODE == kScore && grow < args.M) {
+                    const float zlin = dot + __ldg(args.b_last);
+                    args.scores[grow] = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;   // utils.py:256,270
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));
+            }
+            if (++ab == 2) { ab = 0; aphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_tmap(gn_handle* h, CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box) {
+    if (!h->encode_tiled) return GN_E_NODEVICE;
+    cuuint64_t gdim[5], gstr[4];
+    cuuint32_t bx[5], es[5];
+    for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+    for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
+    CUresult r = reinterpret_cast<EncodeTiledFn>(h->encode_tiled)(
+        m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? GN_OK : (int)r;
+}
+
+// [rows][K] bf16 row-major -> 2-D map, box (64, box_rows)
+int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, int64_t K, int64_t ld, int box_rows) {
+    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+    const uint64_t str[1] = {(uint64_t)ld * 2};
+    const uint32_t box[2] = {(uint32_t)kBK, (uint32_t)box_rows};
+    return make_tmap(h, m, base, 2, dims, str, box);
+}
+
+template <int MT, int BN, int STAGES, int MODE>
+int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
+           cudaStream_t st) {
+    using C = Cfg<MT, BN, STAGES, MODE>;
+    auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE>;
+    static bool attr = false;
+    if (!attr) {
+        GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+        attr = true;
+    }
+    const int grid = (int)(tiles < h->num_sms ? tiles : h->num_sms);
+    if (grid <= 0) return GN_OK;
+    kern<<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, a);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}
+
+// conv block: in = zero-bordered NHWC [n][OH+2][OW+2][Cin]; weights K-major [Cout][9*Cin]
+template <int MT, int BN, int STAGES>
+int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int OH, int Cin, const __nv_bfloat16* wk, int Cout,
+             const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad, cudaStream_t st) {
+    CUtensorMap ta, tb;
+    const int IW = OH + 2;
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)IW, (uint64_t)IW, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)IW * Cin * 2, (uint64_t)IW * IW * Cin * 2};
+    const uint32_t box[4] = {(uint32_t)kBK, (uint32_t)OH, (uint32_t)OH, 1};
+    int rc = make_tmap(m->h, &ta, in, 4, dims, str, box);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, Cout, 9 * Cin, 9 * Cin, BN);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = n; a.N = Cout; a.K = 9 * Cin;
+    a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
+    a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
+    if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
+    return launch<MT, BN, STAGES, kConv>(m->h, ta, tb, a, n * (Cout / BN), st);
+}
+
+template <int BN, int STAGES, int MODE>
+int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, const __nv_bfloat16* wk, int N,
+               const float* bias, __nv_bfloat16* out, int ld_out, int col_off, float* out_f32, const float* w_last,
+               const float* b_last, float* scores, cudaStream_t st) {
+    if (K % kBK || N % BN) return GN_E_SHAPE;
+    CUtensorMap ta, tb;
+    int rc = make_tmap_2d(m->h, &ta, A, M, K, lda, 128);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = ld_out; a.col_off = col_off;
+    a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores;
+    return launch<1, BN, STAGES, MODE>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
+}
+
+}  // namespace
+
+// conv2 -> conv3 -> linear5 -> fusion MLP -> scores, all on the tensor cores.
+int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
+                          cudaStream_t st) {
+    int rc;
+    // block 2: conv2 (64 -> 256) on 13x13, pool -> 11x11, written with a zero border for conv3
+    rc = run_conv<2, 128, 3>(m, n, ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
+                             ws.a2p, 1, st);
+    if (rc) return rc;
+    // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
+    rc = run_conv<1, 256, 3>(m, n, ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
+                             ws.a3, 0, st);
+    if (rc) return rc;
+    const int K5 = m->P3 * m->P3 * 512;
+    const int aoff = m->audio_included ? 128 : 0;
+    // linear5 + ReLU -> columns [aoff, aoff+512) of the fusion input (audio features occupy [0,128))
+    rc = run_linear<256, 4, kLinear>(m, n, ws.a3, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff,
+                                     d_visfeat, nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+    rc = run_linear<256, 4, kLinear>(m, n, ws.h0, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr,
+                                     nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+    rc = run_linear<256, 4, kLinear>(m, n, ws.h1, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr,
+                                     nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+    rc = run_linear<256, 4, kLinear>(m, n, ws.h2, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr,
+                                     nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+    // fusion.9 + ReLU + fusion.12 + sigmoid + 4y+1 -> scores
+    rc = run_linear<128, 4, kScore>(m, n, ws.h3, 256, 256, m->f_wk[3], 128, m->f_b[3], nullptr, 0, 0, nullptr,
+                                    m->f12_w, m->f12_b, d_scores, st);
+    return rc;
+}

@@ -1,0 +1,562 @@
+"""Drop-in mirror of the reference's `utils.py` for the per-frame scoring path.
+
+Same names, argument meaning and error convention (`AssertionError('E: ...')`) as the functions
+`main.py:11` / `baseline.py:9` import from the reference's `utils`; the arithmetic runs in the
+sm_100a CUDA kernels behind the C-ABI of include/goalnet_b200.h.  PyTorch is used for device memory
+and streams only.  File-based signatures keep their reference form and delegate, after the I/O, to an
+array-based twin (`*_array`) -- the twins are what the tests, the benchmark and multi-GPU code call.
+
+There is no CPU fallback: every function here needs the native library and a B200.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from functools import lru_cache
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib, dsp
+
+__all__ = [
+    "AVM", "VisBl", "AudBl", "dataloader", "extract_condensed_frame_tensor", "extract_condensed_frame_tensor_array",
+    "extract_audio_features", "extract_audio_features_array", "expand_array", "get_clip_information", "knapsack",
+    "postprocess", "postprocess_array", "get_fscore", "postprocess_and_get_fscores",
+    "postprocess_and_get_fscores_array", "get_frame_tensor",
+]
+
+
+# --------------------------------------------------------------------------------------------------
+# plumbing
+# --------------------------------------------------------------------------------------------------
+def _device(device=None) -> torch.device:
+    if not torch.cuda.is_available():
+        raise _lib.GoalNetError(-4, "device", "no CUDA device: this package has no CPU fallback")
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise _lib.GoalNetError(-4, "device", "a CUDA device is required")
+    return torch.device("cuda", device.index if device.index is not None else torch.cuda.current_device())
+
+
+def _to_dev(x, dtype, device) -> torch.Tensor:
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(np.ascontiguousarray(x))
+    elif not torch.is_tensor(x):
+        x = torch.as_tensor(x)
+    return x.to(device=device, dtype=dtype, non_blocking=True).contiguous()
+
+
+def _ptr(t) -> C.c_void_p:
+    return C.c_void_p(t.data_ptr() if t is not None else 0)
+
+
+def _stream(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _h(device):
+    return _lib.handle(device.index)
+
+
+# --------------------------------------------------------------------------------------------------
+# (a1) frames  -- reference utils.py:274-292
+# --------------------------------------------------------------------------------------------------
+def extract_condensed_frame_tensor_array(frames_u8, S: int = 40, device=None, out=None, as_numpy: bool = False):
+    """Array twin of `extract_condensed_frame_tensor`: uint8 BGR (N,H,W,3) already decoded and
+    subsampled -> float32 (N,3,S,S) on the device (utils.py:284-285,292)."""
+    dev = _device(device if device is not None else (frames_u8.device if torch.is_tensor(frames_u8) and frames_u8.is_cuda else None))
+    fr = _to_dev(frames_u8, torch.uint8, dev)
+    assert fr.dim() == 4 and fr.shape[-1] == 3, "E: frames must have shape (N, H, W, 3)"
+    n, H, W, _ = fr.shape
+    if out is None:
+        out = torch.empty((n, 3, S, S), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().gn_preprocess_u8_bgr(_h(dev), _ptr(fr), n, H, W, S, _ptr(out), None, _stream(dev)),
+                   "gn_preprocess_u8_bgr")
+    return out.cpu().numpy() if as_numpy else out
+
+
+def extract_condensed_frame_tensor(fp: str, skip_frames: int):
+    """utils.py:274-292, same signature and return: (np.ndarray (N,3,40,40) float32, full_n_frames).
+    Decoding is host I/O through OpenCV exactly as in the reference; the arithmetic is on the GPU."""
+    import cv2
+    video = cv2.VideoCapture(fp)
+    count = 0
+    success = True
+    frames = []
+    while success:
+        success, image = video.read()
+        if count % skip_frames == 0 and success:
+            frames.append(image)
+        count += 1
+    full_n_frames = count - 1
+    video.release()
+    if not frames:
+        return np.zeros((0, 3, 40, 40), np.float32), full_n_frames
+    return extract_condensed_frame_tensor_array(np.stack(frames), 40, as_numpy=True), full_n_frames
+
+
+def get_frame_tensor(fp: str):
+    """utils.py:294-305 (pure I/O, kept for `infer`)."""
+    import cv2
+    video = cv2.VideoCapture(fp)
+    frames = []
+    while True:
+        success, image = video.read()
+        if not success:
+            break
+        frames.append(image)
+    return np.array(frames)
+
+
+# --------------------------------------------------------------------------------------------------
+# (a2) audio  -- reference utils.py:313-349
+# --------------------------------------------------------------------------------------------------
+@lru_cache(maxsize=8)
+def _audio_tables(sr: int, dev_index: int):
+    dev = torch.device("cuda", dev_index)
+    start, count, offset, w = dsp.mel_filterbank_csr(int(sr))
+    return dict(start=torch.from_numpy(start).to(dev), count=torch.from_numpy(count).to(dev),
+                offset=torch.from_numpy(offset).to(dev), w=torch.from_numpy(w).to(dev),
+                dct=torch.from_numpy(dsp.dct_matrix()).to(dev))
+
+
+@lru_cache(maxsize=32)
+def _segment_plan(n_samples: int, n_frames: int, B: int, dev_index: int):
+    dev = torch.device("cuda", dev_index)
+    start, length = dsp.segment_bounds(n_samples, n_frames)
+    q = 1 + length // dsp.HOP
+    assert n_frames == 0 or int(q.min()) >= 4, "E: Shape mismatch"   # interp1d(kind='cubic') needs >= 4 columns
+    assert n_frames == 0 or int(q.max()) <= 64, "E: audio segment too long for one frame slot (q > 64)"
+    offs, mats, table = np.zeros(n_frames, np.int32), [], {}
+    pos = 0
+    for qq in np.unique(q):
+        table[int(qq)] = pos
+        mats.append(dsp.cubic_resample_matrix(int(qq), B).reshape(-1))
+        pos += mats[-1].size
+    for i in range(n_frames):
+        offs[i] = table[int(q[i])]
+    wcat = np.concatenate(mats) if mats else np.zeros(1, np.float32)
+    return dict(start=torch.from_numpy(start).to(dev), length=torch.from_numpy(length).to(dev),
+                w_offset=torch.from_numpy(offs).to(dev), w=torch.from_numpy(wcat).to(dev),
+                max_q=int(q.max()) if n_frames else 4)
+
+
+def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, device=None, out=None,
+                                 as_numpy: bool = False):
+    """Array twin of `extract_audio_features` (utils.py:313-349) with `(y, sr)` replacing librosa.load:
+    float32 (N,30,B) MFCC features, cubic-resampled to B columns per frame slot."""
+    dev = _device(device if device is not None else (y.device if torch.is_tensor(y) and y.is_cuda else None))
+    yd = _to_dev(y, torch.float32, dev).reshape(-1)
+    B = int(bin_length)
+    plan = _segment_plan(int(yd.numel()), int(n_frames), B, dev.index)
+    tab = _audio_tables(int(sr), dev.index)
+    if out is None:
+        out = torch.empty((n_frames, dsp.N_MFCC, B), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().gn_mfcc_resampled(
+            _h(dev), _ptr(yd), yd.numel(), _ptr(plan["start"]), _ptr(plan["length"]), _ptr(plan["w_offset"]),
+            _ptr(plan["w"]), n_frames, B, plan["max_q"], _ptr(tab["start"]), _ptr(tab["count"]), _ptr(tab["offset"]),
+            _ptr(tab["w"]), _ptr(tab["dct"]), _ptr(out), _stream(dev)), "gn_mfcc_resampled")
+    return out.cpu().numpy() if as_numpy else out
+
+
+def extract_audio_features(audio_fp: str, n_frames: int, bin_length: int = 30) -> np.ndarray:
+    """utils.py:313-349.  `bin_length` defaults to the paper's B = 30 so that `infer`'s two-argument call
+    (main.py:321, quirk Q2) works.  Loading/resampling the file is librosa's job, as in the reference."""
+    try:
+        import librosa
+    except ImportError as e:  # pragma: no cover - librosa is not in this image
+        raise AssertionError("E: librosa is required to load audio files; use extract_audio_features_array(y, sr, ...)") from e
+    y, sr = librosa.load(audio_fp)
+    feats = extract_audio_features_array(y, sr, n_frames, bin_length, as_numpy=True)
+    assert feats.shape[-1] == bin_length, "E: Shape mismatch"
+    return feats
+
+
+# --------------------------------------------------------------------------------------------------
+# (a3-a5) model  -- reference utils.py:145-272
+# --------------------------------------------------------------------------------------------------
+class VisBl(nn.Module):
+    """Parameter container with the reference's names/shapes (utils.py:145-170), materialised for SxS frames."""
+
+    def __init__(self, S: int = 40):
+        super().__init__()
+        c1 = (S + 6 - 3) // 3 + 1
+        p3 = c1 - 6
+        self.conv1 = nn.Conv2d(3, 64, 3, stride=3, padding=3)
+        self.bnorm1 = nn.BatchNorm2d(64)
+        self.conv2 = nn.Conv2d(64, 256, 3, stride=1, padding=1)
+        self.bnorm2 = nn.BatchNorm2d(256)
+        self.conv3 = nn.Conv2d(256, 512, 3, stride=1, padding=1)
+        self.bnorm3 = nn.BatchNorm2d(512)
+        self.linear5 = nn.Linear(512 * p3 * p3, 512)
+
+
+class AudBl(nn.Module):
+    """utils.py:197-212 parameter container, materialised for B audio bins."""
+
+    def __init__(self, B: int = 30):
+        super().__init__()
+        l1 = (B + 2 - 3) // 2 + 1
+        l2 = (l1 + 2 - 3) // 2 + 1
+        self.conv1 = nn.Conv1d(30, 64, 3, stride=2, padding=1)
+        self.conv2 = nn.Conv1d(64, 128, 3, stride=2, padding=1)
+        self.linear3 = nn.Linear(128 * l2, 128)
+
+
+class AVM(nn.Module):
+    """Audio-visual frame-importance model (utils.py:229-272), eval-mode forward on the B200.
+
+    `AVM(audio_included)`; `forward(audio_input, visual_input)` (audio FIRST, utils.py:260) returns a
+    (N,1) float32 CUDA tensor in [1,5].  `state_dict()` / `load_state_dict()` use the reference's key
+    names and tensor layouts, so checkpoints written by the reference's `torch.save(model.state_dict())`
+    (main.py:263,282) load unchanged.  Dropout is the identity and BatchNorm uses running statistics
+    (parity is defined in eval mode).
+    """
+
+    def __init__(self, audio_included: bool, S: int = 40, B: int = 30):
+        super().__init__()
+        self.audio_included = bool(audio_included)
+        self.S, self.B = S, B
+        self.visbl = VisBl(S)
+        if self.audio_included:
+            self.audbl = AudBl(B)
+        fin = 512 + (128 if self.audio_included else 0)
+        # same Sequential indices as the reference (ReLU / Dropout occupy 1,2,4,5,7,8,10,11,13)
+        self.fusion = nn.Sequential(
+            nn.Linear(fin, 512), nn.ReLU(), nn.Dropout(0.2), nn.Linear(512, 512), nn.ReLU(), nn.Dropout(0.2),
+            nn.Linear(512, 256), nn.ReLU(), nn.Dropout(0.2), nn.Linear(256, 128), nn.ReLU(), nn.Dropout(0.2),
+            nn.Linear(128, 1), nn.Sigmoid())
+        self._native = {}       # device index -> (gn_model*, packed state version)
+        self._version = 0
+        self._workspace = {}
+        self.last_visual_features = None
+
+    # -- weights ----------------------------------------------------------------------------------
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        sd = {k: (torch.as_tensor(np.asarray(v)) if not torch.is_tensor(v) else v) for k, v in state_dict.items()}
+        res = super().load_state_dict(sd, strict=strict)
+        self._version += 1
+        return res
+
+    def invalidate(self):
+        """Call after mutating parameters in place so that the packed device copy is rebuilt."""
+        self._version += 1
+
+    def _release(self):
+        lib = _lib.load()
+        for (mptr, _) in self._native.values():
+            lib.gn_model_destroy(mptr)
+        self._native = {}
+
+    def __del__(self):
+        try:
+            self._release()
+        except Exception:
+            pass
+
+    def _model(self, dev):
+        cur = self._native.get(dev.index)
+        if cur is not None and cur[1] == self._version:
+            return cur[0]
+        lib = _lib.load()
+        if cur is not None:
+            lib.gn_model_destroy(cur[0])
+            del self._native[dev.index]
+        sd = self.state_dict()
+        keep, st = [], _lib.gn_avm_state()
+        for field, key in _lib.STATE_KEYS.items():
+            if key not in sd:
+                setattr(st, field, None)
+                continue
+            t = sd[key].detach().to(device=dev, dtype=torch.float32).contiguous()
+            keep.append(t)
+            setattr(st, field, t.data_ptr())
+        mptr = C.c_void_p()
+        with torch.cuda.device(dev):
+            _lib.check(lib.gn_model_create(_h(dev), C.byref(mptr), C.byref(st), int(self.audio_included), self.S,
+                                           self.B, _stream(dev)), "gn_model_create")
+        del keep
+        self._native[dev.index] = (mptr, self._version)
+        return mptr
+
+    def _ws(self, dev, mptr, n):
+        need = int(_lib.load().gn_avm_workspace_bytes(mptr, n))
+        ws = self._workspace.get(dev.index)
+        if ws is None or ws.numel() < need:
+            ws = self._workspace[dev.index] = torch.empty(need, dtype=torch.uint8, device=dev)
+        return ws, need
+
+    # -- forward ------------------------------------------------------------------------------------
+    def forward(self, audio_input, visual_input, out=None, return_features: bool = False, _simt: bool = False):
+        dev = _device(visual_input.device if torch.is_tensor(visual_input) and visual_input.is_cuda else None)
+        vis = _to_dev(visual_input, torch.float32, dev)
+        assert vis.dim() == 4 and tuple(vis.shape[1:]) == (3, self.S, self.S), "E: Invalid shape for visual input"
+        n = vis.shape[0]
+        aud = None
+        if self.audio_included:
+            aud = _to_dev(audio_input, torch.float32, dev)
+            assert tuple(aud.shape) == (n, 30, self.B), "E: Inconsistency in data loader definition"
+        mptr = self._model(dev)
+        ws, need = self._ws(dev, mptr, n)
+        scores = out if out is not None else torch.empty((n, 1), dtype=torch.float32, device=dev)
+        feats = torch.empty((n, 512), dtype=torch.float32, device=dev) if return_features else None
+        lib = _lib.load()
+        fn = lib.gn_dbg_avm_forward_simt if _simt else lib.gn_avm_forward
+        with torch.cuda.device(dev):
+            _lib.check(fn(mptr, _ptr(vis), _ptr(aud), n, _ptr(scores), _ptr(feats), _ptr(ws), need, _stream(dev)),
+                       "gn_avm_forward")
+        self.last_visual_features = feats
+        return scores
+
+    def read_activation(self, which: int, n: int, device=None):
+        """Validation helper: block outputs 1..3 as (n,C,P,P) float32, 4 = fusion input (n,Fin)."""
+        dev = _device(device)
+        mptr = self._model(dev)
+        ws, _ = self._ws(dev, mptr, n)
+        shapes = {1: (n, 64, 13, 13), 2: (n, 256, 11, 11), 3: (n, 512, 9, 9),
+                  4: (n, 512 + (128 if self.audio_included else 0))}
+        out = torch.empty(shapes[which], dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().gn_dbg_read_activation(mptr, which, n, _ptr(ws), _ptr(out), _stream(dev)),
+                       "gn_dbg_read_activation")
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
+# (a6-a9) keyshot selection  -- reference utils.py:396-410, 445-510, 606-643
+# --------------------------------------------------------------------------------------------------
+def expand_array(arr, expansion_rate, length):
+    """utils.py:396-410 (list plumbing; on the hot path it is fused into gn_clip_information)."""
+    if len(arr) == length:
+        return arr
+    expanded_arr = [el for el in arr for _ in range(expansion_rate)]
+    if len(expanded_arr) >= length:
+        return expanded_arr[:length]
+    return expanded_arr + [expanded_arr[-1]] * (length - len(expanded_arr))
+
+
+def _clip_information_device(scores_dev, n, skip_frames, n_raw, clips_dev, dev):
+    n_clips = clips_dev.shape[0]
+    values = torch.empty(n_clips, dtype=torch.int32, device=dev)
+    lengths = torch.empty(n_clips, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().gn_clip_information(_h(dev), _ptr(scores_dev), n, skip_frames, n_raw, _ptr(clips_dev),
+                                                   n_clips, _ptr(values), _ptr(lengths), _stream(dev)),
+                   "gn_clip_information")
+    return values, lengths
+
+
+def get_clip_information(clip_intervals, importances, device=None):
+    """utils.py:445-464: per clip [a,b]: value = sum(imp[a:b]), length = len(imp[a:b]) (end-exclusive)."""
+    dev = _device(device)
+    imp = np.asarray(importances)
+    assert imp.ndim == 1, "E: importances must be a flat per-frame list"
+    n_raw = int(imp.shape[0])
+    ci = np.asarray(clip_intervals, dtype=np.int64).reshape(-1, 2)
+    if ci.shape[0] == 0:
+        return [], [], clip_intervals
+    assert n_raw > 0 and np.all(np.abs(imp) <= 127) and np.all(imp == np.round(imp)), "E: importances must be int8 values"
+    assert ci.min() >= 0, "E: negative clip bounds are not supported"
+    v, l = _clip_information_device(_to_dev(imp, torch.float32, dev), n_raw, 1, n_raw,
+                                    _to_dev(np.minimum(ci, 2 ** 31 - 1), torch.int32, dev), dev)
+    return v.cpu().tolist(), l.cpu().tolist(), clip_intervals
+
+
+def _knapsack_device(values_dev, weights_dev, n_items, cap_cols, cap_rem, batch, dev):
+    lib = _lib.load()
+    need = int(lib.gn_knapsack_workspace_bytes(n_items, cap_cols)) * batch
+    ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+    sel = torch.empty((batch, max(n_items, 1)), dtype=torch.uint8, device=dev)
+    best = torch.empty(batch, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.gn_knapsack(_h(dev), _ptr(values_dev), _ptr(weights_dev), n_items, cap_cols, cap_rem, batch,
+                                   _ptr(sel), _ptr(best), _ptr(ws), need, _stream(dev)), "gn_knapsack")
+    return sel[:, :n_items], best
+
+
+def _scale_problem(weights, capacity, scale_factor):
+    """utils.py:478-479 on the host, plus the exact common-divisor compression of the table columns."""
+    w = [int(x * scale_factor) for x in weights]
+    cap = int(capacity * scale_factor)
+    assert all(x >= 0 for x in w), "E: negative clip weights are not supported"
+    unit = 0
+    for x in w:
+        unit = math.gcd(unit, x)
+    unit = max(unit, 1)
+    if cap < 0:
+        cap = -1
+    return [x // unit for x in w], cap // unit if cap >= 0 else -1, (cap % unit) if cap >= 0 else 0
+
+
+def knapsack(values, weights, capacity, scale_factor=5, device=None):
+    """utils.py:466-510: indices of the selected clips, ascending.  Bit-exact with the reference."""
+    n = len(values)
+    assert len(weights) == n, "E: values and weights differ in length"
+    if n == 0:
+        return []
+    vals = [int(v) for v in values]
+    assert all(v == fv for v, fv in zip(vals, values)), "E: clip values must be integers"
+    assert sum(abs(v) for v in vals) < 2 ** 31, "E: clip values overflow int32"
+    w, cap_cols, cap_rem = _scale_problem(weights, capacity, scale_factor)
+    if cap_cols < 0:
+        return []          # K[n][capacity] is not reachable with a negative capacity in the reference either
+    dev = _device(device)
+    sel, _ = _knapsack_device(_to_dev(np.asarray(vals, np.int32), torch.int32, dev),
+                              _to_dev(np.minimum(np.asarray(w, np.int64), 2 ** 31 - 1).astype(np.int32), torch.int32, dev),
+                              n, cap_cols, cap_rem, 1, dev)
+    return torch.nonzero(sel[0]).flatten().cpu().tolist()
+
+
+def postprocess_array(batch_importances, skip_frames, full_n_frames, change_points, full_frames=None, device=None,
+                      return_device: bool = False):
+    """HDF5-free `postprocess` (utils.py:608-613,627-643): scores (N,1)|(N,) -> (summarized_video|None,
+    uint8 indicator over the raw frames).  `change_points` is the (n_clips,2) inclusive KTS array the
+    reference reads from the h5 file (utils.py:625).  Everything from the rounding on is integer work on
+    the GPU and bit-exact with the reference."""
+    dev = _device(device if device is not None else
+                  (batch_importances.device if torch.is_tensor(batch_importances) and batch_importances.is_cuda else None))
+    sc = _to_dev(batch_importances, torch.float32, dev)
+    if sc.dim() != 1:
+        assert sc.dim() == 2 and sc.shape[-1] == 1, "E: Invalid shape for importance tensor"
+        sc = sc[:, 0].contiguous()
+    n = int(sc.shape[0])
+    n_raw = int(full_n_frames)
+    cps_host = np.asarray(change_points.cpu() if torch.is_tensor(change_points) else change_points).reshape(-1, 2)
+    cps = _to_dev(cps_host.astype(np.int32), torch.int32, dev)
+    n_clips = int(cps.shape[0])
+    lib = _lib.load()
+    ind = torch.zeros(n_raw, dtype=torch.uint8, device=dev)
+    sel = torch.zeros(max(n_clips, 1), dtype=torch.uint8, device=dev)
+    if n_clips > 0 and n > 0:
+        values, lengths = _clip_information_device(sc, n, int(skip_frames), n_raw, cps, dev)
+        # weights = int(len * 5), capacity = int(int(0.15 * N_raw) * 5) (utils.py:478-479, 629): both are
+        # multiples of 5, so the table compresses exactly to int(0.15 * N_raw) + 1 columns (unit = 5).
+        cap = int(0.15 * n_raw)
+        sel2, _ = _knapsack_device(values, lengths, n_clips, cap, 0, 1, dev)
+        sel = sel2[0].contiguous()
+        with torch.cuda.device(dev):
+            _lib.check(lib.gn_summary_indicator(_h(dev), _ptr(cps), _ptr(sel), n_clips, n_raw, _ptr(ind), _stream(dev)),
+                       "gn_summary_indicator")
+    summarized_video = None
+    if full_frames is not None:
+        chosen = torch.nonzero(sel[:n_clips]).flatten().cpu().tolist()
+        parts = [full_frames[int(cps_host[j][0]):int(cps_host[j][1])] for j in chosen]      # utils.py:634
+        summarized_video = np.concatenate(parts, axis=0) if parts else None
+    if return_device:
+        return summarized_video, ind
+    return summarized_video, ind.cpu().numpy()
+
+
+def _read_change_points(video_id, h5_file_path, mat_file_path):
+    """utils.py:615-625 (HDF5 I/O, unchanged semantics; needs h5py, which this image lacks)."""
+    try:
+        import h5py
+    except ImportError as e:  # pragma: no cover
+        raise AssertionError("E: h5py is required to read change points; use postprocess_array(...)") from e
+    with h5py.File(h5_file_path, "r") as f5:
+        h5 = [[vid, f5[str(vid)]["change_points"][-1][1]] for vid in f5.keys()]
+    with h5py.File(mat_file_path, "r") as fm:
+        def deref(refs, cast):
+            return [cast(fm[r]) for ra in refs for r in ra]
+        names = deref(fm["tvsum50"]["video"][:], lambda d: "".join(chr(c[0]) for c in d))
+        counts = [int(c[0]) for ra in fm["tvsum50"]["nframes"][:] for r in ra for c in fm[r]]
+    id_map = {}
+    for vm, cm in zip(names, counts):
+        for vh, ch in h5:
+            if cm == ch + 1:
+                id_map[vm] = vh
+    with h5py.File(h5_file_path, "r") as f5:
+        return f5[id_map[video_id]]["change_points"][:]
+
+
+def postprocess(video_id, h5_file_path, mat_file_path, batch_importances, skip_frames, full_n_frames,
+                full_frames=None):
+    """utils.py:606-643, same signature; the HDF5 reads stay host I/O, the rest runs on the GPU."""
+    cps = _read_change_points(video_id, h5_file_path, mat_file_path)
+    return postprocess_array(batch_importances, skip_frames, full_n_frames, cps, full_frames)
+
+
+# --------------------------------------------------------------------------------------------------
+# (a10) evaluation  -- reference utils.py:552-604
+# --------------------------------------------------------------------------------------------------
+def fscore_counts(gd_summary_indices, predicted_summary_indices, device=None):
+    """Device counts behind utils.py:571-573: (overlap[u], sum(G_u)[u], sum(S)) as Python ints."""
+    dev = _device(device)
+    G = _to_dev(gd_summary_indices, torch.uint8, dev)
+    S = _to_dev(predicted_summary_indices, torch.uint8, dev)
+    assert G.dim() == 2 and G.shape[1] == S.shape[0]
+    n_users, n_raw = int(G.shape[0]), int(G.shape[1])
+    counts = torch.empty(2 * n_users + 1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().gn_fscore_counts(_h(dev), _ptr(S), _ptr(G), n_users, n_raw, _ptr(counts), _stream(dev)),
+                   "gn_fscore_counts")
+    c = counts.cpu().tolist()
+    return c[:n_users], c[n_users:2 * n_users], c[2 * n_users]
+
+
+def get_fscore(gd_summary_indices, predicted_summary_indices, device=None):
+    """utils.py:552-580: (mean, max) F-score over the annotators.  Counts are integer sums on the GPU
+    (NumPy-1 semantics); the float64 tail follows the reference's operation order."""
+    overlap, gsum, ssum = fscore_counts(gd_summary_indices, predicted_summary_indices, device)
+    f_scores = []
+    for ov, sg in zip(overlap, gsum):
+        precision = ov / ssum if ssum != 0 else 0
+        recall = ov / sg if sg != 0 else 0
+        f_scores.append(2 * precision * recall / (precision + recall) if (precision + recall) != 0 else 0)
+    acc = 0.0
+    for f in f_scores:          # plain left-to-right adds, like sum() over np.float64 scalars (utils.py:580)
+        acc = acc + f
+    return acc / len(f_scores), max(f_scores)
+
+
+def postprocess_and_get_fscores_array(batch_predictions, full_n_batch_frames, gd_summarized_video_frame_indices,
+                                      skip_frames, change_points, device=None):
+    """Array twin of utils.py:587-604."""
+    _, ind = postprocess_array(batch_predictions, skip_frames, full_n_batch_frames, change_points, device=device,
+                               return_device=True)
+    return get_fscore(gd_summarized_video_frame_indices, ind, device=ind.device)
+
+
+def postprocess_and_get_fscores(video_id, batch_predictions, full_n_batch_frames, gd_summarized_video_frame_indices,
+                                h5_file_path, mat_file_path, skip_frames):
+    """utils.py:587-604, same signature."""
+    cps = _read_change_points(video_id, h5_file_path, mat_file_path)
+    return postprocess_and_get_fscores_array(batch_predictions, full_n_batch_frames,
+                                             gd_summarized_video_frame_indices, skip_frames, cps)
+
+
+# --------------------------------------------------------------------------------------------------
+# dataset container  -- reference utils.py:16-76 (tuple order only; TSV titles are optional here)
+# --------------------------------------------------------------------------------------------------
+class dataloader(torch.utils.data.Dataset):
+    def __init__(self, fps, frames, full_n_frames, audios, labels=None, gd_summarized_video_frame_indices=None,
+                 titles=None):
+        self.fps = fps
+        self.video_ids = [fp.split("/")[-1].split(".")[0] for fp in fps]
+        self.frames = [torch.as_tensor(f, dtype=torch.float32) for f in frames]
+        self.full_n_frames = full_n_frames
+        self.audios = audios if audios[0][0] is None else [torch.as_tensor(a, dtype=torch.float32) for a in audios]
+        if labels is None:
+            self.labels = self.gd_summarized_video_frame_indices = [None for _ in range(len(frames))]
+            assert len(self.frames) == len(self.audios), "E: Inconsistency in data loader definition"
+        else:
+            self.labels = [torch.as_tensor(l, dtype=torch.float32) for l in labels]
+            self.gd_summarized_video_frame_indices = gd_summarized_video_frame_indices
+            assert len(self.frames) == len(self.audios) == len(self.labels), "E: Inconsistency in data loader definition"
+        self.titles = titles if titles is not None else list(self.video_ids)
+        self.N = len(self.frames)
+
+    def __len__(self):
+        return self.N
+
+    def __getitem__(self, video_idx):
+        self.title = self.titles[video_idx]
+        self.full_n_frames_ = self.full_n_frames[video_idx]
+        return (self.video_ids[video_idx], self.frames[video_idx], self.audios[video_idx], self.labels[video_idx],
+                self.gd_summarized_video_frame_indices[video_idx])

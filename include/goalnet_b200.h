@@ -1,0 +1,179 @@
+/*
+ * goalnet_b200.h -- C-ABI of the B200-native per-frame scoring path of CVML-GoalNet.
+ *
+ * The reference (Vasilispapg/CVML-GoalNet) is pure Python and has no FFI / plugin registry: its
+ * "boundary" is the set of plain functions main.py:11 imports from utils.py.  Each entry point
+ * below replaces the arithmetic of one of those functions (cited per declaration, paths relative to
+ * the reference root); the Python mirror of the reference interface (cvml_goalnet_b200/utils.py)
+ * binds them through ctypes, and INTEGRATION.md shows the stub a maintainer of the reference adds.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *   - every `const T* d_...` / `T* d_...` argument is a DEVICE pointer owned by the caller;
+ *     `h_...` arguments are HOST pointers;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is
+ *     enqueued on it and the call returns without synchronising unless stated;
+ *   - return value: 0 = ok, <0 = argument/shape error (GN_E_*), >0 = a cudaError_t / CUresult
+ *     value; nothing throws; gn_status_string() describes any code;
+ *   - the library allocates nothing persistent except the two opaque objects created by
+ *     gn_create() / gn_model_create(); it is re-entrant per handle, starts no threads and has NO
+ *     CPU fallback: without a CUDA device every compute entry point returns an error.
+ */
+#ifndef GOALNET_B200_H_
+#define GOALNET_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GN_ABI_VERSION 1
+
+#define GN_OK 0
+#define GN_E_ARG (-1)       /* null pointer / negative size / inconsistent arguments */
+#define GN_E_SHAPE (-2)     /* a shape this build does not support (see each entry point) */
+#define GN_E_WORKSPACE (-3) /* caller workspace too small */
+#define GN_E_NODEVICE (-4)  /* no usable CUDA device / driver entry point missing */
+#define GN_E_RANGE (-5)     /* integer overflow risk (values do not fit the device integer type) */
+
+typedef struct gn_handle gn_handle; /* per-device context: SM count, driver entry points, tables */
+typedef struct gn_model gn_model;   /* packed AVM weights on the device */
+
+int gn_abi_version(void);
+const char* gn_status_string(int status);
+
+/* Create / destroy the per-device context.  `device` is a CUDA ordinal. */
+int gn_create(gn_handle** out, int device);
+int gn_destroy(gn_handle* h);
+/* Kernel launches issued through `h` since creation (bench.py's `gpu_launches`). */
+int64_t gn_launch_count(const gn_handle* h);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a1) frame preprocessing -- replaces the arithmetic of utils.py:284-285,292
+ *      (`extract_condensed_frame_tensor`): per-frame global min/max over H*W*3 bytes,
+ *      (x-min)/(max-min+1e-7), cv2.resize INTER_LINEAR to SxS, HWC->CHW.  BGR order is kept.
+ * d_frames : uint8 [n][H][W][3];  d_out_nchw : float32 [n][3][S][S] or NULL;
+ * d_out_nhwc_bf16 : bf16 [n][S][S][3] or NULL (at least one output must be given).
+ * ------------------------------------------------------------------------------------------- */
+int gn_preprocess_u8_bgr(gn_handle* h, const uint8_t* d_frames, int64_t n, int H, int W, int S,
+                         float* d_out_nchw, void* d_out_nhwc_bf16, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a2) audio features -- replaces utils.py:322-349 (`extract_audio_features` after librosa.load):
+ *      per frame-slot MFCC(30) of its sample segment (librosa.feature.mfcc defaults: STFT 2048/512
+ *      periodic hann, centre zero padding, power 2, 128 Slaney mels, power_to_db top_db 80 per
+ *      segment, DCT-II ortho) followed by the cubic time resampling to B columns, given as the
+ *      linear operator W (B x q).
+ * d_y        : float32 mono samples [n_samples]
+ * d_seg_start: int64 [n]  first sample of each slot;  d_seg_len : int32 [n] samples per slot
+ *              (q_i = 1 + len_i/512 STFT columns, 4 <= q_i <= GN_MFCC_MAX_Q)
+ * d_w_offset : int32 [n]  offset (in floats) of slot i's row-major W (B x q_i) inside d_w
+ * d_mel_*    : the mel filterbank in CSR-like form: for mel m, bins [start[m], start[m]+count[m])
+ *              with weights d_mel_w[offset[m] ...]  (128 entries each)
+ * d_dct      : float32 [30][128] DCT-II ortho rows
+ * d_out      : float32 [n][30][B]
+ * ------------------------------------------------------------------------------------------- */
+#define GN_MFCC_MAX_Q 64
+int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_samples, const int64_t* d_seg_start,
+                      const int32_t* d_seg_len, const int32_t* d_w_offset, const float* d_w, int64_t n,
+                      int B, int max_q, const int32_t* d_mel_start, const int32_t* d_mel_count,
+                      const int32_t* d_mel_offset, const float* d_mel_w, const float* d_dct, float* d_out,
+                      void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a3-a5) AVM forward, eval mode -- replaces utils.py:172-195 (VisBl), 214-227 (AudBl),
+ *      260-272 (AVM.forward).  Weights are given in the reference's own state_dict layout
+ *      (float32, PyTorch memory order); gn_model_create packs them for the kernels.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct gn_avm_state {
+    /* visbl.conv{1,2,3}.weight [O][I][3][3], .bias [O] */
+    const float *conv1_w, *conv1_b, *conv2_w, *conv2_b, *conv3_w, *conv3_b;
+    /* visbl.bnorm{1,2,3}: weight, bias, running_mean, running_var [C] */
+    const float *bn1_w, *bn1_b, *bn1_m, *bn1_v;
+    const float *bn2_w, *bn2_b, *bn2_m, *bn2_v;
+    const float *bn3_w, *bn3_b, *bn3_m, *bn3_v;
+    /* visbl.linear5.weight [512][512*P*P] (C,H,W flatten order), .bias [512] */
+    const float *linear5_w, *linear5_b;
+    /* audbl.* (NULL when audio_included == 0): conv1 [64][30][3], conv2 [128][64][3], linear3 [128][128*L2] */
+    const float *aconv1_w, *aconv1_b, *aconv2_w, *aconv2_b, *alinear3_w, *alinear3_b;
+    /* fusion.{0,3,6,9,12}: [512][Fin], [512][512], [256][512], [128][256], [1][128] + biases */
+    const float *f0_w, *f0_b, *f3_w, *f3_b, *f6_w, *f6_b, *f9_w, *f9_b, *f12_w, *f12_b;
+} gn_avm_state;
+
+/* All pointers in `sd` are DEVICE pointers.  S = frame side (40 in the reference, utils.py:285),
+ * B = audio bins (30).  This build supports S = 40 and B with 128*L2 = 1024 (B in 29..32).
+ * Synchronises `stream` before returning (the caller may free `sd` tensors afterwards). */
+int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state* sd, int audio_included, int S, int B,
+                    void* stream);
+int gn_model_destroy(gn_model* m);
+
+/* Bytes of caller workspace gn_avm_forward needs for n frames. */
+int64_t gn_avm_workspace_bytes(const gn_model* m, int64_t n);
+
+/* d_visual : float32 [n][3][S][S] (the tensor `extract_condensed_frame_tensor` returns)
+ * d_audio  : float32 [n][30][B]  (ignored / may be NULL when the model has no audio branch)
+ * d_scores : float32 [n]  (the reference's (n,1) output of utils.py:270, values in [1,5])
+ * d_visual_features : optional bf16-rounded float32 [n][512] copy of VisBl's output, or NULL. */
+int gn_avm_forward(gn_model* m, const float* d_visual, const float* d_audio, int64_t n, float* d_scores,
+                   float* d_visual_features, void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a6-a9) keyshot selection -- replaces utils.py:608-613,627-641 (`postprocess` without its HDF5
+ *      reads), 396-410 (`expand_array`), 445-464 (`get_clip_information`), 466-510 (`knapsack`).
+ *      Integer arithmetic, bit-exact with the reference.
+ * ------------------------------------------------------------------------------------------- */
+
+/* scores -> rounded int8 importances (torch.round half-to-even, utils.py:611) -> per-clip value and
+ * length over the expanded raw-rate importance vector (utils.py:613,627).  Clips are inclusive [a,b]
+ * pairs whose statistics use the end-EXCLUSIVE slice imp[a:b] (utils.py:460-462).
+ * d_scores float32 [n]; d_clips int32 [n_clips][2]; outputs int32 [n_clips] each. */
+int gn_clip_information(gn_handle* h, const float* d_scores, int64_t n, int skip_frames, int64_t n_raw,
+                        const int32_t* d_clips, int n_clips, int32_t* d_values, int32_t* d_lengths,
+                        void* stream);
+
+/* Bytes of workspace gn_knapsack needs (decision bits + row buffers) for one problem. */
+int64_t gn_knapsack_workspace_bytes(int n_items, int64_t capacity_columns);
+
+/* 0/1 knapsack of utils.py:466-510 for `batch` independent problems that share n_items and
+ * capacity (one thread-block per problem).  `d_weights` are the ALREADY SCALED integer weights
+ * (int(w*scale_factor), utils.py:478) divided by `unit`, and `capacity` is
+ * int(capacity*scale_factor)/unit, where `unit` is a common divisor of all scaled weights chosen by
+ * the caller (1 is always valid); `capacity_rem` = int(capacity*scale_factor) % unit.  Dividing by
+ * a common divisor leaves the table cells the reference's backtrack visits unchanged.
+ * d_values int32 [batch][n_items]; d_weights int32 [batch][n_items];
+ * d_selected uint8 [batch][n_items] (1 = clip chosen, ascending order as utils.py:509);
+ * d_best int32 [batch] = K[n][capacity]. */
+int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t* d_weights, int n_items,
+                int64_t capacity, int capacity_rem, int batch, uint8_t* d_selected, int32_t* d_best,
+                void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* utils.py:638-641: uint8 indicator over raw frames, 1 on a..b INCLUSIVE of every selected clip. */
+int gn_summary_indicator(gn_handle* h, const int32_t* d_clips, const uint8_t* d_selected, int n_clips,
+                         int64_t n_raw, uint8_t* d_indicator, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a10) evaluation -- replaces the counting in utils.py:571-573 (`get_fscore`): for each
+ *      annotator u: |S and G_u|, sum(G_u); plus sum(S).  d_counts int64 [2*n_users + 1] =
+ *      {overlap_0.., gsum_0.., ssum}.  The float64 tail (utils.py:572-580) stays on the host.
+ * ------------------------------------------------------------------------------------------- */
+int gn_fscore_counts(gn_handle* h, const uint8_t* d_pred, const uint8_t* d_gd, int n_users, int64_t n_raw,
+                     int64_t* d_counts, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Validation kernels (plain CUDA-core fp32 accumulate).  NOT a backend: tests use them to localise
+ * a tensor-core kernel fault layer by layer on the GPU.  Same argument meaning as gn_avm_forward.
+ * ------------------------------------------------------------------------------------------- */
+int gn_dbg_avm_forward_simt(gn_model* m, const float* d_visual, const float* d_audio, int64_t n,
+                            float* d_scores, float* d_visual_features, void* d_workspace,
+                            int64_t workspace_bytes, void* stream);
+/* Copy an intermediate activation of the LAST forward on `m` out of the workspace as float32:
+ * which = 1,2,3 -> VisBl block outputs in NCHW (utils.py:177,182,187); 4 -> fusion input [n][Fin]. */
+int gn_dbg_read_activation(gn_model* m, int which, int64_t n, const void* d_workspace, float* d_out,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GOALNET_B200_H_ */

@@ -1,0 +1,277 @@
+"""Parity tests proper: the CUDA path (through the C-ABI / ctypes) against the CPU oracle and the golden
+vectors produced by the reference's own code.  Integer work is bit-exact; floating point within the
+tolerance written in each test."""
+import numpy as np
+import pytest
+import torch
+
+from cvml_goalnet_b200 import synthetic as syn
+from oracle import goalnet_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def U(cuda_device):
+    from cvml_goalnet_b200 import utils
+    return utils
+
+
+@pytest.fixture(scope="module")
+def weights():
+    return syn.make_weights(seed=0)
+
+
+# ------------------------------------------------------------------ (a1) preprocess
+PRE_TOL = 5e-7   # abs, on values in [0,1]: closed form vs cv2 is <= 1.2e-7, plus fp32 FMA reassociation
+
+
+def test_preprocess_golden(U, golden):
+    g = golden("preprocess")
+    for name in ("down", "down2", "up", "flat"):
+        out = U.extract_condensed_frame_tensor_array(g[f"{name}_frames"], as_numpy=True)
+        assert out.shape == g[f"{name}_out"].shape and out.dtype == np.float32
+        assert np.abs(out - g[f"{name}_out"]).max() <= PRE_TOL, name
+    if "file_out" in g.files:
+        dec = g["file_decoded_frames"][:: int(g["file_skip_frames"])]
+        assert np.abs(U.extract_condensed_frame_tensor_array(dec, as_numpy=True) - g["file_out"]).max() <= PRE_TOL
+
+
+@pytest.mark.parametrize("n,H,W", [(1, 224, 224), (37, 224, 224), (3, 45, 45), (2, 270, 480), (0, 32, 32),
+                                   (5, 17, 23), (2, 1080, 1920)])
+def test_preprocess_vs_oracle(U, n, H, W):
+    fr = syn.make_frames(n, H, W, seed=H + W)
+    out = U.extract_condensed_frame_tensor_array(fr, as_numpy=True)
+    ref = O.extract_condensed_frame_tensor_array(fr, 40)
+    assert out.shape == (n, 3, 40, 40)
+    if n:
+        assert np.abs(out - ref).max() <= PRE_TOL
+
+
+def test_preprocess_unaligned_device_view(U):
+    """frames whose device address is not 16-byte aligned (head/tail scalar path)."""
+    fr = syn.make_frames(3, 33, 35, seed=9)
+    buf = torch.zeros(fr.size + 64, dtype=torch.uint8, device="cuda")
+    for off in (1, 7, 16):
+        view = buf[off:off + fr.size].view(fr.shape)
+        view.copy_(torch.from_numpy(fr))
+        out = U.extract_condensed_frame_tensor_array(view).cpu().numpy()
+        assert np.abs(out - O.extract_condensed_frame_tensor_array(fr, 40)).max() <= PRE_TOL
+
+
+# ------------------------------------------------------------------ (a2) audio
+# MFCC values span roughly [-600, 200]; the oracle evaluates the STFT in float64 and the rest in float32,
+# the kernel is float32 throughout: 2e-3 abs + 1e-4 rel.
+MFCC_ATOL, MFCC_RTOL = 2e-3, 1e-4
+
+
+def test_audio_golden(U, golden):
+    g = golden("audio")
+    for name in ("int", "ragged", "b16"):
+        sr, n_frames, B = (int(x) for x in g[f"{name}_args"])
+        out = U.extract_audio_features_array(g[f"{name}_y"], sr, n_frames, B, as_numpy=True)
+        ref = g[f"{name}_features"]
+        assert out.shape == ref.shape
+        np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
+
+
+@pytest.mark.parametrize("n,spf,sr", [(64, 8000, 16000), (5, 11025, 22050), (3, 2100, 16000), (0, 8000, 16000)])
+def test_audio_vs_oracle(U, n, spf, sr):
+    y = syn.make_audio(max(n, 1), spf, sr, seed=n)[: max(n, 1) * spf]
+    if n == 0:
+        assert U.extract_audio_features_array(y, sr, 0, 30).shape == (0, 30, 30)
+        return
+    out = U.extract_audio_features_array(y, sr, n, 30, as_numpy=True)
+    ref = O.extract_audio_features_array(y, sr, n, 30)
+    np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
+
+
+def test_audio_silence_and_short_segment_errors(U):
+    out = U.extract_audio_features_array(np.zeros(4 * 8000, np.float32), 16000, 4, 30, as_numpy=True)
+    ref = O.extract_audio_features_array(np.zeros(4 * 8000, np.float32), 16000, 4, 30)
+    np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
+    with pytest.raises(AssertionError):          # q < 4 columns: interp1d(kind='cubic') fails in the reference too
+        U.extract_audio_features_array(np.zeros(1000, np.float32), 16000, 1, 30)
+
+
+# ------------------------------------------------------------------ (a3-a5) model
+SCORE_RTOL = 1e-3          # north_star: <= 1e-3 relative on scores (bf16 operands, fp32 accumulate)
+FEAT_TOL = 2e-2            # visual features: bf16 activations through K = 41472; relative to the max feature
+
+
+def _model(U, w, audio_included=True):
+    m = U.AVM(audio_included)
+    m.load_state_dict(w)
+    return m
+
+
+def test_model_golden_reference_avm(U, golden):
+    g = golden("model")
+    for tag, audio_included, gain in (("av", True, 1.0), ("v", False, 1.0), ("av_gain", True, 100.0)):
+        w = syn.make_weights(seed=0, audio_included=audio_included, score_gain=gain)
+        m = _model(U, w, audio_included)
+        for simt in (True, False):
+            y = m(g["audio_input"], g["visual_input"], return_features=True, _simt=simt).cpu().numpy()
+            ref = g[f"{tag}_scores"]
+            assert y.shape == ref.shape == (6, 1)
+            tol = SCORE_RTOL if gain == 1.0 else 2e-2     # the x100 last layer amplifies bf16 rounding
+            assert np.abs(y - ref).max() / np.abs(ref).max() <= tol, (tag, simt)
+            vf = m.last_visual_features.cpu().numpy()
+            rv = g[f"{tag}_visual_features"]
+            assert np.abs(vf - rv).max() <= FEAT_TOL * max(np.abs(rv).max(), 1e-3), (tag, simt)
+            for which, key in ((1, "vis1"), (2, "vis2"), (3, "vis3")):
+                act = m.read_activation(which, 6).cpu().numpy()[:2]
+                r = g[f"{tag}_{key}"]
+                assert np.abs(act - r).max() <= FEAT_TOL * np.abs(r).max(), (tag, simt, key)
+
+
+@pytest.mark.parametrize("n", [1, 7, 128, 129, 300])
+def test_model_vs_oracle_and_simt(U, weights, n):
+    vis = O.extract_condensed_frame_tensor_array(syn.make_frames(n, 48, 48, seed=n), 40)
+    rng = np.random.default_rng(n)
+    aud = (25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)
+    aud[:, 0] -= 250.0
+    m = _model(U, weights)
+    y_tc = m(aud, vis, return_features=True).cpu().numpy()
+    f_tc = m.last_visual_features.cpu().numpy()
+    h0_tc = m.read_activation(4, n).cpu().numpy()
+    y_simt = m(aud, vis, return_features=True, _simt=True).cpu().numpy()
+    f_simt = m.last_visual_features.cpu().numpy()
+    ref, feats = O.avm_forward(weights, aud, vis, return_features=True)
+    ref = ref.numpy()
+    assert np.abs(y_tc - ref).max() / np.abs(ref).max() <= SCORE_RTOL
+    assert np.abs(y_simt - ref).max() / np.abs(ref).max() <= SCORE_RTOL
+    rv = feats["visual_features"].numpy()
+    assert np.abs(f_tc - rv).max() <= FEAT_TOL * np.abs(rv).max()
+    # tensor-core path vs the CUDA-core validation path: same bf16 operands, only summation order differs
+    assert np.abs(f_tc - f_simt).max() <= 4e-3 * np.abs(rv).max()
+    ra = feats["audio_features"].numpy()
+    assert np.abs(h0_tc[:, :128] - ra).max() <= 1e-2 * max(np.abs(ra).max(), 1e-3)   # bf16 store of fp32 AudBl
+
+
+def test_model_empty_and_shape_errors(U, weights):
+    m = _model(U, weights)
+    assert m(np.zeros((0, 30, 30), np.float32), np.zeros((0, 3, 40, 40), np.float32)).shape == (0, 1)
+    with pytest.raises(AssertionError):
+        m(np.zeros((2, 30, 30), np.float32), np.zeros((2, 3, 32, 32), np.float32))
+    with pytest.raises(AssertionError):
+        m(np.zeros((3, 30, 30), np.float32), np.zeros((2, 3, 40, 40), np.float32))
+
+
+def test_state_dict_round_trip(U, weights):
+    m = _model(U, weights)
+    sd = m.state_dict()
+    assert sorted(sd.keys()) == sorted(weights.keys())
+    for k, v in weights.items():
+        assert tuple(sd[k].shape) == tuple(np.asarray(v).shape), k
+
+
+# ------------------------------------------------------------------ (a6-a9) integer path, bit-exact
+def test_knapsack_golden(U, golden):
+    g = golden("integer_path")
+    for i in range(int(g["knap_n"])):
+        v, w, c = g[f"knap_{i}_values"].tolist(), g[f"knap_{i}_weights"].tolist(), int(g[f"knap_{i}_cap"])
+        assert U.knapsack(v, w, c) == g[f"knap_{i}_sel"].tolist(), i
+
+
+def test_knapsack_random_vs_oracle(U):
+    rng = np.random.default_rng(5)
+    for t in range(25):
+        n = int(rng.integers(1, 120))
+        v = rng.integers(0, 400, n).tolist()
+        w = (rng.integers(0, 60, n) * int(rng.choice([1, 1, 3]))).tolist()
+        cap = int(rng.integers(0, max(2, sum(w))))
+        scale = int(rng.choice([1, 5, 7]))
+        assert U.knapsack(v, w, cap, scale) == O.knapsack_rows(v, w, cap, scale), t
+    # float weights: int(w * scale) truncation (utils.py:478)
+    v, w = [10, 20, 30, 40], [1.5, 2.25, 3.9, 0.1]
+    assert U.knapsack(v, w, 4.4) == O.knapsack(v, w, 4.4)
+
+
+def test_knapsack_wide_table_global_rows(U):
+    """capacity too wide for shared-memory rows -> rows in the workspace."""
+    rng = np.random.default_rng(11)
+    n = 40
+    v = rng.integers(1, 1000, n).tolist()
+    w = rng.integers(1000, 9000, n).tolist()     # gcd 1 -> 60001 columns
+    assert U.knapsack(v, w, 60000, 1) == O.knapsack_rows(v, w, 60000, 1)
+
+
+def test_clip_information_golden(U, golden):
+    g = golden("integer_path")
+    v, l, _ = U.get_clip_information(g["clip_cps"].tolist(), g["clip_imp"].tolist())
+    assert v == g["clip_values"].tolist() and l == g["clip_lengths"].tolist()
+
+
+def test_postprocess_golden(U, golden):
+    g = golden("postprocess")
+    for name in ("a", "b", "c"):
+        skip, n_raw = (int(x) for x in g[f"{name}_args"])
+        _, ind = U.postprocess_array(g[f"{name}_scores"], skip, n_raw, g[f"{name}_cps"])
+        assert ind.dtype == np.uint8
+        np.testing.assert_array_equal(ind, g[f"{name}_indicator"])
+
+
+@pytest.mark.parametrize("N,skip,n_raw", [(240, 15, 3600), (240, 15, 3590), (240, 15, 3700), (10800, 15, 162000),
+                                          (500, 1, 500), (1, 30, 17)])
+def test_postprocess_vs_oracle(U, N, skip, n_raw):
+    scores = syn.make_scores(N, seed=N)
+    scores[::7] = np.round(scores[::7]) + 0.5          # exercise round-half-to-even
+    cps = syn.make_change_points(n_raw, seed=N + 1)
+    _, ind = U.postprocess_array(scores, skip, n_raw, cps)
+    _, ref = O.postprocess_array(scores, skip, n_raw, cps)
+    np.testing.assert_array_equal(ind, ref)
+    full = np.arange(n_raw)[:, None] * np.ones((1, 2), np.int64)
+    vid, _ = U.postprocess_array(scores, skip, n_raw, cps, full_frames=full)
+    sel, _ = O.postprocess_array(scores, skip, n_raw, cps)
+    if sel:
+        exp = np.concatenate([full[cps[j][0]:cps[j][1]] for j in sel])
+        np.testing.assert_array_equal(vid, exp)
+
+
+def test_fscore_golden_and_oracle(U, golden):
+    g = golden("integer_path")
+    assert list(U.get_fscore(g["fs_G"], g["fs_S"])) == g["fs_avg_max"].tolist()            # bit-exact float64
+    assert list(U.get_fscore(g["fs_G"], np.zeros_like(g["fs_S"]))) == g["fs_empty_avg_max"].tolist()
+    rng = np.random.default_rng(3)
+    for n_raw in (162000, 3601, 16, 5):
+        G = (rng.random((20, n_raw)) < 0.3).astype(np.uint8)
+        S = (rng.random(n_raw) < 0.15).astype(np.uint8)
+        assert U.get_fscore(G, S) == O.get_fscore(G, S)
+
+
+def test_gt_summaries_like_get_dataloaders(U):
+    """utils.py:102-118: one postprocess per annotator builds the ground-truth summaries."""
+    n_raw, skip = 3600, 15
+    ann = syn.make_annotator_importances(n_raw, 20, seed=2)
+    cps = syn.make_change_points(n_raw, seed=2)
+    for u in (0, 7, 19):
+        _, ind = U.postprocess_array(ann[u][:, None], skip, n_raw, cps)
+        _, ref = O.postprocess_array(ann[u][:, None], skip, n_raw, cps)
+        np.testing.assert_array_equal(ind, ref)
+
+
+# ------------------------------------------------------------------ whole path
+def test_end_to_end_config1(U, weights):
+    """BASELINE config 1: 2-min clip, 224x224 source, 2 fps, 16 kHz audio -> scores, keyshots, F-score."""
+    n, skip, sr = 240, 15, 16000
+    n_raw = n * skip
+    frames = syn.make_frames(n, 224, 224, seed=1)
+    y = syn.make_audio(n, 8000, sr, seed=1)
+    cps = syn.make_change_points(n_raw, seed=1)
+    m = _model(U, weights)
+    vis = U.extract_condensed_frame_tensor_array(frames)
+    aud = U.extract_audio_features_array(y, sr, n, 30)
+    scores = m(aud, vis)
+    _, ind = U.postprocess_array(scores, skip, n_raw, cps)
+    o_scores, _, o_ind, _ = O.score_and_summarize(weights, frames, y, sr, skip, n_raw, cps)
+    s = scores.cpu().numpy()
+    assert np.abs(s - o_scores).max() / np.abs(o_scores).max() <= SCORE_RTOL
+    # keyshots: bit-exact whenever the rounded scores agree (they do unless a score sits on x.5 +- tol)
+    if np.array_equal(np.round(s), np.round(o_scores)):
+        np.testing.assert_array_equal(ind, o_ind)
+    _, ind_from_oracle_scores = U.postprocess_array(o_scores, skip, n_raw, cps)
+    np.testing.assert_array_equal(ind_from_oracle_scores, o_ind)
+    gd = np.stack([O.postprocess_array(a[:, None], skip, n_raw, cps)[1]
+                   for a in syn.make_annotator_importances(n_raw, 20, seed=1)])
+    assert U.get_fscore(gd, o_ind) == O.get_fscore(gd, o_ind)
