@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Benchmark of the per-frame scoring path (BASELINE.json metric: frames/s scored end to end).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference]
+
+A "step" is one pass of the hot path over one synthetic 90-minute match (BASELINE config 2: 10 800
+frames of 224x224 BGR uint8 at 2 fps + 16 kHz mono audio, skip_frames 15 -> 162 000 raw frames):
+frame preprocessing -> MFCC features -> AVM forward -> clip statistics -> 0/1 knapsack -> summary
+indicator -> F-score counts against 20 synthetic annotators.  With N > 1 every rank scores its own match
+(weak scaling) and the per-frame scores are all-gathered over NCCL before the selection step.
+
+`value`  : device-resident inputs (already in HBM when the timed region starts).
+`e2e`    : the same step through the public host API (MatchScorer.score_match) with pinned HOST buffers,
+           host->device copies and the device->host read of scores + indicator inside the timed region.
+`--impl reference` times the CPU oracle port of the reference (oracle/goalnet_oracle.py; the reference is
+pure Python and cannot travel to the GPU box) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "frames_per_sec_scored_end_to_end"
+UNIT = "frames/s"
+FRAMES, H, W = 10800, 224, 224
+SR, SPF, SKIP = 16000, 8000, 15
+N_USERS = 20
+CPU_SAMPLE_FRAMES = 120
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs (same law as cvml_goalnet_b200/synthetic.py, generated on the device for speed)
+# ------------------------------------------------------------------------------------------------
+def device_frames(n, h, w, seed, dev):
+    g = torch.Generator(device=dev)
+    g.manual_seed(12344321 + seed)
+    out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=dev)
+    yy = (torch.arange(h, device=dev, dtype=torch.float32) / h)[None, :, None, None]
+    xx = (torch.arange(w, device=dev, dtype=torch.float32) / w)[None, None, :, None]
+    for a in range(0, n, 256):
+        b = min(a + 256, n)
+        k = b - a
+        lo = torch.randint(0, 64, (k, 1, 1, 1), generator=g, device=dev).float()
+        hi = torch.randint(192, 256, (k, 1, 1, 1), generator=g, device=dev).float()
+        f = torch.rand((k, 2, 1, 1), generator=g, device=dev) * 3.5 + 0.5
+        ph = torch.rand((k, 1, 1, 3), generator=g, device=dev) * 6.2831853
+        pat = 0.5 + 0.5 * torch.sin(6.2831853 * (f[:, 0:1] * yy + f[:, 1:2] * xx) + ph)
+        u = torch.rand((k, h, w, 3), generator=g, device=dev)
+        out[a:b] = torch.clamp(torch.round(lo + (hi - lo) * (0.7 * pat + 0.3 * u)), 0, 255).to(torch.uint8)
+    return out
+
+
+def device_audio(n_slots, spf, sr, seed, dev):
+    g = torch.Generator(device=dev)
+    g.manual_seed(12344321 + 77 + seed)
+    n = n_slots * spf
+    t = torch.arange(n, device=dev, dtype=torch.float64) / sr
+    y = torch.zeros(n, device=dev, dtype=torch.float64)
+    par = torch.rand(10, generator=g, device=dev, dtype=torch.float64)
+    for i in range(3):
+        y += (0.1 + 0.4 * par[3 * i]) * torch.sin(6.283185307179586 * (100 + 3900 * par[3 * i + 1]) * t + 6.28 * par[3 * i + 2])
+    y *= 0.6 + 0.4 * torch.sin(6.283185307179586 * 0.05 * t + 6.28 * par[9])
+    y += 0.05 * torch.randn(n, generator=g, device=dev, dtype=torch.float64)
+    return y.float()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU oracle leg (cpu_baseline and --impl reference)
+# ------------------------------------------------------------------------------------------------
+def cpu_sample_inputs(n):
+    from cvml_goalnet_b200 import synthetic as syn
+    frames = syn.make_frames(n, H, W, seed=0)
+    y = syn.make_audio(n, SPF, SR, seed=0)
+    cps = syn.make_change_points(n * SKIP, seed=0)
+    return syn.make_weights(seed=0), frames, y, cps
+
+
+def cpu_step(O, w, frames, y, cps, gd):
+    n = len(frames)
+    return O.score_and_summarize(w, frames, y, SR, SKIP, n * SKIP, cps, gd=gd)
+
+
+def run_cpu(steps, warmup):
+    """Oracle port of the reference path on all host threads; returns (frames/s, ms/step, cores, sample)."""
+    from oracle import goalnet_oracle as O
+    from cvml_goalnet_b200 import synthetic as syn
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n = CPU_SAMPLE_FRAMES
+    w, frames, y, cps = cpu_sample_inputs(n)
+    gd = np.stack([O.postprocess_array(a[:, None], SKIP, n * SKIP, cps)[1]
+                   for a in syn.make_annotator_importances(n * SKIP, N_USERS, seed=0)])
+    for _ in range(warmup):
+        cpu_step(O, w, frames, y, cps, gd)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(O, w, frames, y, cps, gd)
+    dt = time.perf_counter() - t0
+    sample = (f"{n} frames ({n // 2} s of the config-2 match: {H}x{W} source, 2 fps, 16 kHz audio, "
+              f"{n * SKIP} raw frames) per step, {steps} steps; torch threads {torch.get_num_threads()}")
+    return n * steps / dt, 1e3 * dt / steps, cores, sample
+
+
+def reference_arm(args, rank):
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 20))
+    warm = max(0, min(args.warmup, 3))
+    v, ms, cores, sample = run_cpu(steps, warm)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "config-2 90-min match, bounded CPU sample", "frames_per_step": CPU_SAMPLE_FRAMES,
+                       "source": f"{H}x{W}", "fps": 2, "audio_hz": SR, "skip_frames": SKIP},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# native arm
+# ------------------------------------------------------------------------------------------------
+def native_arm(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import _lib, synthetic as syn, utils as U
+    from cvml_goalnet_b200.main import MatchScorer
+
+    peaks = load_peaks()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    n, n_raw = args.frames, args.frames * SKIP
+    samples = n * SPF
+
+    model = U.AVM(True)
+    model.load_state_dict(syn.make_weights(seed=0))
+    frames = device_frames(n, H, W, seed=rank, dev=dev)
+    audio = device_audio(n, SPF, SR, seed=rank, dev=dev)
+    cps_host = syn.make_change_points(n_raw, seed=rank)
+    cps = torch.from_numpy(cps_host).to(dev)
+    # ground-truth summaries: one postprocess per annotator (reference utils.py:102-118)
+    ann = syn.make_annotator_importances(n_raw, N_USERS, seed=rank)
+    gd = torch.stack([U.postprocess_array(torch.from_numpy(a[:, None]).to(dev), SKIP, n_raw, cps, device=dev,
+                                          return_device=True)[1] for a in ann])
+    scorer = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev)
+    gathered = torch.empty((world, n, 1), dtype=torch.float32, device=dev) if world > 1 else None
+
+    def step_device():
+        scores, ind, fs = scorer.score_device(frames, audio, cps, None)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, scores)       # exchange step: every rank sees all scores
+        counts = U.fscore_counts(gd, ind, device=dev)            # D2H read of the step's result
+        return counts
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        l0 = _lib.launch_count(dev.index)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = _lib.launch_count(dev.index) - l0
+        clocks = sampler.stop()
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches, clocks
+
+    ms, launches, clocks = timed(step_device, args.steps, args.warmup)
+    value = world * n * args.steps / (ms * 1e-3)
+
+    # ---- e2e: pinned host inputs, H2D + D2H inside the timed region ------------------------------
+    frames_host = torch.empty(frames.shape, dtype=torch.uint8).pin_memory()
+    audio_host = torch.empty(audio.shape, dtype=torch.float32).pin_memory()
+    frames_host.copy_(frames)
+    audio_host.copy_(audio)
+    gd_host_dev = gd
+
+    def step_host():
+        scores, ind, fs = scorer.score_match(frames_host, audio_host, cps, gd_host_dev)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, scorer.scores)
+        return fs
+
+    ms_e2e, _, _ = timed(step_host, args.steps, args.warmup)
+    e2e_value = world * n * args.steps / (ms_e2e * 1e-3)
+
+    # ---- per-stage device time (CUDA events on the launching stream), same workload ---------------
+    model.set_timing(True, dev)
+    acc = {}
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    for _ in range(args.steps):
+        ev[0].record()
+        U.extract_condensed_frame_tensor_array(frames, 40, out=scorer.vis)
+        ev[1].record()
+        U.extract_audio_features_array(audio, SR, n, 30, out=scorer.aud)
+        ev[2].record()
+        model(scorer.aud, scorer.vis, out=scorer.scores)
+        ev[3].record()
+        U.postprocess_array(scorer.scores, SKIP, n_raw, cps, device=dev, return_device=True)
+        ev[4].record()
+        torch.cuda.synchronize(dev)
+        st = model.stage_ms(dev)
+        st.update(preprocess=ev[0].elapsed_time(ev[1]), mfcc=ev[1].elapsed_time(ev[2]),
+                  avm_forward=ev[2].elapsed_time(ev[3]), select=ev[3].elapsed_time(ev[4]))
+        for k, v in st.items():
+            acc[k] = acc.get(k, 0.0) + v / args.steps
+    model.set_timing(False, dev)
+
+    if rank != 0:
+        return
+    conv3_flops = 2.0 * 121 * 512 * 2304 * n            # algorithmic FLOPs of one conv3 launch
+    achieved = conv3_flops / (acc["conv3_block"] * 1e-3) / 1e12
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("conv3_block_dram_bytes_per_launch")
+    roofline = {"kernel": "tc_gemm_kernel<1,256,3,conv> (conv3 block: implicit GEMM + ReLU + maxpool + BN)",
+                "bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["tf_sustained"], "traffic": traffic,
+                "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['src']}); kernel timed inside the step",
+                "flops_per_launch": conv3_flops, "ms_per_launch": acc["conv3_block"]}
+    pre_bytes = n * (H * W * 3 + 40 * 40 * 3 * 4)
+    stages = {k: round(v, 4) for k, v in acc.items()}
+    stages["preprocess_GBps"] = round(pre_bytes / (acc["preprocess"] * 1e-3) / 1e9, 1)
+    stages["preprocess_frac_of_hbm_peak"] = round(stages["preprocess_GBps"] / peaks["hbm"], 3)
+    stages["mfcc_GBps"] = round(n * (4 * SPF + 4 * 30 * 30) / (acc["mfcc"] * 1e-3) / 1e9, 1)
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, cms, cores, sample = run_cpu(steps=3, warmup=1)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "config-2: synthetic 90-min match at 2 fps + audio, end-to-end summary"
+                                   if n == FRAMES else f"reduced match of {n} frames",
+                       "frames_per_match": n, "matches_per_step": world, "source": f"{H}x{W} BGR uint8",
+                       "model_input": "40x40 (reference utils.py:285)", "audio": f"{SR} Hz mono, {SPF} samples/frame",
+                       "skip_frames": SKIP, "raw_frames": n_raw, "clips": int(cps_host.shape[0]), "annotators": N_USERS,
+                       "parallelism": f"dp{world} (one match per rank, NCCL all-gather of scores)",
+                       "l2": f"inputs are {(frames.numel() + audio.numel() * 4) / 1e9:.2f} GB per step (> 126 MB L2); no flush needed"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(scorer.h2d_bytes), "d2h_bytes_per_step": int(scorer.d2h_bytes) + 8 * (2 * N_USERS + 1)},
+            "gpu_launches": int(launches),
+            "roofline": roofline, "stages_ms": stages}
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--frames", type=int, default=FRAMES, help="frames per match (default: config 2)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        native_arm(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

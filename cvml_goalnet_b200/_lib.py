@@ -91,6 +91,8 @@ SIGNATURES = {
     "gn_model_destroy": (_I, [_P]),
     "gn_avm_workspace_bytes": (_L, [_P, _L]),
     "gn_avm_forward": (_I, [_P, _P, _P, _L, _P, _P, _P, _L, _P]),
+    "gn_model_set_timing": (_I, [_P, _I]),
+    "gn_model_get_timing": (_I, [_P, C.POINTER(C.c_float), _I]),
     "gn_clip_information": (_I, [_P, _P, _L, _I, _L, _P, _I, _P, _P, _P]),
     "gn_knapsack_workspace_bytes": (_L, [_I, _L]),
     "gn_knapsack": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P, _P, _L, _P]),

@@ -54,7 +54,10 @@ struct gn_model {
     __nv_bfloat16 *linear5_wk;   // [512][81*512]  k = p*512 + c   (reference flatten is c*81 + p)
     __nv_bfloat16 *f_wk[4];      // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
     void* arena;                 // one allocation backing everything above
+    int timing;                  // record per-stage events in gn_avm_forward
+    cudaEvent_t ev[GN_AVM_STAGES + 1];
 };
+#define GN_STAGE_MARK(m, k, st) do { if ((m)->timing) cudaEventRecord((m)->ev[k], st); } while (0)
 
 // Workspace layout for n frames (all bf16 unless noted); offsets are computed by gn_ws_layout().
 struct gn_ws {

@@ -247,8 +247,25 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
     return GN_OK;
 }
 
+extern "C" int gn_model_set_timing(gn_model* m, int enable) {
+    if (!m) return GN_E_ARG;
+    if (enable && !m->ev[0])
+        for (int i = 0; i <= GN_AVM_STAGES; ++i) GN_CUDA(cudaEventCreate(&m->ev[i]));
+    m->timing = enable ? 1 : 0;
+    return GN_OK;
+}
+
+extern "C" int gn_model_get_timing(gn_model* m, float* h_ms, int n_stages) {
+    if (!m || !h_ms || n_stages < GN_AVM_STAGES || !m->ev[0]) return GN_E_ARG;
+    GN_CUDA(cudaEventSynchronize(m->ev[GN_AVM_STAGES]));
+    for (int i = 0; i < GN_AVM_STAGES; ++i) GN_CUDA(cudaEventElapsedTime(&h_ms[i], m->ev[i], m->ev[i + 1]));
+    return GN_OK;
+}
+
 extern "C" int gn_model_destroy(gn_model* m) {
     if (!m) return GN_OK;
+    if (m->ev[0])
+        for (int i = 0; i <= GN_AVM_STAGES; ++i) cudaEventDestroy(m->ev[i]);
     cudaFree(m->arena);
     free(m);
     return GN_OK;
@@ -294,10 +311,13 @@ static int avm_forward_impl(gn_model* m, const float* d_visual, const float* d_a
     const gn_ws ws = gn_ws_layout(m, n, d_ws);
     if (ws.bytes > ws_bytes) return GN_E_WORKSPACE;
     cudaStream_t st = gn_stream(stream);
+    GN_STAGE_MARK(m, 0, st);
     int rc = gn_launch_visbl_front(m, d_visual, n, ws, st);
     if (rc) return rc;
+    GN_STAGE_MARK(m, 1, st);
     rc = gn_launch_audbl(m, d_audio, n, ws, st);
     if (rc) return rc;
+    GN_STAGE_MARK(m, 2, st);
     return simt ? gn_launch_simt_backbone(m, n, ws, d_scores, d_visfeat, st)
                 : gn_launch_tc_backbone(m, n, ws, d_scores, d_visfeat, st);
 }
@@ -435,14 +455,17 @@ int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_sc
     simt_conv_block<<<dim3((unsigned)n, 4), 256, m->P1 * m->P1 * 64 * 4, st>>>(
         ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1], ws.a2p, 1);
     GN_LAUNCHED(m->h);
+    GN_STAGE_MARK(m, 3, st);
     simt_conv_block<<<dim3((unsigned)n, 8), 256, m->P2 * m->P2 * 64 * 4, st>>>(
         ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2], ws.a3, 0);
     GN_LAUNCHED(m->h);
+    GN_STAGE_MARK(m, 4, st);
     const int K5 = m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     const int grid = m->h->num_sms * 8;
     simt_linear<<<grid, 256, 0, st>>>(ws.a3, n, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff, d_visfeat);
     GN_LAUNCHED(m->h);
+    GN_STAGE_MARK(m, 5, st);
     simt_linear<<<grid, 256, 0, st>>>(ws.h0, n, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr);
     GN_LAUNCHED(m->h);
     simt_linear<<<grid, 256, 0, st>>>(ws.h1, n, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr);
@@ -451,6 +474,7 @@ int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_sc
     GN_LAUNCHED(m->h);
     simt_score<<<grid, 256, 0, st>>>(ws.h3, n, 256, m->f_wk[3], m->f_b[3], m->f12_w, m->f12_b, d_scores);
     GN_LAUNCHED(m->h);
+    GN_STAGE_MARK(m, 6, st);
     return GN_OK;
 }
 

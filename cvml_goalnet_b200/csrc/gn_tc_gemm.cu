@@ -404,16 +404,19 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
     rc = run_conv<2, 128, 3>(m, n, ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
                              ws.a2p, 1, st);
     if (rc) return rc;
+    GN_STAGE_MARK(m, 3, st);
     // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
     rc = run_conv<1, 256, 3>(m, n, ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
                              ws.a3, 0, st);
     if (rc) return rc;
+    GN_STAGE_MARK(m, 4, st);
     const int K5 = m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     // linear5 + ReLU -> columns [aoff, aoff+512) of the fusion input (audio features occupy [0,128))
     rc = run_linear<256, 4, kLinear>(m, n, ws.a3, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff,
                                      d_visfeat, nullptr, nullptr, nullptr, st);
     if (rc) return rc;
+    GN_STAGE_MARK(m, 5, st);
     rc = run_linear<256, 4, kLinear>(m, n, ws.h0, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr,
                                      nullptr, nullptr, nullptr, st);
     if (rc) return rc;
@@ -426,5 +429,6 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
     // fusion.9 + ReLU + fusion.12 + sigmoid + 4y+1 -> scores
     rc = run_linear<128, 4, kScore>(m, n, ws.h3, 256, 256, m->f_wk[3], 128, m->f_b[3], nullptr, 0, 0, nullptr,
                                     m->f12_w, m->f12_b, d_scores, st);
+    GN_STAGE_MARK(m, 6, st);
     return rc;
 }

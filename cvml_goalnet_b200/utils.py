@@ -74,6 +74,8 @@ def extract_condensed_frame_tensor_array(frames_u8, S: int = 40, device=None, ou
     n, H, W, _ = fr.shape
     if out is None:
         out = torch.empty((n, 3, S, S), dtype=torch.float32, device=dev)
+    if n == 0:
+        return out.cpu().numpy() if as_numpy else out
     with torch.cuda.device(dev):
         _lib.check(_lib.load().gn_preprocess_u8_bgr(_h(dev), _ptr(fr), n, H, W, S, _ptr(out), None, _stream(dev)),
                    "gn_preprocess_u8_bgr")
@@ -153,6 +155,9 @@ def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, dev
     dev = _device(device if device is not None else (y.device if torch.is_tensor(y) and y.is_cuda else None))
     yd = _to_dev(y, torch.float32, dev).reshape(-1)
     B = int(bin_length)
+    if int(n_frames) == 0:
+        out = torch.empty((0, dsp.N_MFCC, B), dtype=torch.float32, device=dev)
+        return out.cpu().numpy() if as_numpy else out
     plan = _segment_plan(int(yd.numel()), int(n_frames), B, dev.index)
     tab = _audio_tables(int(sr), dev.index)
     if out is None:
@@ -314,6 +319,19 @@ class AVM(nn.Module):
         self.last_visual_features = feats
         return scores
 
+    STAGES = ("visbl_block1", "audbl", "conv2_block", "conv3_block", "linear5", "fusion_mlp")
+
+    def set_timing(self, enable: bool, device=None):
+        """Record CUDA events around each stage of the forward (read them with `stage_ms`)."""
+        dev = _device(device)
+        _lib.check(_lib.load().gn_model_set_timing(self._model(dev), int(bool(enable))), "gn_model_set_timing")
+
+    def stage_ms(self, device=None) -> dict:
+        dev = _device(device)
+        buf = (C.c_float * len(self.STAGES))()
+        _lib.check(_lib.load().gn_model_get_timing(self._model(dev), buf, len(self.STAGES)), "gn_model_get_timing")
+        return {k: float(buf[i]) for i, k in enumerate(self.STAGES)}
+
     def read_activation(self, which: int, n: int, device=None):
         """Validation helper: block outputs 1..3 as (n,C,P,P) float32, 4 = fusion input (n,Fin)."""
         dev = _device(device)
@@ -427,8 +445,10 @@ def postprocess_array(batch_importances, skip_frames, full_n_frames, change_poin
         sc = sc[:, 0].contiguous()
     n = int(sc.shape[0])
     n_raw = int(full_n_frames)
-    cps_host = np.asarray(change_points.cpu() if torch.is_tensor(change_points) else change_points).reshape(-1, 2)
-    cps = _to_dev(cps_host.astype(np.int32), torch.int32, dev)
+    if torch.is_tensor(change_points):
+        cps = _to_dev(change_points.reshape(-1, 2), torch.int32, dev)
+    else:
+        cps = _to_dev(np.asarray(change_points).reshape(-1, 2).astype(np.int32), torch.int32, dev)
     n_clips = int(cps.shape[0])
     lib = _lib.load()
     ind = torch.zeros(n_raw, dtype=torch.uint8, device=dev)
@@ -445,6 +465,7 @@ def postprocess_array(batch_importances, skip_frames, full_n_frames, change_poin
                        "gn_summary_indicator")
     summarized_video = None
     if full_frames is not None:
+        cps_host = cps.cpu().numpy()
         chosen = torch.nonzero(sel[:n_clips]).flatten().cpu().tolist()
         parts = [full_frames[int(cps_host[j][0]):int(cps_host[j][1])] for j in chosen]      # utils.py:634
         summarized_video = np.concatenate(parts, axis=0) if parts else None

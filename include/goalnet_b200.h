@@ -119,6 +119,13 @@ int64_t gn_avm_workspace_bytes(const gn_model* m, int64_t n);
 int gn_avm_forward(gn_model* m, const float* d_visual, const float* d_audio, int64_t n, float* d_scores,
                    float* d_visual_features, void* d_workspace, int64_t workspace_bytes, void* stream);
 
+/* Per-stage device timing of gn_avm_forward (CUDA events recorded on the forward's stream).
+ * GN_AVM_STAGES stages: 0 VisBl block 1 (conv1), 1 AudBl, 2 conv2 block, 3 conv3 block, 4 linear5,
+ * 5 fusion MLP.  gn_model_get_timing synchronises on the last forward and writes milliseconds. */
+#define GN_AVM_STAGES 6
+int gn_model_set_timing(gn_model* m, int enable);
+int gn_model_get_timing(gn_model* m, float* h_ms, int n_stages);
+
 /* ---------------------------------------------------------------------------------------------
  * (a6-a9) keyshot selection -- replaces utils.py:608-613,627-641 (`postprocess` without its HDF5
  *      reads), 396-410 (`expand_array`), 445-464 (`get_clip_information`), 466-510 (`knapsack`).
