@@ -223,7 +223,7 @@ def native_arm(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, profile=False):
         for _ in range(warmup):
             fn()
         barrier()
@@ -231,11 +231,15 @@ def native_arm(args, rank, world, local_rank):
         sampler.start()
         l0 = _lib.launch_count(dev.index)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if profile:
+            torch.cuda.profiler.start()      # `ncu --profile-from-start off` captures exactly the timed steps
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         barrier()
+        if profile:
+            torch.cuda.profiler.stop()
         ms = e0.elapsed_time(e1)
         launches = _lib.launch_count(dev.index) - l0
         clocks = sampler.stop()
@@ -245,7 +249,7 @@ def native_arm(args, rank, world, local_rank):
             ms = float(t.item())
         return ms, launches, clocks
 
-    ms, launches, clocks = timed(step_device, args.steps, args.warmup)
+    ms, launches, clocks = timed(step_device, args.steps, args.warmup, profile=True)
     value = world * n * args.steps / (ms * 1e-3)
 
     # ---- e2e: pinned host inputs, H2D + D2H inside the timed region ------------------------------

@@ -143,8 +143,9 @@ def test_model_vs_oracle_and_simt(U, weights, n):
     assert np.abs(y_simt - ref).max() / np.abs(ref).max() <= SCORE_RTOL
     rv = feats["visual_features"].numpy()
     assert np.abs(f_tc - rv).max() <= FEAT_TOL * np.abs(rv).max()
-    # tensor-core path vs the CUDA-core validation path: same bf16 operands, only summation order differs
-    assert np.abs(f_tc - f_simt).max() <= 4e-3 * np.abs(rv).max()
+    # tensor-core path vs the CUDA-core validation path: same bf16 operands, only the summation order differs,
+    # which can flip the final bf16 rounding of a feature by one ulp (2^-8 relative)
+    assert np.abs(f_tc - f_simt).max() <= 8e-3 * np.abs(rv).max()
     ra = feats["audio_features"].numpy()
     assert np.abs(h0_tc[:, :128] - ra).max() <= 1e-2 * max(np.abs(ra).max(), 1e-3)   # bf16 store of fp32 AudBl
 
