@@ -3,14 +3,14 @@
 // resampling W (B x q).  Replaces reference utils.py:322-349 (librosa.feature.mfcc + interp1d loop).
 //
 // One CTA per slot.  Two STFT columns share one complex 2048-point FFT (column j in the real part,
-// column j+1 in the imaginary part), radix-2 DIF in shared memory; mel sums and the segment max are
-// warp-shuffle reductions.  HBM traffic is the slot's samples in and 30*B floats out.
+// column j+1 in the imaginary part), four Stockham passes of radix 4/8/8/8 with register butterflies
+// (gn_fft.cuh); mel sums and the segment max are warp-shuffle reductions.  HBM traffic is the slot's samples in and 30*B floats out.
 #include "gn_common.cuh"
+#include "gn_fft.cuh"
 
 namespace {
 
 constexpr int kFFT = 2048;
-constexpr int kLog2FFT = 11;
 constexpr int kHop = 512;
 constexpr int kMels = 128;
 constexpr int kMfcc = 30;
@@ -34,10 +34,15 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             const int32_t* __restrict__ mel_offset, const float* __restrict__ mel_w,
             const float* __restrict__ dct, const float2* __restrict__ twiddle, const float* __restrict__ hann,
             float* __restrict__ out) {
+    using gnfft::kBufA; using gnfft::kBufB; using gnfft::kTwCount; using gnfft::kTw2048; using gnfft::kTw256;
+    using gnfft::kTw32; using gnfft::pass1; using gnfft::pass8;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* z = reinterpret_cast<float2*>(smem_raw);            // [2048] FFT buffer
-    float2* tw = z + kFFT;                                       // [1024] twiddles
-    float* pw0 = reinterpret_cast<float*>(tw + kFFT / 2);        // [1025] power of column j
+    float* are = reinterpret_cast<float*>(smem_raw);             // FFT buffer A (pass-1 padding), re / im
+    float* aim = are + kBufA;
+    float* bre = aim + kBufA;                                    // FFT buffer B (pass-2 padding), re / im
+    float* bim = bre + kBufB;
+    float2* tw = reinterpret_cast<float2*>(bim + kBufB);         // [kTwCount] per-pass twiddle tables
+    float* pw0 = reinterpret_cast<float*>(tw + kTwCount);        // [1025] power of column j
     float* pw1 = pw0 + (kFFT / 2 + 1);                           // [1025] power of column j+1
     float* mel = pw1 + (kFFT / 2 + 1);                           // [128][max_q] log-mel
     float* cep = mel + kMels * max_q;                            // [30][max_q]
@@ -45,7 +50,13 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
     __shared__ float s_max;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < kFFT / 2; i += kThreads) tw[i] = twiddle[i];
+    // twiddle[k] = exp(-2 pi i k / 2048), k < 1024
+    tw[kTw2048 + tid] = twiddle[tid];
+    if (tid < 32) tw[kTw256 + tid] = twiddle[8 * tid];
+    if (tid < 4) tw[kTw32 + tid] = twiddle[64 * tid];
+    float hw[8];                                                 // this thread's window taps t = tid + 256 s
+#pragma unroll
+    for (int s = 0; s < 8; ++s) hw[s] = hann[tid + 256 * s];
 
     for (int64_t slot = blockIdx.x; slot < n; slot += gridDim.x) {
         const int64_t s0 = seg_start[slot];
@@ -55,37 +66,32 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
         __syncthreads();
         for (int j = 0; j < q; j += 2) {
             const bool two = (j + 1 < q);
-            // windowed columns j (re) and j+1 (im); samples outside [0,L) are the centre zero padding
-            for (int t = tid; t < kFFT; t += kThreads) {
-                const float w = hann[t];
+            // windowed columns j (re) and j+1 (im); samples outside [0,L) are the centre zero padding.
+            // Pass 1 consumes the points straight from registers (t = tid + 256 s).
+            float2 z[8];
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                const int t = tid + 256 * s;
                 const int i0 = j * kHop - kFFT / 2 + t;
                 const int i1 = i0 + kHop;
-                float a = (i0 >= 0 && i0 < L) ? seg[i0] * w : 0.f;
-                float b = (two && i1 >= 0 && i1 < L) ? seg[i1] * w : 0.f;
-                z[t] = make_float2(a, b);
+                const float a = (i0 >= 0 && i0 < L) ? __ldg(seg + i0) * hw[s] : 0.f;
+                const float b = (two && i1 >= 0 && i1 < L) ? __ldg(seg + i1) * hw[s] : 0.f;
+                z[s] = make_float2(a, b);
             }
+            pass1(tid, z, are, aim);
             __syncthreads();
-            // radix-2 decimation-in-frequency, in place; output index is bit-reversed
-#pragma unroll 1
-            for (int s = 0; s < kLog2FFT; ++s) {
-                const int m = kFFT >> (s + 1);
-                for (int bfly = tid; bfly < kFFT / 2; bfly += kThreads) {
-                    const int pos = bfly & (m - 1);
-                    const int i = ((bfly - pos) << 1) + pos;
-                    const float2 a = z[i], c = z[i + m];
-                    const float2 wv = tw[pos << s];
-                    const float dx = a.x - c.x, dy = a.y - c.y;
-                    z[i] = make_float2(a.x + c.x, a.y + c.y);
-                    z[i + m] = make_float2(dx * wv.x - dy * wv.y, dx * wv.y + dy * wv.x);
-                }
-                __syncthreads();
-            }
+            pass8<4, 1, 2>(tid, are, aim, bre, bim, tw + kTw32);
+            __syncthreads();
+            pass8<32, 2, 0>(tid, bre, bim, are, aim, tw + kTw256);
+            __syncthreads();
+            pass8<256, 0, 0>(tid, are, aim, bre, bim, tw + kTw2048);
+            __syncthreads();
             // split the two real spectra: X1[k] = (Z[k] + conj Z[N-k])/2, X2[k] = (Z[k] - conj Z[N-k])/(2i)
             for (int k = tid; k <= kFFT / 2; k += kThreads) {
-                const float2 zk = z[__brev((unsigned)k) >> (32 - kLog2FFT)];
-                const float2 zn = z[__brev((unsigned)((kFFT - k) & (kFFT - 1))) >> (32 - kLog2FFT)];
-                const float x1r = 0.5f * (zk.x + zn.x), x1i = 0.5f * (zk.y - zn.y);
-                const float x2r = 0.5f * (zk.y + zn.y), x2i = -0.5f * (zk.x - zn.x);
+                const int kn = (kFFT - k) & (kFFT - 1);
+                const float zkx = bre[k], zky = bim[k], znx = bre[kn], zny = bim[kn];
+                const float x1r = 0.5f * (zkx + znx), x1i = 0.5f * (zky - zny);
+                const float x2r = 0.5f * (zky + zny), x2i = -0.5f * (zkx - znx);
                 pw0[k] = x1r * x1r + x1i * x1i;
                 pw1[k] = x2r * x2r + x2i * x2i;
             }
@@ -96,7 +102,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                 const float* wv = mel_w + mel_offset[mband];
                 float a0 = 0.f, a1 = 0.f;
                 for (int i = lane; i < cnt; i += 32) {
-                    const float w = wv[i];
+                    const float w = __ldg(wv + i);
                     a0 = fmaf(w, pw0[st + i], a0);
                     a1 = fmaf(w, pw1[st + i], a1);
                 }
@@ -107,8 +113,10 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                     if (two) mel[mband * max_q + j + 1] = a1;
                 }
             }
-            __syncthreads();
+            // no barrier needed here: the next column's passes 1-4 do not touch pw0/pw1/mel, and their
+            // barriers order this iteration's pw reads before the next split overwrites pw0/pw1
         }
+        __syncthreads();
         // power_to_db: 10 log10(max(1e-10, S)), floored at (segment max - 80 dB)
         float lmax = -INFINITY;
         for (int i = tid; i < kMels * q; i += kThreads) {
@@ -134,7 +142,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             float acc = 0.f;
 #pragma unroll 8
             for (int mband = 0; mband < kMels; ++mband)
-                acc = fmaf(d[mband], fmaxf(mel[mband * max_q + j], floor_db), acc);
+                acc = fmaf(__ldg(d + mband), fmaxf(mel[mband * max_q + j], floor_db), acc);
             cep[c * max_q + j] = acc;
         }
         __syncthreads();
@@ -144,7 +152,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
         for (int i = tid; i < kMfcc * B; i += kThreads) {
             const int c = i / B, b = i - c * B;
             float acc = 0.f;
-            for (int j = 0; j < q; ++j) acc = fmaf(W[b * q + j], cep[c * max_q + j], acc);
+            for (int j = 0; j < q; ++j) acc = fmaf(__ldg(W + b * q + j), cep[c * max_q + j], acc);
             o[i] = acc;
         }
     }
@@ -166,8 +174,8 @@ extern "C" int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_sampl
     if (!d_y || !d_seg_start || !d_seg_len || !d_w_offset || !d_w || !d_mel_start || !d_mel_count ||
         !d_mel_offset || !d_mel_w || !d_dct || !d_out) return GN_E_ARG;
     const gn_mfcc_tables t = gn_get_mfcc_tables(h);
-    const size_t smem = sizeof(float2) * (kFFT + kFFT / 2) + sizeof(float) * (2 * (kFFT / 2 + 1)) +
-                        sizeof(float) * (size_t)(kMels + kMfcc) * max_q + 16;
+    const size_t smem = sizeof(float) * 2 * (gnfft::kBufA + gnfft::kBufB) + sizeof(float2) * gnfft::kTwCount +
+                        sizeof(float) * (2 * (kFFT / 2 + 1)) + sizeof(float) * (size_t)(kMels + kMfcc) * max_q + 16;
     static bool attr_set = false;
     if (!attr_set) {
         GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));

@@ -3,6 +3,8 @@
 //   gn_knapsack          <- utils.py:466-510 (0/1 DP + backtrack)
 //   gn_summary_indicator <- utils.py:638-641
 //   gn_fscore_counts     <- utils.py:571-573 (the three sums per annotator)
+#include <stdio.h>
+#include <stdlib.h>
 #include "gn_common.cuh"
 
 namespace {
@@ -110,6 +112,120 @@ knapsack_kernel(const int32_t* __restrict__ values_all, const int32_t* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
+// 0/1 knapsack, thread-block-cluster version: the table columns are split over the CTAs of one
+// cluster (one cluster per problem); every CTA keeps its slice of the previous/current row in its
+// own shared memory and reads K[i-1][w - wt] from the owning CTA through distributed shared memory.
+// One barrier.cluster per item replaces the single-CTA __syncthreads() and divides the per-row work
+// by the cluster size.  The backtrack is a single warp that tests 32 rows per L2 round trip (rows
+// whose decision bit at the current w is clear leave w unchanged, so they can be skipped together).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ int32_t ld_cluster_s32(uint32_t addr) {
+    int32_t v;
+    asm volatile("ld.shared::cluster.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS, 1)
+knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* __restrict__ weights_all, int n_items,
+                        int capacity, int zero_col_forced, uint8_t* __restrict__ selected_all,
+                        int32_t* __restrict__ best_all, uint32_t* bits_all, int words, int slice_w) {
+    extern __shared__ int32_t row_smem[];            // [2][slice_w]
+    const uint32_t rank = cluster_ctarank();
+    const int prob = (int)cluster_id_x();
+    const int32_t* values = values_all + (size_t)prob * n_items;
+    const int32_t* weights = weights_all + (size_t)prob * n_items;
+    uint8_t* selected = selected_all + (size_t)prob * n_items;
+    uint32_t* bits = bits_all + (size_t)prob * n_items * words;
+    const int C = capacity + 1;
+    const int c0 = (int)rank * slice_w;              // first table column of this CTA's slice
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(row_smem);
+
+    for (int l = tid; l < 2 * slice_w; l += THREADS) row_smem[l] = 0;      // K[0][*] = 0 (utils.py:487)
+    if (rank == 0)
+        for (int i = tid; i < n_items; i += THREADS) selected[i] = 0;
+    cluster_barrier();
+
+    int pb = 0;                                       // buffer holding row i-1
+    for (int i = 0; i < n_items; ++i) {
+        const int32_t wt = __ldg(weights + i), v = __ldg(values + i);
+        const int q = wt / slice_w, rem = wt - q * slice_w;
+        const int own_a = (int)rank - q, own_b = own_a - 1;         // CTAs holding K[i-1][w - wt]
+        const int32_t* prev = row_smem + pb * slice_w;
+        int32_t* cur = row_smem + (pb ^ 1) * slice_w;
+        const uint32_t prev_addr = smem_base + (uint32_t)(pb * slice_w) * 4u;
+        // shared::cluster addresses of row i-1 in the two CTAs that can hold column w - wt
+        const uint32_t rem_a = map_to_cta(prev_addr, (uint32_t)(own_a >= 0 ? own_a : 0));
+        const uint32_t rem_b = map_to_cta(prev_addr, (uint32_t)(own_b >= 0 ? own_b : 0));
+        uint32_t* brow = bits + (size_t)i * words + (c0 >> 5);
+#pragma unroll 1
+        for (int l = tid; l < slice_w; l += THREADS) {
+            const int w = c0 + l;
+            const int32_t old = prev[l];
+            int32_t nv = old;
+            // utils.py:487-492; column 0 of the reference table is forced to 0
+            if (w < C && wt <= w && !(w == 0 && zero_col_forced)) {
+                const int sl = l - rem;
+                const uint32_t addr = sl >= 0 ? rem_a + (uint32_t)sl * 4u : rem_b + (uint32_t)(sl + slice_w) * 4u;
+                const int32_t cand = v + ld_cluster_s32(addr);
+                nv = cand > old ? cand : old;
+            }
+            cur[l] = nv;
+            const uint32_t word = __ballot_sync(0xffffffffu, nv != old);
+#ifdef GN_KNAP_DEBUG
+            if (lane == 0 && (c0 + l) < words * 32 && ((c0 >> 5) + (l >> 5) >= words)) printf("bad bits idx rank %u l %d\n", rank, l);
+#endif
+            if (lane == 0 && (c0 + l) < words * 32) brow[l >> 5] = word;
+        }
+        cluster_barrier();       // row i complete everywhere; row i-1 no longer read by anyone
+        pb ^= 1;
+    }
+    // K[n][capacity]
+    if (tid == 0 && capacity >= c0 && capacity < c0 + slice_w) best_all[prob] = row_smem[pb * slice_w + capacity - c0];
+    // backtrack (utils.py:495-509): skip item i when K[i][w] == K[i-1][w]
+    if (rank == 0 && tid < 32) {
+        int w = capacity;
+        int i = n_items;
+        while (i > 0) {
+            const int row = i - 1 - lane;
+            uint32_t bit = 0;
+            if (row >= 0) {
+                const volatile uint32_t* bp = bits + (size_t)row * words + (w >> 5);
+                bit = (*bp >> (w & 31)) & 1u;
+            }
+            const uint32_t mask = __ballot_sync(0xffffffffu, bit != 0);
+            if (mask == 0) { i -= 32; continue; }
+            const int r = i - 1 - (__ffs(mask) - 1);          // nearest selected row below i
+#ifdef GN_KNAP_DEBUG
+            if (lane == 0 && (r < 0 || r >= n_items || w < 0 || w > capacity)) printf("bad backtrack r %d w %d i %d\n", r, w, i);
+#endif
+            if (lane == 0) selected[r] = 1;
+            w -= __ldg(weights + r);
+            i = r;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // summary indicator
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -211,19 +327,44 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
     const int64_t words = knap_words(capacity);
     const int64_t per = gn_knapsack_workspace_bytes(n_items, capacity);
     if (per * batch > workspace_bytes || (!d_workspace && per > 0)) return GN_E_WORKSPACE;
-    const int64_t row_bytes = 2 * words * 32 * 4;
-    const int use_smem = row_bytes <= kKnapSmemLimit ? 1 : 0;
-    static bool attr = false;
-    if (!attr) {
-        GN_CUDA(cudaFuncSetAttribute(knapsack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
-        attr = true;
-    }
+    // cluster path: columns split over up to 8 CTAs (portable cluster size), at least 1024 columns per CTA
+    int cl = 8;
+    while (cl > 1 && (capacity + 1) < (int64_t)cl * 1024) cl >>= 1;
+    if (const char* e = getenv("GN_KNAP_CL")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) cl = v; }
+    int64_t slice = (capacity + 1 + cl - 1) / cl;
+    slice = (slice + 31) & ~31LL;
+    const int use_smem = 2 * slice * 4 <= kKnapSmemLimit ? 1 : 0;
     // workspace: [batch][n_items][words] bits, then (if needed) [batch][2][words*32] rows
     uint32_t* bits = reinterpret_cast<uint32_t*>(d_workspace);
+    if (use_smem) {
+        constexpr int kT = 1024;
+        auto kern = knapsack_cluster_kernel<kT>;
+        static bool cattr = false;
+        if (!cattr) {
+            GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
+            cattr = true;
+        }
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)(batch * cl));
+        cfg.blockDim = dim3(kT);
+        cfg.dynamicSmemBytes = (size_t)(2 * slice * 4);
+        cfg.stream = gn_stream(stream);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)cl;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        GN_CUDA(cudaLaunchKernelEx(&cfg, kern, d_values, d_weights, n_items, (int)capacity,
+                                   capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, (int)words, (int)slice));
+        GN_LAUNCHED(h);
+        return GN_OK;
+    }
     int32_t* rows = reinterpret_cast<int32_t*>(bits + (size_t)batch * n_items * words);
-    knapsack_kernel<<<batch, kKnapThreads, use_smem ? (size_t)row_bytes : 0, gn_stream(stream)>>>(
+    knapsack_kernel<<<batch, kKnapThreads, 0, gn_stream(stream)>>>(
         d_values, d_weights, n_items, capacity, capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, words, rows,
-        use_smem);
+        0);
     GN_LAUNCHED(h);
     return GN_OK;
 }

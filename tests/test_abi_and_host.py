@@ -100,3 +100,17 @@ def test_expand_array_host():
     from cvml_goalnet_b200.utils import expand_array
     for arr, r, L in (([1, 2, 3], 2, 5), ([1, 2, 3], 2, 9), ([4, 5], 3, 2), ([7], 5, 5)):
         assert list(expand_array(list(arr), r, L)) == list(O.expand_array(list(arr), r, L))
+
+
+def test_fft_passes_host_check(tmp_path):
+    """gn_fft.cuh (the MFCC kernel's 2048-point Stockham FFT) run on the CPU against a direct DFT in double."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    exe = str(tmp_path / "fft_host_check")
+    subprocess.run([nvcc, "-std=c++17", "-O2", "-Wno-deprecated-gpu-targets", "-o", exe,
+                    os.path.join(ROOT, "tests", "native", "fft_host_check.cu")], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr

@@ -189,13 +189,40 @@ def test_knapsack_random_vs_oracle(U):
     assert U.knapsack(v, w, 4.4) == O.knapsack(v, w, 4.4)
 
 
-def test_knapsack_wide_table_global_rows(U):
-    """capacity too wide for shared-memory rows -> rows in the workspace."""
+def test_knapsack_wide_table_cluster_slices(U):
+    """60 001 columns: 8 cluster CTAs x 7 520-column slices; weights larger than a slice reach across CTAs."""
     rng = np.random.default_rng(11)
     n = 40
     v = rng.integers(1, 1000, n).tolist()
     w = rng.integers(1000, 9000, n).tolist()     # gcd 1 -> 60001 columns
     assert U.knapsack(v, w, 60000, 1) == O.knapsack_rows(v, w, 60000, 1)
+    w2 = rng.integers(1, 30000, n).tolist()      # weights spanning up to 4 slices
+    assert U.knapsack(v, w2, 60000, 1) == O.knapsack_rows(v, w2, 60000, 1)
+
+
+def test_knapsack_very_wide_table_global_rows(U):
+    """capacity too wide even for 8 shared-memory slices -> single-CTA kernel with rows in the workspace."""
+    rng = np.random.default_rng(12)
+    n = 10
+    v = rng.integers(1, 1000, n).tolist()
+    w = rng.integers(20000, 90000, n).tolist()
+    assert U.knapsack(v, w, 230000, 1) == O.knapsack_rows(v, w, 230000, 1)
+
+
+def test_knapsack_batched_problems(U):
+    """gn_knapsack batch > 1 (one cluster per problem): the 20 annotator knapsacks of utils.py:102-118 at once."""
+    import torch
+    rng = np.random.default_rng(13)
+    batch, n, cap = 20, 60, 5400
+    vals = rng.integers(0, 900, (batch, n)).astype(np.int32)
+    wts = np.tile(rng.integers(30, 300, n).astype(np.int32), (batch, 1))
+    from cvml_goalnet_b200.utils import _knapsack_device
+    dev = torch.device("cuda", 0)
+    sel, best = _knapsack_device(torch.from_numpy(vals).to(dev), torch.from_numpy(wts).to(dev), n, cap, 0, batch, dev)
+    sel = sel.cpu().numpy()
+    for b in range(batch):
+        ref = O.knapsack_rows(vals[b].tolist(), wts[b].tolist(), cap, 1)
+        assert np.nonzero(sel[b])[0].tolist() == ref, b
 
 
 def test_clip_information_golden(U, golden):
