@@ -15,6 +15,8 @@ constexpr int kHop = 512;
 constexpr int kMels = 128;
 constexpr int kMfcc = 30;
 constexpr int kThreads = 256;
+constexpr int kMelWMax = 2304;              // >= 2 * 1025: every FFT bin feeds at most two triangular filters
+static_assert(kThreads == 2 * kMels, "one thread per (mel band, STFT column of the pair)");
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -46,6 +48,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
     float* pw1 = pw0 + (kFFT / 2 + 1);                           // [1025] power of column j+1
     float* mel = pw1 + (kFFT / 2 + 1);                           // [128][max_q] log-mel
     float* cep = mel + kMels * max_q;                            // [30][max_q]
+    float* melw = cep + kMfcc * max_q;                           // [kMelWMax] mel filter weights
     __shared__ float red[kThreads / 32];
     __shared__ float s_max;
 
@@ -54,6 +57,14 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
     tw[kTw2048 + tid] = twiddle[tid];
     if (tid < 32) tw[kTw256 + tid] = twiddle[8 * tid];
     if (tid < 4) tw[kTw32 + tid] = twiddle[64 * tid];
+    // mel filterbank weights (CSR) in shared memory when they fit; this thread owns band tid & 127 of column tid >> 7
+    const int n_mel_w = mel_offset[kMels - 1] + mel_count[kMels - 1];
+    const bool melw_fits = n_mel_w <= kMelWMax;
+    if (melw_fits)
+        for (int i = tid; i < n_mel_w; i += kThreads) melw[i] = mel_w[i];
+    const int my_band = tid & (kMels - 1), my_col = tid >> 7;
+    const int my_st = mel_start[my_band], my_cnt = mel_count[my_band];
+    const float* my_w = (melw_fits ? melw : mel_w) + mel_offset[my_band];
     float hw[8];                                                 // this thread's window taps t = tid + 256 s
 #pragma unroll
     for (int s = 0; s < 8; ++s) hw[s] = hann[tid + 256 * s];
@@ -96,22 +107,12 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                 pw1[k] = x2r * x2r + x2i * x2i;
             }
             __syncthreads();
-            // mel filterbank: one warp per mel band, lanes stride over the band's bins
-            for (int mband = warp; mband < kMels; mband += kThreads / 32) {
-                const int st = mel_start[mband], cnt = mel_count[mband];
-                const float* wv = mel_w + mel_offset[mband];
-                float a0 = 0.f, a1 = 0.f;
-                for (int i = lane; i < cnt; i += 32) {
-                    const float w = __ldg(wv + i);
-                    a0 = fmaf(w, pw0[st + i], a0);
-                    a1 = fmaf(w, pw1[st + i], a1);
-                }
-                a0 = warp_sum(a0);
-                a1 = warp_sum(a1);
-                if (lane == 0) {
-                    mel[mband * max_q + j] = a0;
-                    if (two) mel[mband * max_q + j + 1] = a1;
-                }
+            // mel filterbank: thread = (band, column); the band's bins are contiguous (triangular filter)
+            {
+                const float* pwc = my_col ? pw1 : pw0;
+                float acc = 0.f;
+                for (int i = 0; i < my_cnt; ++i) acc = fmaf(my_w[i], pwc[my_st + i], acc);
+                if (my_col == 0 || two) mel[my_band * max_q + j + my_col] = acc;
             }
             // no barrier needed here: the next column's passes 1-4 do not touch pw0/pw1/mel, and their
             // barriers order this iteration's pw reads before the next split overwrites pw0/pw1
@@ -175,7 +176,7 @@ extern "C" int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_sampl
         !d_mel_offset || !d_mel_w || !d_dct || !d_out) return GN_E_ARG;
     const gn_mfcc_tables t = gn_get_mfcc_tables(h);
     const size_t smem = sizeof(float) * 2 * (gnfft::kBufA + gnfft::kBufB) + sizeof(float2) * gnfft::kTwCount +
-                        sizeof(float) * (2 * (kFFT / 2 + 1)) + sizeof(float) * (size_t)(kMels + kMfcc) * max_q + 16;
+                        sizeof(float) * (2 * (kFFT / 2 + 1)) + sizeof(float) * (size_t)(kMels + kMfcc) * max_q + sizeof(float) * kMelWMax + 16;
     static bool attr_set = false;
     if (!attr_set) {
         GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));

@@ -143,12 +143,14 @@ __device__ __forceinline__ void cluster_barrier() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+constexpr int kKnapRing = 32;     // rows of decision bits buffered in shared memory between flushes
+
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS, 1)
 knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* __restrict__ weights_all, int n_items,
                         int capacity, int zero_col_forced, uint8_t* __restrict__ selected_all,
                         int32_t* __restrict__ best_all, uint32_t* bits_all, int words, int slice_w) {
-    extern __shared__ int32_t row_smem[];            // [2][slice_w]
+    extern __shared__ int32_t row_smem[];            // [2][slice_w] rows, then [kKnapRing][slice_w/32] decision bits
     const uint32_t rank = cluster_ctarank();
     const int prob = (int)cluster_id_x();
     const int32_t* values = values_all + (size_t)prob * n_items;
@@ -157,6 +159,10 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
     uint32_t* bits = bits_all + (size_t)prob * n_items * words;
     const int C = capacity + 1;
     const int c0 = (int)rank * slice_w;              // first table column of this CTA's slice
+    const int sw = slice_w >> 5;                     // decision words per row in this slice
+    const int w0 = c0 >> 5;                          // first decision word of this slice
+    const int nw = (w0 + sw <= words) ? sw : (words > w0 ? words - w0 : 0);   // words of the slice that exist
+    uint32_t* ring = reinterpret_cast<uint32_t*>(row_smem + 2 * slice_w);
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(row_smem);
 
@@ -176,7 +182,7 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
         // shared::cluster addresses of row i-1 in the two CTAs that can hold column w - wt
         const uint32_t rem_a = map_to_cta(prev_addr, (uint32_t)(own_a >= 0 ? own_a : 0));
         const uint32_t rem_b = map_to_cta(prev_addr, (uint32_t)(own_b >= 0 ? own_b : 0));
-        uint32_t* brow = bits + (size_t)i * words + (c0 >> 5);
+        uint32_t* rrow = ring + (i & (kKnapRing - 1)) * sw;
 #pragma unroll 1
         for (int l = tid; l < slice_w; l += THREADS) {
             const int w = c0 + l;
@@ -185,16 +191,30 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
             // utils.py:487-492; column 0 of the reference table is forced to 0
             if (w < C && wt <= w && !(w == 0 && zero_col_forced)) {
                 const int sl = l - rem;
-                const uint32_t addr = sl >= 0 ? rem_a + (uint32_t)sl * 4u : rem_b + (uint32_t)(sl + slice_w) * 4u;
-                const int32_t cand = v + ld_cluster_s32(addr);
+                int32_t src;
+                if (q == 0 && sl >= 0) {
+                    src = prev[sl];                                   // same CTA: plain shared load
+                } else {
+                    const uint32_t addr = sl >= 0 ? rem_a + (uint32_t)sl * 4u : rem_b + (uint32_t)(sl + slice_w) * 4u;
+                    src = ld_cluster_s32(addr);
+                }
+                const int32_t cand = v + src;
                 nv = cand > old ? cand : old;
             }
             cur[l] = nv;
             const uint32_t word = __ballot_sync(0xffffffffu, nv != old);
-#ifdef GN_KNAP_DEBUG
-            if (lane == 0 && (c0 + l) < words * 32 && ((c0 >> 5) + (l >> 5) >= words)) printf("bad bits idx rank %u l %d\n", rank, l);
-#endif
-            if (lane == 0 && (c0 + l) < words * 32) brow[l >> 5] = word;
+            if (lane == 0) rrow[l >> 5] = word;
+        }
+        // Decision bits leave shared memory once per kKnapRing rows, so that the release fence of the
+        // per-row cluster barrier normally has no global stores to wait for.
+        if ((i & (kKnapRing - 1)) == kKnapRing - 1 || i == n_items - 1) {
+            __syncthreads();
+            const int r0 = i & ~(kKnapRing - 1);
+            const int nr = i - r0 + 1;
+            for (int e = tid; e < nr * sw; e += THREADS) {
+                const int r = e / sw, wi = e - r * sw;
+                if (wi < nw) bits[(size_t)(r0 + r) * words + w0 + wi] = ring[e];
+            }
         }
         cluster_barrier();       // row i complete everywhere; row i-1 no longer read by anyone
         pb ^= 1;
@@ -215,9 +235,6 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
             const uint32_t mask = __ballot_sync(0xffffffffu, bit != 0);
             if (mask == 0) { i -= 32; continue; }
             const int r = i - 1 - (__ffs(mask) - 1);          // nearest selected row below i
-#ifdef GN_KNAP_DEBUG
-            if (lane == 0 && (r < 0 || r >= n_items || w < 0 || w > capacity)) printf("bad backtrack r %d w %d i %d\n", r, w, i);
-#endif
             if (lane == 0) selected[r] = 1;
             w -= __ldg(weights + r);
             i = r;
@@ -333,7 +350,8 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
     if (const char* e = getenv("GN_KNAP_CL")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) cl = v; }
     int64_t slice = (capacity + 1 + cl - 1) / cl;
     slice = (slice + 31) & ~31LL;
-    const int use_smem = 2 * slice * 4 <= kKnapSmemLimit ? 1 : 0;
+    const int64_t cl_smem = 2 * slice * 4 + kKnapRing * (slice / 32) * 4;
+    const int use_smem = cl_smem <= kKnapSmemLimit ? 1 : 0;
     // workspace: [batch][n_items][words] bits, then (if needed) [batch][2][words*32] rows
     uint32_t* bits = reinterpret_cast<uint32_t*>(d_workspace);
     if (use_smem) {
@@ -347,7 +365,7 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)(batch * cl));
         cfg.blockDim = dim3(kT);
-        cfg.dynamicSmemBytes = (size_t)(2 * slice * 4);
+        cfg.dynamicSmemBytes = (size_t)cl_smem;
         cfg.stream = gn_stream(stream);
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
