@@ -8,8 +8,10 @@
 // tcgen05.mma (cta_group::1, M=128) into fp32 accumulators in TMEM (two 256-column buffers so that
 // the epilogue of tile i overlaps the MMAs of tile i+1), and read back with tcgen05.ld.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..9 = epilogue (TMEM lane quarter = warp_id % 4; the two warps of a quarter split the
+// 32-column chunks).  The conv epilogue is the larger half of a conv tile's work, so it gets two
+// warps per scheduler and 16-byte shared/global accesses throughout.
 #include "gn_common.cuh"
 #include "gn_tc_ptx.cuh"
 
@@ -17,10 +19,13 @@ namespace {
 
 using namespace tcx;
 
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;             // two epilogue warps per TMEM lane quarter (they split the column chunks)
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;
 constexpr int kBK = 64;                  // bf16 elements per k-step = one 128-byte swizzle row
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;            // columns per accumulator buffer (MT * BN)
+constexpr int kMaxN = 512;               // widest layer: per-channel parameter vectors staged in shared memory
 
 enum Mode { kConv = 0, kLinear = 1, kScore = 2 };
 
@@ -54,28 +59,41 @@ struct Cfg {
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kStgStride = BN * 2 + 16;          // padded bf16 row of the pooling stage
     static constexpr int kStgBytes = (MODE == kConv) ? (MT * 128 * kStgStride) : 0;
-    static constexpr int kSmemBytes = 1024 /*align slack*/ + STAGES * kStageBytes + kStgBytes + 256 /*barriers*/;
+    static constexpr int kParamBytes = 3 * kMaxN * 4;       // bias | bn_scale | bn_shift (or bias | w_last)
+    static constexpr int kSmemBytes = 1024 /*align slack*/ + STAGES * kStageBytes + kStgBytes + kParamBytes + 256 /*barriers*/;
     static_assert(MT * BN <= kAccCols, "an accumulator buffer is at most 256 TMEM columns");
     static_assert(MODE == kConv || MT == 1, "linear modes use one 128-row M tile");
+    static_assert(kSmemBytes <= 232448, "exceeds the 227 KB shared memory of one CTA");
 };
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ uint32_t hmax2_u32(uint32_t a, uint32_t b) {
+    __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+    return *reinterpret_cast<uint32_t*>(&r);
+}
+__device__ __forceinline__ uint4 hmax2_u4(uint4 a, uint4 b) {
+    return make_uint4(hmax2_u32(a.x, b.x), hmax2_u32(a.y, b.y), hmax2_u32(a.z, b.z), hmax2_u32(a.w, b.w));
+}
+__device__ __forceinline__ float2 bf2_to_f2(uint32_t v) {
+    return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&v));
+}
 
-template <int MT, int BN, int STAGES, int MODE>
+template <int MT, int BN, int STAGES, int MODE, int OHT>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmArgs args) {
     using C = Cfg<MT, BN, STAGES, MODE>;
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: SWIZZLE_128B atoms are 8 rows x 128 B and the swizzle is address based.
-    unsigned char* smem = reinterpret_cast<unsigned char*>(
-        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    // (offset arithmetic on the shared pointer keeps the address space known to the compiler)
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char* stage_base = smem;
     unsigned char* stg = smem + STAGES * C::kStageBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(stg + C::kStgBytes);
+    float* s_par = reinterpret_cast<float*>(stg + C::kStgBytes);      // [3][kMaxN]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stg + C::kStgBytes + C::kParamBytes);
     uint64_t* full_bar = bars;                    // [STAGES]
     uint64_t* empty_bar = bars + STAGES;          // [STAGES]
     uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
@@ -90,6 +108,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int64_t num_tiles = m_blocks * n_blocks;
     const int k_iters = args.K / kBK;
 
+    // per-channel epilogue parameters: global -> shared once per CTA
+    for (int i = threadIdx.x; i < args.N; i += kThreads) {
+        s_par[i] = __ldg(args.bias + i);
+        if (MODE == kConv) {
+            s_par[kMaxN + i] = __ldg(args.bn_scale + i);
+            s_par[2 * kMaxN + i] = __ldg(args.bn_shift + i);
+        } else if (MODE == kScore) {
+            s_par[kMaxN + i] = __ldg(args.w_last + i);
+        }
+    }
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
         prefetch_tmap(&tmap_b);
@@ -99,7 +127,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(smem_u32(&tfull_bar[b]), 1);
-            mbar_init(smem_u32(&tempty_bar[b]), 4);   // one arrive per epilogue warp
+            mbar_init(smem_u32(&tempty_bar[b]), kEpiWarps);   // one arrive per epilogue warp
         }
         fence_barrier_init();
     }
@@ -126,7 +154,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         const int tap = kt / args.g.cin_blocks;
                         const int cb = kt - tap * args.g.cin_blocks;
                         const int ky = tap / 3, kx = tap - ky * 3;
-                        mbar_expect_tx(fb, (uint32_t)(args.g.OH * args.g.OW * 128 + C::kBBytes));
+                        mbar_expect_tx(fb, (uint32_t)(OHT * OHT * 128 + C::kBBytes));
                         // box (64 ch, OW, OH, 1 frame) of the zero-bordered NHWC input, shifted by the tap
                         tma_load_4d(sa, &tmap_a, fb, cb * kBK, kx, ky, (int)m_blk);
                     } else {
@@ -173,10 +201,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (++ab == 2) { ab = 0; aphase ^= 1; }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
+        // ===================== epilogue (warps 2..9) =====================
         const int q = warp & 3;                     // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;           // which half of the 32-column chunks this warp takes
         const int row = q * 32 + lane;              // accumulator row owned by this thread
-        const int et = (warp - 2) * 32 + lane;      // 0..127 among epilogue threads
+        const int et = (warp - 2) * 32 + lane;      // 0..255 among epilogue threads
+        const float* s_bias = s_par;
         int ab = 0;
         uint32_t aphase = 0;
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -188,29 +218,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * kAccCols);
 
             if (MODE == kConv) {
-                const int npix = args.g.OH * args.g.OW;
+                constexpr int npix = OHT * OHT;
+                // ---- phase 1: TMEM -> (+bias, ReLU) -> bf16 staging tile [pixel][BN] ----
 #pragma unroll 1
                 for (int mt = 0; mt < MT; ++mt) {
                     const int pix = mt * 128 + row;
 #pragma unroll 1
-                    for (int c = 0; c < BN / 32; ++c) {
+                    for (int c = half; c < BN / 32; c += 2) {
                         uint32_t r[32];
                         tmem_ld32(tbase + (uint32_t)(mt * BN + c * 32), r);
                         tmem_ld_wait();
                         if (pix < npix) {
-                            const float* bp = args.bias + n0 + c * 32;
+                            const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
                             uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)pix * C::kStgStride + c * 64);
 #pragma unroll
                             for (int v = 0; v < 4; ++v) {
-                                uint32_t w[4];
-#pragma unroll
-                                for (int e = 0; e < 4; ++e) {
-                                    const int i = v * 8 + e * 2;
-                                    const float x0 = fmaxf(__uint_as_float(r[i]) + __ldg(bp + i), 0.f);
-                                    const float x1 = fmaxf(__uint_as_float(r[i + 1]) + __ldg(bp + i + 1), 0.f);
-                                    w[e] = pack_bf16(x0, x1);
-                                }
-                                dst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+                                const float4 b0 = bp[2 * v], b1 = bp[2 * v + 1];
+                                const int i = v * 8;
+                                dst[v] = make_uint4(
+                                    pack_bf16(fmaxf(__uint_as_float(r[i]) + b0.x, 0.f), fmaxf(__uint_as_float(r[i + 1]) + b0.y, 0.f)),
+                                    pack_bf16(fmaxf(__uint_as_float(r[i + 2]) + b0.z, 0.f), fmaxf(__uint_as_float(r[i + 3]) + b0.w, 0.f)),
+                                    pack_bf16(fmaxf(__uint_as_float(r[i + 4]) + b1.x, 0.f), fmaxf(__uint_as_float(r[i + 5]) + b1.y, 0.f)),
+                                    pack_bf16(fmaxf(__uint_as_float(r[i + 6]) + b1.z, 0.f), fmaxf(__uint_as_float(r[i + 7]) + b1.w, 0.f)));
                             }
                         }
                     }
@@ -218,60 +247,68 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));      // TMEM buffer may be overwritten
-                asm volatile("bar.sync 1, 128;" ::: "memory");               // staging tile complete
-                // MaxPool(3, stride 1) over the ReLU'd tile, then BatchNorm affine, bf16 store.
-                const int P = args.g.P, OW = args.g.OW;
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile complete
+                // ---- phase 2: MaxPool(3, stride 1) over the ReLU'd tile, BatchNorm affine, bf16 NHWC store ----
+                // item = (pooled pixel, group of 8 channels): 9 x 16-byte shared loads, one 16-byte global store
+                constexpr int P = OHT - 2;
+                constexpr int CG = BN / 8;
                 const int PW = P + 2 * args.g.out_pad;
-                constexpr int kPairs = BN / 2;
                 __nv_bfloat16* obase = args.out + (size_t)m_blk * PW * PW * args.g.cout + n0;
-                for (int item = et; item < P * P * kPairs; item += 128) {
-                    const int op = item / kPairs, cp = item - op * kPairs;
+                for (int item = et; item < P * P * CG; item += kEpiThreads) {
+                    const int op = item / CG, cg = item - op * CG;
                     const int oy = op / P, ox = op - oy * P;
-                    const unsigned char* s0 = stg + (size_t)(oy * OW + ox) * C::kStgStride + cp * 4;
-                    __nv_bfloat162 m = *reinterpret_cast<const __nv_bfloat162*>(s0);
+                    const unsigned char* s0 = stg + (size_t)(oy * OHT + ox) * C::kStgStride + cg * 16;
+                    uint4 m = *reinterpret_cast<const uint4*>(s0);
 #pragma unroll
                     for (int dy = 0; dy < 3; ++dy)
 #pragma unroll
                         for (int dx = 0; dx < 3; ++dx) {
                             if (dy == 0 && dx == 0) continue;
-                            m = __hmax2(m, *reinterpret_cast<const __nv_bfloat162*>(
-                                               s0 + (size_t)(dy * OW + dx) * C::kStgStride));
+                            m = hmax2_u4(m, *reinterpret_cast<const uint4*>(s0 + (size_t)(dy * OHT + dx) * C::kStgStride));
                         }
-                    const float2 sc = __ldg(reinterpret_cast<const float2*>(args.bn_scale + n0) + cp);
-                    const float2 sh = __ldg(reinterpret_cast<const float2*>(args.bn_shift + n0) + cp);
-                    const float2 mf = __bfloat1622float2(m);
-                    const uint32_t o = pack_bf16(fmaf(mf.x, sc.x, sh.x), fmaf(mf.y, sc.y, sh.y));
+                    const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
+                    const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
+                    const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
+                    const float2 f0 = bf2_to_f2(m.x), f1 = bf2_to_f2(m.y), f2 = bf2_to_f2(m.z), f3 = bf2_to_f2(m.w);
+                    const uint4 o = make_uint4(pack_bf16(fmaf(f0.x, sc0.x, sh0.x), fmaf(f0.y, sc0.y, sh0.y)),
+                                               pack_bf16(fmaf(f1.x, sc0.z, sh0.z), fmaf(f1.y, sc0.w, sh0.w)),
+                                               pack_bf16(fmaf(f2.x, sc1.x, sh1.x), fmaf(f2.y, sc1.y, sh1.y)),
+                                               pack_bf16(fmaf(f3.x, sc1.z, sh1.z), fmaf(f3.y, sc1.w, sh1.w)));
                     const int opix = (oy + args.g.out_pad) * PW + ox + args.g.out_pad;
-                    *reinterpret_cast<uint32_t*>(obase + (size_t)opix * args.g.cout + cp * 2) = o;
+                    *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
                 }
                 if (args.g.out_pad) {   // zero border of the next conv's input (padding = 1)
                     const int nborder = 4 * PW - 4;
-                    for (int item = et; item < nborder * kPairs; item += 128) {
-                        const int bi = item / kPairs, cp = item - bi * kPairs;
+                    for (int item = et; item < nborder * CG; item += kEpiThreads) {
+                        const int bi = item / CG, cg = item - bi * CG;
                         int by, bx;
                         if (bi < PW) { by = 0; bx = bi; }
                         else if (bi < 2 * PW) { by = PW - 1; bx = bi - PW; }
                         else { const int t = bi - 2 * PW; by = 1 + (t >> 1); bx = (t & 1) ? PW - 1 : 0; }
-                        *reinterpret_cast<uint32_t*>(obase + (size_t)(by * PW + bx) * args.g.cout + cp * 2) = 0u;
+                        *reinterpret_cast<uint4*>(obase + (size_t)(by * PW + bx) * args.g.cout + cg * 8) =
+                            make_uint4(0u, 0u, 0u, 0u);
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");               // staging tile may be reused
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile may be reused
             } else {
                 const int64_t grow = m_blk * 128 + row;
                 float dot = 0.f;
+                // kScore keeps the whole row in one warp (the last layer is a dot product over the row)
+                const int c_begin = (MODE == kScore) ? (half == 0 ? 0 : BN / 32) : half;
+                const int c_step = (MODE == kScore) ? 1 : 2;
 #pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
+                for (int c = c_begin; c < BN / 32; c += c_step) {
                     uint32_t r[32];
                     tmem_ld32(tbase + (uint32_t)(c * 32), r);
                     tmem_ld_wait();
-                    const float* bp = args.bias + n0 + c * 32;
+                    const float* bp = s_bias + n0 + c * 32;
                     float x[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) x[i] = fmaxf(__uint_as_float(r[i]) + __ldg(bp + i), 0.f);
+                    for (int i = 0; i < 32; ++i) x[i] = fmaxf(__uint_as_float(r[i]) + bp[i], 0.f);
                     if (MODE == kScore) {
-                        const float* wl = args.w_last + n0 + c * 32;
+                        const float* wl = s_par + kMaxN + n0 + c * 32;
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) dot = fmaf(x[i], __ldg(wl + i), dot);
+                        for (int i = 0; i < 32; ++i) dot = fmaf(x[i], wl[i], dot);
                     } else if (grow < args.M) {
                         uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
                                                               n0 + c * 32);
@@ -292,7 +329,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         }
                     }
                 }
-                if (MODE == kScore && grow < args.M) {
+                if (MODE == kScore && half == 0 && grow < args.M) {
                     const float zlin = dot + __ldg(args.b_last);
                     args.scores[grow] = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;   // utils.py:256,270
                 }
@@ -340,11 +377,12 @@ int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, i
     return make_tmap(h, m, base, 2, dims, str, box);
 }
 
-template <int MT, int BN, int STAGES, int MODE>
+template <int MT, int BN, int STAGES, int MODE, int OHT>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
     using C = Cfg<MT, BN, STAGES, MODE>;
-    auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE>;
+    if (a.N > kMaxN) return GN_E_SHAPE;
+    auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT>;
     static bool attr = false;
     if (!attr) {
         GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -358,8 +396,8 @@ int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const Gem
 }
 
 // conv block: in = zero-bordered NHWC [n][OH+2][OW+2][Cin]; weights K-major [Cout][9*Cin]
-template <int MT, int BN, int STAGES>
-int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int OH, int Cin, const __nv_bfloat16* wk, int Cout,
+template <int MT, int BN, int STAGES, int OH>
+int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __nv_bfloat16* wk, int Cout,
              const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad, cudaStream_t st) {
     CUtensorMap ta, tb;
     const int IW = OH + 2;
@@ -375,7 +413,7 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int OH, int Cin, c
     a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
     a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
     if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
-    return launch<MT, BN, STAGES, kConv>(m->h, ta, tb, a, n * (Cout / BN), st);
+    return launch<MT, BN, STAGES, kConv, OH>(m->h, ta, tb, a, n * (Cout / BN), st);
 }
 
 template <int BN, int STAGES, int MODE>
@@ -391,7 +429,7 @@ int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, c
     GemmArgs a{};
     a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = ld_out; a.col_off = col_off;
     a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores;
-    return launch<1, BN, STAGES, MODE>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
+    return launch<1, BN, STAGES, MODE, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
 }
 
 }  // namespace
@@ -401,12 +439,13 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
                           cudaStream_t st) {
     int rc;
     // block 2: conv2 (64 -> 256) on 13x13, pool -> 11x11, written with a zero border for conv3
-    rc = run_conv<2, 128, 3>(m, n, ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
+    if (m->P1 != 13 || m->P2 != 11) return GN_E_SHAPE;
+    rc = run_conv<2, 128, 3, 13>(m, n, ws.a1p, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
                              ws.a2p, 1, st);
     if (rc) return rc;
     GN_STAGE_MARK(m, 3, st);
     // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
-    rc = run_conv<1, 256, 3>(m, n, ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
+    rc = run_conv<1, 256, 3, 11>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
                              ws.a3, 0, st);
     if (rc) return rc;
     GN_STAGE_MARK(m, 4, st);
