@@ -53,6 +53,8 @@ struct gn_model {
     __nv_bfloat16 *conv3_wk;     // [512][9*256]
     __nv_bfloat16 *linear5_wk;   // [512][81*512]  k = p*512 + c   (reference flatten is c*81 + p)
     __nv_bfloat16 *f_wk[4];      // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
+    __nv_bfloat16 *aconv2_wk;    // [128][3*64]    k = tap*64 + ci
+    __nv_bfloat16 *alinear3_wk;  // [128][L2*128]  k = l*128 + c   (reference flatten is c*L2 + l)
     void* arena;                 // one allocation backing everything above
     int timing;                  // record per-stage events in gn_avm_forward
     cudaEvent_t ev[GN_AVM_STAGES + 1];
@@ -64,6 +66,8 @@ struct gn_ws {
     __nv_bfloat16* a1p;   // [n][15][15][64]   block-1 output, zero border (conv2 input)
     __nv_bfloat16* a2p;   // [n][13][13][256]  block-2 output, zero border (conv3 input)
     __nv_bfloat16* a3;    // [n][81][512]      block-3 output, (p, c) order (linear5 input)
+    __nv_bfloat16* ac1;   // [n][L1+2][64]     AudBl conv1 output, (l, c) order, zero rows at l = -1 and l = L1
+    __nv_bfloat16* ac2;   // [n][L2][128]      AudBl conv2 output, (l, c) order (linear3 input)
     __nv_bfloat16* h0;    // [n][fin]          [audio128 | visual512]
     __nv_bfloat16* h1;    // [n][512]
     __nv_bfloat16* h2;    // [n][512]
@@ -74,7 +78,8 @@ gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
 
 // ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);
-int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st);
+int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt);
+int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st);   // conv2 + linear3 on tensor cores
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
                           cudaStream_t st);
 int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,

@@ -9,56 +9,91 @@
 namespace {
 
 constexpr int kVThreads = 256;
+constexpr int kS = 40;             // frame side (reference utils.py:285)
+constexpr int kC1 = 15;            // conv1 output side: (40 + 2*3 - 3)/3 + 1
+constexpr int kPatch = 28;         // 27 taps padded to 7 float4
 
-__global__ void __launch_bounds__(kVThreads)
-visbl_block1_kernel(const float* __restrict__ vis, int64_t n, int S, int C1, const float* __restrict__ w /*[27][64]*/,
+// conv1 has stride == kernel size (k3 s3 p3), so its im2col is a permutation of the zero-padded image:
+// pixel (y,x) of channel ci is tap (ci, y%3, x%3) of output pixel (y/3+1, x/3+1); row/column 0 of the
+// output see only padding.  The image is scattered into patch-major shared memory once, after which a
+// warp computes one output pixel for all 64 channels (2 per lane, weights in registers) from 7
+// broadcast 16-byte loads.
+__global__ void __launch_bounds__(kVThreads, 2)
+visbl_block1_kernel(const float* __restrict__ vis, int64_t n, const float* __restrict__ w /*[27][64], k=(ky*3+kx)*3+ci*/,
                     const float* __restrict__ b, const float* __restrict__ sc, const float* __restrict__ sh,
                     __nv_bfloat16* __restrict__ a1p) {
     extern __shared__ __align__(16) float sm[];
-    float* img = sm;                      // [3][S][S]
-    float* wsm = img + 3 * S * S;         // [27][64]
-    float* c1 = wsm + 27 * 64;            // [C1*C1][64]  conv + ReLU
-    const int tid = threadIdx.x;
-    for (int i = tid; i < 27 * 64; i += kVThreads) wsm[i] = w[i];
-    const int P = C1 - 2;                 // pooled size; the padded output is C1 x C1 again
-    const int co = tid & 63, pg = tid >> 6;
-    const float bias = b[co], scale = sc[co], shift = sh[co];
+    float* patch = sm;                                         // [225][28]
+    float* c1 = patch + kC1 * kC1 * kPatch;                    // [225][64]  conv + ReLU
+    unsigned short* dsto = reinterpret_cast<unsigned short*>(c1 + kC1 * kC1 * 64);   // [4800] scatter offsets
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < kC1 * kC1 * kPatch; i += kVThreads) patch[i] = 0.f;
+    for (int e = tid; e < 3 * kS * kS; e += kVThreads) {
+        const int ci = e / (kS * kS), r = e - ci * kS * kS, y = r / kS, x = r - y * kS;
+        dsto[e] = (unsigned short)(((y / 3 + 1) * kC1 + (x / 3 + 1)) * kPatch + ci * 9 + (y % 3) * 3 + (x % 3));
+    }
+    float w0[27], w1[27];                                       // weights of channels 2*lane, 2*lane+1, k = ci*9 + tap
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const float2 wv = *reinterpret_cast<const float2*>(w + (tap * 3 + ci) * 64 + 2 * lane);
+            w0[ci * 9 + tap] = wv.x;
+            w1[ci * 9 + tap] = wv.y;
+        }
+    const float2 bias = *reinterpret_cast<const float2*>(b + 2 * lane);
+    const float2 scale = *reinterpret_cast<const float2*>(sc + 2 * lane);
+    const float2 shift = *reinterpret_cast<const float2*>(sh + 2 * lane);
+    constexpr int P = kC1 - 2;                                  // pooled size; the padded output is C1 x C1 again
     for (int64_t f = blockIdx.x; f < n; f += gridDim.x) {
         __syncthreads();
-        const float4* src = reinterpret_cast<const float4*>(vis + f * 3 * S * S);
-        for (int i = tid; i < 3 * S * S / 4; i += kVThreads) reinterpret_cast<float4*>(img)[i] = src[i];
-        __syncthreads();
-        for (int p = pg; p < C1 * C1; p += kVThreads / 64) {
-            const int oy = p / C1, ox = p - oy * C1;
-            float acc = bias;
-#pragma unroll
-            for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-                for (int ky = 0; ky < 3; ++ky) {
-                    const int iy = oy * 3 - 3 + ky;
-#pragma unroll
-                    for (int kx = 0; kx < 3; ++kx) {
-                        const int ix = ox * 3 - 3 + kx;
-                        const float v = (iy >= 0 && iy < S && ix >= 0 && ix < S) ? img[(ci * S + iy) * S + ix] : 0.f;
-                        acc = fmaf(v, wsm[((ky * 3 + kx) * 3 + ci) * 64 + co], acc);
-                    }
-                }
-            c1[p * 64 + co] = fmaxf(acc, 0.f);
+        const float4* src = reinterpret_cast<const float4*>(vis + f * 3 * kS * kS);
+        for (int i = tid; i < 3 * kS * kS / 4; i += kVThreads) {
+            const float4 v = __ldg(src + i);
+            const uint2 o = *reinterpret_cast<const uint2*>(dsto + 4 * i);
+            patch[o.x & 0xffffu] = v.x;
+            patch[o.x >> 16] = v.y;
+            patch[o.y & 0xffffu] = v.z;
+            patch[o.y >> 16] = v.w;
         }
         __syncthreads();
-        __nv_bfloat16* o = a1p + f * (int64_t)C1 * C1 * 64;
-        for (int p = pg; p < C1 * C1; p += kVThreads / 64) {
-            const int y = p / C1, x = p - y * C1;
-            float r = 0.f;
+        for (int p = warp; p < kC1 * kC1; p += kVThreads / 32) {
+            const float4* pp = reinterpret_cast<const float4*>(patch + p * kPatch);
+            float in[kPatch];
+#pragma unroll
+            for (int v = 0; v < kPatch / 4; ++v) {
+                const float4 t = pp[v];
+                in[4 * v] = t.x; in[4 * v + 1] = t.y; in[4 * v + 2] = t.z; in[4 * v + 3] = t.w;
+            }
+            float a0 = bias.x, a1 = bias.y;
+#pragma unroll
+            for (int k = 0; k < 27; ++k) {
+                a0 = fmaf(in[k], w0[k], a0);
+                a1 = fmaf(in[k], w1[k], a1);
+            }
+            *reinterpret_cast<float2*>(c1 + p * 64 + 2 * lane) = make_float2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+        }
+        __syncthreads();
+        uint32_t* o = reinterpret_cast<uint32_t*>(a1p + f * (int64_t)kC1 * kC1 * 64);
+        for (int p = warp; p < kC1 * kC1; p += kVThreads / 32) {
+            const int y = p / kC1, x = p - y * kC1;
+            uint32_t r = 0u;                                     // zero border = conv2's padding
             if (y >= 1 && y <= P && x >= 1 && x <= P) {
-                float m = -INFINITY;
+                const float* base = c1 + ((y - 1) * kC1 + x - 1) * 64 + 2 * lane;
+                float2 m = *reinterpret_cast<const float2*>(base);
 #pragma unroll
                 for (int dy = 0; dy < 3; ++dy)
 #pragma unroll
-                    for (int dx = 0; dx < 3; ++dx) m = fmaxf(m, c1[((y - 1 + dy) * C1 + x - 1 + dx) * 64 + co]);
-                r = fmaf(m, scale, shift);
+                    for (int dx = 0; dx < 3; ++dx) {
+                        if (dy == 0 && dx == 0) continue;
+                        const float2 t = *reinterpret_cast<const float2*>(base + (dy * kC1 + dx) * 64);
+                        m.x = fmaxf(m.x, t.x);
+                        m.y = fmaxf(m.y, t.y);
+                    }
+                const __nv_bfloat162 h = __floats2bfloat162_rn(fmaf(m.x, scale.x, shift.x), fmaf(m.y, scale.y, shift.y));
+                r = *reinterpret_cast<const uint32_t*>(&h);
             }
-            o[p * 64 + co] = __float2bfloat16(r);
+            o[p * 32 + lane] = r;
         }
     }
 }
@@ -142,33 +177,95 @@ audbl_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, int L2, co
     }
 }
 
+// AudBl conv1 (30 -> 64, k3 s2 p1) + ReLU on CUDA cores (fp32: the raw MFCCs span +-600), written as
+// bf16 (position, channel)-major rows with a zero row on each side for the tensor-core conv2.
+// thread = (output channel, position group); its 90 weights live in registers, the inputs of kCF frames
+// are staged transposed ([t][ci], ci padded to 32) so that a tap is 8 broadcast 16-byte loads.
+constexpr int kCThreads = 256;
+constexpr int kCF = 4;
+
+__global__ void __launch_bounds__(kCThreads, 2)
+audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, const float* __restrict__ w1,
+                   const float* __restrict__ b1, __nv_bfloat16* __restrict__ ac1) {
+    extern __shared__ __align__(16) float sm[];            // [kCF][B+2][32]
+    const int tid = threadIdx.x, co = tid & 63, g = tid >> 6;
+    const int rows = B + 2;
+    float wr[90];
+#pragma unroll
+    for (int i = 0; i < 90; ++i) wr[i] = __ldg(w1 + co * 90 + i);     // [ci][k]
+    const float bias = __ldg(b1 + co);
+    for (int i = tid; i < kCF * rows * 32; i += kCThreads) sm[i] = 0.f;   // pad rows / pad channels stay zero
+    for (int64_t f0 = (int64_t)blockIdx.x * kCF; f0 < n; f0 += (int64_t)gridDim.x * kCF) {
+        const int nf = (int)((n - f0) < kCF ? (n - f0) : kCF);
+        __syncthreads();
+        for (int i = tid; i < nf * 30 * B; i += kCThreads) {
+            const int f = i / (30 * B), r = i - f * 30 * B, ci = r / B, t = r - ci * B;
+            sm[(f * rows + t + 1) * 32 + ci] = __ldg(aud + f0 * 30 * B + i);
+        }
+        __syncthreads();
+        for (int f = 0; f < nf; ++f) {
+            __nv_bfloat16* o = ac1 + (f0 + f) * (int64_t)(L1 + 2) * 64;
+            if (g == 0) { o[co] = __float2bfloat16(0.f); o[(L1 + 1) * 64 + co] = __float2bfloat16(0.f); }
+            for (int l = g; l < L1; l += kCThreads / 64) {
+                float acc = bias;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float4* xr = reinterpret_cast<const float4*>(sm + (f * rows + 2 * l + k) * 32);   // t = 2l-1+k
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) {
+                        const float4 x = xr[v];
+                        acc = fmaf(x.x, wr[(4 * v) * 3 + k], acc);
+                        acc = fmaf(x.y, wr[(4 * v + 1) * 3 + k], acc);
+                        if (v < 7) {
+                            acc = fmaf(x.z, wr[(4 * v + 2) * 3 + k], acc);
+                            acc = fmaf(x.w, wr[(4 * v + 3) * 3 + k], acc);
+                        }
+                    }
+                }
+                o[(l + 1) * 64 + co] = __float2bfloat16(fmaxf(acc, 0.f));
+            }
+        }
+    }
+}
+
 }  // namespace
 
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
-    const size_t smem = sizeof(float) * (3 * m->S * m->S + 27 * 64 + (size_t)m->C1 * m->C1 * 64);
+    if (m->S != kS || m->C1 != kC1) return GN_E_SHAPE;
+    const size_t smem = sizeof(float) * (size_t)(kC1 * kC1 * (kPatch + 64)) + sizeof(unsigned short) * 3 * kS * kS;
     static bool attr = false;
     if (!attr) {
         GN_CUDA(cudaFuncSetAttribute(visbl_block1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         attr = true;
     }
-    if (smem > 100 * 1024) return GN_E_SHAPE;
     const int64_t cap = (int64_t)m->h->num_sms * 2;
     const int grid = (int)(n < cap ? n : cap);
-    visbl_block1_kernel<<<grid, kVThreads, smem, st>>>(d_visual, n, m->S, m->C1, m->conv1_w, m->conv1_b,
-                                                       m->bn_scale[0], m->bn_shift[0], ws.a1p);
+    visbl_block1_kernel<<<grid, kVThreads, smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0],
+                                                       m->bn_shift[0], ws.a1p);
     GN_LAUNCHED(m->h);
     return GN_OK;
 }
 
-int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st) {
+int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt) {
     if (!m->audio_included) return GN_OK;
-    const size_t smem = sizeof(float) * kAFrames * (30 * m->B + 64 * m->L1 + 128 * m->L2);
+    if (simt) {
+        // validation path: the whole AudBl on CUDA cores in fp32
+        const size_t smem = sizeof(float) * kAFrames * (30 * m->B + 64 * m->L1 + 128 * m->L2);
+        if (smem > 48 * 1024) return GN_E_SHAPE;
+        const int64_t groups = (n + kAFrames - 1) / kAFrames;
+        const int64_t cap = (int64_t)m->h->num_sms * 4;
+        const int grid = (int)(groups < cap ? groups : cap);
+        audbl_kernel<<<grid, kAThreads, smem, st>>>(d_audio, n, m->B, m->L1, m->L2, m->aconv1_w, m->aconv1_b,
+                                                    m->aconv2_w, m->aconv2_b, m->alinear3_w, m->alinear3_b, ws.h0, m->fin);
+        GN_LAUNCHED(m->h);
+        return GN_OK;
+    }
+    const size_t smem = sizeof(float) * kCF * (m->B + 2) * 32;
     if (smem > 48 * 1024) return GN_E_SHAPE;
-    const int64_t groups = (n + kAFrames - 1) / kAFrames;
-    const int64_t cap = (int64_t)m->h->num_sms * 4;
+    const int64_t groups = (n + kCF - 1) / kCF;
+    const int64_t cap = (int64_t)m->h->num_sms * 2;
     const int grid = (int)(groups < cap ? groups : cap);
-    audbl_kernel<<<grid, kAThreads, smem, st>>>(d_audio, n, m->B, m->L1, m->L2, m->aconv1_w, m->aconv1_b,
-                                                m->aconv2_w, m->aconv2_b, m->alinear3_w, m->alinear3_b, ws.h0, m->fin);
+    audbl_conv1_kernel<<<grid, kCThreads, smem, st>>>(d_audio, n, m->B, m->L1, m->aconv1_w, m->aconv1_b, ws.ac1);
     GN_LAUNCHED(m->h);
-    return GN_OK;
+    return gn_launch_tc_audbl(m, n, ws, st);
 }

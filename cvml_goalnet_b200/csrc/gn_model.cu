@@ -125,6 +125,23 @@ __global__ void pack_linear5(const float* __restrict__ w, int C, int PP, __nv_bf
         out[i] = __float2bfloat16(w[o * K + (int64_t)c * PP + p]);
     }
 }
+// AudBl conv2 weight [128][64][3] -> bf16 [128][tap*64 + ci]
+__global__ void pack_aconv2(const float* __restrict__ w, __nv_bfloat16* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 128 * 192) {
+        const int co = i / 192, k = i - co * 192, tap = k / 64, ci = k - tap * 64;
+        out[i] = __float2bfloat16(w[(co * 64 + ci) * 3 + tap]);
+    }
+}
+// AudBl linear3 weight [128][128*L2] with column c*L2 + l -> bf16 [128][l*128 + c]
+__global__ void pack_alinear3(const float* __restrict__ w, int L2, __nv_bfloat16* __restrict__ out) {
+    const int K = 128 * L2;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 128 * K) {
+        const int j = i / K, k = i - j * K, l = k / 128, c = k - l * 128;
+        out[i] = __float2bfloat16(w[j * K + c * L2 + l]);
+    }
+}
 __global__ void cast_bf16(const float* __restrict__ w, int64_t total, __nv_bfloat16* __restrict__ out) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
         out[i] = __float2bfloat16(w[i]);
@@ -165,7 +182,7 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
     if (S != 40) return GN_E_SHAPE;   // the tensor-core tiles are laid out for the reference's 40x40 frames
     const int C1 = conv_out(S, 3, 3, 3), P1 = C1 - 2, P2 = P1 - 2, P3 = P2 - 2;
     const int L1 = conv_out(B, 3, 2, 1), L2 = conv_out(L1, 3, 2, 1);
-    if (audio_included && (B < 4 || 128 * L2 > 4096)) return GN_E_SHAPE;
+    if (audio_included && (B < 4 || L2 != 8 || B > 32)) return GN_E_SHAPE;   // tensor-core AudBl tiles: 16 frames x 8 positions
     const float* need[] = {sd->conv1_w, sd->conv1_b, sd->conv2_w, sd->conv2_b, sd->conv3_w, sd->conv3_b, sd->bn1_w,
                            sd->bn1_b, sd->bn1_m, sd->bn1_v, sd->bn2_w, sd->bn2_b, sd->bn2_m, sd->bn2_v, sd->bn3_w,
                            sd->bn3_b, sd->bn3_m, sd->bn3_v, sd->linear5_w, sd->linear5_b, sd->f0_w, sd->f0_b,
@@ -181,7 +198,7 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
     m->fin = 512 + (audio_included ? 128 : 0);
     const int64_t K5 = 512LL * P3 * P3;
     const size_t cap = (size_t)(512 * K5 + 512 * 2304 + 256 * 576 + 512 * 640 + 512 * 512 + 256 * 512 + 128 * 256) * 2 +
-                       (size_t)(64 * 90 + 128 * 192 + 128 * 128 * L2) * 4 + (1 << 20);
+                       (size_t)(64 * 90 + 128 * 192 + 128 * 128 * L2) * 6 + (1 << 20);
     cudaError_t e = cudaMalloc(&m->arena, cap);
     if (e != cudaSuccess) { free(m); return (int)e; }
     Arena A{reinterpret_cast<char*>(m->arena), 0, cap};
@@ -223,6 +240,10 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
         m->aconv2_b = copyf(sd->aconv2_b, 128);
         m->alinear3_w = copyf(sd->alinear3_w, 128LL * 128 * L2);
         m->alinear3_b = copyf(sd->alinear3_b, 128);
+        m->aconv2_wk = A.take<__nv_bfloat16>(128 * 192);
+        pack_aconv2<<<(128 * 192 + T - 1) / T, T, 0, st>>>(sd->aconv2_w, m->aconv2_wk);
+        m->alinear3_wk = A.take<__nv_bfloat16>((size_t)128 * 128 * L2);
+        pack_alinear3<<<(128 * 128 * L2 + T - 1) / T, T, 0, st>>>(sd->alinear3_w, L2, m->alinear3_wk);
     }
     const float* fw[4] = {sd->f0_w, sd->f3_w, sd->f6_w, sd->f9_w};
     const float* fb[4] = {sd->f0_b, sd->f3_b, sd->f6_b, sd->f9_b};
@@ -287,6 +308,8 @@ gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base) {
     w.a1p = take(nn * m->C1 * m->C1 * 64);
     w.a2p = take(nn * m->P1 * m->P1 * 256);
     w.a3 = take(nn * m->P3 * m->P3 * 512);
+    w.ac1 = take(nn * (m->L1 + 2) * 64);
+    w.ac2 = take(nn * m->L2 * 128);
     w.h0 = take(nn * m->fin);
     w.h1 = take(nn * 512);
     w.h2 = take(nn * 512);
@@ -315,7 +338,7 @@ static int avm_forward_impl(gn_model* m, const float* d_visual, const float* d_a
     int rc = gn_launch_visbl_front(m, d_visual, n, ws, st);
     if (rc) return rc;
     GN_STAGE_MARK(m, 1, st);
-    rc = gn_launch_audbl(m, d_audio, n, ws, st);
+    rc = gn_launch_audbl(m, d_audio, n, ws, st, simt);
     if (rc) return rc;
     GN_STAGE_MARK(m, 2, st);
     return simt ? gn_launch_simt_backbone(m, n, ws, d_scores, d_visfeat, st)

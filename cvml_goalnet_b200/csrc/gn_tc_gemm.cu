@@ -49,6 +49,8 @@ struct GemmArgs {
     const float* w_last;     // score: fusion.12 weight [128]
     const float* b_last;     // score: fusion.12 bias [1]
     float* scores;           // score: [M]
+    int a3d_rows;            // linear: 0 = A is a 2-D [M][K] map; else A is a 3-D (k, position, frame) map with this many
+                             //         positions per frame (AudBl conv2: overlapping 192-element windows, 128/rows frames per tile)
     ConvGeom g;
 };
 
@@ -159,7 +161,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         tma_load_4d(sa, &tmap_a, fb, cb * kBK, kx, ky, (int)m_blk);
                     } else {
                         mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
-                        tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
+                        if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
+                        else               tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
                     }
                     tma_load_2d(sb, &tmap_b, fb, kt * kBK, n_blk * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -433,6 +436,31 @@ int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, c
 }
 
 }  // namespace
+
+// AudBl conv2 (64 -> 128, k3 s2 p1) and linear3 on the tensor cores (reference utils.py:219-225).
+// conv1's output ws.ac1 is (position, channel)-major with a zero row on each side, so the im2col row of
+// output position l is the 192 contiguous elements starting at row 2*l: a 3-D TMA map with overlapping
+// rows (row pitch 128 elements) feeds the GEMM directly.  16 frames x 8 positions make one 128-row tile.
+int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st) {
+    const int L2 = m->L2, rows = m->L1 + 2;
+    if (128 % L2) return GN_E_SHAPE;
+    CUtensorMap ta, tb;
+    const uint64_t dims[3] = {192, (uint64_t)L2, (uint64_t)n};
+    const uint64_t str[2] = {128 * 2, (uint64_t)rows * 64 * 2};
+    const uint32_t box[3] = {(uint32_t)kBK, (uint32_t)L2, (uint32_t)(128 / L2)};
+    int rc = make_tmap(m->h, &ta, ws.ac1, 3, dims, str, box);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, m->aconv2_wk, 128, 192, 192, 128);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = n * L2; a.N = 128; a.K = 192; a.bias = m->aconv2_b; a.out = ws.ac2; a.ld_out = 128; a.col_off = 0;
+    a.a3d_rows = L2;
+    rc = launch<1, 128, 3, kLinear, 0>(m->h, ta, tb, a, (a.M + 127) / 128, st);
+    if (rc) return rc;
+    // linear3 + ReLU -> columns [0,128) of the fusion input (audio first, utils.py:266)
+    return run_linear<128, 4, kLinear>(m, n, ws.ac2, 128 * L2, 128 * L2, m->alinear3_wk, 128, m->alinear3_b, ws.h0,
+                                       m->fin, 0, nullptr, nullptr, nullptr, nullptr, st);
+}
 
 // conv2 -> conv3 -> linear5 -> fusion MLP -> scores, all on the tensor cores.
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
