@@ -42,6 +42,15 @@ class MatchScorer:
         self.ind_host = torch.empty(self.n_raw, dtype=torch.uint8).pin_memory()
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        # audio samples each H2D chunk must bring along (slot boundaries of utils.py:322-330); consecutive
+        # chunks may share a boundary sample, so each range starts where the previous one ended at the latest
+        bounds = np.linspace(0, self.n, self.h2d_chunks + 1).astype(np.int64)
+        self._audio_ranges, prev_hi = [], 0
+        for i in range(self.h2d_chunks):
+            lo, hi = U.audio_slot_sample_range(self.samples, self.n, int(bounds[i]), int(bounds[i + 1]))
+            lo = min(lo, prev_hi)
+            self._audio_ranges.append((lo, max(hi, lo)))
+            prev_hi = max(hi, prev_hi)
 
     # ---- device-resident path (inputs already in HBM) ------------------------------------------------
     def score_device(self, frames_dev, audio_dev, change_points_dev_or_host, gd_dev=None):
@@ -69,25 +78,26 @@ class MatchScorer:
         main = torch.cuda.current_stream(d)
         cs = self.copy_stream
         cs.wait_stream(main)                       # previous step's readers of the staging buffers are done
+        ah = ah.reshape(-1)
         bounds = np.linspace(0, self.n, self.h2d_chunks + 1).astype(np.int64)
         events = []
         with torch.cuda.stream(cs):
-            self.audio_dev.copy_(ah.reshape(-1), non_blocking=True)
-            ev_a = torch.cuda.Event()
-            ev_a.record(cs)
             for i in range(self.h2d_chunks):
                 a, b = int(bounds[i]), int(bounds[i + 1])
+                if self.model.audio_included:
+                    lo, hi = self._audio_ranges[i]
+                    self.audio_dev[lo:hi].copy_(ah[lo:hi], non_blocking=True)
                 self.frames_dev[a:b].copy_(fh[a:b], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(cs)
                 events.append((a, b, ev))
-        main.wait_event(ev_a)
-        if self.model.audio_included:
-            U.extract_audio_features_array(self.audio_dev, self.sr, self.n, self.B, out=self.aud)
+        # chunk i is preprocessed and scored while chunk i+1 is still crossing PCIe
         for a, b, ev in events:
             main.wait_event(ev)
+            if self.model.audio_included:
+                U.extract_audio_features_array(self.audio_dev, self.sr, self.n, self.B, out=self.aud, slots=(a, b))
             U.extract_condensed_frame_tensor_array(self.frames_dev[a:b], self.model.S, out=self.vis[a:b])
-        self.model(self.aud, self.vis, out=self.scores)
+            self.model(self.aud[a:b], self.vis[a:b], out=self.scores[a:b])
         _, ind = U.postprocess_array(self.scores, self.skip, self.n_raw, change_points, device=d, return_device=True)
         self.scores_host.copy_(self.scores, non_blocking=True)
         self.ind_host.copy_(ind, non_blocking=True)

@@ -145,13 +145,22 @@ def _segment_plan(n_samples: int, n_frames: int, B: int, dev_index: int):
     wcat = np.concatenate(mats) if mats else np.zeros(1, np.float32)
     return dict(start=torch.from_numpy(start).to(dev), length=torch.from_numpy(length).to(dev),
                 w_offset=torch.from_numpy(offs).to(dev), w=torch.from_numpy(wcat).to(dev),
-                max_q=int(q.max()) if n_frames else 4)
+                max_q=int(q.max()) if n_frames else 4, start_host=start, length_host=length)
+
+
+def audio_slot_sample_range(n_samples: int, n_frames: int, a: int, b: int):
+    """Sample range [lo, hi) that the frame slots a..b-1 of utils.py:322-330 read."""
+    start, length = dsp.segment_bounds(int(n_samples), int(n_frames)) if n_frames else (np.zeros(0), np.zeros(0))
+    if b <= a:
+        return 0, 0
+    return int(start[a]), int((start[a:b] + length[a:b]).max())
 
 
 def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, device=None, out=None,
-                                 as_numpy: bool = False):
+                                 as_numpy: bool = False, slots=None):
     """Array twin of `extract_audio_features` (utils.py:313-349) with `(y, sr)` replacing librosa.load:
-    float32 (N,30,B) MFCC features, cubic-resampled to B columns per frame slot."""
+    float32 (N,30,B) MFCC features, cubic-resampled to B columns per frame slot.
+    `slots=(a, b)` computes only the frame slots a..b-1 (rows a..b-1 of `out`), for chunked pipelines."""
     dev = _device(device if device is not None else (y.device if torch.is_tensor(y) and y.is_cuda else None))
     yd = _to_dev(y, torch.float32, dev).reshape(-1)
     B = int(bin_length)
@@ -162,11 +171,15 @@ def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, dev
     tab = _audio_tables(int(sr), dev.index)
     if out is None:
         out = torch.empty((n_frames, dsp.N_MFCC, B), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
-        _lib.check(_lib.load().gn_mfcc_resampled(
-            _h(dev), _ptr(yd), yd.numel(), _ptr(plan["start"]), _ptr(plan["length"]), _ptr(plan["w_offset"]),
-            _ptr(plan["w"]), n_frames, B, plan["max_q"], _ptr(tab["start"]), _ptr(tab["count"]), _ptr(tab["offset"]),
-            _ptr(tab["w"]), _ptr(tab["dct"]), _ptr(out), _stream(dev)), "gn_mfcc_resampled")
+    a, b = (0, int(n_frames)) if slots is None else (int(slots[0]), int(slots[1]))
+    assert 0 <= a <= b <= n_frames, "E: Shape mismatch"
+    if b > a:
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().gn_mfcc_resampled(
+                _h(dev), _ptr(yd), yd.numel(), _ptr(plan["start"][a:]), _ptr(plan["length"][a:]),
+                _ptr(plan["w_offset"][a:]), _ptr(plan["w"]), b - a, B, plan["max_q"], _ptr(tab["start"]),
+                _ptr(tab["count"]), _ptr(tab["offset"]), _ptr(tab["w"]), _ptr(tab["dct"]), _ptr(out[a:]), _stream(dev)),
+                "gn_mfcc_resampled")
     return out.cpu().numpy() if as_numpy else out
 
 
@@ -291,11 +304,13 @@ class AVM(nn.Module):
         return mptr
 
     def _ws(self, dev, mptr, n):
+        """Workspace view for n frames, 1024-byte aligned (TMA / swizzle atoms), grown on demand."""
         need = int(_lib.load().gn_avm_workspace_bytes(mptr, n))
         ws = self._workspace.get(dev.index)
-        if ws is None or ws.numel() < need:
-            ws = self._workspace[dev.index] = torch.empty(need, dtype=torch.uint8, device=dev)
-        return ws, need
+        if ws is None or ws.numel() < need + 1024:
+            ws = self._workspace[dev.index] = torch.empty(need + 1024, dtype=torch.uint8, device=dev)
+        off = (-ws.data_ptr()) % 1024
+        return ws[off:off + need], need
 
     # -- forward ------------------------------------------------------------------------------------
     def forward(self, audio_input, visual_input, out=None, return_features: bool = False, _simt: bool = False):

@@ -303,3 +303,31 @@ def test_end_to_end_config1(U, weights):
     gd = np.stack([O.postprocess_array(a[:, None], skip, n_raw, cps)[1]
                    for a in syn.make_annotator_importances(n_raw, 20, seed=1)])
     assert U.get_fscore(gd, o_ind) == O.get_fscore(gd, o_ind)
+
+
+def test_match_scorer_chunked_host_path_equals_device_path(U, weights):
+    """MatchScorer.score_match (pinned host inputs, chunked H2D, per-chunk MFCC / preprocess / forward) gives the
+    same bits as the one-shot device-resident path, and both match the oracle."""
+    import torch
+    from cvml_goalnet_b200.main import MatchScorer
+    n, skip, sr, spf = 50, 15, 16000, 8013          # non-integer-friendly slot length: ragged slot boundaries
+    n_raw = n * skip
+    frames = syn.make_frames(n, 64, 80, seed=4)
+    y = syn.make_audio(n, spf, sr, seed=4)[: n * spf - 7]
+    cps = syn.make_change_points(n_raw, seed=4, lo=10, hi=60)
+    gd = np.stack([O.postprocess_array(a[:, None], skip, n_raw, cps)[1]
+                   for a in syn.make_annotator_importances(n_raw, 20, seed=4)])
+    m = _model(U, weights)
+    sc = MatchScorer(m, n, 64, 80, y.size, sr, skip, n_raw, h2d_chunks=3)
+    s_host, ind_host, fs_host = sc.score_match(frames, y, cps, gd)
+    s_host, ind_host = s_host.copy(), ind_host.copy()
+    dev = torch.device("cuda", 0)
+    s_dev, ind_dev, fs_dev = sc.score_device(torch.from_numpy(frames).to(dev), torch.from_numpy(y).to(dev), cps,
+                                             torch.from_numpy(gd).to(dev))
+    np.testing.assert_array_equal(s_host, s_dev.cpu().numpy())
+    np.testing.assert_array_equal(ind_host, ind_dev.cpu().numpy())
+    assert fs_host == fs_dev
+    o_scores, _, o_ind, _ = O.score_and_summarize(weights, frames, y, sr, skip, n_raw, cps)
+    assert np.abs(s_host - o_scores).max() / np.abs(o_scores).max() <= SCORE_RTOL
+    if np.array_equal(np.round(s_host), np.round(o_scores)):
+        np.testing.assert_array_equal(ind_host, o_ind)

@@ -1,0 +1,67 @@
+"""2-GPU NCCL tests (skipped with fewer than two devices): a frame-sharded match and a batch of matches give the
+same bits as the single-GPU path."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import distributed as D, synthetic as syn, utils as U
+    from cvml_goalnet_b200.main import MatchScorer
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        n, skip, sr, spf = 101, 15, 16000, 8000
+        n_raw = n * skip
+        frames = syn.make_frames(n, 48, 64, seed=3)
+        y = syn.make_audio(n, spf, sr, seed=3)
+        cps = syn.make_change_points(n_raw, seed=3, lo=10, hi=80)
+        model = U.AVM(True)
+        model.load_state_dict(syn.make_weights(seed=0))
+        # single-GPU result on this rank
+        sc = MatchScorer(model, n, 48, 64, y.size, sr, skip, n_raw, device=dev, h2d_chunks=2)
+        s_ref, ind_ref, _ = sc.score_match(frames, y, cps, None)
+        s_ref, ind_ref = s_ref.copy(), ind_ref.copy()
+        # one match, frames sharded
+        a, b = D.shard_bounds(n, world)[rank]
+        scores, ind = D.score_match_frame_sharded(model, frames[a:b], y, sr, n, skip, n_raw, cps)
+        ok1 = np.array_equal(scores.cpu().numpy(), s_ref) and np.array_equal(ind.cpu().numpy(), ind_ref)
+        # three matches, whole matches per rank
+        matches = []
+        for mi in range(3):
+            matches.append((syn.make_frames(n, 48, 64, seed=10 + mi), syn.make_audio(n, spf, sr, seed=10 + mi),
+                            syn.make_change_points(n_raw, seed=10 + mi, lo=10, hi=80)))
+        S, I = D.score_matches_sharded(sc, matches)
+        ok2 = True
+        for mi, (fr, yy, cp) in enumerate(matches):
+            s1, i1, _ = sc.score_match(fr, yy, cp, None)
+            ok2 = ok2 and np.array_equal(S[mi].cpu().numpy(), s1.reshape(-1)) and np.array_equal(I[mi].cpu().numpy(), i1)
+        np.save(os.path.join(out_dir, f"ok_{rank}.npy"), np.array([ok1, ok2]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_sharded_paths_match_single_gpu(tmp_path):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    import torch.multiprocessing as mp
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        assert np.load(tmp_path / f"ok_{r}.npy").all(), r
