@@ -1,23 +1,29 @@
-// 2048-point complex FFT as four Stockham (autosort) passes of radix 4, 8, 8, 8 over split
-// real/imaginary shared-memory arrays.  256 threads cooperate on one transform; every thread keeps
-// its 8 (or 2 x 4) points in registers for the butterfly, so a transform costs four shared-memory
-// round trips instead of eleven radix-2 ones.  The intermediate buffers use per-pass index padding
-// that makes every strided write bank-conflict free (32-bit accesses, one element per bank):
-//   pass 1 (R=4, Ns=1)   writes idx -> idx + idx/32          (stride-4 writes)
-//   pass 2 (R=8, Ns=4)   writes idx -> idx + 4*(idx/32)      (4 consecutive, then stride 32)
-//   pass 3 (R=8, Ns=32)  and pass 4 (R=8, Ns=256) write unpadded (warp-contiguous).
-// The functions are __host__ __device__ so that tests can run the same index/twiddle logic on the CPU.
+// 2048-point complex FFT computed by ONE WARP with the points in registers: 2048 = 64 x 32.
+//   stage 1: lane n2 holds x[32 n1 + n2], n1 = 0..63, runs a 64-point DFT over n1 in registers (8 x 8,
+//            all indices compile-time) and multiplies Y[k1] by W_2048^(n2 k1);
+//   transpose through a per-warp shared-memory tile T[k1][n2] (rows padded to 33 float2, so both the
+//            row-wise writes and the column-wise reads are bank-conflict free);
+//   stage 2: lane l reads the two rows k1 = l and k1 = 64 - l (lane 0: rows 0 and 32) and runs two
+//            32-point DFTs over n2 in registers (8 x 4), giving X[k1 + 64 k2], k2 = 0..31.
+// The row pairing puts X[k] and X[2048 - k] in the SAME lane, so the two real spectra packed into one
+// complex transform (column j in the real part, column j+1 in the imaginary part) are separated and
+// squared without any further exchange.  One shared-memory round trip per transform, no block barrier.
+// Everything is __host__ __device__ so that tests/native/fft_host_check.cu runs the same code on the CPU.
 #pragma once
 #include <cuda_runtime.h>
+
+#if defined(__CUDACC__)
+#define GNFFT_UNROLL _Pragma("unroll")
+#else
+#define GNFFT_UNROLL
+#endif
 
 namespace gnfft {
 
 constexpr int kN = 2048;
-constexpr int kThreads = 256;
-constexpr int kBufA = kN + kN / 32;        // pass-1 padding
-constexpr int kBufB = kN + 4 * (kN / 32);  // pass-2 padding
-// twiddle table layout (float2): [0,256) exp(-2 pi i k/2048), [256,288) exp(-2 pi i k/256), [288,292) exp(-2 pi i k/32)
-constexpr int kTw2048 = 0, kTw256 = 256, kTw32 = 288, kTwCount = 292;
+constexpr int kRow = 33;                    // padded row length of the transpose tile (float2)
+constexpr int kTile = 64 * kRow;            // float2 per warp
+constexpr int kTwLane = 64 * 32;            // twiddle table tw[k1 * 32 + n2] = W_2048^(n2 k1)
 
 __host__ __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
     return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
@@ -25,6 +31,48 @@ __host__ __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
 __host__ __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __host__ __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __host__ __device__ __forceinline__ float2 mul_mi(float2 a) { return make_float2(a.y, -a.x); }   // a * (-i)
+
+// W_64^m = exp(-2 pi i m / 64); m is a compile-time constant after unrolling, so this folds to immediates
+__host__ __device__ __forceinline__ float2 w64(int m) {
+    m &= 63;
+    const int q = m >> 4, r = m & 15;
+    float c = 1.f, s = 0.f;                 // cos, sin of 2 pi r / 64
+    switch (r) {
+        case 1: c = 0.9951847266721969f; s = 0.0980171403295606f; break;
+        case 2: c = 0.9807852804032304f; s = 0.19509032201612825f; break;
+        case 3: c = 0.9569403357322088f; s = 0.29028467725446233f; break;
+        case 4: c = 0.9238795325112867f; s = 0.3826834323650898f; break;
+        case 5: c = 0.881921264348355f; s = 0.47139673682599764f; break;
+        case 6: c = 0.8314696123025452f; s = 0.5555702330196022f; break;
+        case 7: c = 0.773010453362737f; s = 0.6343932841636455f; break;
+        case 8: c = 0.7071067811865476f; s = 0.7071067811865476f; break;
+        case 9: c = 0.6343932841636455f; s = 0.773010453362737f; break;
+        case 10: c = 0.5555702330196023f; s = 0.8314696123025452f; break;
+        case 11: c = 0.4713967368259978f; s = 0.8819212643483549f; break;
+        case 12: c = 0.38268343236508984f; s = 0.9238795325112867f; break;
+        case 13: c = 0.29028467725446233f; s = 0.9569403357322089f; break;
+        case 14: c = 0.19509032201612833f; s = 0.9807852804032304f; break;
+        case 15: c = 0.09801714032956077f; s = 0.9951847266721968f; break;
+        default: break;
+    }
+    // (c, -s) times (-i)^q
+    if (q == 0) return make_float2(c, -s);
+    if (q == 1) return make_float2(-s, -c);
+    if (q == 2) return make_float2(-c, s);
+    return make_float2(s, c);
+}
+
+// v * W_64^m with the trivial factors special-cased (m compile-time)
+__host__ __device__ __forceinline__ float2 mul_w64(float2 v, int m) {
+    m &= 63;
+    if (m == 0) return v;
+    if (m == 16) return mul_mi(v);
+    if (m == 32) return make_float2(-v.x, -v.y);
+    if (m == 48) return make_float2(-v.y, v.x);
+    if (m == 8) { const float s = 0.70710678118654752440f; return make_float2(s * (v.x + v.y), s * (v.y - v.x)); }
+    if (m == 24) { const float s = 0.70710678118654752440f; return make_float2(s * (v.y - v.x), -s * (v.x + v.y)); }
+    return cmul(v, w64(m));
+}
 
 // forward DFT-4, natural order in and out
 __host__ __device__ __forceinline__ void dft4(float2& x0, float2& x1, float2& x2, float2& x3) {
@@ -51,52 +99,97 @@ __host__ __device__ __forceinline__ void dft8(float2 (&v)[8]) {
     v[3] = cadd(e3, o3); v[7] = csub(e3, o3);
 }
 
-__host__ __device__ __forceinline__ int pad1(int a) { return a + (a >> 5); }
-__host__ __device__ __forceinline__ int pad2(int a) { return a + ((a >> 5) << 2); }
-
-// pass 1: radix 4, Ns = 1 (no twiddles).  Butterfly j in [0,512) takes x[j + 512 r]; this thread does
-// j = tid and j = tid + 256, i.e. input points z[tid + 256 s], s = 0..7 (z[s] below).
-__host__ __device__ __forceinline__ void pass1(int tid, const float2 (&z)[8], float* are, float* aim) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        float2 x0 = z[h], x1 = z[h + 2], x2 = z[h + 4], x3 = z[h + 6];
-        dft4(x0, x1, x2, x3);
-        const int j0 = (tid + 256 * h) * 4;
-        are[pad1(j0)] = x0.x;     aim[pad1(j0)] = x0.y;
-        are[pad1(j0 + 1)] = x1.x; aim[pad1(j0 + 1)] = x1.y;
-        are[pad1(j0 + 2)] = x2.x; aim[pad1(j0 + 2)] = x2.y;
-        are[pad1(j0 + 3)] = x3.x; aim[pad1(j0 + 3)] = x3.y;
+// In-register 64-point DFT (n = 8a + b, k = c + 8d).  Output is permuted: z[8c + d] = Y[c + 8d].
+__host__ __device__ __forceinline__ constexpr int perm64(int p) { return (p >> 3) + 8 * (p & 7); }
+__host__ __device__ __forceinline__ void dft64(float2 (&z)[64]) {
+    GNFFT_UNROLL
+    for (int b = 0; b < 8; ++b) {
+        float2 v[8];
+        GNFFT_UNROLL
+        for (int a = 0; a < 8; ++a) v[a] = z[8 * a + b];
+        dft8(v);
+        GNFFT_UNROLL
+        for (int c = 0; c < 8; ++c) z[8 * c + b] = mul_w64(v[c], b * c);      // t[b][c] * W_64^(bc), kept at z[8c + b]
+    }
+    GNFFT_UNROLL
+    for (int c = 0; c < 8; ++c) {
+        float2 v[8];
+        GNFFT_UNROLL
+        for (int b = 0; b < 8; ++b) v[b] = z[8 * c + b];
+        dft8(v);
+        GNFFT_UNROLL
+        for (int d = 0; d < 8; ++d) z[8 * c + d] = v[d];
     }
 }
 
-// generic radix-8 Stockham pass: v[r] = in[j + 256 r] * w^r, DFT-8, out[j0 + r Ns]
-template <int NS, int PAD_IN, int PAD_OUT>
-__host__ __device__ __forceinline__ void pass8(int j, const float* ire, const float* iim, float* ore, float* oim,
-                                               const float2* tw /* table for this pass, index k = j % NS */) {
-    float2 v[8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        const int a = j + 256 * r;
-        const int ia = PAD_IN == 1 ? pad1(a) : (PAD_IN == 2 ? pad2(a) : a);
-        v[r] = make_float2(ire[ia], iim[ia]);
+// In-register 32-point DFT (n = 4a + b, k = c + 8d).  Output is permuted: v[4c + d] = X[c + 8d].
+__host__ __device__ __forceinline__ constexpr int perm32(int p) { return (p >> 2) + 8 * (p & 3); }
+__host__ __device__ __forceinline__ constexpr int inv32(int k) { return 4 * (k & 7) + (k >> 3); }
+__host__ __device__ __forceinline__ void dft32(float2 (&x)[32]) {
+    GNFFT_UNROLL
+    for (int b = 0; b < 4; ++b) {
+        float2 v[8];
+        GNFFT_UNROLL
+        for (int a = 0; a < 8; ++a) v[a] = x[4 * a + b];
+        dft8(v);
+        GNFFT_UNROLL
+        for (int c = 0; c < 8; ++c) x[4 * c + b] = mul_w64(v[c], 2 * b * c);  // W_32^(bc) = W_64^(2bc)
     }
-    const int k = j & (NS - 1);
-    const float2 w1 = tw[k];
-    float2 w = w1;
-    v[1] = cmul(v[1], w);
-#pragma unroll
-    for (int r = 2; r < 8; ++r) {
-        w = cmul(w, w1);
-        v[r] = cmul(v[r], w);
+    GNFFT_UNROLL
+    for (int c = 0; c < 8; ++c) dft4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+}
+
+// Stage 1 for lane n2: z[n1] = x[32 n1 + n2] on entry.  tw = the lane-major twiddle table (kTwLane entries).
+__host__ __device__ __forceinline__ void warp_fft_stage1(int lane, float2 (&z)[64], const float2* tw, float2* tile) {
+    dft64(z);
+    GNFFT_UNROLL
+    for (int p = 0; p < 64; ++p) {
+        const int k1 = perm64(p);
+        tile[k1 * kRow + lane] = k1 == 0 ? z[p] : cmul(z[p], tw[k1 * 32 + lane]);
     }
-    dft8(v);
-    const int j0 = (j / NS) * (NS * 8) + k;
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        const int a = j0 + r * NS;
-        const int oa = PAD_OUT == 1 ? pad1(a) : (PAD_OUT == 2 ? pad2(a) : a);
-        ore[oa] = v[r].x;
-        oim[oa] = v[r].y;
+}
+
+// rows of the transpose tile that lane l transforms in stage 2
+__host__ __device__ __forceinline__ int stage2_row_a(int lane) { return lane; }
+__host__ __device__ __forceinline__ int stage2_row_b(int lane) { return lane == 0 ? 32 : 64 - lane; }
+
+// Stage 2 for lane l: a[inv32(k2)] = X[rowA + 64 k2], b[inv32(k2)] = X[rowB + 64 k2].
+__host__ __device__ __forceinline__ void warp_fft_stage2(int lane, const float2* tile, float2 (&a)[32], float2 (&b)[32]) {
+    const float2* ra = tile + stage2_row_a(lane) * kRow;
+    const float2* rb = tile + stage2_row_b(lane) * kRow;
+    GNFFT_UNROLL
+    for (int n = 0; n < 32; ++n) { a[n] = ra[n]; b[n] = rb[n]; }
+    dft32(a);
+    dft32(b);
+}
+
+// Power spectra of the two real sequences packed as z = x1 + i x2, from Z[k] and Z[N - k]:
+//   X1 = (Z[k] + conj Z[N-k]) / 2,  X2 = (Z[k] - conj Z[N-k]) / (2i)
+__host__ __device__ __forceinline__ void split_power(float2 zk, float2 zn, float& p1, float& p2) {
+    const float ar = zk.x + zn.x, ai = zk.y - zn.y;
+    const float br = zk.y + zn.y, bi = zk.x - zn.x;
+    p1 = 0.25f * (ar * ar + ai * ai);
+    p2 = 0.25f * (br * br + bi * bi);
+}
+
+// After stage 2: write |X1[k]|^2 -> pw1[k], |X2[k]|^2 -> pw2[k] for this lane's bins k <= 1024.
+__host__ __device__ __forceinline__ void warp_fft_power(int lane, const float2 (&a)[32], const float2 (&b)[32],
+                                                        float* pw1, float* pw2) {
+    if (lane != 0) {
+        // a = row l, b = row 64 - l; X[N - (l + 64 k2)] = b[31 - k2] and vice versa
+        GNFFT_UNROLL
+        for (int k2 = 0; k2 < 16; ++k2) {
+            const int ka = lane + 64 * k2, kb = 64 - lane + 64 * k2;
+            split_power(a[inv32(k2)], b[inv32(31 - k2)], pw1[ka], pw2[ka]);
+            split_power(b[inv32(k2)], a[inv32(31 - k2)], pw1[kb], pw2[kb]);
+        }
+    } else {
+        // a = row 0 (self-paired with k2 -> 32 - k2), b = row 32 (self-paired with k2 -> 31 - k2)
+        GNFFT_UNROLL
+        for (int k2 = 0; k2 <= 16; ++k2) split_power(a[inv32(k2)], a[inv32((32 - k2) & 31)], pw1[64 * k2], pw2[64 * k2]);
+        GNFFT_UNROLL
+        for (int k2 = 0; k2 < 16; ++k2)
+            split_power(b[inv32(k2)], b[inv32(31 - k2)], pw1[32 + 64 * k2], pw2[32 + 64 * k2]);
     }
 }
 

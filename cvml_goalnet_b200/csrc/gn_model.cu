@@ -10,7 +10,7 @@
 // handle
 // ================================================================================================
 struct gn_handle_tables {
-    float2* twiddle;   // [1024] exp(-2 pi i k / 2048)
+    float2* twiddle;   // [64][32] lane-major: tw[k1 * 32 + n2] = exp(-2 pi i k1 n2 / 2048)  (gn_fft.cuh)
     float* hann;       // [2048] periodic hann
 };
 static gn_handle_tables* tables_of(gn_handle* h) { return reinterpret_cast<gn_handle_tables*>(h + 1); }
@@ -63,16 +63,17 @@ extern "C" int gn_create(gn_handle** out, int device) {
     h->encode_tiled = fn;
     // FFT tables, computed in double on the host
     gn_handle_tables* t = tables_of(h);
-    float2* tw = reinterpret_cast<float2*>(malloc(sizeof(float2) * 1024));
+    float2* tw = reinterpret_cast<float2*>(malloc(sizeof(float2) * 2048));
     float* hn = reinterpret_cast<float*>(malloc(sizeof(float) * 2048));
-    for (int k = 0; k < 1024; ++k) {
-        const double a = -2.0 * M_PI * (double)k / 2048.0;
-        tw[k] = make_float2((float)cos(a), (float)sin(a));
-    }
+    for (int k1 = 0; k1 < 64; ++k1)
+        for (int n2 = 0; n2 < 32; ++n2) {
+            const double a = -2.0 * M_PI * (double)(k1 * n2) / 2048.0;
+            tw[k1 * 32 + n2] = make_float2((float)cos(a), (float)sin(a));
+        }
     for (int i = 0; i < 2048; ++i) hn[i] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * (double)i / 2048.0));
-    cudaError_t e = cudaMalloc(&t->twiddle, sizeof(float2) * 1024);
+    cudaError_t e = cudaMalloc(&t->twiddle, sizeof(float2) * 2048);
     if (e == cudaSuccess) e = cudaMalloc(&t->hann, sizeof(float) * 2048);
-    if (e == cudaSuccess) e = cudaMemcpy(t->twiddle, tw, sizeof(float2) * 1024, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(t->twiddle, tw, sizeof(float2) * 2048, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(t->hann, hn, sizeof(float) * 2048, cudaMemcpyHostToDevice);
     free(tw);
     free(hn);

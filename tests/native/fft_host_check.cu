@@ -1,5 +1,6 @@
-// Host-side check of gn_fft.cuh: runs the four Stockham passes for all 256 "threads" sequentially on the
-// CPU and compares with a direct O(N^2) DFT in double.  Exit code 0 = max relative error below 2e-6.
+// Host-side check of gn_fft.cuh: runs the warp-level 2048-point FFT (stage 1, transpose tile, stage 2) for the
+// 32 "lanes" sequentially on the CPU and compares (a) the complex spectrum and (b) the two packed real power
+// spectra with a direct O(N^2) DFT in double.  Exit code 0 = max relative error below 2e-6.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -9,33 +10,50 @@
 
 int main() {
     using namespace gnfft;
-    std::vector<float2> x(kN), tw(kTwCount);
+    const double PI = 3.14159265358979323846;
+    std::vector<float2> x(kN), tw(kTwLane), tile(kTile);
     srand(7);
     for (int i = 0; i < kN; ++i) x[i] = make_float2((float)rand() / RAND_MAX - 0.5f, (float)rand() / RAND_MAX - 0.5f);
-    const double PI = 3.14159265358979323846;
-    for (int k = 0; k < 256; ++k) tw[kTw2048 + k] = make_float2((float)cos(-2 * PI * k / 2048), (float)sin(-2 * PI * k / 2048));
-    for (int k = 0; k < 32; ++k) tw[kTw256 + k] = make_float2((float)cos(-2 * PI * k / 256), (float)sin(-2 * PI * k / 256));
-    for (int k = 0; k < 4; ++k) tw[kTw32 + k] = make_float2((float)cos(-2 * PI * k / 32), (float)sin(-2 * PI * k / 32));
-    std::vector<float> are(kBufA), aim(kBufA), bre(kBufB), bim(kBufB);
-    for (int tid = 0; tid < kThreads; ++tid) {
-        float2 z[8];
-        for (int s = 0; s < 8; ++s) z[s] = x[tid + 256 * s];
-        pass1(tid, z, are.data(), aim.data());
+    for (int k1 = 0; k1 < 64; ++k1)
+        for (int n2 = 0; n2 < 32; ++n2) {
+            const double a = -2 * PI * (double)(k1 * n2) / kN;
+            tw[k1 * 32 + n2] = make_float2((float)cos(a), (float)sin(a));
+        }
+    for (int lane = 0; lane < 32; ++lane) {
+        float2 z[64];
+        for (int n1 = 0; n1 < 64; ++n1) z[n1] = x[32 * n1 + lane];
+        warp_fft_stage1(lane, z, tw.data(), tile.data());
     }
-    for (int tid = 0; tid < kThreads; ++tid) pass8<4, 1, 2>(tid, are.data(), aim.data(), bre.data(), bim.data(), tw.data() + kTw32);
-    for (int tid = 0; tid < kThreads; ++tid) pass8<32, 2, 0>(tid, bre.data(), bim.data(), are.data(), aim.data(), tw.data() + kTw256);
-    for (int tid = 0; tid < kThreads; ++tid) pass8<256, 0, 0>(tid, are.data(), aim.data(), bre.data(), bim.data(), tw.data() + kTw2048);
-    double max_err = 0, max_ref = 0;
-    for (int k = 0; k < kN; k += 1) {
-        double re = 0, im = 0;
+    std::vector<float2> X(kN);
+    std::vector<float> pw1(kN / 2 + 1, -1.f), pw2(kN / 2 + 1, -1.f);
+    for (int lane = 0; lane < 32; ++lane) {
+        float2 a[32], b[32];
+        warp_fft_stage2(lane, tile.data(), a, b);
+        for (int k2 = 0; k2 < 32; ++k2) {
+            X[stage2_row_a(lane) + 64 * k2] = a[inv32(k2)];
+            X[stage2_row_b(lane) + 64 * k2] = b[inv32(k2)];
+        }
+        warp_fft_power(lane, a, b, pw1.data(), pw2.data());
+    }
+    double max_err = 0, max_ref = 0, perr = 0, pref = 0;
+    for (int k = 0; k < kN; ++k) {
+        double re = 0, im = 0, r1 = 0, i1 = 0, r2 = 0, i2 = 0;
         for (int n = 0; n < kN; ++n) {
             const double a = -2 * PI * (double)((long long)n * k % kN) / kN;
-            re += x[n].x * cos(a) - x[n].y * sin(a);
-            im += x[n].x * sin(a) + x[n].y * cos(a);
+            const double c = cos(a), s = sin(a);
+            re += x[n].x * c - x[n].y * s;
+            im += x[n].x * s + x[n].y * c;
+            r1 += x[n].x * c; i1 += x[n].x * s;
+            r2 += x[n].y * c; i2 += x[n].y * s;
         }
-        max_err = fmax(max_err, fmax(fabs(re - bre[k]), fabs(im - bim[k])));
+        max_err = fmax(max_err, fmax(fabs(re - X[k].x), fabs(im - X[k].y)));
         max_ref = fmax(max_ref, fmax(fabs(re), fabs(im)));
+        if (k <= kN / 2) {
+            perr = fmax(perr, fmax(fabs(r1 * r1 + i1 * i1 - pw1[k]), fabs(r2 * r2 + i2 * i2 - pw2[k])));
+            pref = fmax(pref, fmax(r1 * r1 + i1 * i1, r2 * r2 + i2 * i2));
+        }
     }
-    printf("max_abs_err %.3e max_ref %.3e rel %.3e\n", max_err, max_ref, max_err / max_ref);
-    return max_err / max_ref < 2e-6 ? 0 : 1;
+    printf("spectrum: max_abs_err %.3e max_ref %.3e rel %.3e\n", max_err, max_ref, max_err / max_ref);
+    printf("power   : max_abs_err %.3e max_ref %.3e rel %.3e\n", perr, pref, perr / pref);
+    return (max_err / max_ref < 2e-6 && perr / pref < 4e-6) ? 0 : 1;
 }
