@@ -15,7 +15,9 @@ struct gn_handle {
     // cuTensorMapEncodeTiled, resolved through cudaGetDriverEntryPoint so that the library does not
     // link against libcuda (it must load, and export its symbols, on a box without a driver).
     void* encode_tiled;
+    void* pre_plans;             // gn_preprocess.cu: cached tap plans per (H, W, S)
 };
+void gn_preprocess_free_plans(gn_handle* h);
 
 #define GN_CUDA(expr)                                   \
     do {                                                \

@@ -87,6 +87,7 @@ extern "C" int gn_destroy(gn_handle* h) {
     gn_handle_tables* t = tables_of(h);
     cudaFree(t->twiddle);
     cudaFree(t->hann);
+    gn_preprocess_free_plans(h);
     free(h);
     return GN_OK;
 }

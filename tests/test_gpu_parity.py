@@ -48,6 +48,21 @@ def test_preprocess_vs_oracle(U, n, H, W):
         assert np.abs(out - ref).max() <= PRE_TOL
 
 
+@pytest.mark.parametrize("n,H,W,S", [(3, 1080, 1920, 224), (9, 224, 224, 224), (4, 270, 480, 224), (2, 64, 64, 2),
+                                     (3, 720, 1280, 40), (300, 96, 128, 40)])
+def test_preprocess_other_sizes_and_cluster_split(U, n, H, W, S, monkeypatch):
+    """R224 (BASELINE config 5: 1080p -> 224 runs as a thread-block cluster per frame), up-scaling, tiny S;
+    the tap-capturing kernel and the L2 kernel must agree bit for bit (same arithmetic, different staging)."""
+    fr = syn.make_frames(n, H, W, seed=H + W + S)
+    out = U.extract_condensed_frame_tensor_array(fr, S, as_numpy=True)
+    ref = O.extract_condensed_frame_tensor_array(fr[: min(n, 4)], S)
+    assert out.shape == (n, 3, S, S)
+    assert np.abs(out[: min(n, 4)] - ref).max() <= PRE_TOL
+    monkeypatch.setenv("GN_PREPROCESS_L2", "1")
+    out_l2 = U.extract_condensed_frame_tensor_array(fr, S, as_numpy=True)
+    assert np.array_equal(out, out_l2)
+
+
 def test_preprocess_unaligned_device_view(U):
     """frames whose device address is not 16-byte aligned (head/tail scalar path)."""
     fr = syn.make_frames(3, 33, 35, seed=9)
