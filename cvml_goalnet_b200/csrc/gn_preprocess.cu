@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "gn_common.cuh"
+#include "gn_tc_ptx.cuh"
 
 namespace {
 
@@ -26,20 +27,22 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
 
 
 // Byte-wise min/max.  The packed-byte video instructions (__vminu4/__vmaxu4) are emulated on sm_100 (~7 SASS
-// instructions each); the packed 16-bit three-input min/max (VIMNMX3.U16x2) is native.  A word is split into
-// its even and odd bytes as two u16x2 values (one PRMT each) and folded into u16x2 accumulators.
+// instructions each); the packed 16-bit three-input min/max (VIMNMX3.U16x2) is native.  The accumulators are
+// u16x2 values whose HIGH bytes carry the result (a u16 compare is decided by its high byte first, so the low
+// bytes may hold anything): a word w contributes its odd bytes as it is and its even bytes as w << 8 --
+// three instructions per four bytes.
 struct ByteMinMax {
-    unsigned int mn, mx;                      // two u16 lanes each
-    __device__ __forceinline__ ByteMinMax() : mn(0x00FF00FFu), mx(0u) {}
+    unsigned int mn, mx;
+    __device__ __forceinline__ ByteMinMax() : mn(0xFFFFFFFFu), mx(0u) {}
     __device__ __forceinline__ void word(unsigned int w) {
-        const unsigned int e = __byte_perm(w, 0u, 0x4240), o = __byte_perm(w, 0u, 0x4341);
-        mn = __vimin3_u16x2(mn, e, o);
-        mx = __vimax3_u16x2(mx, e, o);
+        const unsigned int e = w << 8;
+        mn = __vimin3_u16x2(mn, w, e);
+        mx = __vimax3_u16x2(mx, w, e);
     }
     __device__ __forceinline__ void vec(uint4 v) { word(v.x); word(v.y); word(v.z); word(v.w); }
     __device__ __forceinline__ void byte(unsigned int b) { word(b * 0x01010101u); }
-    __device__ __forceinline__ unsigned int lo() const { return min(mn & 0xFFFFu, mn >> 16); }
-    __device__ __forceinline__ unsigned int hi() const { return max(mx & 0xFFFFu, mx >> 16); }
+    __device__ __forceinline__ unsigned int lo() const { return min((mn >> 8) & 0xFFu, mn >> 24); }
+    __device__ __forceinline__ unsigned int hi() const { return max((mx >> 8) & 0xFFu, mx >> 24); }
 };
 
 // cv2.resize INTER_LINEAR taps for one axis, formed in double like OpenCV does (oracle: _bilinear_taps).
@@ -153,16 +156,16 @@ preprocess_l2_kernel(const uint8_t* __restrict__ frames, int64_t n, int H, int W
 
 // ---------------------------------------------------------------------------------------------
 // tap-capturing version.  A host-built plan (one per (H, W, S), cached in the handle) lists, as 32-bit
-// words:  header[20] | ly0[S] ly1[S] fy[S] | cb0 cb1 fx on oh [3S each] | rowslot[H] | wordmap[3W/4] | rank[CL][5]
+// words:  header[20] | ly0[S] ly1[S] fy[S] | cb0[S] cb1[S] fx[S] | rowslot[H] | srcword[nWc] | rank[CL][5]
 //   ly0/ly1  compact index of the two source rows of output row y       rowslot  source row -> compact index or -1
-//   cb0/cb1  byte offset inside a compact row of tap xc = c*S + x       wordmap  source word -> compact word or -1
-//   fx, on, oh (per xc): horizontal weight, NCHW offset c*S*S + x, NHWC offset x*3 + c
+//   cb0/cb1  byte offset inside a compact row of the B byte of tap x     srcword  compact word -> source word of the row
+//   (a pixel's 3 bytes stay adjacent in a compact row: consecutive source words that hold taps stay consecutive)
 //   rank r   {ya, yb, sa, se, first}: output rows [ya,yb), streamed source rows [sa,se), first compact row
 // ---------------------------------------------------------------------------------------------
 constexpr int kTapThreads = 512;
 constexpr int kTapWarps = kTapThreads / 32;
-enum { PP_S = 0, PP_H, PP_W, PP_CL, PP_NWC, PP_ROWSMAX, PP_LY0, PP_LY1, PP_FY, PP_CB0, PP_CB1, PP_FX, PP_ON, PP_OH,
-       PP_ROWSLOT, PP_WORDMAP, PP_RANK, PP_TOTAL, PP_HEADER = 20 };
+enum { PP_S = 0, PP_H, PP_W, PP_CL, PP_NWC, PP_ROWSMAX, PP_LY0, PP_LY1, PP_FY, PP_CB0, PP_CB1, PP_FX, PP_K,
+       PP_ROWSLOT, PP_SRCWORD, PP_RANK, PP_TOTAL, PP_HEADER = 20 };
 
 __device__ __forceinline__ uint32_t pp_cluster_ctarank() {
     uint32_t r;
@@ -182,24 +185,61 @@ __device__ __forceinline__ void pp_st_cluster(uint32_t local_addr, uint32_t rank
 __device__ __forceinline__ void pp_cluster_barrier() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tap_scatter(uint4 d, const int32_t* wm, uint32_t* dst) {
-    const int4 m = *reinterpret_cast<const int4*>(wm);
-    if (m.x >= 0) dst[m.x] = d.x;
-    if (m.y >= 0) dst[m.y] = d.y;
-    if (m.z >= 0) dst[m.z] = d.z;
-    if (m.w >= 0) dst[m.w] = d.w;
+// Streaming structure: warp 16 is a producer whose lane 0 walks the CTA's (frame, chunk of K whole rows <= 16 KB)
+// sequence and issues cp.async.bulk copies into a ring of kRing shared-memory slots (full/empty mbarriers), so
+// that loads for the next chunks -- and for the next frame, during the resize pass -- are always in flight.
+// The 16 consumer warps take each chunk from shared memory: byte min/max over all of it, then the words of
+// its tap rows are copied to the tap buffer (one warp per row).
+constexpr int kChunkBytes = 16 * 1024;
+constexpr int kChunkVec = kChunkBytes / 16;
+constexpr int kRing = 4;
+constexpr int kTapLaunchThreads = kTapThreads + 32;
+
+__device__ __forceinline__ void bar_consumers() { asm volatile("bar.sync 1, %0;" ::"n"(kTapThreads) : "memory"); }
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t local_bar, uint32_t rank) {
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_bar), "r"(rank));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ra) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 
-__global__ void __launch_bounds__(kTapThreads, 3)
+__global__ void __launch_bounds__(kTapLaunchThreads, 2)
 preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32_t* __restrict__ plan,
                       float* __restrict__ out_nchw, __nv_bfloat16* __restrict__ out_nhwc) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    int32_t* sp = reinterpret_cast<int32_t*>(smem_raw);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint4* ring = reinterpret_cast<uint4*>(smem_raw);                  // [kRing][kChunkVec]
+    int32_t* sp = reinterpret_cast<int32_t*>(smem_raw + kRing * kChunkBytes);
     __shared__ unsigned int red_min[kTapWarps], red_max[kTapWarps];
+    __shared__ __align__(8) uint64_t bars[2 * kRing + 1];              // full[kRing], empty[kRing], exchange
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = plan[PP_TOTAL];
-    for (int i = tid; i < total; i += kTapThreads) sp[i] = plan[i];
+    for (int i = tid; i < total; i += kTapLaunchThreads) sp[i] = plan[i];
+    const uint32_t bar0 = tcx::smem_u32(bars);
+    const int CLk = plan[PP_CL];
+    if (tid == 0) {
+        for (int i = 0; i < kRing; ++i) {
+            tcx::mbar_init(bar0 + 8 * i, 1);                           // full: the producer's expect_tx arrival
+            tcx::mbar_init(bar0 + 8 * (kRing + i), kTapWarps);         // empty: one arrival per consumer warp
+        }
+        tcx::mbar_init(bar0 + 8 * 2 * kRing, CLk);                     // exchange: one arrival per CTA of the cluster
+        tcx::fence_barrier_init();
+    }
     __syncthreads();
+    if (CLk > 1) pp_cluster_barrier();                                 // peers' exchange barriers exist before anyone arrives
     const int S = sp[PP_S], H = sp[PP_H], W = sp[PP_W], CL = sp[PP_CL], nWc = sp[PP_NWC], rowsMax = sp[PP_ROWSMAX];
     const int* ly0 = sp + sp[PP_LY0];
     const int* ly1 = sp + sp[PP_LY1];
@@ -207,10 +247,9 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
     const int* cb0 = sp + sp[PP_CB0];
     const int* cb1 = sp + sp[PP_CB1];
     const float* fx = reinterpret_cast<const float*>(sp + sp[PP_FX]);
-    const int* on = sp + sp[PP_ON];
-    const int* oh = sp + sp[PP_OH];
     const int* rowslot = sp + sp[PP_ROWSLOT];
-    const int* wordmap = sp + sp[PP_WORDMAP];
+    const int* srcword = sp + sp[PP_SRCWORD];
+    const int K = sp[PP_K];                                            // rows per chunk
     float* lut = reinterpret_cast<float*>(sp + total);                 // 256 normalised byte levels
     unsigned int* xch = reinterpret_cast<unsigned int*>(lut + 256);    // [2 parities][8 ranks][min, max]
     uint32_t* tap = xch + 32;                                          // [rowsMax][nWc] captured words
@@ -223,41 +262,60 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
     const int ya = rk[0], yb = rk[1], sa = rk[2], se = rk[3], first = rk[4];
     const int RB = 3 * W, vpr = RB >> 4;
     const int64_t frame_bytes = (int64_t)H * RB;
-    const uint32_t xch_addr = (uint32_t)__cvta_generic_to_shared(xch);
+    const int nrows = se - sa;                                         // rows this CTA streams per frame
+    const int nchunk = (nrows + K - 1) / K;
+    const uint32_t ring_addr = tcx::smem_u32(ring);
 
-    // thread-constant starting points and steps of the two flat loops (no division inside them)
-    const int row0 = tid / vpr, v0 = tid - row0 * vpr;                    // pass 1: vector tid of the band
-    const int drow = kTapThreads / vpr, dv = kTapThreads - drow * vpr;
-    const int XC = 3 * S, ny = yb - ya;
-    const int yy0 = tid / XC, xc0 = tid - yy0 * XC;                       // pass 2: item tid = (y - ya, xc)
-    const int dyy = kTapThreads / XC, dxc = kTapThreads - dyy * XC;
-
-    int parity = 0;
-    for (int64_t f = cid; f < n; f += ncl, parity ^= 1) {
-        const uint8_t* p = frames + f * frame_bytes;
-        // ---- pass 1: stream rows [sa, se): packed-byte min/max, tap words -> shared memory ----
-        ByteMinMax mm;
-        {
-            const uint4* pv = reinterpret_cast<const uint4*>(p + (int64_t)sa * RB);
-            const int nv = (se - sa) * vpr;
-            int row = sa + row0, v = v0;                                  // (row, vector in row) of vector i
-            for (int i = tid; i < nv; i += 4 * kTapThreads) {             // 4 x 16 B in flight per thread
-                uint4 d[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    d[k] = (i + k * kTapThreads < nv) ? ld_stream(pv + i + k * kTapThreads) : d[0];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    mm.vec(d[k]);
-                    if (i + k * kTapThreads < nv) {
-                        const int slot = rowslot[row];
-                        const int l = slot - first;
-                        if (slot >= 0 && l >= 0 && l < rowsMax) tap_scatter(d[k], wordmap + 4 * v, tap + l * nWc);
-                    }
-                    row += drow; v += dv;
-                    if (v >= vpr) { v -= vpr; ++row; }
+    if (warp == kTapWarps) {
+        // ---------------- producer ----------------
+        if (lane == 0) {
+            int slot = 0;
+            uint32_t phase = 0;
+            for (int64_t f = cid; f < n; f += ncl) {
+                const uint8_t* src = frames + f * frame_bytes + (int64_t)sa * RB;
+                for (int c = 0; c < nchunk; ++c) {
+                    tcx::mbar_wait(bar0 + 8 * (kRing + slot), phase ^ 1);          // slot drained by all consumer warps
+                    const int r0 = c * K;
+                    const uint32_t bytes = (uint32_t)((nrows - r0 < K ? nrows - r0 : K) * RB);
+                    tcx::mbar_expect_tx(bar0 + 8 * slot, bytes);
+                    bulk_g2s(ring_addr + slot * kChunkBytes, src + (int64_t)r0 * RB, bytes, bar0 + 8 * slot);
+                    if (++slot == kRing) { slot = 0; phase ^= 1; }
                 }
             }
+        }
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    // thread-constant starting point and step of the resize loop (no division inside it)
+    const int ny = yb - ya, RW = RB >> 2;
+    const int yy0 = tid / S, x0s = tid - yy0 * S;                         // item tid = pixel (y - ya, x)
+    const int dyy = kTapThreads / S, dxs = kTapThreads - dyy * S;
+    const uint32_t xch_addr = tcx::smem_u32(xch);
+    const uint32_t xbar = bar0 + 8 * 2 * kRing;
+
+    int slot = 0;
+    uint32_t phase = 0, parity = 0;
+    for (int64_t f = cid; f < n; f += ncl, parity ^= 1) {
+        // ---- pass 1: chunks of rows [sa, se) from the ring: byte min/max, tap words -> tap buffer ----
+        ByteMinMax mm;
+        for (int c = 0; c < nchunk; ++c) {
+            const int r0 = c * K;
+            const int nr = nrows - r0 < K ? nrows - r0 : K;
+            const int nvc = nr * vpr;
+            tcx::mbar_wait(bar0 + 8 * slot, phase);
+            const uint4* cv = ring + slot * kChunkVec;
+            for (int j = tid; j < nvc; j += kTapThreads) mm.vec(cv[j]);
+            const uint32_t* cw = reinterpret_cast<const uint32_t*>(cv);
+            for (int r = warp; r < nr; r += kTapWarps) {
+                const int sl = rowslot[sa + r0 + r];
+                const int l = sl - first;
+                if (sl >= 0 && l >= 0 && l < rowsMax)
+                    for (int t = lane; t < nWc; t += 32) tap[l * nWc + t] = cw[r * RW + srcword[t]];
+            }
+            __syncwarp();
+            if (lane == 0) tcx::mbar_arrive(bar0 + 8 * (kRing + slot));
+            if (++slot == kRing) { slot = 0; phase ^= 1; }
         }
         unsigned int mn = mm.lo(), mx = mm.hi();
 #pragma unroll
@@ -266,7 +324,7 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
             mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
         }
         if (lane == 0) { red_min[warp] = mn; red_max[warp] = mx; }
-        __syncthreads();
+        bar_consumers();
         if (warp == 0) {
             mn = lane < kTapWarps ? red_min[lane] : 255u;
             mx = lane < kTapWarps ? red_max[lane] : 0u;
@@ -276,18 +334,19 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
                 mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
             }
             if (CL > 1) {
-                // every CTA of the cluster publishes its (min, max) into every CTA's exchange slot
+                // publish (min, max) into every CTA's exchange slot, then arrive on that CTA's exchange barrier
                 if (lane < CL) {
-                    const uint32_t slot = xch_addr + (uint32_t)((parity * 8 + rank) * 2) * 4u;
-                    pp_st_cluster(slot, (uint32_t)lane, mn);
-                    pp_st_cluster(slot + 4u, (uint32_t)lane, mx);
+                    const uint32_t dst = xch_addr + (uint32_t)((parity * 8 + rank) * 2) * 4u;
+                    pp_st_cluster(dst, (uint32_t)lane, mn);
+                    pp_st_cluster(dst + 4u, (uint32_t)lane, mx);
+                    mbar_arrive_remote(xbar, (uint32_t)lane);
                 }
             } else if (lane == 0) {
                 xch[0] = mn;
                 xch[1] = mx;
             }
         }
-        if (CL > 1) pp_cluster_barrier(); else __syncthreads();
+        if (CL > 1) mbar_wait_cluster(xbar, parity); else bar_consumers();
         // ---- normalisation LUT: float32((v - min) / (max - min + 1e-7)) formed in double (utils.py:284) ----
         if (tid < 256) {
             unsigned int gmn = 255u, gmx = 0u;
@@ -303,27 +362,38 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
             const double rng = (double)((int)gmx - (int)gmn) + 1e-7;
             lut[tid] = (float)(((double)tid - (double)gmn) / rng);
         }
-        __syncthreads();
+        bar_consumers();
         // ---- pass 2: bilinear taps from the captured words (horizontal then vertical, like cv2) ----
-        const int tapRB = nWc * 4;
-        float* onc = out_nchw ? out_nchw + f * 3 * S * S : nullptr;
-        __nv_bfloat16* onh = out_nhwc ? out_nhwc + f * 3 * S * S : nullptr;
-        int yy = yy0, xc = xc0;
-        for (int idx = tid; idx < ny * XC; idx += kTapThreads) {
+        const int tapRB = nWc * 4, SS = S * S;
+        float* onc = out_nchw ? out_nchw + f * 3 * SS : nullptr;
+        __nv_bfloat16* onh = out_nhwc ? out_nhwc + f * 3 * SS : nullptr;
+        int yy = yy0, x = x0s;
+        for (int idx = tid; idx < ny * S; idx += kTapThreads) {           // one pixel = its three channels
             const int y = ya + yy;
-            const uint8_t* r0 = tapb + (ly0[y] - first) * tapRB;
-            const uint8_t* r1 = tapb + (ly1[y] - first) * tapRB;
-            const int o0 = cb0[xc], o1 = cb1[xc];
-            const float ax = fx[xc], ay = fy[y];
-            const float top = lut[r0[o0]] * (1.f - ax) + lut[r0[o1]] * ax;
-            const float bot = lut[r1[o0]] * (1.f - ax) + lut[r1[o1]] * ax;
-            const float val = top * (1.f - ay) + bot * ay;
-            if (onc) onc[y * S + on[xc]] = val;
-            if (onh) onh[y * XC + oh[xc]] = __float2bfloat16(val);
-            yy += dyy; xc += dxc;
-            if (xc >= XC) { xc -= XC; ++yy; }
+            const uint8_t* a0 = tapb + (ly0[y] - first) * tapRB + cb0[x];
+            const uint8_t* a1 = tapb + (ly0[y] - first) * tapRB + cb1[x];
+            const uint8_t* b0 = tapb + (ly1[y] - first) * tapRB + cb0[x];
+            const uint8_t* b1 = tapb + (ly1[y] - first) * tapRB + cb1[x];
+            const float ax = fx[x], ay = fy[y], bx = 1.f - ax, by = 1.f - ay;
+            float val[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float top = lut[a0[c]] * bx + lut[a1[c]] * ax;
+                const float bot = lut[b0[c]] * bx + lut[b1[c]] * ax;
+                val[c] = top * by + bot * ay;
+            }
+            if (onc) {
+                float* o = onc + y * S + x;
+                o[0] = val[0]; o[SS] = val[1]; o[2 * SS] = val[2];
+            }
+            if (onh) {
+                __nv_bfloat16* o = onh + (y * S + x) * 3;
+                o[0] = __float2bfloat16(val[0]); o[1] = __float2bfloat16(val[1]); o[2] = __float2bfloat16(val[2]);
+            }
+            yy += dyy; x += dxs;
+            if (x >= S) { x -= S; ++yy; }
         }
-        __syncthreads();   // lut / tap / xch[0..1] are reused by the next frame
+        bar_consumers();   // lut / tap / xch[0..1] are reused by the next frame
     }
 }
 
@@ -357,6 +427,8 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
         for (int c = 0; c < 3; ++c) { wordmap[(x0[d] * 3 + c) >> 2] = 0; wordmap[(x1[d] * 3 + c) >> 2] = 0; }
     int nWc = 0;
     for (size_t w = 0; w < wordmap.size(); ++w) if (wordmap[w] == 0) wordmap[w] = nWc++;
+    const int K = kChunkBytes / (3 * W);                 // whole rows per ring slot
+    if (K < 1) return false;
     for (int pass = 0; pass < 2; ++pass) {
         const size_t limit = pass == 0 ? kTapSmemTwo : kTapSmemOne;
         for (int CL = 1; CL <= 8; CL *= 2) {
@@ -379,38 +451,31 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
             const int o_ly0 = off; off += S;
             const int o_ly1 = off; off += S;
             const int o_fy = off; off += S;
-            const int o_cb0 = off; off += 3 * S;
-            const int o_cb1 = off; off += 3 * S;
-            const int o_fx = off; off += 3 * S;
-            const int o_on = off; off += 3 * S;
-            const int o_oh = off; off += 3 * S;
+            const int o_cb0 = off; off += S;
+            const int o_cb1 = off; off += S;
+            const int o_fx = off; off += S;
             const int o_rowslot = off; off += H;
-            off = (off + 3) & ~3;
-            const int o_wordmap = off; off += (int)wordmap.size();
+            const int o_srcword = off; off += nWc;
             const int o_rank = off; off += 5 * CL;
             const int total = (off + 3) & ~3;
-            const size_t smem = (size_t)(total + 256 + 32) * 4 + (size_t)rowsMax * nWc * 4;
+            const size_t smem = (size_t)kRing * kChunkBytes + (size_t)(total + 256 + 32) * 4 + (size_t)rowsMax * nWc * 4;
             if (smem > limit) continue;
             out.assign(total, 0);
             out[PP_S] = S; out[PP_H] = H; out[PP_W] = W; out[PP_CL] = CL; out[PP_NWC] = nWc; out[PP_ROWSMAX] = rowsMax;
             out[PP_LY0] = o_ly0; out[PP_LY1] = o_ly1; out[PP_FY] = o_fy; out[PP_CB0] = o_cb0; out[PP_CB1] = o_cb1;
-            out[PP_FX] = o_fx; out[PP_ON] = o_on; out[PP_OH] = o_oh; out[PP_ROWSLOT] = o_rowslot; out[PP_WORDMAP] = o_wordmap; out[PP_RANK] = o_rank;
+            out[PP_FX] = o_fx; out[PP_K] = K; out[PP_ROWSLOT] = o_rowslot; out[PP_SRCWORD] = o_srcword; out[PP_RANK] = o_rank;
             out[PP_TOTAL] = total;
             for (int d = 0; d < S; ++d) {
                 out[o_ly0 + d] = rowslot[y0[d]];
                 out[o_ly1 + d] = rowslot[y1[d]];
                 memcpy(&out[o_fy + d], &fyv[d], 4);
-                for (int c = 0; c < 3; ++c) {
-                    const int b0 = x0[d] * 3 + c, b1 = x1[d] * 3 + c, xc = c * S + d;
-                    out[o_cb0 + xc] = wordmap[b0 >> 2] * 4 + (b0 & 3);
-                    out[o_cb1 + xc] = wordmap[b1 >> 2] * 4 + (b1 & 3);
-                    memcpy(&out[o_fx + xc], &fxv[d], 4);
-                    out[o_on + xc] = c * S * S + d;
-                    out[o_oh + xc] = d * 3 + c;
-                }
+                memcpy(&out[o_fx + d], &fxv[d], 4);
+                const int b0 = x0[d] * 3, b1 = x1[d] * 3;
+                out[o_cb0 + d] = wordmap[b0 >> 2] * 4 + (b0 & 3);
+                out[o_cb1 + d] = wordmap[b1 >> 2] * 4 + (b1 & 3);
             }
             for (int r = 0; r < H; ++r) out[o_rowslot + r] = rowslot[r];
-            for (size_t w = 0; w < wordmap.size(); ++w) out[o_wordmap + w] = wordmap[w];
+            for (size_t w = 0; w < wordmap.size(); ++w) if (wordmap[w] >= 0) out[o_srcword + wordmap[w]] = (int32_t)w;
             for (int i = 0; i < 5 * CL; ++i) out[o_rank + i] = rk[i];
             CL_out = CL;
             smem_out = smem;
@@ -435,7 +500,7 @@ const PrePlan* get_plan(gn_handle* h, int H, int W, int S, int* status) {
             e = cudaFuncSetAttribute(preprocess_tap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTapSmemOne);
         if (e != cudaSuccess) { *status = (int)e; return nullptr; }
         int per = (int)((227 * 1024) / (pl.smem + 1024));
-        pl.ctas_per_sm = per > 3 ? 3 : (per < 1 ? 1 : per);   // 39 registers x 512 threads: three CTAs per SM
+        pl.ctas_per_sm = per > 2 ? 2 : (per < 1 ? 1 : per);
     }
     cache->plans.push_back(pl);                    // a plan without tables records "use the L2 kernel"
     const PrePlan& back = cache->plans.back();
@@ -471,7 +536,7 @@ extern "C" int gn_preprocess_u8_bgr(gn_handle* h, const uint8_t* d_frames, int64
             if (clusters > n) clusters = n;
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3((unsigned)(clusters * pl->CL));
-            cfg.blockDim = dim3(kTapThreads);
+            cfg.blockDim = dim3(kTapLaunchThreads);
             cfg.dynamicSmemBytes = pl->smem;
             cfg.stream = gn_stream(stream);
             cudaLaunchAttribute at[1];
