@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include "gn_common.cuh"
+#include "gn_tc_ptx.cuh"
 
 namespace {
 
@@ -149,10 +150,13 @@ template <int THREADS>
 __global__ void __launch_bounds__(THREADS, 1)
 knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* __restrict__ weights_all, int n_items,
                         int capacity, int zero_col_forced, uint8_t* __restrict__ selected_all,
-                        int32_t* __restrict__ best_all, uint32_t* bits_all, int words, int slice_w) {
-    extern __shared__ int32_t row_smem[];            // [2][slice_w] rows, then [kKnapRing][slice_w/32] decision bits
+                        int32_t* __restrict__ best_all, uint32_t* bits_all, int words, int slice_w,
+                        const int* __restrict__ status_all) {
+    extern __shared__ int32_t row_smem[];            // [2][slice_w] rows, [kKnapRing][slice_w/32] decision bits, items
     const uint32_t rank = cluster_ctarank();
     const int prob = (int)cluster_id_x();
+    // launched behind the multi-row kernel: nothing to do unless that one declined the problem (status 1)
+    if (status_all != nullptr && status_all[prob] == 0) return;
     const int32_t* values = values_all + (size_t)prob * n_items;
     const int32_t* weights = weights_all + (size_t)prob * n_items;
     uint8_t* selected = selected_all + (size_t)prob * n_items;
@@ -163,9 +167,13 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
     const int w0 = c0 >> 5;                          // first decision word of this slice
     const int nw = (w0 + sw <= words) ? sw : (words > w0 ? words - w0 : 0);   // words of the slice that exist
     uint32_t* ring = reinterpret_cast<uint32_t*>(row_smem + 2 * slice_w);
+    // (weight, value) of every item in shared memory: the per-row cluster barrier invalidates L1, so a global
+    // load at the top of each row would pay an L2 round trip on the critical path
+    int2* items = reinterpret_cast<int2*>(ring + kKnapRing * sw);
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(row_smem);
 
+    for (int i = tid; i < n_items; i += THREADS) items[i] = make_int2(weights[i], values[i]);
     for (int l = tid; l < 2 * slice_w; l += THREADS) row_smem[l] = 0;      // K[0][*] = 0 (utils.py:487)
     if (rank == 0)
         for (int i = tid; i < n_items; i += THREADS) selected[i] = 0;
@@ -173,7 +181,8 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
 
     int pb = 0;                                       // buffer holding row i-1
     for (int i = 0; i < n_items; ++i) {
-        const int32_t wt = __ldg(weights + i), v = __ldg(values + i);
+        const int2 it = items[i];
+        const int32_t wt = it.x, v = it.y;
         const int q = wt / slice_w, rem = wt - q * slice_w;
         const int own_a = (int)rank - q, own_b = own_a - 1;         // CTAs holding K[i-1][w - wt]
         const int32_t* prev = row_smem + pb * slice_w;
@@ -237,6 +246,193 @@ knapsack_cluster_kernel(const int32_t* __restrict__ values_all, const int32_t* _
             const int r = i - 1 - (__ffs(mask) - 1);          // nearest selected row below i
             if (lane == 0) selected[r] = 1;
             w -= __ldg(weights + r);
+            i = r;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 0/1 knapsack, T rows per step, neighbour-to-neighbour pipeline.  Row i only depends on row i-1 at columns
+// w and w - wt_i, so rows i0 .. i0+T-1 at column w are a function of row i0-1 at the 2^T columns
+// w - (sum of a subset of the T weights).  Every thread loads those 2^T values and evaluates the T levels in
+// registers (one add-max per cell).  Data only ever flows towards higher columns, so there is no cluster-wide
+// barrier: after a step, a CTA PUSHES the tail of its new row into the halo of its right neighbour through
+// distributed shared memory and arrives on that neighbour's mbarrier; the neighbour returns a credit once it
+// has finished reading a halo buffer.  CTA r simply runs a little behind CTA r-1.
+// Columns to the left of column 0 hold a large negative sentinel, so "item does not fit" needs no test.
+// Declines (status 1; the one-row kernel behind it then runs) when T * max weight exceeds the halo, when a
+// zero weight meets the forced-zero column, or when values are large enough to threaten the sentinel.
+// ---------------------------------------------------------------------------------------------
+constexpr int32_t kKnapNeg = -(1 << 29);
+
+template <int THREADS, int T, int CPT>
+__global__ void __launch_bounds__(THREADS, 1)
+knapsack_multirow_kernel(const int32_t* __restrict__ values_all, const int32_t* __restrict__ weights_all, int n_items,
+                         int capacity, int zero_col_forced, uint8_t* __restrict__ selected_all,
+                         int32_t* __restrict__ best_all, uint32_t* bits_all, int words, int slice_w, int halo,
+                         int* __restrict__ status_all, int cl) {
+    constexpr int NS = 1 << T;
+    constexpr int NWARPS = THREADS / 32;
+    extern __shared__ int32_t row_smem[];            // [2][halo + slice_w] rows, [kKnapRing][slice_w/32] bits, items
+    __shared__ int s_maxw, s_minw, s_maxv;
+    __shared__ __align__(8) uint64_t bars[4];        // full[2] (halo of buffer b has arrived), credit[2] (right
+                                                     // neighbour has finished reading its halo of buffer b)
+    const uint32_t rank = tcx::cluster_ctarank();
+    const int prob = (int)tcx::cluster_id_x();
+    const int32_t* values = values_all + (size_t)prob * n_items;
+    const int32_t* weights = weights_all + (size_t)prob * n_items;
+    uint8_t* selected = selected_all + (size_t)prob * n_items;
+    uint32_t* bits = bits_all + (size_t)prob * n_items * words;
+    const int c0 = (int)rank * slice_w;
+    const int sw = slice_w >> 5;
+    const int w0 = c0 >> 5;
+    const int nw = (w0 + sw <= words) ? sw : (words > w0 ? words - w0 : 0);
+    const int rowlen = halo + slice_w;
+    uint32_t* ring = reinterpret_cast<uint32_t*>(row_smem + 2 * rowlen);
+    int2* items = reinterpret_cast<int2*>(ring + kKnapRing * sw);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t smem_base = tcx::smem_u32(row_smem);
+    const uint32_t bar0 = tcx::smem_u32(bars);
+    const bool has_left = rank > 0, has_right = (int)rank + 1 < cl;
+
+    if (tid == 0) {
+        s_maxw = 0; s_minw = 0x7fffffff; s_maxv = 0;
+        tcx::mbar_init(bar0, NWARPS); tcx::mbar_init(bar0 + 8, NWARPS);      // full[0], full[1]
+        tcx::mbar_init(bar0 + 16, 1); tcx::mbar_init(bar0 + 24, 1);          // credit[0], credit[1]
+        tcx::fence_barrier_init();
+    }
+    __syncthreads();
+    int mw = 0, mnw = 0x7fffffff, mv = 0;
+    for (int i = tid; i < n_items; i += THREADS) {
+        const int2 it = make_int2(weights[i], values[i]);
+        items[i] = it;
+        mw = max(mw, it.x); mnw = min(mnw, it.x); mv = max(mv, abs(it.y));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mw = max(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+        mnw = min(mnw, __shfl_xor_sync(0xffffffffu, mnw, o));
+        mv = max(mv, __shfl_xor_sync(0xffffffffu, mv, o));
+    }
+    if (lane == 0) { atomicMax(&s_maxw, mw); atomicMin(&s_minw, mnw); atomicMax(&s_maxv, mv); }
+    // K[0][*] = 0 (utils.py:487); columns left of column 0 (the halo of rank 0) = sentinel
+    for (int l = tid; l < 2 * rowlen; l += THREADS) {
+        const int p = l < rowlen ? l : l - rowlen;
+        row_smem[l] = (rank == 0 && p < halo) ? kKnapNeg : 0;
+    }
+    if (rank == 0)
+        for (int i = tid; i < n_items; i += THREADS) selected[i] = 0;
+    __syncthreads();
+    // the host picked this kernel without knowing the items: tell it to use the one-row kernel instead
+    const bool decline = (int64_t)s_maxw * T > halo || s_minw < 0 || (s_minw == 0 && zero_col_forced) ||
+                         (int64_t)s_maxv * (int64_t)(n_items + T) >= (1 << 28);
+    if (rank == 0 && tid == 0) status_all[prob] = decline ? 1 : 0;
+    if (decline) return;                               // uniform over the whole cluster: same data everywhere
+    tcx::cluster_sync_all();                           // every CTA's mbarriers exist before anyone arrives remotely
+
+    const int nsteps = (n_items + T - 1) / T;
+    for (int k = 0; k < nsteps; ++k) {
+        const int i0 = k * T;
+        const int pb = k & 1;                          // buffer holding row i0 - 1
+        // this step's items (missing ones at the tail: weight 0, value 0 = no-op rows) and the 2^T subset offsets
+        int val[T], off[NS];
+        int need_next = 0;
+        off[0] = 0;
+#pragma unroll
+        for (int j = 0; j < T; ++j) {
+            const int2 it = (i0 + j < n_items) ? items[i0 + j] : make_int2(0, 0);
+            val[j] = it.y;
+#pragma unroll
+            for (int sidx = 0; sidx < (1 << j); ++sidx) off[sidx | (1 << j)] = off[sidx] + it.x;
+            if (i0 + T + j < n_items) need_next += items[i0 + T + j].x;
+        }
+        int32_t* prev = row_smem + pb * rowlen;
+        int32_t* cur = row_smem + (pb ^ 1) * rowlen;
+        // the halo of row i0-1 was pushed by the left neighbour after its step k-1
+        if (has_left && k > 0) tcx::mbar_wait_acq_cluster(bar0 + 8 * pb, ((k - 1) >> 1) & 1);
+        const int rbase = i0 & (kKnapRing - 1);        // kKnapRing is a multiple of every T used
+        // CPT columns per thread and pass, THREADS apart: the 2^T load addresses are formed once and the other
+        // columns of the pass reach theirs through immediate offsets
+#pragma unroll 1
+        for (int lb = tid; lb < slice_w; lb += CPT * THREADS) {
+            const int32_t* pp = prev + halo + lb;
+            int32_t a[CPT][NS];
+#pragma unroll
+            for (int sidx = 0; sidx < NS; ++sidx) {
+                const int32_t* ps = pp - off[sidx];
+#pragma unroll
+                for (int c = 0; c < CPT; ++c) a[c][sidx] = ps[c * THREADS];
+            }
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) {
+                const int l = lb + c * THREADS;
+                {                                       // slice_w is a multiple of CPT * THREADS (host)
+                    uint32_t dec[T];
+                    // K = max(K[w], v + K[w - wt]) (utils.py:489-490); a column left of 0 holds the sentinel and loses
+#pragma unroll
+                    for (int j = 0; j < T; ++j) {
+                        const int32_t old = a[c][0];
+#pragma unroll
+                        for (int sidx = 0; sidx < NS; ++sidx)
+                            if ((sidx & ((2 << j) - 1)) == 0)
+                                a[c][sidx] = max(a[c][sidx], val[j] + a[c][sidx | (1 << j)]);
+                        dec[j] = a[c][0] != old;
+                    }
+                    cur[halo + l] = a[c][0];
+#pragma unroll
+                    for (int j = 0; j < T; ++j) {
+                        const uint32_t word = __ballot_sync(0xffffffffu, dec[j] != 0);
+                        if (lane == 0) ring[(rbase + j) * sw + (l >> 5)] = word;
+                    }
+                }
+            }
+        }
+        __syncthreads();                               // row i0+T-1 complete in this CTA; nobody reads `prev` any more
+        // decision bits leave shared memory once per kKnapRing rows
+        const int last = (i0 + T < n_items) ? i0 + T - 1 : n_items - 1;
+        if (((i0 + T) & (kKnapRing - 1)) == 0 || i0 + T >= n_items) {
+            const int r0 = i0 & ~(kKnapRing - 1);
+            const int nr = last - r0 + 1;
+            for (int e = tid; e < nr * sw; e += THREADS) {
+                const int r = e / sw, wi = e - r * sw;
+                if (wi < nw) bits[(size_t)(r0 + r) * words + w0 + wi] = ring[e];
+            }
+            __syncthreads();                           // the ring is rewritten by the next step
+        }
+        if (k + 1 < nsteps) {
+            // credit to the left neighbour: this CTA no longer reads its halo of buffer pb
+            if (has_left && tid == 0) tcx::mbar_arrive_cluster(tcx::mapa(bar0 + 16 + 8 * pb, rank - 1));
+            if (has_right) {
+                // the right neighbour reads its halo of buffer pb^1 at step k+1 and read it last at step k-1
+                if (k > 0) tcx::mbar_wait_acq_cluster(bar0 + 16 + 8 * (pb ^ 1), ((k - 1) >> 1) & 1);
+                const uint32_t dst = tcx::mapa(smem_base + (uint32_t)((pb ^ 1) * rowlen) * 4u, rank + 1);
+                for (int h = tid; h < need_next; h += THREADS)
+                    tcx::st_cluster_u32(dst + (uint32_t)(halo - 1 - h) * 4u, (uint32_t)cur[rowlen - 1 - h]);
+                __syncwarp();
+                if (lane == 0) tcx::mbar_arrive_cluster(tcx::mapa(bar0 + 8 * (pb ^ 1), rank + 1));
+            }
+        }
+    }
+    tcx::cluster_sync_all();                           // all decision bits are in global memory; no DSMEM traffic left
+    const int pbl = nsteps & 1;
+    if (tid == 0 && capacity >= c0 && capacity < c0 + slice_w)
+        best_all[prob] = row_smem[pbl * rowlen + halo + capacity - c0];
+    // backtrack (utils.py:495-509): skip item i when K[i][w] == K[i-1][w]
+    if (rank == 0 && tid < 32) {
+        int w = capacity;
+        int i = n_items;
+        while (i > 0) {
+            const int row = i - 1 - lane;
+            uint32_t bit = 0;
+            if (row >= 0) {
+                const volatile uint32_t* bp = bits + (size_t)row * words + (w >> 5);
+                bit = (*bp >> (w & 31)) & 1u;
+            }
+            const uint32_t mask = __ballot_sync(0xffffffffu, bit != 0);
+            if (mask == 0) { i -= 32; continue; }
+            const int r = i - 1 - (__ffs(mask) - 1);          // nearest selected row below i
+            if (lane == 0) selected[r] = 1;
+            w -= items[r].x;
             i = r;
         }
     }
@@ -331,7 +527,7 @@ extern "C" int64_t gn_knapsack_workspace_bytes(int n_items, int64_t capacity_col
     const int64_t words = knap_words(capacity_columns);
     int64_t bytes = (int64_t)n_items * words * 4;                 // decision bits
     if (2 * words * 32 * 4 > kKnapSmemLimit) bytes += 2 * words * 32 * 4;   // rows do not fit shared memory
-    return (bytes + 255) & ~255LL;
+    return ((bytes + 255) & ~255LL) + 256;                        // + status word of the multi-row kernel
 }
 
 extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t* d_weights, int n_items,
@@ -344,28 +540,30 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
     const int64_t words = knap_words(capacity);
     const int64_t per = gn_knapsack_workspace_bytes(n_items, capacity);
     if (per * batch > workspace_bytes || (!d_workspace && per > 0)) return GN_E_WORKSPACE;
-    // cluster path: columns split over up to 8 CTAs (portable cluster size), at least 1024 columns per CTA
-    int cl = 8;
+    // cluster path: columns split over the CTAs of one cluster, at least 1024 columns per CTA.  A single wide
+    // problem takes a 16-CTA cluster (non-portable size, one GPC); batches keep the portable 8 so that more
+    // problems are resident at once.
+    int cl = batch <= 4 ? 16 : 8;
     while (cl > 1 && (capacity + 1) < (int64_t)cl * 1024) cl >>= 1;
-    if (const char* e = getenv("GN_KNAP_CL")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) cl = v; }
+    if (const char* e = getenv("GN_KNAP_CL")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) cl = v; }
     int64_t slice = (capacity + 1 + cl - 1) / cl;
     slice = (slice + 31) & ~31LL;
-    const int64_t cl_smem = 2 * slice * 4 + kKnapRing * (slice / 32) * 4;
+    constexpr int kMT = 512, kMCPT = 3;            // multi-row kernel: threads, columns per thread and pass
+    {
+        // whole passes for the multi-row kernel when that costs little padding
+        const int64_t padded = (slice + kMT * kMCPT - 1) / (kMT * kMCPT) * (kMT * kMCPT);
+        if (padded * 4 <= slice * 5) slice = padded;
+    }
+    const int64_t cl_smem = 2 * slice * 4 + kKnapRing * (slice / 32) * 4 + 8 + (int64_t)n_items * 8;
     const int use_smem = cl_smem <= kKnapSmemLimit ? 1 : 0;
     // workspace: [batch][n_items][words] bits, then (if needed) [batch][2][words*32] rows
     uint32_t* bits = reinterpret_cast<uint32_t*>(d_workspace);
+    int* status = reinterpret_cast<int*>(reinterpret_cast<char*>(d_workspace) + per * batch - 256 * (int64_t)batch);
     if (use_smem) {
         constexpr int kT = 1024;
-        auto kern = knapsack_cluster_kernel<kT>;
-        static bool cattr = false;
-        if (!cattr) {
-            GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
-            cattr = true;
-        }
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)(batch * cl));
         cfg.blockDim = dim3(kT);
-        cfg.dynamicSmemBytes = (size_t)cl_smem;
         cfg.stream = gn_stream(stream);
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
@@ -374,8 +572,45 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
         at[0].val.clusterDim.z = 1;
         cfg.attrs = at;
         cfg.numAttrs = 1;
+        // multi-row kernel first (T rows per cluster barrier); it declines, per problem, when T * max weight
+        // does not fit its halo, and the one-row kernel behind it then does that problem
+        int rows_per_step = 4;
+        if (const char* e = getenv("GN_KNAP_T")) rows_per_step = atoi(e);
+        int64_t halo = slice < 4096 ? slice : 4096;
+        const int64_t mr_smem = 2 * (halo + slice) * 4 + kKnapRing * (slice / 32) * 4 + 8 + (int64_t)n_items * 8;
+        const int* skip = nullptr;
+        if ((rows_per_step == 2 || rows_per_step == 4) && mr_smem <= kKnapSmemLimit && n_items > 0 &&
+            slice % (kMT * kMCPT) == 0) {
+            // 512 threads -> 128 registers per thread: 3 columns x 16 cells in flight
+            auto k4 = knapsack_multirow_kernel<kMT, 4, kMCPT>;
+            auto k2 = knapsack_multirow_kernel<kMT, 2, kMCPT>;
+            cfg.blockDim = dim3(kMT);
+            static bool mattr = false;
+            if (!mattr) {
+                GN_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
+                GN_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
+                GN_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+                GN_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+                mattr = true;
+            }
+            cfg.dynamicSmemBytes = (size_t)mr_smem;
+            GN_CUDA(cudaLaunchKernelEx(&cfg, rows_per_step == 4 ? k4 : k2, d_values, d_weights, n_items, (int)capacity,
+                                       capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, (int)words, (int)slice,
+                                       (int)halo, status, cl));
+            GN_LAUNCHED(h);
+            skip = status;
+            cfg.blockDim = dim3(kT);
+        }
+        auto kern = knapsack_cluster_kernel<kT>;
+        static bool cattr = false;
+        if (!cattr) {
+            GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
+            GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            cattr = true;
+        }
+        cfg.dynamicSmemBytes = (size_t)cl_smem;
         GN_CUDA(cudaLaunchKernelEx(&cfg, kern, d_values, d_weights, n_items, (int)capacity,
-                                   capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, (int)words, (int)slice));
+                                   capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, (int)words, (int)slice, skip));
         GN_LAUNCHED(h);
         return GN_OK;
     }

@@ -215,6 +215,26 @@ def test_knapsack_wide_table_cluster_slices(U):
     assert U.knapsack(v, w2, 60000, 1) == O.knapsack_rows(v, w2, 60000, 1)
 
 
+@pytest.mark.parametrize("rows_per_step", ["1", "2", "4"])
+def test_knapsack_rows_per_barrier_variants(U, monkeypatch, rows_per_step):
+    """The multi-row kernel (2 or 4 DP rows per cluster barrier, halo from the neighbour CTAs) against the
+    one-row kernel and the oracle: match-sized table (984 clips x 24 301 columns), item counts that are not
+    a multiple of the step, zero weights, a weight-0/column-0 corner, and weights that exceed the halo (the
+    kernel declines and the one-row kernel behind it takes over)."""
+    monkeypatch.setenv("GN_KNAP_T", rows_per_step)
+    rng = np.random.default_rng(21)
+    cases = []
+    n = 984
+    cases.append((rng.integers(30, 1500, n).tolist(), rng.integers(30, 301, n).tolist(), 24300, 1))
+    for n in (1, 2, 3, 5, 33, 127):
+        cases.append((rng.integers(0, 500, n).tolist(), rng.integers(0, 200, n).tolist(), 9000, 1))
+    cases.append((rng.integers(1, 500, 50).tolist(), rng.integers(1, 40, 50).tolist(), 300, 5))     # narrow table
+    cases.append((rng.integers(1, 500, 37).tolist(), rng.integers(3000, 20000, 37).tolist(), 50000, 1))  # > halo
+    cases.append(([5, 7, 9, 11], [0, 0, 3, 0], 3, 1))
+    for i, (v, w, cap, scale) in enumerate(cases):
+        assert U.knapsack(v, w, cap, scale) == O.knapsack_rows(v, w, cap, scale), (rows_per_step, i)
+
+
 def test_knapsack_very_wide_table_global_rows(U):
     """capacity too wide even for 8 shared-memory slices -> single-CTA kernel with rows in the workspace."""
     rng = np.random.default_rng(12)
