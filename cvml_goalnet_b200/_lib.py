@@ -13,7 +13,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgoalnet_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu"]
+SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu", "gn_train.cu"]
 NVCC_FLAGS = ["-shared", "-Xcompiler", "-fPIC", "-std=c++17", "-O3", "-lineinfo",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 
@@ -74,6 +74,10 @@ for _i in (1, 2, 3):
     STATE_KEYS[f"bn{_i}_m"] = f"visbl.bnorm{_i}.running_mean"
     STATE_KEYS[f"bn{_i}_v"] = f"visbl.bnorm{_i}.running_var"
 
+class gn_fusion_state(C.Structure):
+    _fields_ = [("weight", C.c_void_p * 5), ("bias", C.c_void_p * 5)]
+
+
 _P = C.c_void_p
 _I = C.c_int
 _L = C.c_int64
@@ -98,6 +102,14 @@ SIGNATURES = {
     "gn_knapsack": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P, _P, _L, _P]),
     "gn_summary_indicator": (_I, [_P, _P, _P, _I, _L, _P, _P]),
     "gn_fscore_counts": (_I, [_P, _P, _P, _I, _L, _P, _P]),
+    "gn_fusion_trainer_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_fusion_state), _I, _L, _P]),
+    "gn_fusion_trainer_destroy": (_I, [_P]),
+    "gn_fusion_param_count": (_L, [_P]),
+    "gn_fusion_set_hyper": (_I, [_P, C.c_float, C.c_float, C.c_float, C.c_float]),
+    "gn_fusion_get_params": (_I, [_P, _P, _P]),
+    "gn_fusion_forward_backward": (_I, [_P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P, _P]),
+    "gn_fusion_adam_step": (_I, [_P, _P, C.c_float, _P]),
+    "gn_fusion_train_step": (_I, [_P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P, _P]),
     "gn_dbg_avm_forward_simt": (_I, [_P, _P, _P, _L, _P, _P, _P, _L, _P]),
     "gn_dbg_read_activation": (_I, [_P, _I, _L, _P, _P, _P]),
 }

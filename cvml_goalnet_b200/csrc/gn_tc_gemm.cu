@@ -27,7 +27,11 @@ constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;            // columns per accumulator buffer (MT * BN)
 constexpr int kMaxN = 512;               // widest layer: per-channel parameter vectors staged in shared memory
 
-enum Mode { kConv = 0, kLinear = 1, kScore = 2 };
+enum Mode { kConv = 0, kLinear = 1, kScore = 2,
+            // training GEMMs of the fusion MLP (gn_train.cu): all are C = A . B^T with K-major bf16 operands
+            kTrainFwd = 3,   // relu(acc + bias), dropout, bf16 out [M][N] and its transpose [N][ld_t]
+            kDgrad = 4,      // acc * scale * [gate > 0], bf16 out [M][N] and its transpose
+            kWgrad = 5 };    // fp32 out [M][N] = acc
 
 struct ConvGeom {
     int OH, OW;        // conv output == input interior (k3 s1 p1)
@@ -51,6 +55,14 @@ struct GemmArgs {
     float* scores;           // score: [M]
     int a3d_rows;            // linear: 0 = A is a 2-D [M][K] map; else A is a 3-D (k, position, frame) map with this many
                              //         positions per frame (AudBl conv2: overlapping 192-element windows, 128/rows frames per tile)
+    // training modes
+    __nv_bfloat16* out_t;    // transposed bf16 output [N][ld_t] (or null)
+    int64_t ld_t;
+    const __nv_bfloat16* gate;   // kDgrad: activations [M][N] of the layer below (gradient flows where > 0)
+    const uint8_t* mask;     // kTrainFwd: dropout keep-mask [M][N] (1 = keep); null -> counter-based hash of `seed`
+    float scale;             // dropout scale 1/(1-p) (1 = no dropout)
+    float keep_prob;         // kTrainFwd without mask: P(keep); >= 1 disables dropout
+    unsigned long long seed;
     ConvGeom g;
 };
 
@@ -111,7 +123,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int k_iters = args.K / kBK;
 
     // per-channel epilogue parameters: global -> shared once per CTA
-    for (int i = threadIdx.x; i < args.N; i += kThreads) {
+    for (int i = threadIdx.x; i < args.N && MODE != kDgrad && MODE != kWgrad; i += kThreads) {
         s_par[i] = __ldg(args.bias + i);
         if (MODE == kConv) {
             s_par[kMaxN + i] = __ldg(args.bn_scale + i);
@@ -306,20 +318,77 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tmem_ld_wait();
                     const float* bp = s_bias + n0 + c * 32;
                     float x[32];
+                    if (MODE == kDgrad || MODE == kWgrad) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) x[i] = fmaxf(__uint_as_float(r[i]) + bp[i], 0.f);
+                        for (int i = 0; i < 32; ++i) x[i] = __uint_as_float(r[i]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) x[i] = fmaxf(__uint_as_float(r[i]) + bp[i], 0.f);
+                    }
+                    if (MODE == kTrainFwd && grow < args.M && args.scale != 1.f) {
+                        // Dropout(0.2) in training (utils.py:244-254): keep with probability keep_prob, scale by 1/keep_prob
+                        const size_t e0 = (size_t)grow * args.N + n0 + c * 32;
+                        if (args.mask) {
+                            const uint4* mp = reinterpret_cast<const uint4*>(args.mask + e0);
+#pragma unroll
+                            for (int v = 0; v < 2; ++v) {
+                                const uint4 mv = mp[v];
+                                const uint32_t w4[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    x[v * 16 + i] = ((w4[i >> 2] >> ((i & 3) * 8)) & 0xFFu) ? x[v * 16 + i] * args.scale : 0.f;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                // splitmix64 of (seed, element index) -> 24 uniform bits
+                                unsigned long long zz = args.seed + (unsigned long long)(e0 + i) * 0x9E3779B97F4A7C15ull;
+                                zz = (zz ^ (zz >> 30)) * 0xBF58476D1CE4E5B9ull;
+                                zz = (zz ^ (zz >> 27)) * 0x94D049BB133111EBull;
+                                zz ^= zz >> 31;
+                                const float u = (float)(unsigned int)(zz >> 40) * (1.f / 16777216.f);
+                                x[i] = u < args.keep_prob ? x[i] * args.scale : 0.f;
+                            }
+                        }
+                    }
+                    if (MODE == kDgrad && grow < args.M) {
+                        const uint4* gp = reinterpret_cast<const uint4*>(args.gate + (size_t)grow * args.N + n0 + c * 32);
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            const uint4 gv = gp[v];
+                            const uint32_t w4[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const uint32_t hb = (w4[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu;     // bf16 bits of the activation
+                                const bool pos = hb != 0u && (hb & 0x8000u) == 0u;               // > 0 (activations are >= 0)
+                                x[v * 8 + i] = pos ? x[v * 8 + i] * args.scale : 0.f;
+                            }
+                        }
+                    }
                     if (MODE == kScore) {
                         const float* wl = s_par + kMaxN + n0 + c * 32;
 #pragma unroll
                         for (int i = 0; i < 32; ++i) dot = fmaf(x[i], wl[i], dot);
                     } else if (grow < args.M) {
-                        uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
-                                                              n0 + c * 32);
+                        if (MODE != kWgrad && args.out) {
+                            uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
+                                                                  n0 + c * 32);
 #pragma unroll
-                        for (int v = 0; v < 4; ++v)
-                            dst[v] = make_uint4(pack_bf16(x[v * 8], x[v * 8 + 1]), pack_bf16(x[v * 8 + 2], x[v * 8 + 3]),
-                                                pack_bf16(x[v * 8 + 4], x[v * 8 + 5]), pack_bf16(x[v * 8 + 6], x[v * 8 + 7]));
-                        if (args.out_f32) {
+                            for (int v = 0; v < 4; ++v)
+                                dst[v] = make_uint4(pack_bf16(x[v * 8], x[v * 8 + 1]), pack_bf16(x[v * 8 + 2], x[v * 8 + 3]),
+                                                    pack_bf16(x[v * 8 + 4], x[v * 8 + 5]), pack_bf16(x[v * 8 + 6], x[v * 8 + 7]));
+                        }
+                        if ((MODE == kTrainFwd || MODE == kDgrad) && args.out_t) {
+                            // transposed copy for the weight-gradient GEMM: lanes = consecutive rows -> coalesced columns
+                            __nv_bfloat16* tp = args.out_t + (size_t)(n0 + c * 32) * args.ld_t + grow;
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) tp[(size_t)i * args.ld_t] = __float2bfloat16(x[i]);
+                        }
+                        if (MODE == kWgrad) {
+                            float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)grow * args.N + n0 + c * 32);
+#pragma unroll
+                            for (int v = 0; v < 8; ++v) df[v] = make_float4(x[v * 4], x[v * 4 + 1], x[v * 4 + 2], x[v * 4 + 3]);
+                        } else if (args.out_f32) {
                             float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)grow * args.N + n0 + c * 32);
 #pragma unroll
                             for (int v = 0; v < 8; ++v) {
@@ -384,7 +453,7 @@ template <int MT, int BN, int STAGES, int MODE, int OHT>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
     using C = Cfg<MT, BN, STAGES, MODE>;
-    if (a.N > kMaxN) return GN_E_SHAPE;
+    if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad) return GN_E_SHAPE;
     auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT>;
     static bool attr = false;
     if (!attr) {
@@ -498,4 +567,31 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
                                     m->f12_w, m->f12_b, d_scores, st);
     GN_STAGE_MARK(m, 6, st);
     return rc;
+}
+
+// Training GEMMs of the fusion MLP (gn_train.cu): C = A[M][K] . B[N][K]^T, bf16 operands, fp32 accumulation.
+//   mode 3 (forward)  : out = dropout(relu(C + bias)) as bf16 [M][N] and transposed [N][ld_t]
+//   mode 4 (dgrad)    : out = C * scale * [gate > 0]  as bf16 [M][N] and transposed [N][ld_t]
+//   mode 5 (wgrad)    : out_f32 [M][N] = C
+int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, int K, int64_t lda,
+                     const __nv_bfloat16* B, int N, int64_t ldb, const float* bias, __nv_bfloat16* out,
+                     __nv_bfloat16* out_t, int64_t ld_t, float* out_f32, const __nv_bfloat16* gate,
+                     const uint8_t* mask, float scale, float keep_prob, unsigned long long seed, cudaStream_t st) {
+    constexpr int BN = 128;
+    if (K % kBK || N % BN || M <= 0) return GN_E_SHAPE;
+    CUtensorMap ta, tb;
+    int rc = make_tmap_2d(h, &ta, A, M, K, lda, 128);
+    if (rc) return rc;
+    rc = make_tmap_2d(h, &tb, B, N, K, ldb, BN);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = N; a.col_off = 0; a.out_f32 = out_f32;
+    a.out_t = out_t; a.ld_t = ld_t; a.gate = gate; a.mask = mask; a.scale = scale; a.keep_prob = keep_prob; a.seed = seed;
+    const int64_t tiles = ((M + 127) / 128) * (N / BN);
+    switch (mode) {
+        case kTrainFwd: return launch<1, BN, 4, kTrainFwd, 0>(h, ta, tb, a, tiles, st);
+        case kDgrad: return launch<1, BN, 4, kDgrad, 0>(h, ta, tb, a, tiles, st);
+        case kWgrad: return launch<1, BN, 4, kWgrad, 0>(h, ta, tb, a, tiles, st);
+        default: return GN_E_ARG;
+    }
 }

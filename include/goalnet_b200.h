@@ -169,6 +169,50 @@ int gn_fscore_counts(gn_handle* h, const uint8_t* d_pred, const uint8_t* d_gd, i
                      int64_t* d_counts, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Fusion-network training step (BASELINE config 4) -- replaces, for `AVM.fusion`
+ * (utils.py:242-258), the reference's train step main.py:187-193:
+ *     optimizer.zero_grad(); pred = model(...); loss = nn.MSELoss()(pred, labels); loss.backward();
+ *     optimizer.step()          with optimizer = optim.Adam(params, lr = 0.001)  (main.py:70)
+ * on precomputed fusion inputs (audio128 | visual512 feature rows).  As written, MSELoss receives
+ * pred (N,1) and labels (N,) and broadcasts to N x N: loss = mean_ij (p_i - l_j)^2 (SURVEY quirk
+ * Q5); fixed_loss = 1 selects mean_i (p_i - l_i)^2.  Dropout(0.2) of utils.py:245-254 is applied
+ * when dropout_p > 0, with caller-supplied keep-masks (uint8 [n][width], widths 512,512,256,128)
+ * or, when d_masks is NULL, a counter-based generator keyed by `seed`.
+ * Parameters, gradients and Adam moments are flat float32 vectors in the reference's parameter
+ * order: fusion.0.weight [512][Fin], fusion.0.bias, fusion.3.*, fusion.6.*, fusion.9.*,
+ * fusion.12.weight [1][128], fusion.12.bias  (gn_fusion_param_count values).
+ * Data parallel: call gn_fusion_forward_backward on every rank, all-reduce (sum) d_grads over
+ * NCCL, then gn_fusion_adam_step with grad_scale = 1 / world_size.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct gn_fusion_trainer gn_fusion_trainer;
+typedef struct gn_fusion_state {
+    const float* weight[5];   /* DEVICE pointers: fusion.{0,3,6,9,12}.weight, PyTorch [out][in] layout */
+    const float* bias[5];     /* fusion.{0,3,6,9,12}.bias */
+} gn_fusion_state;
+
+/* fin = 640 (audio included) or 512; max_rows = largest batch a step will be called with. */
+int gn_fusion_trainer_create(gn_handle* h, gn_fusion_trainer** out, const gn_fusion_state* sd, int fin,
+                             int64_t max_rows, void* stream);
+int gn_fusion_trainer_destroy(gn_fusion_trainer* t);
+int64_t gn_fusion_param_count(const gn_fusion_trainer* t);
+/* torch.optim.Adam hyper-parameters; defaults lr 1e-3, betas (0.9, 0.999), eps 1e-8. */
+int gn_fusion_set_hyper(gn_fusion_trainer* t, float lr, float beta1, float beta2, float eps);
+/* Copy the float32 master parameters (flat, order above) to d_out. */
+int gn_fusion_get_params(gn_fusion_trainer* t, float* d_out, void* stream);
+/* d_features float32 [n][fin]; d_labels float32 [n]; d_grads float32 [param_count] (out);
+ * d_scores float32 [n] predictions in [1,5] (out, may be NULL); d_loss double[1] on the device (out,
+ * may be NULL); d_masks: NULL or 4 device pointers. */
+int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_features, const float* d_labels, int64_t n,
+                               int fixed_loss, float dropout_p, const uint8_t* const* d_masks,
+                               unsigned long long seed, float* d_grads, float* d_scores, double* d_loss,
+                               void* stream);
+int gn_fusion_adam_step(gn_fusion_trainer* t, const float* d_grads, float grad_scale, void* stream);
+/* forward_backward followed by adam_step(grad_scale = 1): the single-GPU train step. */
+int gn_fusion_train_step(gn_fusion_trainer* t, const float* d_features, const float* d_labels, int64_t n,
+                         int fixed_loss, float dropout_p, const uint8_t* const* d_masks, unsigned long long seed,
+                         float* d_grads, float* d_scores, double* d_loss, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Validation kernels (plain CUDA-core fp32 accumulate).  NOT a backend: tests use them to localise
  * a tensor-core kernel fault layer by layer on the GPU.  Same argument meaning as gn_avm_forward.
  * ------------------------------------------------------------------------------------------- */

@@ -209,6 +209,47 @@ def gen_audio(R):
     np.savez_compressed(os.path.join(GOLD, "audio.npz"), **out)
 
 
+def gen_train(R):
+    """The reference's train step (main.py:68-70,187-193) applied to AVM.fusion, run with the REFERENCE model object:
+    eval-mode forward (Dropout identity, so that the vectors are reproducible), nn.MSELoss as written (pred (N,1) vs
+    labels (N,): N x N broadcast, quirk Q5), optim.Adam(lr=0.001).  Features are what `fusion` receives."""
+    import torch
+    import warnings
+    out = {}
+    rng = np.random.default_rng(syn.SEED_BASE + 41)
+    for tag, audio_included, n in (("av", True, 96), ("v", False, 40)):
+        w = syn.make_weights(seed=0, audio_included=audio_included)
+        m = R.AVM(audio_included=audio_included)
+        m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in w.items()})
+        m.eval()
+        fin = 640 if audio_included else 512
+        x = np.abs(rng.standard_normal((n, fin))).astype(np.float32)      # fusion inputs are post-ReLU features
+        lab = rng.integers(1, 6, n).astype(np.float32)
+        opt = torch.optim.Adam(params=m.fusion.parameters(), lr=0.001)
+        crit = torch.nn.MSELoss()
+        losses = []
+        for step in range(3):
+            opt.zero_grad()
+            pred = 4 * m.fusion(torch.from_numpy(x)) + 1                       # utils.py:269-270
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                loss = crit(pred, torch.from_numpy(lab))                       # main.py:191
+            loss.backward()
+            if step == 0:
+                g = np.concatenate([p.grad.numpy().ravel() for p in m.fusion.parameters()])
+                out[f"{tag}_grads_s97"] = g[::97].copy()                        # strided sample keeps the fixture small
+                out[f"{tag}_grads_l2"] = np.array([np.sqrt(np.sum(np.square(p.grad.numpy().astype(np.float64))))
+                                                   for p in m.fusion.parameters()])
+                out[f"{tag}_pred"] = pred.detach().numpy()[:, 0].copy()
+            opt.step()
+            losses.append(float(loss.item()))
+        out[f"{tag}_x"] = x
+        out[f"{tag}_labels"] = lab
+        out[f"{tag}_losses"] = np.array(losses)
+        out[f"{tag}_params3_s97"] = np.concatenate([p.detach().numpy().ravel() for p in m.fusion.parameters()])[::97].copy()
+    np.savez_compressed(os.path.join(GOLD, "train.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     R = import_reference_utils()
@@ -217,6 +258,7 @@ def main():
     gen_integer_path(R)
     gen_postprocess(R)
     gen_audio(R)
+    gen_train(R)
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

@@ -425,3 +425,57 @@ def score_and_summarize(sd, frames_u8, y, sr, skip_frames, full_n_frames, change
     sel, ind = postprocess_array(scores, skip_frames, full_n_frames, change_points)
     fs = get_fscore(gd, ind) if gd is not None else None
     return scores, sel, ind, fs
+
+
+# ------------------------------------------------------------------------------------------------
+# fusion-network training step (BASELINE config 4) -- restates main.py:68-70,187-193 for AVM.fusion
+# ------------------------------------------------------------------------------------------------
+FUSION_KEYS = ["fusion.0", "fusion.3", "fusion.6", "fusion.9", "fusion.12"]
+
+
+def fusion_flat(sd: dict) -> np.ndarray:
+    """Parameters of AVM.fusion as one float32 vector in `model.fusion.parameters()` order (utils.py:242-258)."""
+    parts = []
+    for k in FUSION_KEYS:
+        parts.append(np.asarray(sd[k + ".weight"], np.float32).ravel())
+        parts.append(np.asarray(sd[k + ".bias"], np.float32).ravel())
+    return np.concatenate(parts)
+
+
+def fusion_train_steps(sd: dict, features, labels, steps: int = 1, fixed_loss: bool = False, masks=None,
+                       dropout_p: float = 0.2, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+    """`steps` iterations of  optimizer.zero_grad(); pred = fusion(x); loss = MSELoss()(pred, labels);
+    loss.backward(); optimizer.step()  (main.py:187-193) with optim.Adam(lr) (main.py:70) in float32 on the CPU.
+    As written pred is (N,1) and labels (N,), so MSELoss broadcasts to N x N (quirk Q5); fixed_loss
+    compares element-wise.  Dropout(0.2) (utils.py:245-254): `masks` = per step a list of four uint8
+    keep-masks applied as x * mask / (1 - p); None = dropout off (eval-mode forward).
+    Returns (losses [steps], grads of the FIRST step (flat), predictions of the first step, final flat params)."""
+    import torch
+    import warnings
+    ws = [torch.tensor(np.asarray(sd[k + ".weight"], np.float32), requires_grad=True) for k in FUSION_KEYS]
+    bs = [torch.tensor(np.asarray(sd[k + ".bias"], np.float32), requires_grad=True) for k in FUSION_KEYS]
+    params = [p for pair in zip(ws, bs) for p in pair]
+    opt = torch.optim.Adam(params, lr=lr, betas=betas, eps=eps)
+    crit = torch.nn.MSELoss()
+    x0 = torch.as_tensor(np.asarray(features, np.float32))
+    lab = torch.as_tensor(np.asarray(labels, np.float32))
+    losses, grads0, pred0 = [], None, None
+    for s in range(steps):
+        opt.zero_grad()
+        h = x0
+        for k in range(4):
+            h = torch.relu(h @ ws[k].T + bs[k])
+            if masks is not None:
+                h = h * torch.as_tensor(np.asarray(masks[s][k], np.float32)) / (1.0 - dropout_p)
+        pred = 4 * torch.sigmoid(h @ ws[4].T + bs[4]) + 1            # (N,1), utils.py:256,270
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")                          # the reference's broadcasting UserWarning
+            loss = crit(pred, lab) if not fixed_loss else crit(pred[:, 0], lab)
+        loss.backward()
+        if s == 0:
+            grads0 = np.concatenate([p.grad.detach().numpy().ravel() for p in params])
+            pred0 = pred.detach().numpy()[:, 0].copy()
+        opt.step()
+        losses.append(float(loss.item()))
+    flat = np.concatenate([p.detach().numpy().ravel() for p in params])
+    return np.array(losses), grads0, pred0, flat

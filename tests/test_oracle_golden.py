@@ -104,3 +104,20 @@ def test_cubic_resample_is_linear_operator(golden):
         m = O.mfcc(y[s:e], sr).astype(np.float64)
         W = O.cubic_resample_matrix(m.shape[1], B)
         np.testing.assert_allclose(m @ W.T, g["int_features"][i], rtol=1e-10, atol=1e-9)
+
+
+def test_fusion_train_step_matches_reference(golden):
+    """oracle fusion_train_steps vs the reference's AVM + MSELoss (as written, N x N broadcast) + Adam (gen_train)."""
+    g = golden("train")
+    for tag, ai in (("av", True), ("v", False)):
+        w = syn.make_weights(seed=0, audio_included=ai)
+        losses, grads, pred, flat = O.fusion_train_steps(w, g[f"{tag}_x"], g[f"{tag}_labels"], steps=3)
+        assert np.allclose(losses, g[f"{tag}_losses"], rtol=1e-6)
+        assert np.abs(pred - g[f"{tag}_pred"]).max() <= 1e-6
+        assert np.abs(grads[::97] - g[f"{tag}_grads_s97"]).max() <= 1e-7
+        assert np.abs(flat[::97] - g[f"{tag}_params3_s97"]).max() <= 5e-6
+    # the as-written loss equals the closed form mean p^2 - 2 mean p mean l + mean l^2
+    w = syn.make_weights(seed=0, audio_included=True)
+    losses, _, pred, _ = O.fusion_train_steps(w, g["av_x"], g["av_labels"], steps=1)
+    lab = g["av_labels"]
+    assert abs(losses[0] - (np.mean(pred ** 2) - 2 * pred.mean() * lab.mean() + np.mean(lab ** 2))) <= 1e-5
