@@ -65,3 +65,55 @@ def test_two_gpu_sharded_paths_match_single_gpu(tmp_path):
     mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
     for r in range(2):
         assert np.load(tmp_path / f"ok_{r}.npy").all(), r
+
+
+def _train_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import synthetic as syn, utils as U
+    from cvml_goalnet_b200.train import FusionTrainer
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        n = 256                                     # rows per rank
+        rng = np.random.default_rng(55)
+        x = np.abs(rng.standard_normal((world * n, 640))).astype(np.float32)
+        lab = rng.integers(1, 6, world * n).astype(np.float32)
+        model = U.AVM(True)
+        model.load_state_dict(syn.make_weights(seed=0))
+        # data parallel: each rank its own shard, NCCL all-reduce of the flat gradient, identical Adam step
+        dp = FusionTrainer(model, max_rows=n, fixed_loss=True, dropout_p=0.0, device=dev)
+        for _ in range(3):
+            dp.step(x[rank * n:(rank + 1) * n], lab[rank * n:(rank + 1) * n])
+        p_dp = dp.flat_params()
+        # every rank holds the same parameters afterwards
+        gathered = [torch.empty_like(p_dp) for _ in range(world)]
+        dist.all_gather(gathered, p_dp)
+        same = all(torch.equal(gathered[0], g) for g in gathered)
+        # with the element-wise loss and equal shards, the averaged gradient is the full-batch gradient
+        full = FusionTrainer(model, max_rows=world * n, fixed_loss=True, dropout_p=0.0, device=dev, process_group=False)
+        full.forward_backward(x, lab)
+        g_full = full.grads.clone()
+        dp2 = FusionTrainer(model, max_rows=n, fixed_loss=True, dropout_p=0.0, device=dev)
+        dp2.forward_backward(x[rank * n:(rank + 1) * n], lab[rank * n:(rank + 1) * n])
+        g = dp2.grads.clone()
+        dist.all_reduce(g)
+        g /= world
+        rel = float((g - g_full).norm() / g_full.norm())
+        np.save(os.path.join(out_dir, f"train_{rank}.npy"), np.array([float(same), rel]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_data_parallel_fusion_training(tmp_path):
+    """BASELINE config 4 at world size 2: flat-gradient all-reduce + identical Adam step on every rank."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    import torch.multiprocessing as mp
+    mp.spawn(_train_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        same, rel = np.load(tmp_path / f"train_{r}.npy")
+        assert same == 1.0, r
+        assert rel <= 2e-2, rel          # bf16 rounding of per-shard terms vs the full batch
