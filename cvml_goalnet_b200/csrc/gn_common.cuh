@@ -74,9 +74,12 @@ struct gn_ws {
     __nv_bfloat16* h1;    // [n][512]
     __nv_bfloat16* h2;    // [n][512]
     __nv_bfloat16* h3;    // [n][256]
+    float* part;          // [splits][n][512] fp32 partial sums of a K-split linear5 (null when splits == 1)
     int64_t bytes;
 };
 gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
+int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, int C, cudaStream_t st);   // gn_tc_gemm.cu
+int gn_linear5_splits(const gn_model* m, int64_t n);   // K ranges linear5 is split into for n frames (gn_tc_gemm.cu)
 
 // ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);

@@ -98,6 +98,80 @@ visbl_block1_kernel(const float* __restrict__ vis, int64_t n, const float* __res
     }
 }
 
+// VisBl block 1 for frames of any size S (e.g. 224: conv1 -> 76x76, pool -> 74x74).  One CTA visit = one 16x16 tile of
+// conv1 outputs (tiles overlap by the pooling halo -> 14x14 pooled pixels); a warp computes one conv pixel for all 64
+// channels (2 per lane, weights in registers), its 27 taps fetched by lanes 0..26 and broadcast by shuffles.  This
+// block is 0.1 % of the model's FLOPs at 224x224; the zero border of a1p is written by gn_launch_zero_border.
+constexpr int kT1 = 16, kT1P = kT1 - 2;
+
+__global__ void __launch_bounds__(kVThreads, 2)
+visbl_block1_tiled_kernel(const float* __restrict__ vis, int64_t n, int S, int C1, int tiles,
+                          const float* __restrict__ w /*[27][64]*/, const float* __restrict__ b,
+                          const float* __restrict__ sc, const float* __restrict__ sh, __nv_bfloat16* __restrict__ a1p) {
+    extern __shared__ __align__(16) float sm[];                 // [256][64] conv + ReLU
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float w0[27], w1[27];                                       // k = ci*9 + ky*3 + kx
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const float2 wv = *reinterpret_cast<const float2*>(w + (tap * 3 + ci) * 64 + 2 * lane);
+            w0[ci * 9 + tap] = wv.x;
+            w1[ci * 9 + tap] = wv.y;
+        }
+    const float2 bias = *reinterpret_cast<const float2*>(b + 2 * lane);
+    const float2 scale = *reinterpret_cast<const float2*>(sc + 2 * lane);
+    const float2 shift = *reinterpret_cast<const float2*>(sh + 2 * lane);
+    const int kci = lane / 9, ktap = lane - kci * 9, kky = ktap / 3, kkx = ktap - kky * 3;   // this lane's tap (lane < 27)
+    const int P1 = C1 - 2;
+    const int64_t units = n * tiles * tiles;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+        const int64_t f = u / (tiles * tiles);
+        const int t = (int)(u - f * tiles * tiles);
+        const int ty = t / tiles, tx = t - ty * tiles;
+        const float* src = vis + f * 3 * (int64_t)S * S;
+        __syncthreads();
+        for (int p = warp; p < kT1 * kT1; p += kVThreads / 32) {
+            const int cy = ty * kT1P + p / kT1, cx = tx * kT1P + p % kT1;
+            float2 r = make_float2(0.f, 0.f);
+            if (cy < C1 && cx < C1) {
+                const int iy = 3 * cy - 3 + kky, ix = 3 * cx - 3 + kkx;
+                float v = 0.f;
+                if (lane < 27 && iy >= 0 && iy < S && ix >= 0 && ix < S) v = __ldg(src + ((int64_t)kci * S + iy) * S + ix);
+                float a0 = bias.x, a1 = bias.y;
+#pragma unroll
+                for (int k = 0; k < 27; ++k) {
+                    const float x = __shfl_sync(0xffffffffu, v, k);
+                    a0 = fmaf(x, w0[k], a0);
+                    a1 = fmaf(x, w1[k], a1);
+                }
+                r = make_float2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+            }
+            *reinterpret_cast<float2*>(sm + p * 64 + 2 * lane) = r;
+        }
+        __syncthreads();
+        uint32_t* o = reinterpret_cast<uint32_t*>(a1p + f * (int64_t)C1 * C1 * 64);
+        for (int p = warp; p < kT1P * kT1P; p += kVThreads / 32) {
+            const int oy = p / kT1P, ox = p - oy * kT1P;
+            const int gy = ty * kT1P + oy, gx = tx * kT1P + ox;
+            if (gy >= P1 || gx >= P1) continue;
+            const float* base = sm + (oy * kT1 + ox) * 64 + 2 * lane;
+            float2 m = *reinterpret_cast<const float2*>(base);
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 3; ++dx) {
+                    if (dy == 0 && dx == 0) continue;
+                    const float2 q = *reinterpret_cast<const float2*>(base + (dy * kT1 + dx) * 64);
+                    m.x = fmaxf(m.x, q.x);
+                    m.y = fmaxf(m.y, q.y);
+                }
+            const __nv_bfloat162 h = __floats2bfloat162_rn(fmaf(m.x, scale.x, shift.x), fmaf(m.y, scale.y, shift.y));
+            o[((int64_t)(gy + 1) * C1 + gx + 1) * 32 + lane] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+    }
+}
+
 constexpr int kAThreads = 256;
 constexpr int kAFrames = 4;    // frames per CTA pass: every weight fetched from L1/L2 is used 4 times
 
@@ -231,7 +305,22 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
 }  // namespace
 
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
-    if (m->S != kS || m->C1 != kC1) return GN_E_SHAPE;
+    if (m->S != kS || m->C1 != kC1) {
+        static bool attr_t = false;
+        const size_t smem_t = sizeof(float) * kT1 * kT1 * 64;
+        if (!attr_t) {
+            GN_CUDA(cudaFuncSetAttribute(visbl_block1_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
+            attr_t = true;
+        }
+        const int P1 = m->C1 - 2, tiles = (P1 + kT1P - 1) / kT1P;
+        int rc = gn_launch_zero_border(m->h, ws.a1p, n, m->C1, 64, st);
+        if (rc) return rc;
+        const int64_t units = n * tiles * tiles, cap_t = (int64_t)m->h->num_sms * 2;
+        visbl_block1_tiled_kernel<<<(int)(units < cap_t ? units : cap_t), kVThreads, smem_t, st>>>(
+            d_visual, n, m->S, m->C1, tiles, m->conv1_w, m->conv1_b, m->bn_scale[0], m->bn_shift[0], ws.a1p);
+        GN_LAUNCHED(m->h);
+        return GN_OK;
+    }
     const size_t smem = sizeof(float) * (size_t)(kC1 * kC1 * (kPatch + 64)) + sizeof(unsigned short) * 3 * kS * kS;
     static bool attr = false;
     if (!attr) {

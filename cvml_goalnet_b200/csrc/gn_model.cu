@@ -181,7 +181,7 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
                                void* stream) {
     if (!h || !out || !sd) return GN_E_ARG;
     *out = nullptr;
-    if (S != 40) return GN_E_SHAPE;   // the tensor-core tiles are laid out for the reference's 40x40 frames
+    if (S < 16 || S > 1024) return GN_E_SHAPE;   // 40 = the reference (utils.py:285); others run the tiled conv path
     const int C1 = conv_out(S, 3, 3, 3), P1 = C1 - 2, P2 = P1 - 2, P3 = P2 - 2;
     const int L1 = conv_out(B, 3, 2, 1), L2 = conv_out(L1, 3, 2, 1);
     if (audio_included && (B < 4 || L2 != 8 || B > 32)) return GN_E_SHAPE;   // tensor-core AudBl tiles: 16 frames x 8 positions
@@ -316,6 +316,8 @@ gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base) {
     w.h1 = take(nn * 512);
     w.h2 = take(nn * 512);
     w.h3 = take(nn * 256);
+    const int splits = gn_linear5_splits(m, (int64_t)nn);
+    w.part = splits > 1 ? reinterpret_cast<float*>(take((size_t)splits * nn * 512 * 2)) : nullptr;
     w.bytes = (int64_t)((off + 1023) & ~size_t(1023));
     return w;
 }
@@ -472,6 +474,7 @@ __global__ void read_act_flat(const __nv_bfloat16* __restrict__ in, int64_t tota
 int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
                             cudaStream_t st) {
     if (n > 65535 * 16) return GN_E_SHAPE;
+    if (m->P1 * m->P1 * 64 * 4 > 64 * 1024) return GN_E_SHAPE;   // validation path: one frame's conv tile in shared memory
     static bool attr = false;
     if (!attr) {
         GN_CUDA(cudaFuncSetAttribute(simt_conv_block, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));

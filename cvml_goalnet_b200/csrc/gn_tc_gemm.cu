@@ -31,7 +31,8 @@ enum Mode { kConv = 0, kLinear = 1, kScore = 2,
             // training GEMMs of the fusion MLP (gn_train.cu): all are C = A . B^T with K-major bf16 operands
             kTrainFwd = 3,   // relu(acc + bias), dropout, bf16 out [M][N] and its transpose [N][ld_t]
             kDgrad = 4,      // acc * scale * [gate > 0], bf16 out [M][N] and its transpose
-            kWgrad = 5 };    // fp32 out [M][N] = acc
+            kWgrad = 5,      // fp32 out [M][N] = acc
+            kSplitK = 6 };   // fp32 partial sums out_f32[split][M][N] of one K range (bias/ReLU in splitk_reduce_kernel)
 
 struct ConvGeom {
     int OH, OW;        // conv output == input interior (k3 s1 p1)
@@ -39,6 +40,8 @@ struct ConvGeom {
     int out_pad;       // 1: write into a (P+2)x(P+2) zero-bordered buffer; 0: dense PxP
     int cin_blocks;    // Cin / 64
     int cout;          // total output channels
+    int tiles;         // spatial tiles per frame side (1: the tile is the frame)
+    int pfull;         // pooled size of the whole frame (== P when tiles == 1)
 };
 
 struct GemmArgs {
@@ -63,6 +66,8 @@ struct GemmArgs {
     float scale;             // dropout scale 1/(1-p) (1 = no dropout)
     float keep_prob;         // kTrainFwd without mask: P(keep); >= 1 disables dropout
     unsigned long long seed;
+    int k_splits;            // kSplitK: number of K ranges (1 otherwise)
+    int64_t split_stride;    // kSplitK: elements between the partial-sum slabs (M * N)
     ConvGeom g;
 };
 
@@ -118,12 +123,23 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int lane = threadIdx.x & 31;
 
     const int n_blocks = args.N / BN;
-    const int64_t m_blocks = (MODE == kConv) ? args.M : (args.M + 127) / 128;
-    const int64_t num_tiles = m_blocks * n_blocks;
-    const int k_iters = args.K / kBK;
+    const int tiles_pf = (MODE == kConv) ? args.g.tiles * args.g.tiles : 1;      // spatial tiles per frame
+    const int64_t m_blocks = (MODE == kConv) ? args.M * tiles_pf : (args.M + 127) / 128;
+    const int k_splits = (MODE == kSplitK) ? args.k_splits : 1;
+    const int64_t num_tiles = m_blocks * n_blocks * k_splits;
+    const int k_total = args.K / kBK;
+    const int k_per = (k_total + k_splits - 1) / k_splits;
+    // tile -> (m_blk, n_blk, split): split fastest, then n_blk, so that CTAs running side by side share A and W in L2
+#define GN_TILE_DECODE()                                                                  \
+    const int64_t mn_ = tile / k_splits;                                                  \
+    const int ks = (int)(tile - mn_ * k_splits);                                          \
+    const int64_t m_blk = mn_ / n_blocks;                                                 \
+    const int n_blk = (int)(mn_ - m_blk * n_blocks);                                      \
+    const int k_begin = ks * k_per;                                                       \
+    const int k_iters = (k_total - k_begin) < k_per ? (k_total - k_begin) : k_per;
 
     // per-channel epilogue parameters: global -> shared once per CTA
-    for (int i = threadIdx.x; i < args.N && MODE != kDgrad && MODE != kWgrad; i += kThreads) {
+    for (int i = threadIdx.x; i < args.N && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK; i += kThreads) {
         s_par[i] = __ldg(args.bias + i);
         if (MODE == kConv) {
             s_par[kMaxN + i] = __ldg(args.bn_scale + i);
@@ -157,9 +173,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             int stage = 0;
             uint32_t phase = 0;
             for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int64_t m_blk = tile / n_blocks;
-                const int n_blk = (int)(tile - m_blk * n_blocks);
-                for (int kt = 0; kt < k_iters; ++kt) {
+                GN_TILE_DECODE();
+                int frame = (int)m_blk, tx0 = 0, ty0 = 0;
+                if (MODE == kConv && tiles_pf > 1) {
+                    frame = (int)(m_blk / tiles_pf);
+                    const int t = (int)(m_blk - (int64_t)frame * tiles_pf);
+                    const int ty = t / args.g.tiles;
+                    ty0 = ty * (OHT - 2);
+                    tx0 = (t - ty * args.g.tiles) * (OHT - 2);
+                }
+                for (int kt = k_begin; kt < k_begin + k_iters; ++kt) {
                     mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
                     const uint32_t fb = smem_u32(&full_bar[stage]);
                     const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
@@ -170,7 +193,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         const int ky = tap / 3, kx = tap - ky * 3;
                         mbar_expect_tx(fb, (uint32_t)(OHT * OHT * 128 + C::kBBytes));
                         // box (64 ch, OW, OH, 1 frame) of the zero-bordered NHWC input, shifted by the tap
-                        tma_load_4d(sa, &tmap_a, fb, cb * kBK, kx, ky, (int)m_blk);
+                        // (boxes of edge tiles that reach past the frame are zero-filled; those pixels are never pooled)
+                        tma_load_4d(sa, &tmap_a, fb, cb * kBK, tx0 + kx, ty0 + ky, frame);
                     } else {
                         mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
                         if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
@@ -189,6 +213,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         int ab = 0;
         uint32_t aphase = 0;
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            GN_TILE_DECODE();
+            (void)m_blk; (void)n_blk;
             mbar_wait(smem_u32(&tempty_bar[ab]), aphase ^ 1);     // epilogue drained this buffer
             tc_fence_after();
             for (int kt = 0; kt < k_iters; ++kt) {
@@ -225,8 +251,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         int ab = 0;
         uint32_t aphase = 0;
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int64_t m_blk = tile / n_blocks;
-            const int n_blk = (int)(tile - m_blk * n_blocks);
+            GN_TILE_DECODE();
+            (void)k_iters;
             const int n0 = n_blk * BN;
             mbar_wait(smem_u32(&tfull_bar[ab]), aphase);
             tc_fence_after();
@@ -267,11 +293,22 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // item = (pooled pixel, group of 8 channels): 9 x 16-byte shared loads, one 16-byte global store
                 constexpr int P = OHT - 2;
                 constexpr int CG = BN / 8;
-                const int PW = P + 2 * args.g.out_pad;
-                __nv_bfloat16* obase = args.out + (size_t)m_blk * PW * PW * args.g.cout + n0;
+                const int PW = args.g.pfull + 2 * args.g.out_pad;
+                int64_t frame = m_blk;
+                int gy0 = 0, gx0 = 0;                 // pooled coordinates of this tile's first output
+                if (tiles_pf > 1) {
+                    frame = m_blk / tiles_pf;
+                    const int t = (int)(m_blk - frame * tiles_pf);
+                    const int ty = t / args.g.tiles;
+                    gy0 = ty * P;
+                    gx0 = (t - ty * args.g.tiles) * P;
+                }
+                const int vy = min(P, args.g.pfull - gy0), vx = min(P, args.g.pfull - gx0);   // valid outputs of an edge tile
+                __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + n0;
                 for (int item = et; item < P * P * CG; item += kEpiThreads) {
                     const int op = item / CG, cg = item - op * CG;
                     const int oy = op / P, ox = op - oy * P;
+                    if (oy >= vy || ox >= vx) continue;
                     const unsigned char* s0 = stg + (size_t)(oy * OHT + ox) * C::kStgStride + cg * 16;
                     uint4 m = *reinterpret_cast<const uint4*>(s0);
 #pragma unroll
@@ -289,10 +326,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                                pack_bf16(fmaf(f1.x, sc0.z, sh0.z), fmaf(f1.y, sc0.w, sh0.w)),
                                                pack_bf16(fmaf(f2.x, sc1.x, sh1.x), fmaf(f2.y, sc1.y, sh1.y)),
                                                pack_bf16(fmaf(f3.x, sc1.z, sh1.z), fmaf(f3.y, sc1.w, sh1.w)));
-                    const int opix = (oy + args.g.out_pad) * PW + ox + args.g.out_pad;
+                    const int opix = (gy0 + oy + args.g.out_pad) * PW + gx0 + ox + args.g.out_pad;
                     *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
                 }
-                if (args.g.out_pad) {   // zero border of the next conv's input (padding = 1)
+                if (args.g.out_pad && tiles_pf == 1) {   // zero border of the next conv's input (padding = 1);
+                                                         // tiled frames: zero_border_kernel does it
                     const int nborder = 4 * PW - 4;
                     for (int item = et; item < nborder * CG; item += kEpiThreads) {
                         const int bi = item / CG, cg = item - bi * CG;
@@ -318,7 +356,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tmem_ld_wait();
                     const float* bp = s_bias + n0 + c * 32;
                     float x[32];
-                    if (MODE == kDgrad || MODE == kWgrad) {
+                    if (MODE == kDgrad || MODE == kWgrad || MODE == kSplitK) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) x[i] = __uint_as_float(r[i]);
                     } else {
@@ -370,7 +408,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                         for (int i = 0; i < 32; ++i) dot = fmaf(x[i], wl[i], dot);
                     } else if (grow < args.M) {
-                        if (MODE != kWgrad && args.out) {
+                        if (MODE != kWgrad && MODE != kSplitK && args.out) {
                             uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
                                                                   n0 + c * 32);
 #pragma unroll
@@ -384,8 +422,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                             for (int i = 0; i < 32; ++i) tp[(size_t)i * args.ld_t] = __float2bfloat16(x[i]);
                         }
-                        if (MODE == kWgrad) {
-                            float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)grow * args.N + n0 + c * 32);
+                        if (MODE == kWgrad || MODE == kSplitK) {
+                            float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)ks * args.split_stride +
+                                                                   (size_t)grow * args.N + n0 + c * 32);
 #pragma unroll
                             for (int v = 0; v < 8; ++v) df[v] = make_float4(x[v * 4], x[v * 4 + 1], x[v * 4 + 2], x[v * 4 + 3]);
                         } else if (args.out_f32) {
@@ -453,7 +492,7 @@ template <int MT, int BN, int STAGES, int MODE, int OHT>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
     using C = Cfg<MT, BN, STAGES, MODE>;
-    if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad) return GN_E_SHAPE;
+    if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK) return GN_E_SHAPE;
     auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT>;
     static bool attr = false;
     if (!attr) {
@@ -484,8 +523,105 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __n
     a.M = n; a.N = Cout; a.K = 9 * Cin;
     a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
     a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
+    a.g.tiles = 1; a.g.pfull = OH - 2;
     if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
     return launch<MT, BN, STAGES, kConv, OH>(m->h, ta, tb, a, n * (Cout / BN), st);
+}
+
+// zero the one-pixel border of [n][PW][PW][C] bf16 (the padding the next conv reads); 16 bytes per thread
+__global__ void __launch_bounds__(256)
+zero_border_kernel(__nv_bfloat16* __restrict__ buf, int64_t n, int PW, int C) {
+    const int cg = C / 8, nb = 4 * PW - 4;
+    const int64_t total = n * nb * cg;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t f = i / ((int64_t)nb * cg);
+        const int r = (int)(i - f * nb * cg);
+        const int bi = r / cg, g = r - bi * cg;
+        int by, bx;
+        if (bi < PW) { by = 0; bx = bi; }
+        else if (bi < 2 * PW) { by = PW - 1; bx = bi - PW; }
+        else { const int t = bi - 2 * PW; by = 1 + (t >> 1); bx = (t & 1) ? PW - 1 : 0; }
+        *reinterpret_cast<uint4*>(buf + ((f * PW + by) * PW + bx) * C + g * 8) = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+// conv block on frames of any size: 16x16 conv-output tiles (two 128-row MMA tiles x 128 channels) that overlap by
+// the pooling halo, so each tile yields 14x14 pooled pixels.  in = zero-bordered NHWC [n][OHF+2][OHF+2][Cin].
+constexpr int kTileOH = 16;
+int run_conv_tiled(gn_model* m, int64_t n, const __nv_bfloat16* in, int OHF, int Cin, const __nv_bfloat16* wk, int Cout,
+                   const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad,
+                   cudaStream_t st) {
+    constexpr int BN = 128;
+    CUtensorMap ta, tb;
+    const int IW = OHF + 2, PF = OHF - 2, TP = kTileOH - 2;
+    if (PF < 1 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)IW, (uint64_t)IW, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)IW * Cin * 2, (uint64_t)IW * IW * Cin * 2};
+    const uint32_t box[4] = {(uint32_t)kBK, (uint32_t)kTileOH, (uint32_t)kTileOH, 1};
+    int rc = make_tmap(m->h, &ta, in, 4, dims, str, box);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, Cout, 9 * Cin, 9 * Cin, BN);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = n; a.N = Cout; a.K = 9 * Cin;
+    a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
+    a.g.OH = kTileOH; a.g.OW = kTileOH; a.g.P = TP; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
+    a.g.tiles = (PF + TP - 1) / TP; a.g.pfull = PF;
+    if (n * a.g.tiles * a.g.tiles > (1LL << 40)) return GN_E_RANGE;
+    if (out_pad) {
+        rc = gn_launch_zero_border(m->h, out, n, PF + 2, Cout, st);
+        if (rc) return rc;
+    }
+    return launch<2, BN, 3, kConv, kTileOH>(m->h, ta, tb, a, n * a.g.tiles * a.g.tiles * (Cout / BN), st);
+}
+
+// out[r][col_off + j] = bf16(relu(sum_s part[s][r][j] + bias[j])) (+ fp32 copy of the rounded value); 4 columns / thread
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int N, const float* __restrict__ bias,
+                     __nv_bfloat16* __restrict__ out, int ld_out, int col_off, float* __restrict__ out_f32) {
+    const int64_t total = M * N / 4;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = (i * 4) / N;
+        const int j = (int)(i * 4 - r * N);
+        float4 acc = *reinterpret_cast<const float4*>(bias + j);
+        for (int s = 0; s < splits; ++s) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(part + (size_t)s * M * N) + i);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(fmaxf(acc.x, 0.f), fmaxf(acc.y, 0.f));
+        const __nv_bfloat162 hi = __floats2bfloat162_rn(fmaxf(acc.z, 0.f), fmaxf(acc.w, 0.f));
+        uint2 pk;
+        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(out + r * ld_out + col_off + j) = pk;
+        if (out_f32)
+            *reinterpret_cast<float4*>(out_f32 + r * N + j) =
+                make_float4(__bfloat162float(lo.x), __bfloat162float(lo.y), __bfloat162float(hi.x), __bfloat162float(hi.y));
+    }
+}
+
+// relu(A . W^T + b) with the reduction split into `splits` K ranges, one (tile, range) unit per CTA visit: used when
+// the (M/128) x (N/256) tiles alone would leave SMs idle (few frames, or linear5 at large frame sizes where
+// K = 512 * P3^2 is in the millions).  Deterministic: partial sums go to fp32 slabs, then one reduction pass.
+int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K, const __nv_bfloat16* wk, int N,
+                      const float* bias, int splits, float* part, __nv_bfloat16* out, int ld_out, int col_off,
+                      float* out_f32, cudaStream_t st) {
+    constexpr int BN = 256;
+    if (K % kBK || N % BN || K > (1LL << 31) - 64 || splits < 1 || !part) return GN_E_SHAPE;
+    CUtensorMap ta, tb;
+    int rc = make_tmap_2d(m->h, &ta, A, M, K, K, 128);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = M; a.N = N; a.K = (int)K; a.out_f32 = part; a.k_splits = splits; a.split_stride = M * N;
+    rc = launch<1, BN, 4, kSplitK, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN) * splits, st);
+    if (rc) return rc;
+    const int64_t blocks = (M * N / 4 + 255) / 256, cap = (int64_t)m->h->num_sms * 8;
+    splitk_reduce_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(part, splits, M, N, bias, out, ld_out,
+                                                                             col_off, out_f32);
+    GN_LAUNCHED(m->h);
+    return GN_OK;
 }
 
 template <int BN, int STAGES, int MODE>
@@ -505,6 +641,27 @@ int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, c
 }
 
 }  // namespace
+
+int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, int C, cudaStream_t st) {
+    const int64_t total = n * (4 * PW - 4) * (C / 8);
+    if (total <= 0) return GN_OK;
+    const int64_t cap = (int64_t)h->num_sms * 8, blocks = (total + 255) / 256;
+    zero_border_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(buf, n, PW, C);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}
+
+// K ranges for linear5 (N = 512 -> two 256-wide column tiles): 1 when the row tiles alone fill the GPU.
+int gn_linear5_splits(const gn_model* m, int64_t n) {
+    const int64_t tiles = ((n + 127) / 128) * 2;
+    const int64_t k_total = (int64_t)m->P3 * m->P3 * 512 / kBK;
+    if (tiles >= m->h->num_sms || k_total < 16) return 1;
+    int64_t s = m->h->num_sms / tiles;
+    if (s > k_total / 8) s = k_total / 8;          // at least 8 k-steps per range
+    if (s <= 1) return 1;
+    const int64_t k_per = (k_total + s - 1) / s;
+    return (int)((k_total + k_per - 1) / k_per);   // every range non-empty
+}
 
 // AudBl conv2 (64 -> 128, k3 s2 p1) and linear3 on the tensor cores (reference utils.py:219-225).
 // conv1's output ws.ac1 is (position, channel)-major with a zero row on each side, so the im2col row of
@@ -535,22 +692,37 @@ int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st)
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
                           cudaStream_t st) {
     int rc;
-    // block 2: conv2 (64 -> 256) on 13x13, pool -> 11x11, written with a zero border for conv3
-    if (m->P1 != 13 || m->P2 != 11) return GN_E_SHAPE;
-    rc = run_conv<2, 128, 3, 13>(m, n, ws.a1p, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
-                             ws.a2p, 1, st);
-    if (rc) return rc;
-    GN_STAGE_MARK(m, 3, st);
-    // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
-    rc = run_conv<1, 256, 3, 11>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
-                             ws.a3, 0, st);
+    if (m->P1 == 13 && m->P2 == 11) {
+        // the reference's 40x40 frames: one frame per tile
+        // block 2: conv2 (64 -> 256) on 13x13, pool -> 11x11, written with a zero border for conv3
+        rc = run_conv<2, 128, 3, 13>(m, n, ws.a1p, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
+                                     ws.a2p, 1, st);
+        if (rc) return rc;
+        GN_STAGE_MARK(m, 3, st);
+        // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
+        rc = run_conv<1, 256, 3, 11>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
+                                     ws.a3, 0, st);
+    } else {
+        // any other frame size (e.g. 224x224: conv2 on 74x74, conv3 on 72x72): overlapping 16x16 spatial tiles
+        rc = run_conv_tiled(m, n, ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
+                            ws.a2p, 1, st);
+        if (rc) return rc;
+        GN_STAGE_MARK(m, 3, st);
+        rc = run_conv_tiled(m, n, ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
+                            ws.a3, 0, st);
+    }
     if (rc) return rc;
     GN_STAGE_MARK(m, 4, st);
-    const int K5 = m->P3 * m->P3 * 512;
+    const int64_t K5 = (int64_t)m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     // linear5 + ReLU -> columns [aoff, aoff+512) of the fusion input (audio features occupy [0,128))
-    rc = run_linear<256, 4, kLinear>(m, n, ws.a3, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff,
-                                     d_visfeat, nullptr, nullptr, nullptr, st);
+    const int splits = gn_linear5_splits(m, n);
+    if (splits > 1)
+        rc = run_linear_splitk(m, n, ws.a3, K5, m->linear5_wk, 512, m->linear5_b, splits, ws.part, ws.h0, m->fin, aoff,
+                               d_visfeat, st);
+    else
+        rc = run_linear<256, 4, kLinear>(m, n, ws.a3, (int)K5, (int)K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin,
+                                         aoff, d_visfeat, nullptr, nullptr, nullptr, st);
     if (rc) return rc;
     GN_STAGE_MARK(m, 5, st);
     rc = run_linear<256, 4, kLinear>(m, n, ws.h0, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr,

@@ -352,7 +352,8 @@ class AVM(nn.Module):
         dev = _device(device)
         mptr = self._model(dev)
         ws, _ = self._ws(dev, mptr, n)
-        shapes = {1: (n, 64, 13, 13), 2: (n, 256, 11, 11), 3: (n, 512, 9, 9),
+        p1 = (self.S + 3) // 3 - 1          # conv1 k3 s3 p3 -> (S+3)//3 + 1, then MaxPool(3,1) per block
+        shapes = {1: (n, 64, p1, p1), 2: (n, 256, p1 - 2, p1 - 2), 3: (n, 512, p1 - 4, p1 - 4),
                   4: (n, 512 + (128 if self.audio_included else 0))}
         out = torch.empty(shapes[which], dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):

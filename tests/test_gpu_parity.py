@@ -165,6 +165,31 @@ def test_model_vs_oracle_and_simt(U, weights, n):
     assert np.abs(h0_tc[:, :128] - ra).max() <= 1e-2 * max(np.abs(ra).max(), 1e-3)   # bf16 store of fp32 AudBl
 
 
+@pytest.mark.parametrize("S,n", [(64, 5), (100, 3), (46, 130), (224, 2)])
+def test_model_other_frame_sizes_tiled_conv_and_splitk(U, S, n):
+    """Frame sizes other than the reference's 40 (R224 = BASELINE config 5; legal because every layer of the
+    reference AVM is Lazy*): overlapping 16x16 conv tiles, separate border pass, K-split linear5."""
+    w = syn.make_weights(seed=3, S=S)
+    vis = O.extract_condensed_frame_tensor_array(syn.make_frames(n, S + 9, S + 5, seed=S), S)
+    rng = np.random.default_rng(S)
+    aud = (25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)
+    m = U.AVM(True, S=S)
+    m.load_state_dict(w)
+    y = m(aud, vis, return_features=True).cpu().numpy()
+    vf = m.last_visual_features.cpu().numpy()
+    ref, feats = O.avm_forward(w, aud, vis, return_features=True)
+    for which, key in ((1, "vis1"), (2, "vis2"), (3, "vis3")):
+        act = m.read_activation(which, n).cpu().numpy()
+        r = feats[key].numpy()
+        assert act.shape == r.shape, key
+        assert np.abs(act - r).max() <= FEAT_TOL * np.abs(r).max(), key
+    rv = feats["visual_features"].numpy()
+    assert np.abs(vf - rv).max() <= FEAT_TOL * np.abs(rv).max()
+    assert np.abs(y - ref.numpy()).max() / np.abs(ref.numpy()).max() <= SCORE_RTOL
+    del m
+    torch.cuda.empty_cache()
+
+
 def test_model_empty_and_shape_errors(U, weights):
     m = _model(U, weights)
     assert m(np.zeros((0, 30, 30), np.float32), np.zeros((0, 3, 40, 40), np.float32)).shape == (0, 1)
