@@ -6,6 +6,7 @@
 // thread-block cluster (row bands; min/max exchanged through distributed shared memory).
 // preprocess_l2_kernel is the layout-agnostic version (unaligned rows / views): same arithmetic, taps
 // re-read through L2.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -156,16 +157,17 @@ preprocess_l2_kernel(const uint8_t* __restrict__ frames, int64_t n, int H, int W
 
 // ---------------------------------------------------------------------------------------------
 // tap-capturing version.  A host-built plan (one per (H, W, S), cached in the handle) lists, as 32-bit
-// words:  header[20] | ly0[S] ly1[S] fy[S] | cb0[S] cb1[S] fx[S] | rowslot[H] | srcword[nWc] | rank[CL][5]
+// words:  header[20] | ly0[S] ly1[S] fy[S] | cb0[S] cb1[S] fx[S] | rowslot[H] | rank[CL][5]
 //   ly0/ly1  compact index of the two source rows of output row y       rowslot  source row -> compact index or -1
-//   cb0/cb1  byte offset inside a compact row of the B byte of tap x     srcword  compact word -> source word of the row
-//   (a pixel's 3 bytes stay adjacent in a compact row: consecutive source words that hold taps stay consecutive)
+//   cb0/cb1  byte offset inside a source row of the B byte of the two tap pixels of output column x
 //   rank r   {ya, yb, sa, se, first}: output rows [ya,yb), streamed source rows [sa,se), first compact row
+// A compact tap row holds, per output column, the 6 bytes the resize needs (8-byte slots), so the resize pass reads
+// two conflict-free 8-byte words per pixel and looks the bytes up in a lane-private copy of the normalisation LUT.
 // ---------------------------------------------------------------------------------------------
 constexpr int kTapThreads = 512;
 constexpr int kTapWarps = kTapThreads / 32;
 enum { PP_S = 0, PP_H, PP_W, PP_CL, PP_NWC, PP_ROWSMAX, PP_LY0, PP_LY1, PP_FY, PP_CB0, PP_CB1, PP_FX, PP_K,
-       PP_ROWSLOT, PP_SRCWORD, PP_RANK, PP_TOTAL, PP_HEADER = 20 };
+       PP_ROWSLOT, PP_SRCWORD, PP_RANK, PP_TOTAL, PP_NSLOT, PP_SLOTB, PP_HEADER = 20 };
 
 __device__ __forceinline__ uint32_t pp_cluster_ctarank() {
     uint32_t r;
@@ -191,8 +193,7 @@ __device__ __forceinline__ void pp_cluster_barrier() {
 // The 16 consumer warps take each chunk from shared memory: byte min/max over all of it, then the words of
 // its tap rows are copied to the tap buffer (one warp per row).
 constexpr int kChunkBytes = 16 * 1024;
-constexpr int kChunkVec = kChunkBytes / 16;
-constexpr int kRing = 4;
+constexpr int kRingMax = 8;   // ring slots: as many as shared memory allows (bytes in flight per SM set the HBM rate)
 constexpr int kTapLaunchThreads = kTapThreads + 32;
 
 __device__ __forceinline__ void bar_consumers() { asm volatile("bar.sync 1, %0;" ::"n"(kTapThreads) : "memory"); }
@@ -217,14 +218,16 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
         "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 
+template <bool wide>   // wide: many output columns (S > 64): the resize pass is heavy and a chunk holds only a few rows
 __global__ void __launch_bounds__(kTapLaunchThreads, 2)
 preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32_t* __restrict__ plan,
                       float* __restrict__ out_nchw, __nv_bfloat16* __restrict__ out_nhwc) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint4* ring = reinterpret_cast<uint4*>(smem_raw);                  // [kRing][kChunkVec]
-    int32_t* sp = reinterpret_cast<int32_t*>(smem_raw + kRing * kChunkBytes);
+    const int kRing = plan[PP_NSLOT], slotB = plan[PP_SLOTB];
+    unsigned char* ring = smem_raw;                                    // [kRing][slotB]
+    int32_t* sp = reinterpret_cast<int32_t*>(smem_raw + kRing * slotB);
     __shared__ unsigned int red_min[kTapWarps], red_max[kTapWarps];
-    __shared__ __align__(8) uint64_t bars[2 * kRing + 1];              // full[kRing], empty[kRing], exchange
+    __shared__ __align__(8) uint64_t bars[2 * kRingMax + 1];           // full[kRing], empty[kRing], exchange
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = plan[PP_TOTAL];
     for (int i = tid; i < total; i += kTapLaunchThreads) sp[i] = plan[i];
@@ -240,7 +243,7 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
     }
     __syncthreads();
     if (CLk > 1) pp_cluster_barrier();                                 // peers' exchange barriers exist before anyone arrives
-    const int S = sp[PP_S], H = sp[PP_H], W = sp[PP_W], CL = sp[PP_CL], nWc = sp[PP_NWC], rowsMax = sp[PP_ROWSMAX];
+    const int S = sp[PP_S], H = sp[PP_H], W = sp[PP_W], CL = sp[PP_CL], rowsMax = sp[PP_ROWSMAX];
     const int* ly0 = sp + sp[PP_LY0];
     const int* ly1 = sp + sp[PP_LY1];
     const float* fy = reinterpret_cast<const float*>(sp + sp[PP_FY]);
@@ -248,12 +251,12 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
     const int* cb1 = sp + sp[PP_CB1];
     const float* fx = reinterpret_cast<const float*>(sp + sp[PP_FX]);
     const int* rowslot = sp + sp[PP_ROWSLOT];
-    const int* srcword = sp + sp[PP_SRCWORD];
     const int K = sp[PP_K];                                            // rows per chunk
     float* lut = reinterpret_cast<float*>(sp + total);                 // 256 normalised byte levels
     unsigned int* xch = reinterpret_cast<unsigned int*>(lut + 256);    // [2 parities][8 ranks][min, max]
-    uint32_t* tap = xch + 32;                                          // [rowsMax][nWc] captured words
-    const uint8_t* tapb = reinterpret_cast<const uint8_t*>(tap);
+    float* lutr = reinterpret_cast<float*>(xch + 32);                  // [256][32]: one copy of the LUT per lane = per bank
+    uint2* tap = reinterpret_cast<uint2*>(lutr + (wide ? 256 * 32 : 0));            // [rowsMax][S] captured taps: 6 bytes per output column
+                                                                       //   {B,G,R of column x0, B,G,R of column x1} of one tap row
 
     const int rank = CL > 1 ? (int)pp_cluster_ctarank() : 0;
     const int64_t cid = CL > 1 ? (int64_t)pp_cluster_id() : (int64_t)blockIdx.x;
@@ -278,7 +281,7 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
                     const int r0 = c * K;
                     const uint32_t bytes = (uint32_t)((nrows - r0 < K ? nrows - r0 : K) * RB);
                     tcx::mbar_expect_tx(bar0 + 8 * slot, bytes);
-                    bulk_g2s(ring_addr + slot * kChunkBytes, src + (int64_t)r0 * RB, bytes, bar0 + 8 * slot);
+                    bulk_g2s(ring_addr + slot * slotB, src + (int64_t)r0 * RB, bytes, bar0 + 8 * slot);
                     if (++slot == kRing) { slot = 0; phase ^= 1; }
                 }
             }
@@ -288,7 +291,7 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
 
     // ---------------- consumers ----------------
     // thread-constant starting point and step of the resize loop (no division inside it)
-    const int ny = yb - ya, RW = RB >> 2;
+    const int ny = yb - ya;
     const int yy0 = tid / S, x0s = tid - yy0 * S;                         // item tid = pixel (y - ya, x)
     const int dyy = kTapThreads / S, dxs = kTapThreads - dyy * S;
     const uint32_t xch_addr = tcx::smem_u32(xch);
@@ -304,14 +307,24 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
             const int nr = nrows - r0 < K ? nrows - r0 : K;
             const int nvc = nr * vpr;
             tcx::mbar_wait(bar0 + 8 * slot, phase);
-            const uint4* cv = ring + slot * kChunkVec;
+            const uint4* cv = reinterpret_cast<const uint4*>(ring + slot * slotB);
             for (int j = tid; j < nvc; j += kTapThreads) mm.vec(cv[j]);
-            const uint32_t* cw = reinterpret_cast<const uint32_t*>(cv);
-            for (int r = warp; r < nr; r += kTapWarps) {
+            // tap rows of this chunk: gather the 6 source bytes of every output column into the compact tap buffer
+            const uint8_t* cbytes = reinterpret_cast<const uint8_t*>(cv);
+            // (narrow outputs: one warp per source row; wide outputs, where a chunk is only a few rows: all threads per row)
+            const int rstep = wide ? 1 : kTapWarps, xstep = wide ? kTapThreads : 32;
+            for (int r = wide ? 0 : warp; r < nr; r += rstep) {
                 const int sl = rowslot[sa + r0 + r];
                 const int l = sl - first;
-                if (sl >= 0 && l >= 0 && l < rowsMax)
-                    for (int t = lane; t < nWc; t += 32) tap[l * nWc + t] = cw[r * RW + srcword[t]];
+                if (sl < 0 || l < 0 || l >= rowsMax) continue;
+                for (int x = wide ? tid : lane; x < S; x += xstep) {
+                    const uint8_t* p0 = cbytes + r * RB + cb0[x];
+                    const uint8_t* p1 = cbytes + r * RB + cb1[x];
+                    uint2 v;
+                    v.x = (uint32_t)p0[0] | ((uint32_t)p0[1] << 8) | ((uint32_t)p0[2] << 16) | ((uint32_t)p1[0] << 24);
+                    v.y = (uint32_t)p1[1] | ((uint32_t)p1[2] << 8);
+                    tap[l * S + x] = v;
+                }
             }
             __syncwarp();
             if (lane == 0) tcx::mbar_arrive(bar0 + 8 * (kRing + slot));
@@ -363,23 +376,31 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
             lut[tid] = (float)(((double)tid - (double)gmn) / rng);
         }
         bar_consumers();
-        // ---- pass 2: bilinear taps from the captured words (horizontal then vertical, like cv2) ----
-        const int tapRB = nWc * 4, SS = S * S;
+        if (wide) {
+            for (int i = tid; i < 256 * 32; i += kTapThreads) lutr[i] = lut[i >> 5];   // lane-private copies: conflict-free lookups
+            bar_consumers();
+        }
+        // ---- pass 2: bilinear taps from the captured bytes (horizontal then vertical, like cv2) ----
+        const int SS = S * S;
         float* onc = out_nchw ? out_nchw + f * 3 * SS : nullptr;
         __nv_bfloat16* onh = out_nhwc ? out_nhwc + f * 3 * SS : nullptr;
+        const float* lt = wide ? lutr + lane : lut;
+        const int ls = wide ? 5 : 0;
         int yy = yy0, x = x0s;
         for (int idx = tid; idx < ny * S; idx += kTapThreads) {           // one pixel = its three channels
             const int y = ya + yy;
-            const uint8_t* a0 = tapb + (ly0[y] - first) * tapRB + cb0[x];
-            const uint8_t* a1 = tapb + (ly0[y] - first) * tapRB + cb1[x];
-            const uint8_t* b0 = tapb + (ly1[y] - first) * tapRB + cb0[x];
-            const uint8_t* b1 = tapb + (ly1[y] - first) * tapRB + cb1[x];
+            const uint2 a = tap[(ly0[y] - first) * S + x];
+            const uint2 b = tap[(ly1[y] - first) * S + x];
             const float ax = fx[x], ay = fy[y], bx = 1.f - ax, by = 1.f - ay;
+            const unsigned int a0[3] = {a.x & 0xFFu, (a.x >> 8) & 0xFFu, (a.x >> 16) & 0xFFu};
+            const unsigned int a1[3] = {a.x >> 24, a.y & 0xFFu, (a.y >> 8) & 0xFFu};
+            const unsigned int b0[3] = {b.x & 0xFFu, (b.x >> 8) & 0xFFu, (b.x >> 16) & 0xFFu};
+            const unsigned int b1[3] = {b.x >> 24, b.y & 0xFFu, (b.y >> 8) & 0xFFu};
             float val[3];
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                const float top = lut[a0[c]] * bx + lut[a1[c]] * ax;
-                const float bot = lut[b0[c]] * bx + lut[b1[c]] * ax;
+                const float top = lt[a0[c] << ls] * bx + lt[a1[c] << ls] * ax;
+                const float bot = lt[b0[c] << ls] * bx + lt[b1[c] << ls] * ax;
                 val[c] = top * by + bot * ay;
             }
             if (onc) {
@@ -405,10 +426,11 @@ struct PrePlan {
     int32_t* d_plan;
     size_t smem;
     int ctas_per_sm;
+    int max_clusters;      // co-resident clusters (cudaOccupancyMaxActiveClusters), 0 = not queried yet
 };
 struct PrePlanCache { std::vector<PrePlan> plans; };
 
-constexpr size_t kTapSmemTwo = 110 * 1024;     // two CTAs per SM
+constexpr size_t kTapSmemTwo = 112 * 1024;     // two CTAs per SM
 constexpr size_t kTapSmemOne = 220 * 1024;     // one CTA per SM
 
 // Returns false when no cluster size up to 8 keeps the captured taps in shared memory.
@@ -419,14 +441,11 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
         axis_tap(d, H, S, y0[d], y1[d], fyv[d]);
         axis_tap(d, W, S, x0[d], x1[d], fxv[d]);
     }
-    std::vector<int32_t> rowslot(H, -1), wordmap((3 * W) / 4, -1);
+    std::vector<int32_t> rowslot(H, -1);
     for (int d = 0; d < S; ++d) { rowslot[y0[d]] = 0; rowslot[y1[d]] = 0; }
     int nR = 0;
     for (int r = 0; r < H; ++r) if (rowslot[r] == 0) rowslot[r] = nR++;
-    for (int d = 0; d < S; ++d)
-        for (int c = 0; c < 3; ++c) { wordmap[(x0[d] * 3 + c) >> 2] = 0; wordmap[(x1[d] * 3 + c) >> 2] = 0; }
-    int nWc = 0;
-    for (size_t w = 0; w < wordmap.size(); ++w) if (wordmap[w] == 0) wordmap[w] = nWc++;
+    const int nWc = 2 * S;                               // words per compact tap row (8 bytes per output column)
     const int K = kChunkBytes / (3 * W);                 // whole rows per ring slot
     if (K < 1) return false;
     for (int pass = 0; pass < 2; ++pass) {
@@ -455,27 +474,30 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
             const int o_cb1 = off; off += S;
             const int o_fx = off; off += S;
             const int o_rowslot = off; off += H;
-            const int o_srcword = off; off += nWc;
+            const int o_srcword = off;
             const int o_rank = off; off += 5 * CL;
             const int total = (off + 3) & ~3;
-            const size_t smem = (size_t)kRing * kChunkBytes + (size_t)(total + 256 + 32) * 4 + (size_t)rowsMax * nWc * 4;
-            if (smem > limit) continue;
+            const size_t rest = (size_t)(total + 256 + 32 + (S > 64 ? 256 * 32 : 0)) * 4 + (size_t)rowsMax * nWc * 4;
+            const size_t slotB = ((size_t)K * 3 * W + 127) & ~(size_t)127;
+            if (rest + 2 * slotB > limit) continue;
+            size_t nslot = (limit - rest) / slotB;
+            if (nslot > (size_t)kRingMax) nslot = kRingMax;
+            if (const char* e = getenv("GN_PRE_SLOTS")) { const size_t v = (size_t)atoi(e); if (v >= 2 && v < nslot) nslot = v; }
+            const size_t smem = nslot * slotB + rest;
             out.assign(total, 0);
             out[PP_S] = S; out[PP_H] = H; out[PP_W] = W; out[PP_CL] = CL; out[PP_NWC] = nWc; out[PP_ROWSMAX] = rowsMax;
             out[PP_LY0] = o_ly0; out[PP_LY1] = o_ly1; out[PP_FY] = o_fy; out[PP_CB0] = o_cb0; out[PP_CB1] = o_cb1;
             out[PP_FX] = o_fx; out[PP_K] = K; out[PP_ROWSLOT] = o_rowslot; out[PP_SRCWORD] = o_srcword; out[PP_RANK] = o_rank;
-            out[PP_TOTAL] = total;
+            out[PP_TOTAL] = total; out[PP_NSLOT] = (int32_t)nslot; out[PP_SLOTB] = (int32_t)slotB;
             for (int d = 0; d < S; ++d) {
                 out[o_ly0 + d] = rowslot[y0[d]];
                 out[o_ly1 + d] = rowslot[y1[d]];
                 memcpy(&out[o_fy + d], &fyv[d], 4);
                 memcpy(&out[o_fx + d], &fxv[d], 4);
-                const int b0 = x0[d] * 3, b1 = x1[d] * 3;
-                out[o_cb0 + d] = wordmap[b0 >> 2] * 4 + (b0 & 3);
-                out[o_cb1 + d] = wordmap[b1 >> 2] * 4 + (b1 & 3);
+                out[o_cb0 + d] = x0[d] * 3;          // byte offsets of the two tap pixels inside a source row
+                out[o_cb1 + d] = x1[d] * 3;
             }
             for (int r = 0; r < H; ++r) out[o_rowslot + r] = rowslot[r];
-            for (size_t w = 0; w < wordmap.size(); ++w) if (wordmap[w] >= 0) out[o_srcword + wordmap[w]] = (int32_t)w;
             for (int i = 0; i < 5 * CL; ++i) out[o_rank + i] = rk[i];
             CL_out = CL;
             smem_out = smem;
@@ -491,13 +513,14 @@ const PrePlan* get_plan(gn_handle* h, int H, int W, int S, int* status) {
     PrePlanCache* cache = reinterpret_cast<PrePlanCache*>(h->pre_plans);
     for (const PrePlan& pl : cache->plans)
         if (pl.H == H && pl.W == W && pl.S == S) return pl.d_plan ? &pl : nullptr;
-    PrePlan pl{H, W, S, 0, nullptr, 0, 0};
+    PrePlan pl{H, W, S, 0, nullptr, 0, 0, 0};
     std::vector<int32_t> words;
     if (build_plan(H, W, S, words, pl.CL, pl.smem)) {
         cudaError_t e = cudaMalloc(&pl.d_plan, words.size() * 4);
         if (e == cudaSuccess) e = cudaMemcpy(pl.d_plan, words.data(), words.size() * 4, cudaMemcpyHostToDevice);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(preprocess_tap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTapSmemOne);
+            e = cudaFuncSetAttribute(S > 64 ? preprocess_tap_kernel<true> : preprocess_tap_kernel<false>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTapSmemOne);
         if (e != cudaSuccess) { *status = (int)e; return nullptr; }
         int per = (int)((227 * 1024) / (pl.smem + 1024));
         pl.ctas_per_sm = per > 2 ? 2 : (per < 1 ? 1 : per);
@@ -534,6 +557,7 @@ extern "C" int gn_preprocess_u8_bgr(gn_handle* h, const uint8_t* d_frames, int64
             int64_t clusters = (int64_t)h->num_sms * pl->ctas_per_sm / pl->CL;
             if (clusters < 1) clusters = 1;
             if (clusters > n) clusters = n;
+            auto kern = S > 64 ? preprocess_tap_kernel<true> : preprocess_tap_kernel<false>;
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3((unsigned)(clusters * pl->CL));
             cfg.blockDim = dim3(kTapLaunchThreads);
@@ -546,7 +570,25 @@ extern "C" int gn_preprocess_u8_bgr(gn_handle* h, const uint8_t* d_frames, int64
             at[0].val.clusterDim.z = 1;
             cfg.attrs = at;
             cfg.numAttrs = pl->CL > 1 ? 1 : 0;
-            GN_CUDA(cudaLaunchKernelEx(&cfg, preprocess_tap_kernel, d_frames, n, (const int32_t*)pl->d_plan, d_out_nchw,
+            if (pl->CL > 1) {
+                // a cluster needs CL free SMs inside one GPC: launch only as many clusters as can be resident at once
+                // (frames are strided over clusters, so a cluster that starts late would run its share alone)
+                PrePlan* mut = const_cast<PrePlan*>(pl);
+                if (mut->max_clusters == 0) {
+                    int nc = 0;
+                    cfg.gridDim = dim3((unsigned)(h->num_sms / pl->CL * pl->CL));
+                    if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess || nc < 1) {
+                        cudaGetLastError();
+                        nc = (int)clusters;
+                    }
+                    mut->max_clusters = nc;
+                    if (getenv("GN_DEBUG")) fprintf(stderr, "[gn] preprocess %dx%d->%d: cluster %d, %zu B smem, %d resident clusters\n",
+                                                    pl->H, pl->W, pl->S, pl->CL, pl->smem, nc);
+                }
+                if (clusters > pl->max_clusters) clusters = pl->max_clusters;
+                cfg.gridDim = dim3((unsigned)(clusters * pl->CL));
+            }
+            GN_CUDA(cudaLaunchKernelEx(&cfg, kern, d_frames, n, (const int32_t*)pl->d_plan, d_out_nchw,
                                        reinterpret_cast<__nv_bfloat16*>(d_out_nhwc_bf16)));
             GN_LAUNCHED(h);
             return GN_OK;
