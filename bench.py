@@ -205,8 +205,7 @@ def native_arm(args, rank, world, local_rank):
     cps = torch.from_numpy(cps_host).to(dev)
     # ground-truth summaries: one postprocess per annotator (reference utils.py:102-118)
     ann = syn.make_annotator_importances(n_raw, N_USERS, seed=rank)
-    gd = torch.stack([U.postprocess_array(torch.from_numpy(a[:, None]).to(dev), SKIP, n_raw, cps, device=dev,
-                                          return_device=True)[1] for a in ann])
+    gd = U.gt_summaries_array(np.stack(ann), SKIP, n_raw, cps, device=dev, return_device=True)
     scorer = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev)
     gathered = torch.empty((world, n, 1), dtype=torch.float32, device=dev) if world > 1 else None
 

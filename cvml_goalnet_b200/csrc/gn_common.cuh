@@ -53,7 +53,7 @@ struct gn_model {
     // bf16 K-major GEMM operands: [N_out][K]
     __nv_bfloat16 *conv2_wk;     // [256][9*64]    k = (ky*3+kx)*64 + ci
     __nv_bfloat16 *conv3_wk;     // [512][9*256]
-    __nv_bfloat16 *linear5_wk;   // [512][81*512]  k = p*512 + c   (reference flatten is c*81 + p)
+    __nv_bfloat16 *linear5_wk;   // K-blocked (gn_w5_off), k = p*512 + c   (reference flatten is c*P3^2 + p)
     __nv_bfloat16 *f_wk[4];      // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
     __nv_bfloat16 *aconv2_wk;    // [128][3*64]    k = tap*64 + ci
     __nv_bfloat16 *alinear3_wk;  // [128][L2*128]  k = l*128 + c   (reference flatten is c*L2 + l)
@@ -63,23 +63,34 @@ struct gn_model {
 };
 #define GN_STAGE_MARK(m, k, st) do { if ((m)->timing) cudaEventRecord((m)->ev[k], st); } while (0)
 
+// K-blocked operand layout of linear5 (K = 512 * P3^2 runs into the millions at large frame sizes, where K-major
+// rows are megabytes apart and a 128-row TMA box would touch 128 DRAM pages): K is cut into blocks of 64 elements
+// (one 128-byte swizzle row) and rows are grouped so that every TMA box is ONE contiguous chunk.
+//   a3 : [ceil(n/128)][K/64][128 frames][64]     (16 KB per box)     w5 : [K/64][512][64]   (32 KB per 256-row box)
+__host__ __device__ __forceinline__ int64_t gn_a3_off(int64_t frame, int64_t k, int64_t kblocks) {
+    return ((((frame >> 7) * kblocks + (k >> 6)) << 7) + (frame & 127)) * 64 + (k & 63);
+}
+__host__ __device__ __forceinline__ int64_t gn_w5_off(int64_t row, int64_t k) {
+    return (((k >> 6) << 9) + row) * 64 + (k & 63);
+}
+
 // Workspace layout for n frames (all bf16 unless noted); offsets are computed by gn_ws_layout().
 struct gn_ws {
     __nv_bfloat16* a1p;   // [n][15][15][64]   block-1 output, zero border (conv2 input)
     __nv_bfloat16* a2p;   // [n][13][13][256]  block-2 output, zero border (conv3 input)
-    __nv_bfloat16* a3;    // [n][81][512]      block-3 output, (p, c) order (linear5 input)
+    __nv_bfloat16* a3;    // block-3 output, k = p*512 + c, K-blocked (gn_a3_off): linear5 input
     __nv_bfloat16* ac1;   // [n][L1+2][64]     AudBl conv1 output, (l, c) order, zero rows at l = -1 and l = L1
     __nv_bfloat16* ac2;   // [n][L2][128]      AudBl conv2 output, (l, c) order (linear3 input)
     __nv_bfloat16* h0;    // [n][fin]          [audio128 | visual512]
     __nv_bfloat16* h1;    // [n][512]
     __nv_bfloat16* h2;    // [n][512]
     __nv_bfloat16* h3;    // [n][256]
-    float* part;          // [splits][n][512] fp32 partial sums of a K-split linear5 (null when splits == 1)
+    float* part;          // [splits][rows][512] fp32 partial sums of the K-split part of linear5 (gn_linear5_plan)
     int64_t bytes;
 };
 gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
 int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, int C, cudaStream_t st);   // gn_tc_gemm.cu
-int gn_linear5_splits(const gn_model* m, int64_t n);   // K ranges linear5 is split into for n frames (gn_tc_gemm.cu)
+int gn_linear5_plan(const gn_model* m, int64_t n, int64_t* rows_direct);   // gn_tc_gemm.cu: rows run as whole tiles + K ranges of the rest
 
 // ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);

@@ -118,13 +118,13 @@ __global__ void pack_conv1(const float* __restrict__ w, float* __restrict__ out)
         out[i] = w[(co * 3 + ci) * 9 + tap];
     }
 }
-// linear5 weight [512][C*PP] with column c*PP + p -> bf16 [512][p*C + c]
+// linear5 weight [512][C*PP] with column c*PP + p -> bf16, k = p*C + c, K-blocked [K/64][512][64] (gn_w5_off)
 __global__ void pack_linear5(const float* __restrict__ w, int C, int PP, __nv_bfloat16* __restrict__ out) {
     const int64_t K = (int64_t)C * PP, total = 512 * K;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t o = i / K, k = i - o * K;
         const int p = (int)(k / C), c = (int)(k - (int64_t)p * C);
-        out[i] = __float2bfloat16(w[o * K + (int64_t)c * PP + p]);
+        out[gn_w5_off(o, k)] = __float2bfloat16(w[o * K + (int64_t)c * PP + p]);
     }
 }
 // AudBl conv2 weight [128][64][3] -> bf16 [128][tap*64 + ci]
@@ -309,15 +309,16 @@ gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base) {
     const size_t nn = (size_t)(n > 0 ? n : 1);
     w.a1p = take(nn * m->C1 * m->C1 * 64);
     w.a2p = take(nn * m->P1 * m->P1 * 256);
-    w.a3 = take(nn * m->P3 * m->P3 * 512);
+    w.a3 = take(((nn + 127) / 128 * 128) * m->P3 * m->P3 * 512);
     w.ac1 = take(nn * (m->L1 + 2) * 64);
     w.ac2 = take(nn * m->L2 * 128);
     w.h0 = take(nn * m->fin);
     w.h1 = take(nn * 512);
     w.h2 = take(nn * 512);
     w.h3 = take(nn * 256);
-    const int splits = gn_linear5_splits(m, (int64_t)nn);
-    w.part = splits > 1 ? reinterpret_cast<float*>(take((size_t)splits * nn * 512 * 2)) : nullptr;
+    int64_t rows_direct = 0;
+    const int splits = gn_linear5_plan(m, (int64_t)nn, &rows_direct);
+    w.part = splits > 1 ? reinterpret_cast<float*>(take((size_t)splits * (nn - (size_t)rows_direct) * 512 * 2)) : nullptr;
     w.bytes = (int64_t)((off + 1023) & ~size_t(1023));
     return w;
 }
@@ -371,7 +372,7 @@ namespace {
 __global__ void __launch_bounds__(256)
 simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __nv_bfloat16* __restrict__ wk, int Cout,
                 const float* __restrict__ bias, const float* __restrict__ sc, const float* __restrict__ sh,
-                __nv_bfloat16* __restrict__ out, int out_pad) {
+                __nv_bfloat16* __restrict__ out, int out_pad, int blocked) {
     extern __shared__ float cs[];   // [OH*OH][64]
     const int f = blockIdx.x, cblk = blockIdx.y;
     const int co = cblk * 64 + (threadIdx.x & 63), pg = threadIdx.x >> 6;
@@ -402,7 +403,8 @@ simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __n
                 for (int dx = 0; dx < 3; ++dx) mx = fmaxf(mx, cs[((y + dy) * OH + x + dx) * 64 + (threadIdx.x & 63)]);
             r = fmaf(mx, sc[co], sh[co]);
         }
-        o[(size_t)p * Cout + co] = __float2bfloat16(r);
+        if (blocked) out[gn_a3_off(f, (int64_t)p * Cout + co, (int64_t)PW * PW * Cout / 64)] = __float2bfloat16(r);
+        else o[(size_t)p * Cout + co] = __float2bfloat16(r);
     }
 }
 
@@ -410,7 +412,7 @@ simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __n
 __global__ void __launch_bounds__(256)
 simt_linear(const __nv_bfloat16* __restrict__ A, int64_t M, int K, int lda, const __nv_bfloat16* __restrict__ W, int N,
             const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int ld_out, int col_off,
-            float* __restrict__ out_f32) {
+            float* __restrict__ out_f32, int blocked) {
     const int lane = threadIdx.x & 31;
     const int64_t gw = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -420,6 +422,10 @@ simt_linear(const __nv_bfloat16* __restrict__ A, int64_t M, int K, int lda, cons
         const __nv_bfloat16* a = A + r * lda;
         const __nv_bfloat16* w = W + (size_t)j * K;
         float acc = 0.f;
+        if (blocked) {   // linear5 operands (gn_a3_off / gn_w5_off)
+            for (int k = lane; k < K; k += 32)
+                acc = fmaf(__bfloat162float(A[gn_a3_off(r, k, K / 64)]), __bfloat162float(W[gn_w5_off(j, k)]), acc);
+        } else
         for (int k = lane; k < K; k += 32) acc = fmaf(__bfloat162float(a[k]), __bfloat162float(w[k]), acc);
         for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
         if (lane == 0) {
@@ -460,8 +466,8 @@ __global__ void read_act_nchw(const __nv_bfloat16* __restrict__ in, int64_t n, i
         const int64_t f = i / ((int64_t)C * P * P);
         const int r = (int)(i - f * C * P * P);
         const int c = r / (P * P), p = r - c * P * P, y = p / P, x = p - y * P;
-        (void)chw_order;
-        out[i] = __bfloat162float(in[((f * PW + y + pad) * PW + x + pad) * C + c]);
+        if (chw_order == 2) out[i] = __bfloat162float(in[gn_a3_off(f, (int64_t)p * C + c, (int64_t)P * P * C / 64)]);   // K-blocked a3
+        else out[i] = __bfloat162float(in[((f * PW + y + pad) * PW + x + pad) * C + c]);
     }
 }
 __global__ void read_act_flat(const __nv_bfloat16* __restrict__ in, int64_t total, float* __restrict__ out) {
@@ -481,24 +487,24 @@ int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_sc
         attr = true;
     }
     simt_conv_block<<<dim3((unsigned)n, 4), 256, m->P1 * m->P1 * 64 * 4, st>>>(
-        ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1], ws.a2p, 1);
+        ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1], ws.a2p, 1, 0);
     GN_LAUNCHED(m->h);
     GN_STAGE_MARK(m, 3, st);
     simt_conv_block<<<dim3((unsigned)n, 8), 256, m->P2 * m->P2 * 64 * 4, st>>>(
-        ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2], ws.a3, 0);
+        ws.a2p, m->P2, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2], ws.a3, 0, 1);
     GN_LAUNCHED(m->h);
     GN_STAGE_MARK(m, 4, st);
     const int K5 = m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     const int grid = m->h->num_sms * 8;
-    simt_linear<<<grid, 256, 0, st>>>(ws.a3, n, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff, d_visfeat);
+    simt_linear<<<grid, 256, 0, st>>>(ws.a3, n, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff, d_visfeat, 1);
     GN_LAUNCHED(m->h);
     GN_STAGE_MARK(m, 5, st);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h0, n, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr);
+    simt_linear<<<grid, 256, 0, st>>>(ws.h0, n, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h1, n, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr);
+    simt_linear<<<grid, 256, 0, st>>>(ws.h1, n, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h2, n, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr);
+    simt_linear<<<grid, 256, 0, st>>>(ws.h2, n, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
     simt_score<<<grid, 256, 0, st>>>(ws.h3, n, 256, m->f_wk[3], m->f_b[3], m->f12_w, m->f12_b, d_scores);
     GN_LAUNCHED(m->h);
@@ -516,7 +522,7 @@ extern "C" int gn_dbg_read_activation(gn_model* m, int which, int64_t n, const v
     switch (which) {
         case 1: read_act_nchw<<<grid, 256, 0, st>>>(ws.a1p, n, 64, m->P1, 1, 1, d_out); break;
         case 2: read_act_nchw<<<grid, 256, 0, st>>>(ws.a2p, n, 256, m->P2, 1, 1, d_out); break;
-        case 3: read_act_nchw<<<grid, 256, 0, st>>>(ws.a3, n, 512, m->P3, 0, 1, d_out); break;
+        case 3: read_act_nchw<<<grid, 256, 0, st>>>(ws.a3, n, 512, m->P3, 0, 2, d_out); break;
         case 4: read_act_flat<<<grid, 256, 0, st>>>(ws.h0, n * m->fin, d_out); break;
         default: return GN_E_ARG;
     }

@@ -42,6 +42,7 @@ struct ConvGeom {
     int cout;          // total output channels
     int tiles;         // spatial tiles per frame side (1: the tile is the frame)
     int pfull;         // pooled size of the whole frame (== P when tiles == 1)
+    int blocked;       // 1: dense output in the K-blocked linear5 operand layout (gn_a3_off), k = pixel * cout + channel
 };
 
 struct GemmArgs {
@@ -66,6 +67,7 @@ struct GemmArgs {
     float scale;             // dropout scale 1/(1-p) (1 = no dropout)
     float keep_prob;         // kTrainFwd without mask: P(keep); >= 1 disables dropout
     unsigned long long seed;
+    int kblocked;            // linear modes: A and W are K-blocked (gn_a3_off / gn_w5_off): every TMA box is contiguous
     int k_splits;            // kSplitK: number of K ranges (1 otherwise)
     int64_t split_stride;    // kSplitK: elements between the partial-sum slabs (M * N)
     ConvGeom g;
@@ -197,10 +199,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         tma_load_4d(sa, &tmap_a, fb, cb * kBK, tx0 + kx, ty0 + ky, frame);
                     } else {
                         mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
-                        if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
-                        else               tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
+                        if (args.kblocked)      tma_load_2d(sa, &tmap_a, fb, 0, (int)((m_blk * k_total + kt) * 128));
+                        else if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
+                        else                    tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
                     }
-                    tma_load_2d(sb, &tmap_b, fb, kt * kBK, n_blk * BN);
+                    if (MODE != kConv && args.kblocked) tma_load_2d(sb, &tmap_b, fb, 0, kt * args.N + n_blk * BN);
+                    else                                tma_load_2d(sb, &tmap_b, fb, kt * kBK, n_blk * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -327,7 +331,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                                pack_bf16(fmaf(f2.x, sc1.x, sh1.x), fmaf(f2.y, sc1.y, sh1.y)),
                                                pack_bf16(fmaf(f3.x, sc1.z, sh1.z), fmaf(f3.y, sc1.w, sh1.w)));
                     const int opix = (gy0 + oy + args.g.out_pad) * PW + gx0 + ox + args.g.out_pad;
-                    *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
+                    if (args.g.blocked)
+                        *reinterpret_cast<uint4*>(args.out + gn_a3_off(frame, (int64_t)opix * args.g.cout + n0 + cg * 8,
+                                                                       (int64_t)PW * PW * args.g.cout / 64)) = o;
+                    else
+                        *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
                 }
                 if (args.g.out_pad && tiles_pf == 1) {   // zero border of the next conv's input (padding = 1);
                                                          // tiled frames: zero_border_kernel does it
@@ -523,7 +531,7 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __n
     a.M = n; a.N = Cout; a.K = 9 * Cin;
     a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
     a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
-    a.g.tiles = 1; a.g.pfull = OH - 2;
+    a.g.tiles = 1; a.g.pfull = OH - 2; a.g.blocked = out_pad ? 0 : 1;
     if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
     return launch<MT, BN, STAGES, kConv, OH>(m->h, ta, tb, a, n * (Cout / BN), st);
 }
@@ -566,7 +574,7 @@ int run_conv_tiled(gn_model* m, int64_t n, const __nv_bfloat16* in, int OHF, int
     a.M = n; a.N = Cout; a.K = 9 * Cin;
     a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
     a.g.OH = kTileOH; a.g.OW = kTileOH; a.g.P = TP; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
-    a.g.tiles = (PF + TP - 1) / TP; a.g.pfull = PF;
+    a.g.tiles = (PF + TP - 1) / TP; a.g.pfull = PF; a.g.blocked = out_pad ? 0 : 1;
     if (n * a.g.tiles * a.g.tiles > (1LL << 40)) return GN_E_RANGE;
     if (out_pad) {
         rc = gn_launch_zero_border(m->h, out, n, PF + 2, Cout, st);
@@ -600,6 +608,16 @@ splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int 
     }
 }
 
+// TMA maps of K-blocked operands (gn_a3_off / gn_w5_off): both are [rows'][64] matrices whose boxes are contiguous
+int make_tmaps_kblocked(gn_handle* h, CUtensorMap* ta, CUtensorMap* tb, const __nv_bfloat16* A, int64_t M, int64_t K,
+                        const __nv_bfloat16* wk, int N, int BN) {
+    const int64_t kb = K / kBK, rows_a = (M + 127) / 128 * 128 * kb, rows_b = kb * N;
+    if (rows_a >= (1LL << 31) || rows_b >= (1LL << 31)) return GN_E_RANGE;    // TMA coordinates are int32
+    int rc = make_tmap_2d(h, ta, A, rows_a, kBK, kBK, 128);
+    if (rc) return rc;
+    return make_tmap_2d(h, tb, wk, rows_b, kBK, kBK, BN);
+}
+
 // relu(A . W^T + b) with the reduction split into `splits` K ranges, one (tile, range) unit per CTA visit: used when
 // the (M/128) x (N/256) tiles alone would leave SMs idle (few frames, or linear5 at large frame sizes where
 // K = 512 * P3^2 is in the millions).  Deterministic: partial sums go to fp32 slabs, then one reduction pass.
@@ -609,12 +627,10 @@ int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K,
     constexpr int BN = 256;
     if (K % kBK || N % BN || K > (1LL << 31) - 64 || splits < 1 || !part) return GN_E_SHAPE;
     CUtensorMap ta, tb;
-    int rc = make_tmap_2d(m->h, &ta, A, M, K, K, 128);
-    if (rc) return rc;
-    rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
+    int rc = make_tmaps_kblocked(m->h, &ta, &tb, A, M, K, wk, N, BN);
     if (rc) return rc;
     GemmArgs a{};
-    a.M = M; a.N = N; a.K = (int)K; a.out_f32 = part; a.k_splits = splits; a.split_stride = M * N;
+    a.M = M; a.N = N; a.K = (int)K; a.out_f32 = part; a.k_splits = splits; a.split_stride = M * N; a.kblocked = 1;
     rc = launch<1, BN, 4, kSplitK, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN) * splits, st);
     if (rc) return rc;
     const int64_t blocks = (M * N / 4 + 255) / 256, cap = (int64_t)m->h->num_sms * 8;
@@ -627,14 +643,21 @@ int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K,
 template <int BN, int STAGES, int MODE>
 int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, const __nv_bfloat16* wk, int N,
                const float* bias, __nv_bfloat16* out, int ld_out, int col_off, float* out_f32, const float* w_last,
-               const float* b_last, float* scores, cudaStream_t st) {
+               const float* b_last, float* scores, cudaStream_t st, int kblocked = 0) {
     if (K % kBK || N % BN) return GN_E_SHAPE;
     CUtensorMap ta, tb;
-    int rc = make_tmap_2d(m->h, &ta, A, M, K, lda, 128);
-    if (rc) return rc;
-    rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
-    if (rc) return rc;
+    int rc;
+    if (kblocked) {
+        rc = make_tmaps_kblocked(m->h, &ta, &tb, A, M, K, wk, N, BN);
+        if (rc) return rc;
+    } else {
+        rc = make_tmap_2d(m->h, &ta, A, M, K, lda, 128);
+        if (rc) return rc;
+        rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
+        if (rc) return rc;
+    }
     GemmArgs a{};
+    a.kblocked = kblocked;
     a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = ld_out; a.col_off = col_off;
     a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores;
     return launch<1, BN, STAGES, MODE, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
@@ -651,15 +674,24 @@ int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, i
     return GN_OK;
 }
 
-// K ranges for linear5 (N = 512 -> two 256-wide column tiles): 1 when the row tiles alone fill the GPU.
-int gn_linear5_splits(const gn_model* m, int64_t n) {
-    const int64_t tiles = ((n + 127) / 128) * 2;
+// Work plan for linear5 (N = 512 -> two 256-wide column tiles per 128 rows) on a persistent grid of num_sms CTAs:
+// rows [0, *rows_direct) run as whole tiles in full waves; the remaining rows -- a partial last wave, or everything
+// when there are fewer tiles than SMs -- have their reduction split into the returned number of K ranges so that the
+// tail also fills the GPU.  Returns 1 (and *rows_direct = n) when splitting does not pay.
+int gn_linear5_plan(const gn_model* m, int64_t n, int64_t* rows_direct) {
+    const int sms = m->h->num_sms;
+    const int64_t mb = (n + 127) / 128, tiles = mb * 2;
     const int64_t k_total = (int64_t)m->P3 * m->P3 * 512 / kBK;
-    if (tiles >= m->h->num_sms || k_total < 16) return 1;
-    int64_t s = m->h->num_sms / tiles;
+    *rows_direct = n;
+    if (n <= 0 || k_total < 16) return 1;
+    const int64_t waves = (sms % 2 == 0) ? tiles / sms : 0;
+    const int64_t rem_tiles = tiles - waves * sms;
+    if (rem_tiles == 0 || rem_tiles * 4 > (int64_t)sms * 3) return 1;     // last wave already >= 75 % full
+    int64_t s = sms / rem_tiles;
     if (s > k_total / 8) s = k_total / 8;          // at least 8 k-steps per range
     if (s <= 1) return 1;
     const int64_t k_per = (k_total + s - 1) / s;
+    *rows_direct = waves * (sms / 2) * 128;
     return (int)((k_total + k_per - 1) / k_per);   // every range non-empty
 }
 
@@ -716,14 +748,19 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
     const int64_t K5 = (int64_t)m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     // linear5 + ReLU -> columns [aoff, aoff+512) of the fusion input (audio features occupy [0,128))
-    const int splits = gn_linear5_splits(m, n);
-    if (splits > 1)
-        rc = run_linear_splitk(m, n, ws.a3, K5, m->linear5_wk, 512, m->linear5_b, splits, ws.part, ws.h0, m->fin, aoff,
-                               d_visfeat, st);
-    else
-        rc = run_linear<256, 4, kLinear>(m, n, ws.a3, (int)K5, (int)K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin,
-                                         aoff, d_visfeat, nullptr, nullptr, nullptr, st);
-    if (rc) return rc;
+    int64_t rows_direct = n;
+    const int splits = gn_linear5_plan(m, n, &rows_direct);
+    if (rows_direct > 0) {
+        rc = run_linear<256, 4, kLinear>(m, rows_direct, ws.a3, (int)K5, (int)K5, m->linear5_wk, 512, m->linear5_b, ws.h0,
+                                         m->fin, aoff, d_visfeat, nullptr, nullptr, nullptr, st, 1);
+        if (rc) return rc;
+    }
+    if (rows_direct < n) {
+        rc = run_linear_splitk(m, n - rows_direct, ws.a3 + rows_direct * K5, K5, m->linear5_wk, 512, m->linear5_b, splits,
+                               ws.part, ws.h0 + rows_direct * m->fin, m->fin, aoff,
+                               d_visfeat ? d_visfeat + rows_direct * 512 : nullptr, st);
+        if (rc) return rc;
+    }
     GN_STAGE_MARK(m, 5, st);
     rc = run_linear<256, 4, kLinear>(m, n, ws.h0, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr,
                                      nullptr, nullptr, nullptr, st);

@@ -490,6 +490,40 @@ def postprocess_array(batch_importances, skip_frames, full_n_frames, change_poin
     return summarized_video, ind.cpu().numpy()
 
 
+def gt_summaries_array(annotator_importances, skip_frames, full_n_frames, change_points, device=None,
+                       return_device: bool = False):
+    """Ground-truth summaries of one video, as `get_dataloaders` builds them (utils.py:102-118): one
+    `postprocess` per annotator row of `annotator_importances` (U, n).  The U knapsacks share the clip
+    lengths and the capacity, so they run as ONE batched DP launch (a cluster per annotator) instead of U
+    sequential ones.  Returns uint8 (U, N_raw), bit-exact with U calls of `postprocess_array`."""
+    dev = _device(device)
+    imp = _to_dev(annotator_importances, torch.float32, dev)
+    assert imp.dim() == 2, "E: Invalid shape for importance tensor"
+    users, n = int(imp.shape[0]), int(imp.shape[1])
+    n_raw = int(full_n_frames)
+    if torch.is_tensor(change_points):
+        cps = _to_dev(change_points.reshape(-1, 2), torch.int32, dev)
+    else:
+        cps = _to_dev(np.asarray(change_points).reshape(-1, 2).astype(np.int32), torch.int32, dev)
+    n_clips = int(cps.shape[0])
+    ind = torch.zeros((users, n_raw), dtype=torch.uint8, device=dev)
+    if users and n_clips > 0 and n > 0:
+        lib = _lib.load()
+        values = torch.empty((users, n_clips), dtype=torch.int32, device=dev)
+        lengths = torch.empty((users, n_clips), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            for u in range(users):
+                _lib.check(lib.gn_clip_information(_h(dev), _ptr(imp[u]), n, int(skip_frames), n_raw, _ptr(cps), n_clips,
+                                                   _ptr(values[u]), _ptr(lengths[u]), _stream(dev)), "gn_clip_information")
+        sel, _ = _knapsack_device(values, lengths, n_clips, int(0.15 * n_raw), 0, users, dev)
+        sel = sel.contiguous()
+        with torch.cuda.device(dev):
+            for u in range(users):
+                _lib.check(lib.gn_summary_indicator(_h(dev), _ptr(cps), _ptr(sel[u]), n_clips, n_raw, _ptr(ind[u]),
+                                                    _stream(dev)), "gn_summary_indicator")
+    return ind if return_device else ind.cpu().numpy()
+
+
 def _read_change_points(video_id, h5_file_path, mat_file_path):
     """utils.py:615-625 (HDF5 I/O, unchanged semantics; needs h5py, which this image lacks)."""
     try:

@@ -339,6 +339,19 @@ def test_gt_summaries_like_get_dataloaders(U):
         np.testing.assert_array_equal(ind, ref)
 
 
+@pytest.mark.parametrize("n_raw,users", [(3600, 20), (27000, 20), (162000, 5), (450, 3)])
+def test_gt_summaries_batched_equals_per_annotator(U, n_raw, users):
+    """the U per-annotator knapsacks of utils.py:102-118 as one batched DP launch."""
+    skip = 15
+    ann = np.stack(syn.make_annotator_importances(n_raw, users, seed=n_raw))
+    cps = syn.make_change_points(n_raw, seed=n_raw + 1)
+    out = U.gt_summaries_array(ann, skip, n_raw, cps)
+    assert out.shape == (users, n_raw) and out.dtype == np.uint8
+    for u in range(users):
+        _, ref = O.postprocess_array(ann[u][:, None], skip, n_raw, cps)
+        np.testing.assert_array_equal(out[u], ref, err_msg=f"annotator {u}")
+
+
 # ------------------------------------------------------------------ whole path
 def test_end_to_end_config1(U, weights):
     """BASELINE config 1: 2-min clip, 224x224 source, 2 fps, 16 kHz audio -> scores, keyshots, F-score."""
