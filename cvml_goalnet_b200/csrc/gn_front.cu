@@ -100,7 +100,7 @@ visbl_block1_kernel(const float* __restrict__ vis, int64_t n, const float* __res
 
 // VisBl block 1 for frames of any size S (e.g. 224: conv1 -> 76x76, pool -> 74x74).  One CTA visit = one 16x16 tile of
 // conv1 outputs (tiles overlap by the pooling halo -> 14x14 pooled pixels); a warp computes one conv pixel for all 64
-// channels (2 per lane, weights in registers), its 27 taps fetched by lanes 0..26 and broadcast by shuffles.  This
+// channels (2 per lane, weights in registers) from the tile's input window staged patch-major in shared memory.  This
 // block is 0.1 % of the model's FLOPs at 224x224; the zero border of a1p is written by gn_launch_zero_border.
 constexpr int kT1 = 16, kT1P = kT1 - 2;
 
@@ -108,7 +108,9 @@ __global__ void __launch_bounds__(kVThreads, 2)
 visbl_block1_tiled_kernel(const float* __restrict__ vis, int64_t n, int S, int C1, int tiles,
                           const float* __restrict__ w /*[27][64]*/, const float* __restrict__ b,
                           const float* __restrict__ sc, const float* __restrict__ sh, __nv_bfloat16* __restrict__ a1p) {
-    extern __shared__ __align__(16) float sm[];                 // [256][64] conv + ReLU
+    extern __shared__ __align__(16) float sm[];
+    float* c1 = sm;                                             // [256][64] conv + ReLU
+    float* patch = sm + kT1 * kT1 * 64;                         // [256][28] taps of every conv pixel of the tile (k = ci*9+ky*3+kx)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float w0[27], w1[27];                                       // k = ci*9 + ky*3 + kx
 #pragma unroll
@@ -122,32 +124,47 @@ visbl_block1_tiled_kernel(const float* __restrict__ vis, int64_t n, int S, int C
     const float2 bias = *reinterpret_cast<const float2*>(b + 2 * lane);
     const float2 scale = *reinterpret_cast<const float2*>(sc + 2 * lane);
     const float2 shift = *reinterpret_cast<const float2*>(sh + 2 * lane);
-    const int kci = lane / 9, ktap = lane - kci * 9, kky = ktap / 3, kkx = ktap - kky * 3;   // this lane's tap (lane < 27)
     const int P1 = C1 - 2;
+    constexpr int kIn = 3 * kT1;                                // 48 input rows / columns feed a 16x16 conv tile (k3 s3)
     const int64_t units = n * tiles * tiles;
     for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
         const int64_t f = u / (tiles * tiles);
         const int t = (int)(u - f * tiles * tiles);
         const int ty = t / tiles, tx = t - ty * tiles;
         const float* src = vis + f * 3 * (int64_t)S * S;
+        const int iy0 = 3 * ty * kT1P - 3, ix0 = 3 * tx * kT1P - 3;   // input coordinate of the tile's first tap (padding 3)
+        __syncthreads();
+        // conv1 has stride == kernel size: its im2col is a permutation of the input window -> scatter it patch-major
+        // (thread = one window column and every 5th row: the column part of the index math is loop-invariant)
+        if (tid < 5 * kIn) {
+            const int x = tid % kIn, yy = tid / kIn, ix = ix0 + x;
+            const bool okx = ix >= 0 && ix < S;
+            float* pcol = patch + (x / 3) * kPatch + (x % 3);
+            for (int y = yy; y < kIn; y += 5) {
+                const int iy = iy0 + y;
+                const bool ok = okx && iy >= 0 && iy < S;
+                float* pd = pcol + (y / 3) * (kT1 * kPatch) + (y % 3) * 3;
+                const float* ps = src + (int64_t)iy * S + ix;
+#pragma unroll
+                for (int ci = 0; ci < 3; ++ci) pd[ci * 9] = ok ? __ldg(ps + (int64_t)ci * S * S) : 0.f;
+            }
+        }
         __syncthreads();
         for (int p = warp; p < kT1 * kT1; p += kVThreads / 32) {
-            const int cy = ty * kT1P + p / kT1, cx = tx * kT1P + p % kT1;
-            float2 r = make_float2(0.f, 0.f);
-            if (cy < C1 && cx < C1) {
-                const int iy = 3 * cy - 3 + kky, ix = 3 * cx - 3 + kkx;
-                float v = 0.f;
-                if (lane < 27 && iy >= 0 && iy < S && ix >= 0 && ix < S) v = __ldg(src + ((int64_t)kci * S + iy) * S + ix);
-                float a0 = bias.x, a1 = bias.y;
+            const float4* pp = reinterpret_cast<const float4*>(patch + p * kPatch);
+            float in[kPatch];
 #pragma unroll
-                for (int k = 0; k < 27; ++k) {
-                    const float x = __shfl_sync(0xffffffffu, v, k);
-                    a0 = fmaf(x, w0[k], a0);
-                    a1 = fmaf(x, w1[k], a1);
-                }
-                r = make_float2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+            for (int v = 0; v < kPatch / 4; ++v) {
+                const float4 q = pp[v];
+                in[4 * v] = q.x; in[4 * v + 1] = q.y; in[4 * v + 2] = q.z; in[4 * v + 3] = q.w;
             }
-            *reinterpret_cast<float2*>(sm + p * 64 + 2 * lane) = r;
+            float a0 = bias.x, a1 = bias.y;
+#pragma unroll
+            for (int k = 0; k < 27; ++k) {
+                a0 = fmaf(in[k], w0[k], a0);
+                a1 = fmaf(in[k], w1[k], a1);
+            }
+            *reinterpret_cast<float2*>(c1 + p * 64 + 2 * lane) = make_float2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
         }
         __syncthreads();
         uint32_t* o = reinterpret_cast<uint32_t*>(a1p + f * (int64_t)C1 * C1 * 64);
@@ -155,7 +172,7 @@ visbl_block1_tiled_kernel(const float* __restrict__ vis, int64_t n, int S, int C
             const int oy = p / kT1P, ox = p - oy * kT1P;
             const int gy = ty * kT1P + oy, gx = tx * kT1P + ox;
             if (gy >= P1 || gx >= P1) continue;
-            const float* base = sm + (oy * kT1 + ox) * 64 + 2 * lane;
+            const float* base = c1 + (oy * kT1 + ox) * 64 + 2 * lane;
             float2 m = *reinterpret_cast<const float2*>(base);
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy)
@@ -307,7 +324,7 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
     if (m->S != kS || m->C1 != kC1) {
         static bool attr_t = false;
-        const size_t smem_t = sizeof(float) * kT1 * kT1 * 64;
+        const size_t smem_t = sizeof(float) * kT1 * kT1 * (64 + kPatch);
         if (!attr_t) {
             GN_CUDA(cudaFuncSetAttribute(visbl_block1_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
             attr_t = true;

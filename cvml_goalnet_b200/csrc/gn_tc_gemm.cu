@@ -294,7 +294,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));      // TMEM buffer may be overwritten
                 asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile complete
                 // ---- phase 2: MaxPool(3, stride 1) over the ReLU'd tile, BatchNorm affine, bf16 NHWC store ----
-                // item = (pooled pixel, group of 8 channels): 9 x 16-byte shared loads, one 16-byte global store
                 constexpr int P = OHT - 2;
                 constexpr int CG = BN / 8;
                 const int PW = args.g.pfull + 2 * args.g.out_pad;
@@ -309,19 +308,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
                 const int vy = min(P, args.g.pfull - gy0), vx = min(P, args.g.pfull - gx0);   // valid outputs of an edge tile
                 __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + n0;
-                for (int item = et; item < P * P * CG; item += kEpiThreads) {
-                    const int op = item / CG, cg = item - op * CG;
-                    const int oy = op / P, ox = op - oy * P;
-                    if (oy >= vy || ox >= vx) continue;
-                    const unsigned char* s0 = stg + (size_t)(oy * OHT + ox) * C::kStgStride + cg * 16;
-                    uint4 m = *reinterpret_cast<const uint4*>(s0);
-#pragma unroll
-                    for (int dy = 0; dy < 3; ++dy)
-#pragma unroll
-                        for (int dx = 0; dx < 3; ++dx) {
-                            if (dy == 0 && dx == 0) continue;
-                            m = hmax2_u4(m, *reinterpret_cast<const uint4*>(s0 + (size_t)(dy * OHT + dx) * C::kStgStride));
-                        }
+                // BatchNorm affine + bf16 store of one pooled (pixel, 8-channel group)
+                auto emit = [&](int oy, int ox, int cg, uint4 m) {
                     const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
                     const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
                     const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
@@ -336,6 +324,44 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                                                        (int64_t)PW * PW * args.g.cout / 64)) = o;
                     else
                         *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
+                };
+                if constexpr (P * CG <= kEpiThreads) {
+                    // separable pooling down a column strip: thread = (pooled column, channel group); per conv row one
+                    // 3-wide horizontal max (3 loads), per pooled row the max of the last three of those
+                    const int ox = et / CG, cg = et - ox * CG;
+                    if (ox < vx) {
+                        const unsigned char* s0 = stg + (size_t)ox * C::kStgStride + cg * 16;
+                        uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;
+#pragma unroll
+                        for (int r = 0; r < OHT; ++r) {
+                            if (r < vy + 2) {
+                                const unsigned char* sr = s0 + (size_t)(r * OHT) * C::kStgStride;
+                                const uint4 h2 = hmax2_u4(hmax2_u4(*reinterpret_cast<const uint4*>(sr),
+                                                                   *reinterpret_cast<const uint4*>(sr + C::kStgStride)),
+                                                          *reinterpret_cast<const uint4*>(sr + 2 * C::kStgStride));
+                                if (r >= 2) emit(r - 2, ox, cg, hmax2_u4(hmax2_u4(h0, h1), h2));
+                                h0 = h1;
+                                h1 = h2;
+                            }
+                        }
+                    }
+                } else {
+                    // item = (pooled pixel, group of 8 channels): 9 x 16-byte shared loads, one 16-byte global store
+                    for (int item = et; item < P * P * CG; item += kEpiThreads) {
+                        const int op = item / CG, cg = item - op * CG;
+                        const int oy = op / P, ox = op - oy * P;
+                        if (oy >= vy || ox >= vx) continue;
+                        const unsigned char* s0 = stg + (size_t)(oy * OHT + ox) * C::kStgStride + cg * 16;
+                        uint4 m = *reinterpret_cast<const uint4*>(s0);
+#pragma unroll
+                        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                            for (int dx = 0; dx < 3; ++dx) {
+                                if (dy == 0 && dx == 0) continue;
+                                m = hmax2_u4(m, *reinterpret_cast<const uint4*>(s0 + (size_t)(dy * OHT + dx) * C::kStgStride));
+                            }
+                        emit(oy, ox, cg, m);
+                    }
                 }
                 if (args.g.out_pad && tiles_pf == 1) {   // zero border of the next conv's input (padding = 1);
                                                          // tiled frames: zero_border_kernel does it
