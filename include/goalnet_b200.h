@@ -103,7 +103,9 @@ typedef struct gn_avm_state {
 } gn_avm_state;
 
 /* All pointers in `sd` are DEVICE pointers.  S = frame side (40 in the reference, utils.py:285),
- * B = audio bins (30).  This build supports S = 40 and B with 128*L2 = 1024 (B in 29..32).
+ * B = audio bins (30).  S = 40 runs frame-aligned conv tiles; any other S in 16..1024 (e.g. 224, BASELINE config 5:
+ * the reference's layers are Lazy*, so only the literal at utils.py:285 changes) runs overlapping 16x16 conv tiles.
+ * linear5_w is then [512][512*P3*P3] with P3 = (S+3)/3 - 5.  B must give 128*L2 = 1024 (B in 29..32).
  * Synchronises `stream` before returning (the caller may free `sd` tensors afterwards). */
 int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state* sd, int audio_included, int S, int B,
                     void* stream);
