@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GN_LIB_PATH: development override to A/B two builds of the same ABI on one box (never a different backend)
 LIB_PATH = os.environ.get("GN_LIB_PATH") or os.path.join(_HERE, "libgoalnet_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu", "gn_train.cu"]
+SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu", "gn_train.cu", "gn_train_avm.cu"]
 NVCC_FLAGS = ["-shared", "-Xcompiler", "-fPIC", "-std=c++17", "-O3", "-lineinfo",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 
@@ -110,6 +110,15 @@ SIGNATURES = {
     "gn_fusion_get_params": (_I, [_P, _P, _P]),
     "gn_fusion_forward_backward": (_I, [_P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P, _P]),
     "gn_fusion_adam_step": (_I, [_P, _P, C.c_float, _P]),
+    "gn_avm_trainer_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_avm_state), _I, _I, _I, _L, _P]),
+    "gn_avm_trainer_destroy": (_I, [_P]),
+    "gn_avm_trainer_param_count": (_L, [_P]),
+    "gn_avm_trainer_set_hyper": (_I, [_P, C.c_float, C.c_float, C.c_float, C.c_float]),
+    "gn_avm_trainer_forward_backward": (_I, [_P, _P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P]),
+    "gn_avm_trainer_grads": (_I, [_P, C.POINTER(_P)]),
+    "gn_avm_trainer_adam_step": (_I, [_P, C.c_float, _P]),
+    "gn_avm_train_step": (_I, [_P, _P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P]),
+    "gn_avm_trainer_export": (_I, [_P, C.POINTER(gn_avm_state), _P]),
     "gn_fusion_train_step": (_I, [_P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P, _P]),
     "gn_dbg_avm_forward_simt": (_I, [_P, _P, _P, _L, _P, _P, _P, _L, _P]),
     "gn_dbg_read_activation": (_I, [_P, _I, _L, _P, _P, _P]),

@@ -1,0 +1,683 @@
+// Full-AVM training step -- replaces the reference's train sub-step main.py:187-193
+//     optimizer.zero_grad(); pred = model(audios, frames); loss = MSELoss()(pred, labels); loss.backward(); optimizer.step()
+// for the WHOLE network in train mode, as the reference runs it (it never calls .eval(), quirk Q4):
+// BatchNorm2d uses the statistics of the sub-batch and updates its running buffers (momentum 0.1, unbiased running
+// variance), Dropout(0.2) is active after linear5 and after fusion.0/3/6/9 (utils.py:168,245-254).
+// Sub-batches are 10 frames (main.py:47), so every layer is tiny and latency-bound; this first version is plain
+// fp32 CUDA-core kernels in the reference's own NCHW / [out][in] layouts (no repacking, tight parity with torch
+// autograd).  The tensor-core training GEMMs of gn_train.cu cover the fusion network at batch 4096 (config 4).
+#include <math.h>
+#include <stdlib.h>
+
+#include "gn_common.cuh"
+
+namespace {
+
+constexpr int kT = 256;
+inline int grid_for(int64_t total, int cap) { int64_t b = (total + kT - 1) / kT; return (int)(b < 1 ? 1 : (b > cap ? cap : b)); }
+
+// ---- forward ------------------------------------------------------------------------------------------------
+// y[n][co][oy][ox] = b[co] + sum_{ci,kh,kw} x[n][ci][oy*sh-ph+kh][ox*sw-pw+kw] * w[co][ci][kh][kw]   (+ ReLU)
+__global__ void __launch_bounds__(kT)
+conv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, int N, int Ci, int H,
+                int W, int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW, int relu,
+                float* __restrict__ y) {
+    const int64_t total = (int64_t)N * Co * OH * OW;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int ox = (int)(i % OW), oy = (int)((i / OW) % OH), co = (int)((i / ((int64_t)OW * OH)) % Co);
+        const int n = (int)(i / ((int64_t)OW * OH * Co));
+        float acc = b[co];
+        for (int ci = 0; ci < Ci; ++ci)
+            for (int kh = 0; kh < KH; ++kh) {
+                const int iy = oy * sh - ph + kh;
+                if (iy < 0 || iy >= H) continue;
+                for (int kw = 0; kw < KW; ++kw) {
+                    const int ix = ox * sw - pw + kw;
+                    if (ix < 0 || ix >= W) continue;
+                    acc = fmaf(x[(((int64_t)n * Ci + ci) * H + iy) * W + ix], w[((co * Ci + ci) * KH + kh) * KW + kw], acc);
+                }
+            }
+        y[i] = relu ? fmaxf(acc, 0.f) : acc;
+    }
+}
+
+// p = MaxPool(3, stride 1) of y (already ReLU'd); arg = window offset (dy*3+dx) of the first maximum (torch scan order)
+__global__ void __launch_bounds__(kT)
+pool_fwd_kernel(const float* __restrict__ y, int NC, int OH, int OW, float* __restrict__ p, uint8_t* __restrict__ arg) {
+    const int PH = OH - 2, PW = OW - 2;
+    const int64_t total = (int64_t)NC * PH * PW;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int px = (int)(i % PW), py = (int)((i / PW) % PH);
+        const int64_t nc = i / ((int64_t)PW * PH);
+        const float* base = y + (nc * OH + py) * OW + px;
+        float m = base[0];
+        int a = 0;
+        for (int d = 1; d < 9; ++d) {
+            const float v = base[(d / 3) * OW + d % 3];
+            if (v > m) { m = v; a = d; }
+        }
+        p[i] = m;
+        arg[i] = (uint8_t)a;
+    }
+}
+
+// BatchNorm2d in training mode, one CTA per channel: batch mean / biased variance over (N, H, W), normalise, affine;
+// running_mean/var <- 0.9 * old + 0.1 * (mean, unbiased variance).  Keeps xhat and invstd for the backward.
+__global__ void __launch_bounds__(kT)
+bn_fwd_kernel(const float* __restrict__ p, int N, int C, int HW, const float* __restrict__ gamma,
+              const float* __restrict__ beta, float* __restrict__ rmean, float* __restrict__ rvar, float* __restrict__ xhat,
+              float* __restrict__ invstd_out, float* __restrict__ out) {
+    __shared__ double s1[kT], s2[kT];
+    const int c = blockIdx.x, m = N * HW;
+    double a = 0.0, q = 0.0;
+    for (int i = threadIdx.x; i < m; i += kT) {
+        const float v = p[((int64_t)(i / HW) * C + c) * HW + i % HW];
+        a += v;
+        q += (double)v * v;
+    }
+    s1[threadIdx.x] = a; s2[threadIdx.x] = q;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    const double mean = s1[0] / m;
+    double var = s2[0] / m - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float istd = (float)(1.0 / sqrt(var + 1e-5));
+    if (threadIdx.x == 0) {
+        invstd_out[c] = istd;
+        rmean[c] = 0.9f * rmean[c] + 0.1f * (float)mean;
+        rvar[c] = 0.9f * rvar[c] + 0.1f * (float)(m > 1 ? var * m / (m - 1) : var);
+    }
+    const float g = gamma[c], bt = beta[c], mu = (float)mean;
+    for (int i = threadIdx.x; i < m; i += kT) {
+        const int64_t idx = ((int64_t)(i / HW) * C + c) * HW + i % HW;
+        const float xh = (p[idx] - mu) * istd;
+        xhat[idx] = xh;
+        out[idx] = fmaf(xh, g, bt);
+    }
+}
+
+// y[n][o] = act(b[o] + x[n] . w[o]) ; one warp per output; optional ReLU and dropout keep-mask * scale
+__global__ void __launch_bounds__(kT)
+linear_fwd_kernel(const float* __restrict__ x, int ldx, const float* __restrict__ w, const float* __restrict__ b, int N, int K,
+                  int O, int relu, const uint8_t* __restrict__ mask, float scale, float* __restrict__ y, int ldy,
+                  int col_off) {
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = (blockIdx.x * (int64_t)kT + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * kT) >> 5;
+    for (int64_t o = gw; o < (int64_t)N * O; o += nw) {
+        const int n = (int)(o / O), j = (int)(o - (int64_t)n * O);
+        const float* xr = x + (int64_t)n * ldx;
+        const float* wr = w + (int64_t)j * K;
+        float acc = 0.f;
+        for (int k = lane; k < K; k += 32) acc = fmaf(xr[k], wr[k], acc);
+        for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+        if (lane == 0) {
+            float v = acc + b[j];
+            if (relu) v = fmaxf(v, 0.f);
+            if (mask) v = mask[(int64_t)n * O + j] ? v * scale : 0.f;
+            y[(int64_t)n * ldy + col_off + j] = v;
+        }
+    }
+}
+
+// keep-mask from a counter-based hash (splitmix64 of seed + site offset + element index), P(keep) = keep_prob
+__global__ void __launch_bounds__(kT)
+make_mask_kernel(uint8_t* __restrict__ mask, int64_t total, unsigned long long seed, float keep_prob) {
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        unsigned long long z = seed + (unsigned long long)i * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        mask[i] = ((float)(unsigned int)(z >> 40) * (1.f / 16777216.f)) < keep_prob ? 1 : 0;
+    }
+}
+
+// scores = 4 sigmoid(z) + 1; loss = mean_ij (p_i - l_j)^2 (as written, quirk Q5) or mean_i (p_i - l_i)^2;
+// dz_i = dL/dp_i * 4 s (1 - s).  One CTA (n is a sub-batch).
+__global__ void __launch_bounds__(kT)
+loss_kernel(const float* __restrict__ z, const float* __restrict__ labels, int n, int fixed_loss, float* __restrict__ scores,
+            float* __restrict__ dz, double* __restrict__ loss) {
+    __shared__ double sl[kT], sl2[kT], sp[kT];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < n; i += kT) { a += labels[i]; b += (double)labels[i] * labels[i]; }
+    sl[threadIdx.x] = a; sl2[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; sl2[threadIdx.x] += sl2[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    const double lmean = sl[0] / n, l2mean = sl2[0] / n;
+    double part = 0.0;
+    for (int i = threadIdx.x; i < n; i += kT) {
+        const float s = 1.f / (1.f + expf(-z[i]));
+        const float p = 4.f * s + 1.f;
+        if (scores) scores[i] = p;
+        double dp;
+        if (fixed_loss) {
+            const double d = (double)p - labels[i];
+            part += d * d / n;
+            dp = 2.0 * d / n;
+        } else {
+            // mean_j (p - l_j)^2 = p^2 - 2 p mean(l) + mean(l^2), averaged over i
+            part += ((double)p * p - 2.0 * p * lmean + l2mean) / n;
+            dp = 2.0 * ((double)p - lmean) / n;
+        }
+        dz[i] = (float)(dp * 4.0 * s * (1.0 - s));
+    }
+    sp[threadIdx.x] = part;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sp[threadIdx.x] += sp[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && loss) *loss = sp[0];
+}
+
+}  // namespace
+
+namespace {
+
+// ---- backward -----------------------------------------------------------------------------------------------
+// dx[n][k] = sum_o dy[n][o] * w[o][k]; thread per (n, k)
+__global__ void __launch_bounds__(kT)
+linear_bwd_x_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ w, int N, int K, int O,
+                    float* __restrict__ dx) {
+    const int64_t total = (int64_t)N * K;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int n = (int)(i / K), k = (int)(i - (int64_t)n * K);
+        const float* d = dy + (int64_t)n * ldy + col_off;
+        float acc = 0.f;
+        for (int o = 0; o < O; ++o) acc = fmaf(d[o], w[(int64_t)o * K + k], acc);
+        dx[i] = acc;
+    }
+}
+
+// dw[o][k] = sum_n dy[n][o] * x[n][k]; db[o] = sum_n dy[n][o]; thread per (o, k)
+__global__ void __launch_bounds__(kT)
+linear_bwd_w_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ x, int ldx, int N, int K,
+                    int O, float* __restrict__ dw, float* __restrict__ db) {
+    const int64_t total = (int64_t)O * K;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int o = (int)(i / K), k = (int)(i - (int64_t)o * K);
+        float acc = 0.f, accb = 0.f;
+        for (int n = 0; n < N; ++n) {
+            const float d = dy[(int64_t)n * ldy + col_off + o];
+            acc = fmaf(d, x[(int64_t)n * ldx + k], acc);
+            accb += d;
+        }
+        dw[i] = acc;
+        if (k == 0) db[o] = accb;
+    }
+}
+
+// d <- d * [act > 0] * (mask ? mask * scale : 1): backward of Dropout(ReLU(.)) given the layer's OUTPUT act
+__global__ void __launch_bounds__(kT)
+relu_drop_bwd_kernel(float* __restrict__ d, const float* __restrict__ act, const uint8_t* __restrict__ mask, float scale,
+                     int64_t total) {
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        float v = d[i];
+        if (mask) v = mask[i] ? v * scale : 0.f;       // act already carries the mask; a dropped unit has act == 0
+        d[i] = act[i] > 0.f ? v : 0.f;
+    }
+}
+
+// BatchNorm2d backward (training statistics), one CTA per channel:
+//   dgamma = sum dy*xhat, dbeta = sum dy, dx = gamma*invstd * (dy - dbeta/m - xhat*dgamma/m)
+__global__ void __launch_bounds__(kT)
+bn_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ invstd,
+              const float* __restrict__ gamma, int N, int C, int HW, float* __restrict__ dx, float* __restrict__ dgamma,
+              float* __restrict__ dbeta) {
+    __shared__ double s1[kT], s2[kT];
+    const int c = blockIdx.x, m = N * HW;
+    double a = 0.0, q = 0.0;
+    for (int i = threadIdx.x; i < m; i += kT) {
+        const int64_t idx = ((int64_t)(i / HW) * C + c) * HW + i % HW;
+        a += dy[idx];
+        q += (double)dy[idx] * xhat[idx];
+    }
+    s1[threadIdx.x] = a; s2[threadIdx.x] = q;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    const float sdy = (float)s1[0], sdx = (float)s2[0];
+    if (threadIdx.x == 0) { dbeta[c] = sdy; dgamma[c] = sdx; }
+    const float k = gamma[c] * invstd[c], im = 1.f / (float)m;
+    for (int i = threadIdx.x; i < m; i += kT) {
+        const int64_t idx = ((int64_t)(i / HW) * C + c) * HW + i % HW;
+        dx[idx] = k * (dy[idx] - sdy * im - xhat[idx] * sdx * im);
+    }
+}
+
+// backward of MaxPool(3,1) o ReLU: dy[nc][oy][ox] = [y > 0] * sum of dp over the windows whose argmax is (oy, ox)
+__global__ void __launch_bounds__(kT)
+pool_relu_bwd_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ arg, const float* __restrict__ y, int NC,
+                     int OH, int OW, float* __restrict__ dy) {
+    const int PH = OH - 2, PW = OW - 2;
+    const int64_t total = (int64_t)NC * OH * OW;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int ox = (int)(i % OW), oy = (int)((i / OW) % OH);
+        const int64_t nc = i / ((int64_t)OW * OH);
+        float acc = 0.f;
+        if (y[i] > 0.f) {
+            for (int dy_ = 0; dy_ < 3; ++dy_) {
+                const int py = oy - dy_;
+                if (py < 0 || py >= PH) continue;
+                for (int dx_ = 0; dx_ < 3; ++dx_) {
+                    const int px = ox - dx_;
+                    if (px < 0 || px >= PW) continue;
+                    const int64_t pi = (nc * PH + py) * PW + px;
+                    if (arg[pi] == dy_ * 3 + dx_) acc += dp[pi];
+                }
+            }
+        }
+        dy[i] = acc;
+    }
+}
+
+// dx[n][ci][iy][ix] = sum_{co,kh,kw} dy[n][co][oy][ox] * w[co][ci][kh][kw] with oy*sh - ph + kh == iy (same for x)
+__global__ void __launch_bounds__(kT)
+conv_bwd_x_kernel(const float* __restrict__ dy, const float* __restrict__ w, int N, int Ci, int H, int W, int Co, int KH,
+                  int KW, int sh, int sw, int ph, int pw, int OH, int OW, float* __restrict__ dx) {
+    const int64_t total = (int64_t)N * Ci * H * W;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int ix = (int)(i % W), iy = (int)((i / W) % H), ci = (int)((i / ((int64_t)W * H)) % Ci);
+        const int n = (int)(i / ((int64_t)W * H * Ci));
+        float acc = 0.f;
+        for (int kh = 0; kh < KH; ++kh) {
+            const int ty = iy + ph - kh;
+            if (ty < 0 || ty % sh) continue;
+            const int oy = ty / sh;
+            if (oy >= OH) continue;
+            for (int kw = 0; kw < KW; ++kw) {
+                const int tx = ix + pw - kw;
+                if (tx < 0 || tx % sw) continue;
+                const int ox = tx / sw;
+                if (ox >= OW) continue;
+                const float* d = dy + (((int64_t)n * Co) * OH + oy) * OW + ox;
+                const float* wp = w + ((int64_t)ci * KH + kh) * KW + kw;
+                for (int co = 0; co < Co; ++co)
+                    acc = fmaf(d[(int64_t)co * OH * OW], wp[(int64_t)co * Ci * KH * KW], acc);
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
+// dw[co][ci][kh][kw] = sum_{n,oy,ox} dy[n][co][oy][ox] * x[n][ci][oy*sh-ph+kh][ox*sw-pw+kw]; one warp per weight
+// (lanes stride over the n*OH*OW positions); db[co] = sum dy, from the (ci,kh,kw) = 0 warp
+__global__ void __launch_bounds__(kT)
+conv_bwd_w_kernel(const float* __restrict__ dy, const float* __restrict__ x, int N, int Ci, int H, int W, int Co, int KH,
+                  int KW, int sh, int sw, int ph, int pw, int OH, int OW, float* __restrict__ dw, float* __restrict__ db) {
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = (blockIdx.x * (int64_t)kT + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * kT) >> 5;
+    const int64_t total = (int64_t)Co * Ci * KH * KW;
+    const int npos = N * OH * OW;
+    for (int64_t i = gw; i < total; i += nw) {
+        const int kw = (int)(i % KW), kh = (int)((i / KW) % KH), ci = (int)((i / (KW * KH)) % Ci);
+        const int co = (int)(i / ((int64_t)KW * KH * Ci));
+        float acc = 0.f, accb = 0.f;
+        for (int p = lane; p < npos; p += 32) {
+            const int ox = p % OW, oy = (p / OW) % OH, n = p / (OW * OH);
+            const float d = dy[(((int64_t)n * Co + co) * OH + oy) * OW + ox];
+            accb += d;
+            const int iy = oy * sh - ph + kh, ix = ox * sw - pw + kw;
+            if (iy >= 0 && iy < H && ix >= 0 && ix < W) acc = fmaf(d, x[(((int64_t)n * Ci + ci) * H + iy) * W + ix], acc);
+        }
+        for (int s = 16; s > 0; s >>= 1) {
+            acc += __shfl_xor_sync(0xffffffffu, acc, s);
+            accb += __shfl_xor_sync(0xffffffffu, accb, s);
+        }
+        if (lane == 0) {
+            dw[i] = acc;
+            if (ci == 0 && kh == 0 && kw == 0) db[co] = accb;
+        }
+    }
+}
+
+// torch.optim.Adam (no weight decay, no amsgrad): p -= lr * mhat / (sqrt(vhat) + eps)
+__global__ void __launch_bounds__(kT)
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t total,
+            float grad_scale, float lr, float b1, float b2, float eps, float bc1, float bc2) {
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const float gi = g[i] * grad_scale;
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] -= (lr / bc1) * mi / (sqrtf(vi) / sqrtf(bc2) + eps);
+    }
+}
+
+}  // namespace
+
+// ================================================================================================================
+// trainer object
+// ================================================================================================================
+enum { P_C1W = 0, P_C1B, P_BN1W, P_BN1B, P_C2W, P_C2B, P_BN2W, P_BN2B, P_C3W, P_C3B, P_BN3W, P_BN3B, P_L5W, P_L5B,
+       P_AC1W, P_AC1B, P_AC2W, P_AC2B, P_AL3W, P_AL3B, P_F0W, P_F0B, P_F3W, P_F3B, P_F6W, P_F6B, P_F9W, P_F9B, P_F12W,
+       P_F12B, P_COUNT };
+
+struct gn_avm_trainer {
+    gn_handle* h;
+    int audio, S, B, C1, P1, P2, P3, L1, L2, fin;
+    int64_t max_n, K5;
+    int64_t off[P_COUNT + 1];        // offsets of each tensor in the flat parameter vector (model.parameters() order)
+    int64_t n_params, step;
+    float lr, b1, b2, eps;
+    float *params, *grads, *m, *v;   // flat fp32 [n_params]
+    float* rmean[3];                 // BatchNorm running buffers
+    float* rvar[3];
+    // activations of the last forward (fp32, NCHW) and their gradients
+    float *y[3], *p[3], *xh[3], *a[3], *istd[3];     // conv+ReLU, pooled, normalised, BN output, 1/std per block
+    uint8_t* arg[3];
+    float *h5, *ay1, *ay2, *fin_buf, *f[4], *z, *dz;
+    float *d_big0, *d_big1;          // ping-pong gradient buffers sized for the largest activation
+    float *d_fin, *d_f[4];
+    uint8_t* masks[5];               // keep-masks: linear5 (512), fusion.0/3/6/9 (512, 512, 256, 128)
+    void* arena;
+};
+
+namespace {
+const float* src_of(const gn_avm_state* sd, int k) {
+    switch (k) {
+        case P_C1W: return sd->conv1_w; case P_C1B: return sd->conv1_b; case P_BN1W: return sd->bn1_w; case P_BN1B: return sd->bn1_b;
+        case P_C2W: return sd->conv2_w; case P_C2B: return sd->conv2_b; case P_BN2W: return sd->bn2_w; case P_BN2B: return sd->bn2_b;
+        case P_C3W: return sd->conv3_w; case P_C3B: return sd->conv3_b; case P_BN3W: return sd->bn3_w; case P_BN3B: return sd->bn3_b;
+        case P_L5W: return sd->linear5_w; case P_L5B: return sd->linear5_b;
+        case P_AC1W: return sd->aconv1_w; case P_AC1B: return sd->aconv1_b; case P_AC2W: return sd->aconv2_w;
+        case P_AC2B: return sd->aconv2_b; case P_AL3W: return sd->alinear3_w; case P_AL3B: return sd->alinear3_b;
+        case P_F0W: return sd->f0_w; case P_F0B: return sd->f0_b; case P_F3W: return sd->f3_w; case P_F3B: return sd->f3_b;
+        case P_F6W: return sd->f6_w; case P_F6B: return sd->f6_b; case P_F9W: return sd->f9_w; case P_F9B: return sd->f9_b;
+        case P_F12W: return sd->f12_w; case P_F12B: return sd->f12_b;
+    }
+    return nullptr;
+}
+inline int cout_dim(int n, int k, int s, int p) { return (n + 2 * p - k) / s + 1; }
+}  // namespace
+
+extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const gn_avm_state* sd, int audio_included, int S,
+                                     int B, int64_t max_n, void* stream) {
+    if (!h || !out || !sd || max_n < 1 || S < 16 || S > 1024 || B < 4) return GN_E_ARG;
+    *out = nullptr;
+    gn_avm_trainer* t = reinterpret_cast<gn_avm_trainer*>(calloc(1, sizeof(gn_avm_trainer)));
+    if (!t) return GN_E_ARG;
+    t->h = h; t->audio = audio_included ? 1 : 0; t->S = S; t->B = B; t->max_n = max_n;
+    t->C1 = cout_dim(S, 3, 3, 3); t->P1 = t->C1 - 2; t->P2 = t->P1 - 2; t->P3 = t->P2 - 2;
+    t->L1 = cout_dim(B, 3, 2, 1); t->L2 = cout_dim(t->L1, 3, 2, 1);
+    t->fin = 512 + (t->audio ? 128 : 0);
+    t->K5 = 512LL * t->P3 * t->P3;
+    t->lr = 1e-3f; t->b1 = 0.9f; t->b2 = 0.999f; t->eps = 1e-8f;
+    if (t->P3 < 1) { free(t); return GN_E_SHAPE; }
+    const int64_t sz[P_COUNT] = {64 * 27, 64, 64, 64, 256 * 576, 256, 256, 256, 512 * 2304, 512, 512, 512, 512 * t->K5, 512,
+                                 t->audio ? 64 * 90 : 0, t->audio ? 64 : 0, t->audio ? 128 * 192 : 0, t->audio ? 128 : 0,
+                                 t->audio ? 128LL * 128 * t->L2 : 0, t->audio ? 128 : 0,
+                                 512LL * t->fin, 512, 512 * 512, 512, 256 * 512, 256, 128 * 256, 128, 128, 1};
+    t->off[0] = 0;
+    for (int k = 0; k < P_COUNT; ++k) {
+        if (sz[k] > 0 && !src_of(sd, k)) { free(t); return GN_E_ARG; }
+        t->off[k + 1] = t->off[k] + ((sz[k] + 3) & ~3LL);      // 16-byte aligned tensors
+    }
+    t->n_params = t->off[P_COUNT];
+    const float* bnm[3] = {sd->bn1_m, sd->bn2_m, sd->bn3_m};
+    const float* bnv[3] = {sd->bn1_v, sd->bn2_v, sd->bn3_v};
+    for (int i = 0; i < 3; ++i) if (!bnm[i] || !bnv[i]) { free(t); return GN_E_ARG; }
+
+    const int C[3] = {64, 256, 512}, OH[3] = {t->C1, t->P1, t->P2}, PH[3] = {t->P1, t->P2, t->P3};
+    const int64_t n = max_n;
+    int64_t big = 0;
+    size_t bytes = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        char* base = reinterpret_cast<char*>(t->arena);
+        size_t off = 0;
+        auto take = [&](int64_t elems, size_t es) -> void* {
+            off = (off + 255) & ~size_t(255);
+            void* p = pass ? base + off : nullptr;
+            off += (size_t)elems * es;
+            return p;
+        };
+        t->params = (float*)take(t->n_params, 4); t->grads = (float*)take(t->n_params, 4);
+        t->m = (float*)take(t->n_params, 4); t->v = (float*)take(t->n_params, 4);
+        for (int i = 0; i < 3; ++i) {
+            t->rmean[i] = (float*)take(C[i], 4); t->rvar[i] = (float*)take(C[i], 4); t->istd[i] = (float*)take(C[i], 4);
+            const int64_t ye = n * C[i] * OH[i] * OH[i], pe = n * C[i] * PH[i] * PH[i];
+            t->y[i] = (float*)take(ye, 4); t->p[i] = (float*)take(pe, 4); t->xh[i] = (float*)take(pe, 4);
+            t->a[i] = (float*)take(pe, 4); t->arg[i] = (uint8_t*)take(pe, 1);
+            if (ye > big) big = ye;
+        }
+        t->h5 = (float*)take(n * 512, 4);
+        t->ay1 = (float*)take(n * 64 * t->L1, 4); t->ay2 = (float*)take(n * 128 * t->L2, 4);
+        t->fin_buf = (float*)take(n * t->fin, 4);
+        const int fw[4] = {512, 512, 256, 128};
+        for (int i = 0; i < 4; ++i) { t->f[i] = (float*)take(n * fw[i], 4); t->d_f[i] = (float*)take(n * fw[i], 4); }
+        t->z = (float*)take(n, 4); t->dz = (float*)take(n, 4);
+        t->d_fin = (float*)take(n * t->fin, 4);
+        if (n * 128 * t->L2 > big) big = n * 128 * t->L2;
+        t->d_big0 = (float*)take(big, 4); t->d_big1 = (float*)take(big, 4);
+        const int mw[5] = {512, 512, 512, 256, 128};
+        for (int i = 0; i < 5; ++i) t->masks[i] = (uint8_t*)take(n * mw[i], 1);
+        if (pass == 0) {
+            bytes = off + 256;
+            cudaError_t e = cudaMalloc(&t->arena, bytes);
+            if (e != cudaSuccess) { free(t); return (int)e; }
+        }
+    }
+    cudaStream_t st = gn_stream(stream);
+    cudaError_t e = cudaMemsetAsync(t->arena, 0, bytes, st);
+    for (int k = 0; k < P_COUNT && e == cudaSuccess; ++k)
+        if (sz[k] > 0) e = cudaMemcpyAsync(t->params + t->off[k], src_of(sd, k), sz[k] * 4, cudaMemcpyDeviceToDevice, st);
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
+        e = cudaMemcpyAsync(t->rmean[i], bnm[i], C[i] * 4, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(t->rvar[i], bnv[i], C[i] * 4, cudaMemcpyDeviceToDevice, st);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { cudaFree(t->arena); free(t); return (int)e; }
+    *out = t;
+    return GN_OK;
+}
+
+extern "C" int gn_avm_trainer_destroy(gn_avm_trainer* t) {
+    if (!t) return GN_OK;
+    cudaFree(t->arena);
+    free(t);
+    return GN_OK;
+}
+
+extern "C" int64_t gn_avm_trainer_param_count(const gn_avm_trainer* t) { return t ? t->n_params : GN_E_ARG; }
+
+extern "C" int gn_avm_trainer_set_hyper(gn_avm_trainer* t, float lr, float beta1, float beta2, float eps) {
+    if (!t || lr < 0.f) return GN_E_ARG;
+    t->lr = lr; t->b1 = beta1; t->b2 = beta2; t->eps = eps;
+    return GN_OK;
+}
+
+// Copy parameters and BatchNorm running buffers into the (writable, device) tensors `dst` points at.
+extern "C" int gn_avm_trainer_export(gn_avm_trainer* t, const gn_avm_state* dst, void* stream) {
+    if (!t || !dst) return GN_E_ARG;
+    cudaStream_t st = gn_stream(stream);
+    for (int k = 0; k < P_COUNT; ++k) {
+        const int64_t cnt = t->off[k + 1] - t->off[k];
+        float* d = const_cast<float*>(src_of(dst, k));
+        if (cnt == 0 || !d) continue;
+        int64_t real = cnt;
+        if (k == P_C1W) real = 64 * 27; else if (k == P_F12B) real = 1;      // the only sizes that are not multiples of 4
+        GN_CUDA(cudaMemcpyAsync(d, t->params + t->off[k], real * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    const int C[3] = {64, 256, 512};
+    float* bm[3] = {const_cast<float*>(dst->bn1_m), const_cast<float*>(dst->bn2_m), const_cast<float*>(dst->bn3_m)};
+    float* bv[3] = {const_cast<float*>(dst->bn1_v), const_cast<float*>(dst->bn2_v), const_cast<float*>(dst->bn3_v)};
+    for (int i = 0; i < 3; ++i) {
+        if (bm[i]) GN_CUDA(cudaMemcpyAsync(bm[i], t->rmean[i], C[i] * 4, cudaMemcpyDeviceToDevice, st));
+        if (bv[i]) GN_CUDA(cudaMemcpyAsync(bv[i], t->rvar[i], C[i] * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return GN_OK;
+}
+
+extern "C" int gn_avm_trainer_grads(gn_avm_trainer* t, float** d_grads) {
+    if (!t || !d_grads) return GN_E_ARG;
+    *d_grads = t->grads;
+    return GN_OK;
+}
+
+// ================================================================================================================
+// forward + backward (train mode) and the optimizer step
+// ================================================================================================================
+#define TL(kern, total, ...)                                                             \
+    do {                                                                                 \
+        kern<<<grid_for((total), cap), kT, 0, st>>>(__VA_ARGS__);                        \
+        GN_LAUNCHED(t->h);                                                               \
+    } while (0)
+
+extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d_visual, const float* d_audio,
+                                               const float* d_labels, int64_t n64, int fixed_loss, float dropout_p,
+                                               const uint8_t* const* d_masks, unsigned long long seed, float* d_scores,
+                                               double* d_loss, void* stream) {
+    if (!t || !d_visual || !d_labels || n64 < 1 || n64 > t->max_n) return GN_E_ARG;
+    if (t->audio && !d_audio) return GN_E_ARG;
+    if (dropout_p < 0.f || dropout_p >= 1.f) return GN_E_ARG;
+    cudaStream_t st = gn_stream(stream);
+    const int n = (int)n64, cap = t->h->num_sms * 8;
+    float* P = t->params;
+    float* G = t->grads;
+    const int64_t* o = t->off;
+    const int C[3] = {64, 256, 512}, Cin[3] = {3, 64, 256}, IH[3] = {t->S, t->P1, t->P2};
+    const int OH[3] = {t->C1, t->P1, t->P2}, PH[3] = {t->P1, t->P2, t->P3};
+    const int cw[3] = {P_C1W, P_C2W, P_C3W}, cb[3] = {P_C1B, P_C2B, P_C3B}, bw[3] = {P_BN1W, P_BN2W, P_BN3W},
+              bb[3] = {P_BN1B, P_BN2B, P_BN3B};
+    const int stride[3] = {3, 1, 1}, pad[3] = {3, 1, 1};
+    const float scale = dropout_p > 0.f ? 1.f / (1.f - dropout_p) : 1.f;
+    const int mw[5] = {512, 512, 512, 256, 128};
+    const uint8_t* mk[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (dropout_p > 0.f) {
+        for (int i = 0; i < 5; ++i) {
+            if (d_masks && d_masks[i]) mk[i] = d_masks[i];
+            else {
+                TL(make_mask_kernel, (int64_t)n * mw[i], t->masks[i], (int64_t)n * mw[i],
+                   seed + 0x632BE59BD9B4E019ull * (unsigned long long)(i + 1), 1.f - dropout_p);
+                mk[i] = t->masks[i];
+            }
+        }
+    }
+    GN_CUDA(cudaMemsetAsync(G, 0, t->n_params * 4, st));
+
+    // ---------------- forward: VisBl (utils.py:172-195) ----------------
+    const float* x = d_visual;
+    for (int i = 0; i < 3; ++i) {
+        TL(conv_fwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], IH[i], C[i], 3,
+           3, stride[i], stride[i], pad[i], pad[i], OH[i], OH[i], 1, t->y[i]);
+        TL(pool_fwd_kernel, (int64_t)n * C[i] * PH[i] * PH[i], t->y[i], n * C[i], OH[i], OH[i], t->p[i], t->arg[i]);
+        bn_fwd_kernel<<<C[i], kT, 0, st>>>(t->p[i], n, C[i], PH[i] * PH[i], P + o[bw[i]], P + o[bb[i]], t->rmean[i],
+                                           t->rvar[i], t->xh[i], t->istd[i], t->a[i]);
+        GN_LAUNCHED(t->h);
+        x = t->a[i];
+    }
+    const int aoff = t->audio ? 128 : 0;
+    // linear5 + ReLU + Dropout -> columns [aoff, aoff+512) of the fusion input; NCHW flatten == the reference's order
+    TL(linear_fwd_kernel, (int64_t)n * 512 * 32, t->a[2], (int)t->K5, P + o[P_L5W], P + o[P_L5B], n, (int)t->K5, 512, 1, mk[0],
+       scale, t->fin_buf, t->fin, aoff);
+    // ---------------- forward: AudBl (utils.py:214-227) ----------------
+    if (t->audio) {
+        TL(conv_fwd_kernel, (int64_t)n * 64 * t->L1, d_audio, P + o[P_AC1W], P + o[P_AC1B], n, 30, 1, t->B, 64, 1, 3, 1, 2, 0, 1,
+           1, t->L1, 1, t->ay1);
+        TL(conv_fwd_kernel, (int64_t)n * 128 * t->L2, t->ay1, P + o[P_AC2W], P + o[P_AC2B], n, 64, 1, t->L1, 128, 1, 3, 1, 2, 0,
+           1, 1, t->L2, 1, t->ay2);
+        TL(linear_fwd_kernel, (int64_t)n * 128 * 32, t->ay2, 128 * t->L2, P + o[P_AL3W], P + o[P_AL3B], n, 128 * t->L2, 128, 1,
+           (const uint8_t*)nullptr, 1.f, t->fin_buf, t->fin, 0);
+    }
+    // ---------------- forward: fusion (utils.py:242-258) ----------------
+    const int fw[4] = {512, 512, 256, 128}, fk[4] = {t->fin, 512, 512, 256};
+    const int fwi[4] = {P_F0W, P_F3W, P_F6W, P_F9W}, fbi[4] = {P_F0B, P_F3B, P_F6B, P_F9B};
+    const float* hin = t->fin_buf;
+    for (int i = 0; i < 4; ++i) {
+        TL(linear_fwd_kernel, (int64_t)n * fw[i] * 32, hin, fk[i], P + o[fwi[i]], P + o[fbi[i]], n, fk[i], fw[i], 1, mk[i + 1],
+           scale, t->f[i], fw[i], 0);
+        hin = t->f[i];
+    }
+    TL(linear_fwd_kernel, (int64_t)n * 32, t->f[3], 128, P + o[P_F12W], P + o[P_F12B], n, 128, 1, 0, (const uint8_t*)nullptr,
+       1.f, t->z, 1, 0);
+    loss_kernel<<<1, kT, 0, st>>>(t->z, d_labels, n, fixed_loss, d_scores, t->dz, d_loss);
+    GN_LAUNCHED(t->h);
+
+    // ---------------- backward: fusion ----------------
+    TL(linear_bwd_w_kernel, 128, t->dz, 1, 0, t->f[3], 128, n, 128, 1, G + o[P_F12W], G + o[P_F12B]);
+    TL(linear_bwd_x_kernel, (int64_t)n * 128, t->dz, 1, 0, P + o[P_F12W], n, 128, 1, t->d_f[3]);
+    for (int i = 3; i >= 0; --i) {
+        TL(relu_drop_bwd_kernel, (int64_t)n * fw[i], t->d_f[i], t->f[i], mk[i + 1], scale, (int64_t)n * fw[i]);
+        const float* xin = i ? t->f[i - 1] : t->fin_buf;
+        TL(linear_bwd_w_kernel, (int64_t)fw[i] * fk[i], t->d_f[i], fw[i], 0, xin, fk[i], n, fk[i], fw[i], G + o[fwi[i]],
+           G + o[fbi[i]]);
+        TL(linear_bwd_x_kernel, (int64_t)n * fk[i], t->d_f[i], fw[i], 0, P + o[fwi[i]], n, fk[i], fw[i],
+           i ? t->d_f[i - 1] : t->d_fin);
+    }
+    // d_fin = gradient w.r.t. [audio128 | visual512] (both are post-ReLU outputs; the visual half also post-dropout)
+    // ---------------- backward: AudBl ----------------
+    if (t->audio) {
+        // columns [0,128): gate by the ReLU of linear3 (no dropout)
+        float* dl3 = t->d_big0;          // [n][128]
+        GN_CUDA(cudaMemcpy2DAsync(dl3, 128 * 4, t->d_fin, (size_t)t->fin * 4, 128 * 4, n, cudaMemcpyDeviceToDevice, st));
+        float* al3 = t->d_big1;          // [n][128] copy of the activations for the gate
+        GN_CUDA(cudaMemcpy2DAsync(al3, 128 * 4, t->fin_buf, (size_t)t->fin * 4, 128 * 4, n, cudaMemcpyDeviceToDevice, st));
+        TL(relu_drop_bwd_kernel, (int64_t)n * 128, dl3, al3, (const uint8_t*)nullptr, 1.f, (int64_t)n * 128);
+        const int K3 = 128 * t->L2;
+        TL(linear_bwd_w_kernel, (int64_t)128 * K3, dl3, 128, 0, t->ay2, K3, n, K3, 128, G + o[P_AL3W], G + o[P_AL3B]);
+        float* day2 = t->d_big1;         // [n][128][L2]  (al3 is dead after the gate)
+        TL(linear_bwd_x_kernel, (int64_t)n * K3, dl3, 128, 0, P + o[P_AL3W], n, K3, 128, day2);
+        TL(relu_drop_bwd_kernel, (int64_t)n * K3, day2, t->ay2, (const uint8_t*)nullptr, 1.f, (int64_t)n * K3);
+        TL(conv_bwd_w_kernel, (int64_t)128 * 192 * 32, day2, t->ay1, n, 64, 1, t->L1, 128, 1, 3, 1, 2, 0, 1, 1, t->L2,
+           G + o[P_AC2W], G + o[P_AC2B]);
+        float* day1 = t->d_big0;         // [n][64][L1]
+        TL(conv_bwd_x_kernel, (int64_t)n * 64 * t->L1, day2, P + o[P_AC2W], n, 64, 1, t->L1, 128, 1, 3, 1, 2, 0, 1, 1, t->L2,
+           day1);
+        TL(relu_drop_bwd_kernel, (int64_t)n * 64 * t->L1, day1, t->ay1, (const uint8_t*)nullptr, 1.f, (int64_t)n * 64 * t->L1);
+        TL(conv_bwd_w_kernel, (int64_t)64 * 90 * 32, day1, d_audio, n, 30, 1, t->B, 64, 1, 3, 1, 2, 0, 1, 1, t->L1,
+           G + o[P_AC1W], G + o[P_AC1B]);
+    }
+    // ---------------- backward: VisBl ----------------
+    float* dh5 = t->d_big0;              // [n][512]
+    GN_CUDA(cudaMemcpy2DAsync(dh5, 512 * 4, t->d_fin + aoff, (size_t)t->fin * 4, 512 * 4, n, cudaMemcpyDeviceToDevice, st));
+    GN_CUDA(cudaMemcpy2DAsync(t->h5, 512 * 4, t->fin_buf + aoff, (size_t)t->fin * 4, 512 * 4, n, cudaMemcpyDeviceToDevice, st));
+    TL(relu_drop_bwd_kernel, (int64_t)n * 512, dh5, t->h5, mk[0], scale, (int64_t)n * 512);
+    TL(linear_bwd_w_kernel, 512 * t->K5, dh5, 512, 0, t->a[2], (int)t->K5, n, (int)t->K5, 512, G + o[P_L5W], G + o[P_L5B]);
+    float* da = t->d_big1;               // gradient w.r.t. the BN output of block i
+    TL(linear_bwd_x_kernel, (int64_t)n * t->K5, dh5, 512, 0, P + o[P_L5W], n, (int)t->K5, 512, da);
+    for (int i = 2; i >= 0; --i) {
+        float* dp = (da == t->d_big1) ? t->d_big0 : t->d_big1;
+        bn_bwd_kernel<<<C[i], kT, 0, st>>>(da, t->xh[i], t->istd[i], P + o[bw[i]], n, C[i], PH[i] * PH[i], dp, G + o[bw[i]],
+                                           G + o[bb[i]]);
+        GN_LAUNCHED(t->h);
+        float* dy = da;                  // reuse: da is dead now
+        TL(pool_relu_bwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], dp, t->arg[i], t->y[i], n * C[i], OH[i], OH[i], dy);
+        const float* xin = i ? t->a[i - 1] : d_visual;
+        TL(conv_bwd_w_kernel, (int64_t)C[i] * Cin[i] * 9 * 32, dy, xin, n, Cin[i], IH[i], IH[i], C[i], 3, 3, stride[i], stride[i],
+           pad[i], pad[i], OH[i], OH[i], G + o[cw[i]], G + o[cb[i]]);
+        if (i > 0) {
+            TL(conv_bwd_x_kernel, (int64_t)n * Cin[i] * IH[i] * IH[i], dy, P + o[cw[i]], n, Cin[i], IH[i], IH[i], C[i], 3, 3,
+               stride[i], stride[i], pad[i], pad[i], OH[i], OH[i], dp);
+            da = dp;
+        }
+    }
+    return GN_OK;
+}
+
+extern "C" int gn_avm_trainer_adam_step(gn_avm_trainer* t, float grad_scale, void* stream) {
+    if (!t) return GN_E_ARG;
+    cudaStream_t st = gn_stream(stream);
+    t->step += 1;
+    const float bc1 = 1.f - powf(t->b1, (float)t->step), bc2 = 1.f - powf(t->b2, (float)t->step);
+    adam_kernel<<<grid_for(t->n_params, t->h->num_sms * 8), kT, 0, st>>>(t->params, t->grads, t->m, t->v, t->n_params,
+                                                                         grad_scale, t->lr, t->b1, t->b2, t->eps, bc1, bc2);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+
+extern "C" int gn_avm_train_step(gn_avm_trainer* t, const float* d_visual, const float* d_audio, const float* d_labels,
+                                 int64_t n, int fixed_loss, float dropout_p, const uint8_t* const* d_masks,
+                                 unsigned long long seed, float* d_scores, double* d_loss, void* stream) {
+    int rc = gn_avm_trainer_forward_backward(t, d_visual, d_audio, d_labels, n, fixed_loss, dropout_p, d_masks, seed,
+                                             d_scores, d_loss, stream);
+    if (rc) return rc;
+    return gn_avm_trainer_adam_step(t, 1.f, stream);
+}

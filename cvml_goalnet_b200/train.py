@@ -149,3 +149,148 @@ def fusion_flat(state_dict) -> np.ndarray:
             v = state_dict[name + suffix]
             parts.append((v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v)).astype(np.float32).ravel())
     return np.concatenate(parts)
+
+
+DROPOUT_WIDTHS = (512, 512, 512, 256, 128)     # linear5 (utils.py:168), fusion.0/3/6/9 (utils.py:245-254)
+
+
+class AVMTrainer:
+    """The reference's train sub-step (main.py:187-193) for the WHOLE model in train mode.
+
+    `step(audios, frames, labels)` = optimizer.zero_grad(); pred = model(audios, frames); loss = MSELoss()(pred,
+    labels); loss.backward(); optimizer.step() with optim.Adam(model.parameters(), lr) -- BatchNorm uses the
+    sub-batch statistics and updates its running buffers, Dropout(0.2) is active (quirk Q4), the loss broadcasts to
+    N x N unless fixed_loss (quirk Q5).  Arithmetic: fp32 CUDA kernels in libgoalnet_b200.so (gn_train_avm.cu).
+    `sync_model()` writes the trained parameters and running statistics back into `model`, whose eval-mode forward
+    (the tensor-core scoring path) then uses them.  Data parallel: gradients are averaged over `process_group`.
+    """
+
+    def __init__(self, model: AVM, max_frames: int = 10, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 fixed_loss: bool = False, dropout_p: float = 0.2, device=None, process_group=None, seed: int = 12344321):
+        self.dev = _device(device)
+        self.model = model
+        self.fixed_loss, self.dropout_p = bool(fixed_loss), float(dropout_p)
+        self.group, self.seed, self.steps, self.max_frames = process_group, int(seed), 0, int(max_frames)
+        lib = _lib.load()
+        st, keep = self._state_struct(model.state_dict(), clone=False)
+        p = C.c_void_p()
+        with torch.cuda.device(self.dev):
+            _lib.check(lib.gn_avm_trainer_create(_lib.handle(self.dev.index), C.byref(p), C.byref(st),
+                                                 int(model.audio_included), model.S, model.B, self.max_frames,
+                                                 _stream(self.dev)), "gn_avm_trainer_create")
+            torch.cuda.current_stream(self.dev).synchronize()
+        del keep
+        self._t = p
+        _lib.check(lib.gn_avm_trainer_set_hyper(self._t, lr, betas[0], betas[1], eps), "gn_avm_trainer_set_hyper")
+        self.n_params = int(lib.gn_avm_trainer_param_count(self._t))
+        g = C.c_void_p()
+        _lib.check(lib.gn_avm_trainer_grads(self._t, C.byref(g)), "gn_avm_trainer_grads")
+        self._grads_ptr = g.value
+        self.scores = torch.empty(self.max_frames, dtype=torch.float32, device=self.dev)
+        self.loss = torch.zeros(1, dtype=torch.float64, device=self.dev)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_t", None):
+                _lib.load().gn_avm_trainer_destroy(self._t)
+                self._t = None
+        except Exception:
+            pass
+
+    def _state_struct(self, sd, clone):
+        st, keep = _lib.gn_avm_state(), {}
+        for field, key in _lib.STATE_KEYS.items():
+            if key not in sd:
+                setattr(st, field, None)
+                continue
+            t = sd[key].detach().to(device=self.dev, dtype=torch.float32).contiguous()
+            if clone:
+                t = t.clone()
+            keep[key] = t
+            setattr(st, field, t.data_ptr())
+        return st, keep
+
+    def grads(self) -> torch.Tensor:
+        """Flat float32 gradient of the last forward_backward (a view of the library's buffer)."""
+        n = self.n_params
+
+        class _Holder:     # __cuda_array_interface__ view of library-owned memory
+            pass
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (self._grads_ptr, False), "version": 2}
+        return torch.as_tensor(h, device=self.dev)
+
+    def forward_backward(self, audios, frames, labels, masks=None):
+        vis = _to_dev(frames, torch.float32, self.dev)
+        n = int(vis.shape[0])
+        assert vis.dim() == 4 and tuple(vis.shape[1:]) == (3, self.model.S, self.model.S), "E: Invalid shape for visual input"
+        assert 1 <= n <= self.max_frames, "E: sub-batch larger than max_frames"
+        aud = None
+        if self.model.audio_included:
+            aud = _to_dev(audios, torch.float32, self.dev)
+            assert tuple(aud.shape) == (n, 30, self.model.B), "E: Inconsistency in data loader definition"
+        lab = _to_dev(labels, torch.float32, self.dev).reshape(-1)
+        assert lab.numel() == n, "E: Inconsistency in data loader definition"
+        marg, keep = None, None
+        if masks is not None:
+            assert len(masks) == 5, "E: five dropout masks expected (linear5, fusion.0/3/6/9)"
+            keep = [_to_dev(m, torch.uint8, self.dev) for m in masks]
+            for m, wdt in zip(keep, DROPOUT_WIDTHS):
+                assert tuple(m.shape) == (n, wdt), "E: dropout mask shape"
+            marg = C.cast((C.c_void_p * 5)(*[m.data_ptr() for m in keep]), C.POINTER(C.c_void_p))
+        seed = (self.seed + 0x9E3779B97F4A7C15 * (self.steps + 1)) & 0xFFFFFFFFFFFFFFFF
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.load().gn_avm_trainer_forward_backward(
+                self._t, _ptr(vis), _ptr(aud), _ptr(lab), n, int(self.fixed_loss), self.dropout_p, marg, seed,
+                _ptr(self.scores), _ptr(self.loss), _stream(self.dev)), "gn_avm_trainer_forward_backward")
+        return n
+
+    def optimizer_step(self):
+        scale = 1.0
+        import torch.distributed as dist
+        if self.group is not False and dist.is_available() and dist.is_initialized():
+            group = self.group if self.group is not None else dist.group.WORLD
+            world = dist.get_world_size(group)
+            if world > 1:
+                dist.all_reduce(self.grads(), op=dist.ReduceOp.SUM, group=group)
+                scale = 1.0 / world
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.load().gn_avm_trainer_adam_step(self._t, scale, _stream(self.dev)), "gn_avm_trainer_adam_step")
+        self.steps += 1
+
+    def step(self, audios, frames, labels, masks=None):
+        """One train sub-step.  Returns (loss float64[1] on the device, train-mode predictions (n,1))."""
+        n = self.forward_backward(audios, frames, labels, masks)
+        self.optimizer_step()
+        return self.loss, self.scores[:n].reshape(n, 1)
+
+    def state_dict(self) -> dict:
+        """Trained parameters + BatchNorm running buffers keyed like the reference's state_dict (CUDA tensors)."""
+        st, keep = self._state_struct(self.model.state_dict(), clone=True)
+        with torch.cuda.device(self.dev):
+            _lib.check(_lib.load().gn_avm_trainer_export(self._t, C.byref(st), _stream(self.dev)), "gn_avm_trainer_export")
+        return keep
+
+    def sync_model(self):
+        sd = self.model.state_dict()
+        for k, v in self.state_dict().items():
+            sd[k].copy_(v.to(sd[k].device))
+        self.model.invalidate()
+
+    PARAM_ORDER = ("visbl.conv1", "visbl.bnorm1", "visbl.conv2", "visbl.bnorm2", "visbl.conv3", "visbl.bnorm3",
+                   "visbl.linear5", "audbl.conv1", "audbl.conv2", "audbl.linear3",
+                   "fusion.0", "fusion.3", "fusion.6", "fusion.9", "fusion.12")
+
+    def grad_dict(self) -> dict:
+        """Gradients of the last forward_backward split per parameter (model.parameters() order; every tensor starts
+        at a multiple of 4 elements in the flat vector)."""
+        flat, sd, out, off = self.grads(), self.model.state_dict(), {}, 0
+        for name in self.PARAM_ORDER:
+            if name.startswith("audbl") and not self.model.audio_included:
+                continue
+            for suffix in (".weight", ".bias"):
+                shp = sd[name + suffix].shape
+                cnt = int(np.prod(shp))
+                out[name + suffix] = flat[off:off + cnt].reshape(tuple(shp)).clone()
+                off += (cnt + 3) // 4 * 4
+        return out

@@ -215,6 +215,42 @@ int gn_fusion_train_step(gn_fusion_trainer* t, const float* d_features, const fl
                          float* d_grads, float* d_scores, double* d_loss, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Full-AVM training sub-step -- replaces main.py:187-193 for the WHOLE network in train
+ * mode, as the reference runs it (quirk Q4): BatchNorm2d normalises with the sub-batch statistics
+ * and updates its running buffers (momentum 0.1, unbiased running variance), Dropout(0.2) follows
+ * linear5 and fusion.0/3/6/9 (utils.py:168,245-254), the loss is MSELoss as written (N x N
+ * broadcast, quirk Q5; fixed_loss = 1 for the element-wise form) and the optimizer is
+ * optim.Adam(model.parameters(), lr = 0.001) (main.py:70).  Sub-batches are 10 frames (main.py:47).
+ * Parameters live in one flat float32 vector in model.parameters() order (each tensor padded to a
+ * multiple of 4 elements); its gradient vector is exposed for data-parallel all-reduce.
+ * d_masks: NULL or 5 device pointers to uint8 keep-masks [n][512],[n][512],[n][512],[n][256],
+ * [n][128] (linear5, fusion.0/3/6/9); NULL entries / NULL array -> counter-based generator keyed by
+ * `seed`.  dropout_p = 0 disables dropout.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct gn_avm_trainer gn_avm_trainer;
+int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const gn_avm_state* sd, int audio_included, int S,
+                          int B, int64_t max_n, void* stream);
+int gn_avm_trainer_destroy(gn_avm_trainer* t);
+int64_t gn_avm_trainer_param_count(const gn_avm_trainer* t);
+int gn_avm_trainer_set_hyper(gn_avm_trainer* t, float lr, float beta1, float beta2, float eps);
+/* d_visual float32 [n][3][S][S]; d_audio float32 [n][30][B] (NULL without audio branch); d_labels float32 [n];
+ * d_scores float32 [n] train-mode predictions (out, may be NULL); d_loss double[1] (out, may be NULL). */
+int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d_visual, const float* d_audio,
+                                    const float* d_labels, int64_t n, int fixed_loss, float dropout_p,
+                                    const uint8_t* const* d_masks, unsigned long long seed, float* d_scores,
+                                    double* d_loss, void* stream);
+/* Device pointer to the flat gradient of the last forward_backward (all-reduce it for data parallel). */
+int gn_avm_trainer_grads(gn_avm_trainer* t, float** d_grads);
+int gn_avm_trainer_adam_step(gn_avm_trainer* t, float grad_scale, void* stream);
+/* forward_backward + adam_step(1): the single-GPU train sub-step. */
+int gn_avm_train_step(gn_avm_trainer* t, const float* d_visual, const float* d_audio, const float* d_labels,
+                      int64_t n, int fixed_loss, float dropout_p, const uint8_t* const* d_masks,
+                      unsigned long long seed, float* d_scores, double* d_loss, void* stream);
+/* Copy the trained parameters and BatchNorm running buffers into the WRITABLE device tensors `dst`
+ * points at (same shapes as at creation; NULL entries are skipped). */
+int gn_avm_trainer_export(gn_avm_trainer* t, const gn_avm_state* dst, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Validation kernels (plain CUDA-core fp32 accumulate).  NOT a backend: tests use them to localise
  * a tensor-core kernel fault layer by layer on the GPU.  Same argument meaning as gn_avm_forward.
  * ------------------------------------------------------------------------------------------- */

@@ -250,6 +250,55 @@ def gen_train(R):
     np.savez_compressed(os.path.join(GOLD, "train.npz"), **out)
 
 
+def gen_train_avm(R):
+    """The reference's train sub-step (main.py:187-193) on the WHOLE reference AVM object in train mode (BatchNorm
+    batch statistics + running-buffer updates, as the reference runs it), nn.MSELoss as written, optim.Adam(lr=0.001)
+    over model.parameters() (main.py:70), sub-batch of 10 frames (main.py:47).  Dropout probabilities are set to 0 so
+    that the vectors are reproducible (mask semantics are covered by the oracle <-> CUDA tests)."""
+    import torch
+    import warnings
+    out = {}
+    rng = np.random.default_rng(syn.SEED_BASE + 43)
+    for tag, audio_included, n in (("av", True, 10), ("v", False, 7)):
+        w = syn.make_weights(seed=1, audio_included=audio_included)
+        m = R.AVM(audio_included=audio_included)
+        vis = rng.random((n, 3, 40, 40)).astype(np.float32)
+        aud = (25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)
+        lab = rng.integers(1, 6, n).astype(np.float32)
+        with torch.no_grad():
+            m(torch.from_numpy(aud), torch.from_numpy(vis))                    # materialise the Lazy* layers
+        m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in w.items()})
+        m.train()
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+        opt = torch.optim.Adam(params=m.parameters(), lr=0.001)
+        crit = torch.nn.MSELoss()
+        losses = []
+        for step in range(2):
+            opt.zero_grad()
+            pred = m(torch.from_numpy(aud), torch.from_numpy(vis))
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                loss = crit(pred, torch.from_numpy(lab))
+            loss.backward()
+            if step == 0:
+                out[f"{tag}_pred"] = pred.detach().numpy()[:, 0].copy()
+                for k, p_ in m.named_parameters():
+                    g = p_.grad.numpy()
+                    out[f"{tag}_gl2_{k}"] = np.array(np.sqrt(np.sum(np.square(g.astype(np.float64)))))
+                    out[f"{tag}_gs_{k}"] = g.ravel()[::997].copy()
+            opt.step()
+            losses.append(float(loss.item()))
+        out[f"{tag}_vis"], out[f"{tag}_aud"], out[f"{tag}_labels"] = vis, aud, lab
+        out[f"{tag}_losses"] = np.array(losses)
+        for k, v in m.state_dict().items():
+            if "num_batches" in k:
+                continue
+            out[f"{tag}_p2_{k}"] = v.detach().numpy().ravel()[::997].copy()
+    np.savez_compressed(os.path.join(GOLD, "train_avm.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     R = import_reference_utils()
@@ -259,6 +308,7 @@ def main():
     gen_postprocess(R)
     gen_audio(R)
     gen_train(R)
+    gen_train_avm(R)
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

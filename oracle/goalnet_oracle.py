@@ -479,3 +479,78 @@ def fusion_train_steps(sd: dict, features, labels, steps: int = 1, fixed_loss: b
         losses.append(float(loss.item()))
     flat = np.concatenate([p.detach().numpy().ravel() for p in params])
     return np.array(losses), grads0, pred0, flat
+
+
+# ------------------------------------------------------------------------------------------------
+# full-AVM training sub-step -- restates main.py:187-193 for the whole network in TRAIN mode
+# ------------------------------------------------------------------------------------------------
+AVM_PARAM_KEYS = ["visbl.conv1", "visbl.bnorm1", "visbl.conv2", "visbl.bnorm2", "visbl.conv3", "visbl.bnorm3",
+                  "visbl.linear5", "audbl.conv1", "audbl.conv2", "audbl.linear3",
+                  "fusion.0", "fusion.3", "fusion.6", "fusion.9", "fusion.12"]
+
+
+def avm_train_steps(sd: dict, audio, visual, labels, steps: int = 1, audio_included: bool = True, masks=None,
+                    dropout_p: float = 0.2, fixed_loss: bool = False, lr: float = 1e-3, betas=(0.9, 0.999),
+                    eps: float = 1e-8):
+    """`steps` iterations of the reference's train sub-step (main.py:187-193: zero_grad, forward, MSELoss, backward,
+    Adam step; optim.Adam(lr) of main.py:70) on ONE sub-batch, float32 on the CPU, model in train mode as the
+    reference runs it (quirk Q4): BatchNorm2d normalises with the sub-batch statistics and updates its running
+    buffers (momentum 0.1), Dropout(0.2) follows linear5 and fusion.0/3/6/9 (utils.py:168,245-254).
+    `masks`: per step a list of five uint8 keep-masks ([n,512] x3, [n,256], [n,128]) applied as x * mask / (1-p);
+    None = dropout off.  As written the loss broadcasts (N,1) against (N,) to N x N (quirk Q5).
+    Returns (losses, scores of the first step, gradients of the first step {key: array}, final state_dict)."""
+    import torch
+    import torch.nn.functional as F
+    import warnings
+    P, buf = {}, {}
+    for k in AVM_PARAM_KEYS:
+        if k.startswith("audbl") and not audio_included:
+            continue
+        P[k + ".weight"] = torch.tensor(np.asarray(sd[k + ".weight"], np.float32), requires_grad=True)
+        P[k + ".bias"] = torch.tensor(np.asarray(sd[k + ".bias"], np.float32), requires_grad=True)
+    for i in (1, 2, 3):
+        buf[f"visbl.bnorm{i}.running_mean"] = torch.tensor(np.asarray(sd[f"visbl.bnorm{i}.running_mean"], np.float32))
+        buf[f"visbl.bnorm{i}.running_var"] = torch.tensor(np.asarray(sd[f"visbl.bnorm{i}.running_var"], np.float32))
+    opt = torch.optim.Adam(list(P.values()), lr=lr, betas=betas, eps=eps)
+    crit = torch.nn.MSELoss()
+    vis = torch.as_tensor(np.asarray(visual, np.float32))
+    aud = torch.as_tensor(np.asarray(audio, np.float32)) if audio_included else None
+    lab = torch.as_tensor(np.asarray(labels, np.float32))
+    losses, scores0, grads0 = [], None, None
+
+    def drop(h, s, j):
+        if masks is None:
+            return h
+        return h * torch.as_tensor(np.asarray(masks[s][j], np.float32)) / (1.0 - dropout_p)
+
+    for s in range(steps):
+        opt.zero_grad()
+        x = vis
+        for i, (stride, pad) in zip((1, 2, 3), ((3, 3), (1, 1), (1, 1))):           # utils.py:174-187
+            x = F.conv2d(x, P[f"visbl.conv{i}.weight"], P[f"visbl.conv{i}.bias"], stride=stride, padding=pad)
+            x = F.max_pool2d(F.relu(x), kernel_size=3, stride=1)
+            x = F.batch_norm(x, buf[f"visbl.bnorm{i}.running_mean"], buf[f"visbl.bnorm{i}.running_var"],
+                             P[f"visbl.bnorm{i}.weight"], P[f"visbl.bnorm{i}.bias"], True, 0.1, 1e-5)
+        v = drop(F.relu(F.linear(x.flatten(1), P["visbl.linear5.weight"], P["visbl.linear5.bias"])), s, 0)
+        if audio_included:
+            a = F.relu(F.conv1d(aud, P["audbl.conv1.weight"], P["audbl.conv1.bias"], stride=2, padding=1))
+            a = F.relu(F.conv1d(a, P["audbl.conv2.weight"], P["audbl.conv2.bias"], stride=2, padding=1))
+            a = F.relu(F.linear(a.flatten(1), P["audbl.linear3.weight"], P["audbl.linear3.bias"]))
+            h = torch.cat((a, v), dim=-1)
+        else:
+            h = v
+        for j, idx in enumerate((0, 3, 6, 9)):
+            h = drop(F.relu(F.linear(h, P[f"fusion.{idx}.weight"], P[f"fusion.{idx}.bias"])), s, j + 1)
+        pred = 4 * torch.sigmoid(F.linear(h, P["fusion.12.weight"], P["fusion.12.bias"])) + 1
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            loss = crit(pred, lab) if not fixed_loss else crit(pred[:, 0], lab)
+        loss.backward()
+        if s == 0:
+            scores0 = pred.detach().numpy()[:, 0].copy()
+            grads0 = {k: p.grad.detach().numpy().copy() for k, p in P.items()}
+        opt.step()
+        losses.append(float(loss.item()))
+    out = {k: p.detach().numpy().copy() for k, p in P.items()}
+    out.update({k: b.numpy().copy() for k, b in buf.items()})
+    return np.array(losses), scores0, grads0, out

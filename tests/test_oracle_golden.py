@@ -121,3 +121,18 @@ def test_fusion_train_step_matches_reference(golden):
     losses, _, pred, _ = O.fusion_train_steps(w, g["av_x"], g["av_labels"], steps=1)
     lab = g["av_labels"]
     assert abs(losses[0] - (np.mean(pred ** 2) - 2 * pred.mean() * lab.mean() + np.mean(lab ** 2))) <= 1e-5
+
+
+def test_avm_train_steps_match_reference_model(golden):
+    """Oracle restatement of the full-AVM train sub-step vs the reference AVM object in train mode (gen_train_avm)."""
+    g = golden("train_avm")
+    for tag, audio_included in (("av", True), ("v", False)):
+        w = syn.make_weights(seed=1, audio_included=audio_included)
+        losses, scores0, grads0, out = O.avm_train_steps(w, g[f"{tag}_aud"], g[f"{tag}_vis"], g[f"{tag}_labels"], steps=2,
+                                                         audio_included=audio_included)
+        np.testing.assert_allclose(losses, g[f"{tag}_losses"], rtol=1e-6)
+        np.testing.assert_allclose(scores0, g[f"{tag}_pred"], atol=1e-6)
+        for k, v in grads0.items():
+            np.testing.assert_allclose(v.ravel()[::997], g[f"{tag}_gs_{k}"], rtol=1e-4, atol=1e-9, err_msg=k)
+        for k, v in out.items():
+            np.testing.assert_allclose(v.ravel()[::997], g[f"{tag}_p2_{k}"], rtol=1e-5, atol=1e-6, err_msg=k)

@@ -129,3 +129,104 @@ def test_trainer_argument_errors():
         tr.forward_backward(np.zeros((4, 640), np.float32), np.zeros(5, np.float32))
     with pytest.raises(GoalNetError):
         tr.forward_backward(np.zeros((300, 640), np.float32), np.zeros(300, np.float32))   # > max_rows
+
+
+# ------------------------------------------------------------------ full-AVM train sub-step
+def _avm_case(n, audio_included, seed):
+    rng = np.random.default_rng(seed)
+    w = syn.make_weights(seed=1, audio_included=audio_included)
+    vis = rng.random((n, 3, 40, 40)).astype(np.float32)
+    aud = (25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)
+    lab = rng.integers(1, 6, n).astype(np.float32)
+    return w, vis, aud, lab
+
+
+def _rel(a, b):
+    return float(max(np.abs(a - b).max() - 1e-7, 0.0) / max(np.abs(b).max(), 1e-12))
+
+
+@pytest.mark.parametrize("audio_included,n,fixed", [(True, 10, False), (False, 7, False), (True, 4, True)])
+def test_avm_train_step_vs_oracle_no_dropout(cuda_device, audio_included, n, fixed):
+    from cvml_goalnet_b200 import utils as U
+    from cvml_goalnet_b200.train import AVMTrainer
+    w, vis, aud, lab = _avm_case(n, audio_included, 5 + n)
+    m = U.AVM(audio_included)
+    m.load_state_dict(w)
+    tr = AVMTrainer(m, max_frames=16, dropout_p=0.0, fixed_loss=fixed)
+    losses, scores0, grads0, out = O.avm_train_steps(w, aud, vis, lab, steps=2, audio_included=audio_included,
+                                                     fixed_loss=fixed)
+    tr.forward_backward(aud, vis, lab)
+    assert abs(float(tr.loss.item()) - losses[0]) <= 1e-5 * abs(losses[0])
+    assert np.abs(tr.scores[:n].cpu().numpy() - scores0).max() <= 2e-5
+    g = tr.grad_dict()
+    for k, ref in grads0.items():
+        assert _rel(g[k].cpu().numpy(), ref) <= 2e-3, k           # fp32, different summation order than torch/oneDNN
+    tr.optimizer_step()
+    loss2, _ = tr.step(aud, vis, lab)
+    assert abs(float(loss2.item()) - losses[1]) <= 2e-4 * abs(losses[1])
+    sd = tr.state_dict()
+    for k, ref in out.items():
+        got = sd[k].cpu().numpy()
+        # Adam's first steps move every weight by ~lr * sign(gradient) whatever the gradient's size, so an element
+        # whose gradient is rounding noise (e.g. a conv bias in front of a batch-statistics BatchNorm) may step the
+        # other way: bound the bulk tightly and the outliers by two full steps
+        err = np.abs(got - ref)
+        assert np.median(err) <= 5e-5 and np.mean(err <= 2.5e-4) >= 0.7, k
+        assert err.max() <= 2 * 2 * 1e-3 + 1e-4 * np.abs(ref).max(), k
+
+
+def test_avm_train_step_golden_reference_model(cuda_device, golden):
+    """Against vectors produced by the REFERENCE AVM object in train mode (oracle/gen_golden.py: gen_train_avm)."""
+    from cvml_goalnet_b200 import utils as U
+    from cvml_goalnet_b200.train import AVMTrainer
+    g = golden("train_avm")
+    for tag, audio_included in (("av", True), ("v", False)):
+        w = syn.make_weights(seed=1, audio_included=audio_included)
+        m = U.AVM(audio_included)
+        m.load_state_dict(w)
+        tr = AVMTrainer(m, max_frames=10, dropout_p=0.0)
+        vis, aud, lab = g[f"{tag}_vis"], g[f"{tag}_aud"], g[f"{tag}_labels"]
+        tr.forward_backward(aud, vis, lab)
+        assert abs(float(tr.loss.item()) - g[f"{tag}_losses"][0]) <= 1e-5 * g[f"{tag}_losses"][0]
+        assert np.abs(tr.scores[:len(lab)].cpu().numpy() - g[f"{tag}_pred"]).max() <= 2e-5
+        gd = tr.grad_dict()
+        for k, v in gd.items():
+            got = v.cpu().numpy()
+            ref = g[f"{tag}_gs_{k}"]          # (a dead channel's gradient is rounding noise around 1e-9: absolute floor)
+            assert np.abs(got.ravel()[::997] - ref).max() <= 2e-3 * np.abs(ref).max() + 1e-7, k
+            l2 = float(np.sqrt(np.sum(np.square(got.astype(np.float64)))))
+            assert abs(l2 - float(g[f"{tag}_gl2_{k}"])) <= 2e-3 * float(g[f"{tag}_gl2_{k}"]) + 1e-7, k
+        tr.optimizer_step()
+        loss2, _ = tr.step(aud, vis, lab)
+        assert abs(float(loss2.item()) - g[f"{tag}_losses"][1]) <= 2e-4 * g[f"{tag}_losses"][1]
+
+
+def test_avm_train_step_dropout_masks_and_eval_after_sync(cuda_device):
+    from cvml_goalnet_b200 import utils as U
+    from cvml_goalnet_b200.train import AVMTrainer, DROPOUT_WIDTHS
+    n = 10
+    w, vis, aud, lab = _avm_case(n, True, 99)
+    rng = np.random.default_rng(7)
+    masks = [[(rng.random((n, wd)) < 0.8).astype(np.uint8) for wd in DROPOUT_WIDTHS] for _ in range(2)]
+    m = U.AVM(True)
+    m.load_state_dict(w)
+    tr = AVMTrainer(m, max_frames=n, dropout_p=0.2)
+    losses, scores0, grads0, out = O.avm_train_steps(w, aud, vis, lab, steps=2, masks=masks)
+    tr.forward_backward(aud, vis, lab, masks=masks[0])
+    assert abs(float(tr.loss.item()) - losses[0]) <= 1e-5 * abs(losses[0])
+    g = tr.grad_dict()
+    for k, ref in grads0.items():
+        assert _rel(g[k].cpu().numpy(), ref) <= 2e-3, k
+    tr.optimizer_step()
+    loss2, _ = tr.step(aud, vis, lab, masks=masks[1])
+    assert abs(float(loss2.item()) - losses[1]) <= 2e-4 * abs(losses[1])
+    # generated masks: the step runs and the keep rate is about 0.8 (loss stays finite, parameters move)
+    loss3, _ = tr.step(aud, vis, lab)
+    assert np.isfinite(float(loss3.item()))
+    # trained weights flow back into the eval-mode scoring path
+    tr.sync_model()
+    sd = {k: v.cpu().numpy() for k, v in tr.state_dict().items()}
+    sd.update({k: np.zeros((), np.int64) for k in w if k.endswith("num_batches_tracked")})
+    y = m(aud, vis).cpu().numpy()
+    ref = O.avm_forward(sd, aud, vis).numpy()
+    assert np.abs(y - ref).max() / np.abs(ref).max() <= 1e-3
