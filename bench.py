@@ -582,6 +582,107 @@ def stress_arm(args, rank, world, local_rank):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------
+# full-AVM train sub-step (10 frames, main.py:47,187-193)
+# ------------------------------------------------------------------------------------------------
+def avm_train_arm(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import _lib, synthetic as syn, utils as U
+    from cvml_goalnet_b200.train import AVMTrainer
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    n = 10
+    w = syn.make_weights(seed=0)
+    model = U.AVM(True)
+    model.load_state_dict(w)
+    rng = np.random.default_rng(12344321 + rank)
+    vis_h = torch.from_numpy(rng.random((n, 3, 40, 40)).astype(np.float32)).pin_memory()
+    aud_h = torch.from_numpy((25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)).pin_memory()
+    lab_h = torch.from_numpy(rng.integers(1, 6, n).astype(np.float32)).pin_memory()
+    vis, aud, lab = vis_h.to(dev), aud_h.to(dev), lab_h.to(dev)
+    vis_in, aud_in, lab_in = torch.empty_like(vis), torch.empty_like(aud), torch.empty_like(lab)
+    tr = AVMTrainer(model, max_frames=n, dropout_p=0.2, device=dev)
+    loss_host = torch.empty(1, dtype=torch.float64).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        l0 = _lib.launch_count(dev.index)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.profiler.start()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        torch.cuda.profiler.stop()
+        ms = e0.elapsed_time(e1)
+        launches = _lib.launch_count(dev.index) - l0
+        clocks = sampler.stop()
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches, clocks
+
+    def step_device():
+        tr.step(aud, vis, lab)
+
+    def step_host():
+        vis_in.copy_(vis_h, non_blocking=True); aud_in.copy_(aud_h, non_blocking=True); lab_in.copy_(lab_h, non_blocking=True)
+        tr.step(aud_in, vis_in, lab_in)
+        loss_host.copy_(tr.loss, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+
+    steps = max(args.steps, 20)
+    ms, launches, clocks = timed(step_device, steps, args.warmup)
+    ms_e2e, _, _ = timed(step_host, steps, args.warmup)
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import goalnet_oracle as O
+        torch.set_num_threads(os.cpu_count() or 1)
+        masks = [[(rng.random((n, wd)) < 0.8).astype(np.uint8) for wd in (512, 512, 512, 256, 128)] for _ in range(6)]
+        O.avm_train_steps(w, aud_h.numpy(), vis_h.numpy(), lab_h.numpy(), steps=1, masks=masks)
+        t0 = time.perf_counter()
+        O.avm_train_steps(w, aud_h.numpy(), vis_h.numpy(), lab_h.numpy(), steps=6, masks=masks)
+        dt = (time.perf_counter() - t0) / 6
+        cpu = {"value": n / dt, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": f"6 train sub-steps of {n} frames (torch-CPU autograd restatement of main.py:187-193), "
+                         f"{torch.get_num_threads()} threads; includes the one-off Adam state build"}
+    flops = 3 * 380.9e6 * n
+    line = {"metric": "avm_train_frames_per_sec", "value": world * n * steps / (ms * 1e-3), "unit": "frames/s",
+            "n_gpus": world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms / steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "SURVEY 8f N1: full-AVM train sub-step (forward in train mode, as-written loss, backward, Adam)",
+                       "frames_per_substep": n, "parameters": tr.n_params, "dropout": 0.2,
+                       "parallelism": f"dp{world} (gradients averaged over ranks)",
+                       "l2": "working set (4 x 88 MB of parameters / gradients / Adam moments) exceeds L2 only through linear5"},
+            "clocks": clocks,
+            "e2e": {"value": world * n * steps / (ms_e2e * 1e-3), "unit": "frames/s", "ms_per_step": ms_e2e / steps,
+                    "h2d_bytes_per_step": int((vis_h.numel() + aud_h.numel() + lab_h.numel()) * 4), "d2h_bytes_per_step": 8},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "whole sub-step (fp32 CUDA-core kernels)", "bound": "hbm",
+                         "achieved": (tr.n_params * 4 * 9) / (ms / steps * 1e-3) / 1e9, "peak": load_peaks()["hbm"], "unit": "GB/s",
+                         "frac": (tr.n_params * 4 * 9) / (ms / steps * 1e-3) / 1e9 / load_peaks()["hbm"], "traffic": None,
+                         "note": "algorithmic bytes = parameters read (fwd, dgrad) + gradient written and read + Adam "
+                                 "(p, m, v read and written): 9 x 4 B per parameter; 11.4 GFLOP per sub-step is negligible"}}
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -590,7 +691,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--frames", type=int, default=FRAMES, help="frames per match (default: config 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="match", choices=["match", "fusion_train", "stress"],
+    ap.add_argument("--workload", default="match", choices=["match", "fusion_train", "stress", "avm_train"],
                     help="match = BASELINE config 2 (the headline, default); fusion_train = config 4 "
                          "(fusion-network forward/backward/Adam step, 4096 rows per GPU, data parallel)")
     args = ap.parse_args()
@@ -611,6 +712,8 @@ def main():
             train_arm(args, rank, world, local_rank)
         elif args.workload == "stress":
             stress_arm(args, rank, world, local_rank)
+        elif args.workload == "avm_train":
+            avm_train_arm(args, rank, world, local_rank)
         else:
             native_arm(args, rank, world, local_rank)
     finally:

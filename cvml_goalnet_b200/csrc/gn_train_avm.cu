@@ -354,6 +354,126 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
 
 }  // namespace
 
+namespace {
+
+// ---- convolutions as fp32 GEMMs ---------------------------------------------------------------------------
+// One strided SGEMM serves conv forward, weight gradient and input gradient (through an explicit fp32 im2col buffer;
+// a 10-frame sub-batch makes it 11 MB at conv3):  C(i, j) = sum_l A(i, l) * B(j, l).
+// An operand element (r, l) lives at base[(r / rdiv) * rs_hi + (r % rdiv) * rs_lo + (l / ldiv) * ls_hi + (l % ldiv) * ls_lo],
+// which covers row-major matrices, their transposes and NCHW activations read as (pixel, channel) matrices.
+struct GOp {
+    const float* base;
+    int rdiv; int64_t rs_hi, rs_lo;
+    int ldiv; int64_t ls_hi, ls_lo;
+    int l_fast;            // 1: consecutive l are contiguous in memory (tile loads run along l), 0: consecutive r are
+};
+__device__ __forceinline__ int64_t gop_off(const GOp& o, int r, int l) {
+    return (int64_t)(r / o.rdiv) * o.rs_hi + (int64_t)(r % o.rdiv) * o.rs_lo + (int64_t)(l / o.ldiv) * o.ls_hi +
+           (int64_t)(l % o.ldiv) * o.ls_lo;
+}
+constexpr int kGM = 64, kGN = 64, kGK = 16;
+
+__global__ void __launch_bounds__(256)
+sgemm_strided_kernel(GOp A, GOp B, int M, int N, int K, float* __restrict__ C, int idiv, int64_t is_hi, int64_t is_lo,
+                     int jdiv, int64_t js_hi, int64_t js_lo, const float* __restrict__ bias_j, int relu) {
+    __shared__ __align__(16) float As[kGK][kGM + 4], Bs[kGK][kGN + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int i0 = blockIdx.y * kGM, j0 = blockIdx.x * kGN;
+    float acc[4][4] = {};
+    for (int l0 = 0; l0 < K; l0 += kGK) {
+        for (int e = tid; e < kGM * kGK; e += 256) {
+            int r, l;
+            if (A.l_fast) { r = e / kGK; l = e % kGK; } else { l = e / kGM; r = e % kGM; }
+            As[l][r] = (i0 + r < M && l0 + l < K) ? A.base[gop_off(A, i0 + r, l0 + l)] : 0.f;
+            if (B.l_fast) { r = e / kGK; l = e % kGK; } else { l = e / kGN; r = e % kGN; }
+            Bs[l][r] = (j0 + r < N && l0 + l < K) ? B.base[gop_off(B, j0 + r, l0 + l)] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int l = 0; l < kGK; ++l) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[l][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[l][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int v = 0; v < 4; ++v) acc[u][v] = fmaf(av[u], bv[v], acc[u][v]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int i = i0 + ty * 4 + u;
+        if (i >= M) continue;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            const int j = j0 + tx * 4 + v;
+            if (j >= N) continue;
+            float val = acc[u][v] + (bias_j ? bias_j[j] : 0.f);
+            if (relu) val = fmaxf(val, 0.f);
+            C[(int64_t)(i / idiv) * is_hi + (int64_t)(i % idiv) * is_lo + (int64_t)(j / jdiv) * js_hi + (int64_t)(j % jdiv) * js_lo] = val;
+        }
+    }
+}
+
+// col[p][ci*KH*KW + kh*KW + kw] = x[n][ci][oy*s-pad+kh][ox*s-pad+kw] (0 outside), p = (n, oy, ox)
+__global__ void __launch_bounds__(kT)
+im2col_kernel(const float* __restrict__ x, int N, int Ci, int H, int W, int KH, int KW, int s, int pad, int OH, int OW,
+              float* __restrict__ col) {
+    const int KK = Ci * KH * KW;
+    const int64_t total = (int64_t)N * OH * OW * KK;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int k = (int)(i % KK);
+        const int64_t p = i / KK;
+        const int kw = k % KW, kh = (k / KW) % KH, ci = k / (KW * KH);
+        const int ox = (int)(p % OW), oy = (int)((p / OW) % OH), n = (int)(p / ((int64_t)OW * OH));
+        const int iy = oy * s - pad + kh, ix = ox * s - pad + kw;
+        col[i] = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? x[(((int64_t)n * Ci + ci) * H + iy) * W + ix] : 0.f;
+    }
+}
+
+// dx[n][ci][iy][ix] = sum over (kh, kw) of dcol[p(oy, ox)][ci*KH*KW + kh*KW + kw] with oy*s - pad + kh == iy (same in x)
+__global__ void __launch_bounds__(kT)
+col2im_kernel(const float* __restrict__ dcol, int N, int Ci, int H, int W, int KH, int KW, int s, int pad, int OH, int OW,
+              float* __restrict__ dx) {
+    const int KK = Ci * KH * KW;
+    const int64_t total = (int64_t)N * Ci * H * W;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int ix = (int)(i % W), iy = (int)((i / W) % H), ci = (int)((i / ((int64_t)W * H)) % Ci);
+        const int n = (int)(i / ((int64_t)W * H * Ci));
+        float acc = 0.f;
+        for (int kh = 0; kh < KH; ++kh) {
+            const int ty = iy + pad - kh;
+            if (ty < 0 || ty % s || ty / s >= OH) continue;
+            for (int kw = 0; kw < KW; ++kw) {
+                const int tx = ix + pad - kw;
+                if (tx < 0 || tx % s || tx / s >= OW) continue;
+                const int64_t p = ((int64_t)n * OH + ty / s) * OW + tx / s;
+                acc += dcol[p * KK + (ci * KH + kh) * KW + kw];
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
+// db[c] = sum over (n, pixel) of dy[n][c][pixel]; one CTA per channel
+__global__ void __launch_bounds__(kT)
+bias_grad_kernel(const float* __restrict__ dy, int N, int C, int HW, float* __restrict__ db) {
+    __shared__ float sred[kT];
+    const int c = blockIdx.x;
+    float a = 0.f;
+    for (int i = threadIdx.x; i < N * HW; i += kT) a += dy[((int64_t)(i / HW) * C + c) * HW + i % HW];
+    sred[threadIdx.x] = a;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sred[threadIdx.x] += sred[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) db[c] = sred[0];
+}
+
+}  // namespace
+
 // ================================================================================================================
 // trainer object
 // ================================================================================================================
@@ -376,6 +496,7 @@ struct gn_avm_trainer {
     uint8_t* arg[3];
     float *h5, *ay1, *ay2, *fin_buf, *f[4], *z, *dz;
     float *d_big0, *d_big1;          // ping-pong gradient buffers sized for the largest activation
+    float *col, *dcol;               // im2col of a conv input / gradient w.r.t. it ([n*OH*OW][Cin*9], largest layer)
     float *d_fin, *d_f[4];
     uint8_t* masks[5];               // keep-masks: linear5 (512), fusion.0/3/6/9 (512, 512, 256, 128)
     void* arena;
@@ -457,6 +578,12 @@ extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const g
         t->d_fin = (float*)take(n * t->fin, 4);
         if (n * 128 * t->L2 > big) big = n * 128 * t->L2;
         t->d_big0 = (float*)take(big, 4); t->d_big1 = (float*)take(big, 4);
+        int64_t colmax = 0;
+        for (int i = 0; i < 3; ++i) {
+            const int64_t ce = n * OH[i] * OH[i] * (i == 0 ? 27 : (i == 1 ? 576 : 2304));
+            if (ce > colmax) colmax = ce;
+        }
+        t->col = (float*)take(colmax, 4); t->dcol = (float*)take(colmax, 4);
         const int mw[5] = {512, 512, 512, 256, 128};
         for (int i = 0; i < 5; ++i) t->masks[i] = (uint8_t*)take(n * mw[i], 1);
         if (pass == 0) {
@@ -525,6 +652,50 @@ extern "C" int gn_avm_trainer_grads(gn_avm_trainer* t, float** d_grads) {
 // ================================================================================================================
 // forward + backward (train mode) and the optimizer step
 // ================================================================================================================
+namespace {
+constexpr int kBig = 1 << 30;
+int launch_sgemm(gn_handle* h, const GOp& A, const GOp& B, int M, int N, int K, float* C, int idiv, int64_t is_hi,
+                 int64_t is_lo, int jdiv, int64_t js_hi, int64_t js_lo, const float* bias_j, int relu, cudaStream_t st) {
+    dim3 grid((N + kGN - 1) / kGN, (M + kGM - 1) / kGM);
+    sgemm_strided_kernel<<<grid, 256, 0, st>>>(A, B, M, N, K, C, idiv, is_hi, is_lo, jdiv, js_hi, js_lo, bias_j, relu);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}
+// y = relu(conv(x, w) + b), square images / kernels 3x3
+int conv_fwd_gemm(gn_avm_trainer* t, const float* x, const float* w, const float* b, int n, int Ci, int H, int Co, int s,
+                  int pad, int OH, float* y, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, cap = t->h->num_sms * 8;
+    im2col_kernel<<<grid_for((int64_t)n * OHW * KK, cap), kT, 0, st>>>(x, n, Ci, H, H, 3, 3, s, pad, OH, OH, t->col);
+    GN_LAUNCHED(t->h);
+    const GOp A{t->col, kBig, 0, KK, kBig, 0, 1, 1}, B{w, kBig, 0, KK, kBig, 0, 1, 1};
+    return launch_sgemm(t->h, A, B, n * OHW, Co, KK, y, OHW, (int64_t)Co * OHW, 1, kBig, 0, OHW, b, 1, st);
+}
+// dw[co][k] = sum_p dy(p, co) col(p, k); db[co] = sum_p dy(p, co)
+int conv_bwd_w_gemm(gn_avm_trainer* t, const float* dy, const float* x, int n, int Ci, int H, int Co, int s, int pad, int OH,
+                    float* dw, float* db, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, cap = t->h->num_sms * 8;
+    im2col_kernel<<<grid_for((int64_t)n * OHW * KK, cap), kT, 0, st>>>(x, n, Ci, H, H, 3, 3, s, pad, OH, OH, t->col);
+    GN_LAUNCHED(t->h);
+    const GOp A{dy, kBig, 0, OHW, OHW, (int64_t)Co * OHW, 1, 1}, B{t->col, kBig, 0, 1, kBig, 0, KK, 0};
+    int rc = launch_sgemm(t->h, A, B, Co, KK, n * OHW, dw, kBig, 0, KK, kBig, 0, 1, nullptr, 0, st);
+    if (rc) return rc;
+    bias_grad_kernel<<<Co, kT, 0, st>>>(dy, n, Co, OHW, db);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+// dx = col2im(dy(p, co) . w(co, k))
+int conv_bwd_x_gemm(gn_avm_trainer* t, const float* dy, const float* w, int n, int Ci, int H, int Co, int s, int pad, int OH,
+                    float* dx, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, cap = t->h->num_sms * 8;
+    const GOp A{dy, OHW, (int64_t)Co * OHW, 1, kBig, 0, OHW, 0}, B{w, kBig, 0, 1, kBig, 0, KK, 0};
+    int rc = launch_sgemm(t->h, A, B, n * OHW, KK, Co, t->dcol, kBig, 0, KK, kBig, 0, 1, nullptr, 0, st);
+    if (rc) return rc;
+    col2im_kernel<<<grid_for((int64_t)n * Ci * H * H, cap), kT, 0, st>>>(t->dcol, n, Ci, H, H, 3, 3, s, pad, OH, OH, dx);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+}  // namespace
+
 #define TL(kern, total, ...)                                                             \
     do {                                                                                 \
         kern<<<grid_for((total), cap), kT, 0, st>>>(__VA_ARGS__);                        \
@@ -566,8 +737,8 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     // ---------------- forward: VisBl (utils.py:172-195) ----------------
     const float* x = d_visual;
     for (int i = 0; i < 3; ++i) {
-        TL(conv_fwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], IH[i], C[i], 3,
-           3, stride[i], stride[i], pad[i], pad[i], OH[i], OH[i], 1, t->y[i]);
+        int rc = conv_fwd_gemm(t, x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], t->y[i], st);
+        if (rc) return rc;
         TL(pool_fwd_kernel, (int64_t)n * C[i] * PH[i] * PH[i], t->y[i], n * C[i], OH[i], OH[i], t->p[i], t->arg[i]);
         bn_fwd_kernel<<<C[i], kT, 0, st>>>(t->p[i], n, C[i], PH[i] * PH[i], P + o[bw[i]], P + o[bb[i]], t->rmean[i],
                                            t->rvar[i], t->xh[i], t->istd[i], t->a[i]);
@@ -651,11 +822,11 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
         float* dy = da;                  // reuse: da is dead now
         TL(pool_relu_bwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], dp, t->arg[i], t->y[i], n * C[i], OH[i], OH[i], dy);
         const float* xin = i ? t->a[i - 1] : d_visual;
-        TL(conv_bwd_w_kernel, (int64_t)C[i] * Cin[i] * 9 * 32, dy, xin, n, Cin[i], IH[i], IH[i], C[i], 3, 3, stride[i], stride[i],
-           pad[i], pad[i], OH[i], OH[i], G + o[cw[i]], G + o[cb[i]]);
+        int rc = conv_bwd_w_gemm(t, dy, xin, n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], G + o[cw[i]], G + o[cb[i]], st);
+        if (rc) return rc;
         if (i > 0) {
-            TL(conv_bwd_x_kernel, (int64_t)n * Cin[i] * IH[i] * IH[i], dy, P + o[cw[i]], n, Cin[i], IH[i], IH[i], C[i], 3, 3,
-               stride[i], stride[i], pad[i], pad[i], OH[i], OH[i], dp);
+            rc = conv_bwd_x_gemm(t, dy, P + o[cw[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], dp, st);
+            if (rc) return rc;
             da = dp;
         }
     }
