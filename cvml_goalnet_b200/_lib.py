@@ -110,6 +110,7 @@ SIGNATURES = {
     "gn_fusion_get_params": (_I, [_P, _P, _P]),
     "gn_fusion_forward_backward": (_I, [_P, _P, _P, _L, _I, C.c_float, C.POINTER(_P), C.c_uint64, _P, _P, _P, _P]),
     "gn_fusion_adam_step": (_I, [_P, _P, C.c_float, _P]),
+    "gn_dbg_gemm_tf32": (_I, [_P, _P, _L, _I, _P, _I, _P, _P]),
     "gn_avm_trainer_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_avm_state), _I, _I, _I, _L, _P]),
     "gn_avm_trainer_destroy": (_I, [_P]),
     "gn_avm_trainer_param_count": (_L, [_P]),

@@ -32,7 +32,8 @@ enum Mode { kConv = 0, kLinear = 1, kScore = 2,
             kTrainFwd = 3,   // relu(acc + bias), dropout, bf16 out [M][N] and its transpose [N][ld_t]
             kDgrad = 4,      // acc * scale * [gate > 0], bf16 out [M][N] and its transpose
             kWgrad = 5,      // fp32 out [M][N] = acc
-            kSplitK = 6 };   // fp32 partial sums out_f32[split][M][N] of one K range (bias/ReLU in splitk_reduce_kernel)
+            kSplitK = 6,     // fp32 partial sums out_f32[split][M][N] of one K range (bias/ReLU in splitk_reduce_kernel)
+            kGemmTF32 = 7 }; // fp32 (TF32) operands, fp32 out [M][N] = acc: the conv GEMMs of the full-AVM trainer
 
 struct ConvGeom {
     int OH, OW;        // conv output == input interior (k3 s1 p1)
@@ -129,7 +130,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int64_t m_blocks = (MODE == kConv) ? args.M * tiles_pf : (args.M + 127) / 128;
     const int k_splits = (MODE == kSplitK) ? args.k_splits : 1;
     const int64_t num_tiles = m_blocks * n_blocks * k_splits;
-    const int k_total = args.K / kBK;
+    constexpr int kbk = (MODE == kGemmTF32) ? 32 : kBK;      // elements per 128-byte operand row
+    const int k_total = args.K / kbk;
     const int k_per = (k_total + k_splits - 1) / k_splits;
     // tile -> (m_blk, n_blk, split): split fastest, then n_blk, so that CTAs running side by side share A and W in L2
 #define GN_TILE_DECODE()                                                                  \
@@ -141,7 +143,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int k_iters = (k_total - k_begin) < k_per ? (k_total - k_begin) : k_per;
 
     // per-channel epilogue parameters: global -> shared once per CTA
-    for (int i = threadIdx.x; i < args.N && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK; i += kThreads) {
+    for (int i = threadIdx.x; i < args.N && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32; i += kThreads) {
         s_par[i] = __ldg(args.bias + i);
         if (MODE == kConv) {
             s_par[kMaxN + i] = __ldg(args.bn_scale + i);
@@ -201,17 +203,17 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
                         if (args.kblocked)      tma_load_2d(sa, &tmap_a, fb, 0, (int)((m_blk * k_total + kt) * 128));
                         else if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
-                        else                    tma_load_2d(sa, &tmap_a, fb, kt * kBK, (int)(m_blk * 128));
+                        else                    tma_load_2d(sa, &tmap_a, fb, kt * kbk, (int)(m_blk * 128));
                     }
                     if (MODE != kConv && args.kblocked) tma_load_2d(sb, &tmap_b, fb, 0, kt * args.N + n_blk * BN);
-                    else                                tma_load_2d(sb, &tmap_b, fb, kt * kBK, n_blk * BN);
+                    else                                tma_load_2d(sb, &tmap_b, fb, kt * kbk, n_blk * BN);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+        constexpr uint32_t idesc = (MODE == kGemmTF32) ? make_idesc_tf32(128, BN) : make_idesc_bf16(128, BN);
         int stage = 0;
         uint32_t phase = 0;
         int ab = 0;
@@ -234,7 +236,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         for (int k4 = 0; k4 < kBK / 16; ++k4) {
                             const uint64_t ad = make_desc_sw128(sa + mt * (128 * 128) + k4 * 32);
                             const uint64_t bd = make_desc_sw128(sb + k4 * 32);
-                            umma_bf16(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                            if (MODE == kGemmTF32) umma_tf32(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                            else                   umma_bf16(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
                         }
                     }
                     umma_commit(smem_u32(&empty_bar[stage]));              // smem slot free when MMAs retire
@@ -390,7 +393,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tmem_ld_wait();
                     const float* bp = s_bias + n0 + c * 32;
                     float x[32];
-                    if (MODE == kDgrad || MODE == kWgrad || MODE == kSplitK) {
+                    if (MODE == kDgrad || MODE == kWgrad || MODE == kSplitK || MODE == kGemmTF32) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) x[i] = __uint_as_float(r[i]);
                     } else {
@@ -442,7 +445,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                         for (int i = 0; i < 32; ++i) dot = fmaf(x[i], wl[i], dot);
                     } else if (grow < args.M) {
-                        if (MODE != kWgrad && MODE != kSplitK && args.out) {
+                        if (MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32 && args.out) {
                             uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
                                                                   n0 + c * 32);
 #pragma unroll
@@ -456,7 +459,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                             for (int i = 0; i < 32; ++i) tp[(size_t)i * args.ld_t] = __float2bfloat16(x[i]);
                         }
-                        if (MODE == kWgrad || MODE == kSplitK) {
+                        if (MODE == kWgrad || MODE == kSplitK || MODE == kGemmTF32) {
                             float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)ks * args.split_stride +
                                                                    (size_t)grow * args.N + n0 + c * 32);
 #pragma unroll
@@ -526,7 +529,7 @@ template <int MT, int BN, int STAGES, int MODE, int OHT>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
     using C = Cfg<MT, BN, STAGES, MODE>;
-    if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK) return GN_E_SHAPE;
+    if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32) return GN_E_SHAPE;
     auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT>;
     static bool attr = false;
     if (!attr) {
@@ -829,4 +832,34 @@ int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, 
         case kWgrad: return launch<1, BN, 4, kWgrad, 0>(h, ta, tb, a, tiles, st);
         default: return GN_E_ARG;
     }
+}
+
+// C[M][N] (fp32, row-major) = A[M][K] . B[N][K]^T with fp32 operands multiplied as TF32 on the tensor cores; K % 32 == 0,
+// N % 128 == 0, lda/ldb in elements (multiples of 4).  Rows of A beyond M are zero-filled by TMA and never stored.
+int gn_tc_gemm_tf32(gn_handle* h, const float* A, int64_t M, int K, int64_t lda, const float* B, int N, int64_t ldb,
+                    float* C, cudaStream_t st) {
+    constexpr int BN = 128;
+    if (K % 32 || N % BN || M <= 0 || (lda & 3) || (ldb & 3)) return GN_E_SHAPE;
+    if (!h->encode_tiled) return GN_E_NODEVICE;
+    CUtensorMap ta, tb;
+    for (int which = 0; which < 2; ++which) {
+        const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)(which ? N : M)};
+        const cuuint64_t gstr[1] = {(cuuint64_t)((which ? ldb : lda) * 4)};
+        const cuuint32_t bx[2] = {32u, (cuuint32_t)(which ? BN : 128)};
+        const cuuint32_t es[2] = {1u, 1u};
+        CUresult r = reinterpret_cast<EncodeTiledFn>(h->encode_tiled)(
+            which ? &tb : &ta, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(which ? B : A), gdim, gstr, bx, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return (int)r;
+    }
+    GemmArgs a{};
+    a.M = M; a.N = N; a.K = K; a.out_f32 = C;
+    return launch<1, BN, 4, kGemmTF32, 0>(h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
+}
+
+extern "C" int gn_dbg_gemm_tf32(gn_handle* h, const float* d_a, int64_t M, int K, const float* d_b, int N, float* d_c,
+                                void* stream) {
+    if (!h || !d_a || !d_b || !d_c) return GN_E_ARG;
+    return gn_tc_gemm_tf32(h, d_a, M, K, K, d_b, N, K, d_c, gn_stream(stream));
 }

@@ -262,6 +262,11 @@ int gn_dbg_avm_forward_simt(gn_model* m, const float* d_visual, const float* d_a
 int gn_dbg_read_activation(gn_model* m, int which, int64_t n, const void* d_workspace, float* d_out,
                            void* stream);
 
+/* d_c[M][N] = d_a[M][K] . d_b[N][K]^T, fp32 operands multiplied as TF32 by tcgen05 (K % 32 == 0, N % 128 == 0): the
+ * GEMM behind the full-AVM trainer's convolutions, exported so that tests can check it in isolation. */
+int gn_dbg_gemm_tf32(gn_handle* h, const float* d_a, int64_t M, int K, const float* d_b, int N, float* d_c,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -230,3 +230,24 @@ def test_avm_train_step_dropout_masks_and_eval_after_sync(cuda_device):
     y = m(aud, vis).cpu().numpy()
     ref = O.avm_forward(sd, aud, vis).numpy()
     assert np.abs(y - ref).max() / np.abs(ref).max() <= 1e-3
+
+
+@pytest.mark.parametrize("M,K,N", [(1210, 2304, 512), (1690, 576, 256), (130, 64, 128), (576, 1216, 256)])
+def test_tf32_tcgen05_gemm_vs_torch_fp32(cuda_device, M, K, N):
+    """kind::tf32 tcgen05 GEMM (10-bit mantissa operands, fp32 accumulation) against torch fp32 matmul."""
+    import ctypes as C
+    from cvml_goalnet_b200 import _lib
+    from cvml_goalnet_b200.utils import _h, _ptr, _stream
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(M + K + N)
+    a = torch.randn((M, K), generator=g, device=dev)
+    b = torch.randn((N, K), generator=g, device=dev)
+    c = torch.empty((M, N), device=dev)
+    _lib.check(_lib.load().gn_dbg_gemm_tf32(_h(dev), _ptr(a), M, K, _ptr(b), N, _ptr(c), _stream(dev)), "gn_dbg_gemm_tf32")
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = a.double() @ b.double().T
+    torch.backends.cuda.matmul.allow_tf32 = prev
+    err = (c.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert err <= 2e-3, err
