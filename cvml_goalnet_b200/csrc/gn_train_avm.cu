@@ -456,6 +456,123 @@ col2im_kernel(const float* __restrict__ dcol, int N, int Ci, int H, int W, int K
     }
 }
 
+// Error-compensated TF32 ("3xTF32"): v = hi + lo with hi = v rounded to TF32 (13 low mantissa bits cleared) and lo the
+// exact remainder; a.b ~= a_hi.b_hi + a_hi.b_lo + a_lo.b_hi.  The three products become ONE GEMM by tripling K:
+// an A operand row is [hi | hi | lo], a B operand row is [hi | lo | hi] (segments of `seg` elements).
+__device__ __forceinline__ void store3(float* row, int seg, int k, float v, bool is_a) {
+    const float hi = __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+    const float lo = v - hi;
+    row[k] = hi;
+    row[seg + k] = is_a ? hi : lo;
+    row[2 * seg + k] = is_a ? lo : hi;
+}
+
+// ---- layout shuffles around the TF32 tensor-core GEMMs (gn_tc_gemm_tf32: C[M][N] = A[M][K] . B[N][K]^T, K-major) ----
+// colT[k][ld] : transposed im2col, columns p >= P zero (K padding of the weight-gradient GEMM)
+__global__ void __launch_bounds__(kT)
+im2col_t_kernel(const float* __restrict__ x, int N, int Ci, int H, int W, int s, int pad, int OH, int OW, int ld,
+                float* __restrict__ colT) {
+    const int KK = Ci * 9, P = N * OH * OW;
+    const int64_t total = (int64_t)KK * ld;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int p = (int)(i % ld), k = (int)(i / ld);
+        float v = 0.f;
+        if (p < P) {
+            const int kw = k % 3, kh = (k / 3) % 3, ci = k / 9;
+            const int ox = p % OW, oy = (p / OW) % OH, n = p / (OW * OH);
+            const int iy = oy * s - pad + kh, ix = ox * s - pad + kw;
+            if (iy >= 0 && iy < H && ix >= 0 && ix < W) v = x[(((int64_t)n * Ci + ci) * H + iy) * W + ix];
+        }
+        store3(colT + (int64_t)k * 3 * ld, ld, p, v, true);
+    }
+}
+// NCHW [n][C][HW] -> [C][ld] (p = n*HW + pos; columns >= P zero)   or   -> [rows][C] (rows >= P zero)
+__global__ void __launch_bounds__(kT)
+nchw_to_cp_kernel(const float* __restrict__ t, int N, int C, int HW, int ld, float* __restrict__ out) {
+    const int P = N * HW;
+    const int64_t total = (int64_t)C * ld;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int p = (int)(i % ld), c = (int)(i / ld);
+        store3(out + (int64_t)c * 3 * ld, ld, p, p < P ? t[((int64_t)(p / HW) * C + c) * HW + p % HW] : 0.f, false);
+    }
+}
+__global__ void __launch_bounds__(kT)
+nchw_to_pc_kernel(const float* __restrict__ t, int N, int C, int HW, int rows, float* __restrict__ out) {
+    const int P = N * HW;
+    const int64_t total = (int64_t)rows * C;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int c = (int)(i % C), p = (int)(i / C);
+        store3(out + (int64_t)p * 3 * C, C, c, p < P ? t[((int64_t)(p / HW) * C + c) * HW + p % HW] : 0.f, false);
+    }
+}
+// y[n][c][pos] = relu(yT[p][c] + b[c])
+__global__ void __launch_bounds__(kT)
+pc_bias_relu_to_nchw_kernel(const float* __restrict__ yT, const float* __restrict__ b, int N, int C, int HW,
+                            float* __restrict__ y) {
+    const int64_t total = (int64_t)N * C * HW;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int pos = (int)(i % HW), c = (int)((i / HW) % C), n = (int)(i / ((int64_t)HW * C));
+        y[i] = fmaxf(yT[((int64_t)n * HW + pos) * C + c] + b[c], 0.f);
+    }
+}
+// out[c][r] = in[r][c]  (split: rows of out are 3xTF32 A operands [hi | hi | lo])
+__global__ void __launch_bounds__(kT)
+transpose_kernel(const float* __restrict__ in, int R, int Cc, float* __restrict__ out, int split) {
+    const int64_t total = (int64_t)R * Cc;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int r = (int)(i % R), c = (int)(i / R);
+        const float v = in[(int64_t)r * Cc + c];
+        if (split) store3(out + (int64_t)c * 3 * R, R, r, v, true);
+        else out[i] = v;
+    }
+}
+// 3xTF32 operand copy of a row-major matrix [R][K] -> [R][3K]
+__global__ void __launch_bounds__(kT)
+split3_kernel(const float* __restrict__ in, int R, int K, float* __restrict__ out, int is_a) {
+    const int64_t total = (int64_t)R * K;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int k = (int)(i % K), r = (int)(i / K);
+        store3(out + (int64_t)r * 3 * K, K, k, in[i], is_a != 0);
+    }
+}
+// col[p][3*KK]: im2col as a 3xTF32 A operand
+__global__ void __launch_bounds__(kT)
+im2col_split_kernel(const float* __restrict__ x, int N, int Ci, int H, int W, int s, int pad, int OH, int OW,
+                    float* __restrict__ col) {
+    const int KK = Ci * 9;
+    const int64_t total = (int64_t)N * OH * OW * KK;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int k = (int)(i % KK);
+        const int64_t p = i / KK;
+        const int kw = k % 3, kh = (k / 3) % 3, ci = k / 9;
+        const int ox = (int)(p % OW), oy = (int)((p / OW) % OH), n = (int)(p / ((int64_t)OW * OH));
+        const int iy = oy * s - pad + kh, ix = ox * s - pad + kw;
+        const float v = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? x[(((int64_t)n * Ci + ci) * H + iy) * W + ix] : 0.f;
+        store3(col + p * 3 * KK, KK, k, v, true);
+    }
+}
+// dx from the transposed column gradient dcolT[k][ld]
+__global__ void __launch_bounds__(kT)
+col2im_t_kernel(const float* __restrict__ dcolT, int N, int Ci, int H, int W, int s, int pad, int OH, int OW, int ld,
+                float* __restrict__ dx) {
+    const int64_t total = (int64_t)N * Ci * H * W;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int ix = (int)(i % W), iy = (int)((i / W) % H), ci = (int)((i / ((int64_t)W * H)) % Ci);
+        const int n = (int)(i / ((int64_t)W * H * Ci));
+        float acc = 0.f;
+        for (int kh = 0; kh < 3; ++kh) {
+            const int ty = iy + pad - kh;
+            if (ty < 0 || ty % s || ty / s >= OH) continue;
+            for (int kw = 0; kw < 3; ++kw) {
+                const int tx = ix + pad - kw;
+                if (tx < 0 || tx % s || tx / s >= OW) continue;
+                acc += dcolT[(int64_t)((ci * 3 + kh) * 3 + kw) * ld + ((int64_t)n * OH + ty / s) * OW + tx / s];
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
 // db[c] = sum over (n, pixel) of dy[n][c][pixel]; one CTA per channel
 __global__ void __launch_bounds__(kT)
 bias_grad_kernel(const float* __restrict__ dy, int N, int C, int HW, float* __restrict__ db) {
@@ -496,7 +613,8 @@ struct gn_avm_trainer {
     uint8_t* arg[3];
     float *h5, *ay1, *ay2, *fin_buf, *f[4], *z, *dz;
     float *d_big0, *d_big1;          // ping-pong gradient buffers sized for the largest activation
-    float *col, *dcol;               // im2col of a conv input / gradient w.r.t. it ([n*OH*OW][Cin*9], largest layer)
+    float *col, *dcol, *opb;         // im2col of a conv input / gradient w.r.t. it (largest layer), transposed B operand
+    int use_tc;                      // conv2 / conv3 GEMMs on the tensor cores as TF32 (default) or the fp32 SGEMM
     float *d_fin, *d_f[4];
     uint8_t* masks[5];               // keep-masks: linear5 (512), fusion.0/3/6/9 (512, 512, 256, 128)
     void* arena;
@@ -532,6 +650,7 @@ extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const g
     t->fin = 512 + (t->audio ? 128 : 0);
     t->K5 = 512LL * t->P3 * t->P3;
     t->lr = 1e-3f; t->b1 = 0.9f; t->b2 = 0.999f; t->eps = 1e-8f;
+    t->use_tc = getenv("GN_TRAIN_FP32") ? 0 : 1;     // GN_TRAIN_FP32=1: exact-fp32 SGEMM convolutions (validation)
     if (t->P3 < 1) { free(t); return GN_E_SHAPE; }
     const int64_t sz[P_COUNT] = {64 * 27, 64, 64, 64, 256 * 576, 256, 256, 256, 512 * 2304, 512, 512, 512, 512 * t->K5, 512,
                                  t->audio ? 64 * 90 : 0, t->audio ? 64 : 0, t->audio ? 128 * 192 : 0, t->audio ? 128 : 0,
@@ -583,7 +702,15 @@ extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const g
             const int64_t ce = n * OH[i] * OH[i] * (i == 0 ? 27 : (i == 1 ? 576 : 2304));
             if (ce > colmax) colmax = ce;
         }
-        t->col = (float*)take(colmax, 4); t->dcol = (float*)take(colmax, 4);
+        int64_t bmax = 0;
+        for (int i = 1; i < 3; ++i) {      // tensor-core layers: K-padded / N-padded transposed operands
+            const int64_t pp = ((n * OH[i] * OH[i] + 127) / 128) * 128;
+            const int64_t kk = (i == 1 ? 576 : 2304);
+            const int64_t ce = 3 * pp * kk, be = 3 * (pp * C[i] > C[i] * kk ? pp * C[i] : C[i] * kk);   // 3xTF32 operands
+            if (ce > colmax) colmax = ce;
+            if (be > bmax) bmax = be;
+        }
+        t->col = (float*)take(colmax, 4); t->dcol = (float*)take(colmax, 4); t->opb = (float*)take(bmax, 4);
         const int mw[5] = {512, 512, 512, 256, 128};
         for (int i = 0; i < 5; ++i) t->masks[i] = (uint8_t*)take(n * mw[i], 1);
         if (pass == 0) {
@@ -694,6 +821,49 @@ int conv_bwd_x_gemm(gn_avm_trainer* t, const float* dy, const float* w, int n, i
     GN_LAUNCHED(t->h);
     return GN_OK;
 }
+// ---- the same three products on the tensor cores (kind::tf32), for layers with Cin*9 % 32 == 0 and Cout % 128 == 0 ----
+inline int pad_to(int v, int m) { return (v + m - 1) / m * m; }
+int conv_fwd_tc(gn_avm_trainer* t, const float* x, const float* w, const float* b, int n, int Ci, int H, int Co, int s, int pad,
+                int OH, float* y, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, P = n * OHW, cap = t->h->num_sms * 8;
+    im2col_split_kernel<<<grid_for((int64_t)P * KK, cap), kT, 0, st>>>(x, n, Ci, H, H, s, pad, OH, OH, t->col);
+    GN_LAUNCHED(t->h);
+    split3_kernel<<<grid_for((int64_t)Co * KK, cap), kT, 0, st>>>(w, Co, KK, t->opb, 0);
+    GN_LAUNCHED(t->h);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, P, 3 * KK, 3 * KK, t->opb, Co, 3 * KK, t->dcol, st);        // yT[p][co]
+    if (rc) return rc;
+    pc_bias_relu_to_nchw_kernel<<<grid_for((int64_t)P * Co, cap), kT, 0, st>>>(t->dcol, b, n, Co, OHW, y);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+int conv_bwd_w_tc(gn_avm_trainer* t, const float* dy, const float* x, int n, int Ci, int H, int Co, int s, int pad, int OH,
+                  float* dw, float* db, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, P = n * OHW, ld = pad_to(P, 32), cap = t->h->num_sms * 8;
+    im2col_t_kernel<<<grid_for((int64_t)KK * ld, cap), kT, 0, st>>>(x, n, Ci, H, H, s, pad, OH, OH, ld, t->col);
+    GN_LAUNCHED(t->h);
+    nchw_to_cp_kernel<<<grid_for((int64_t)Co * ld, cap), kT, 0, st>>>(dy, n, Co, OHW, ld, t->opb);
+    GN_LAUNCHED(t->h);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * ld, 3 * ld, t->opb, Co, 3 * ld, t->dcol, st);       // dW^T[k][co]
+    if (rc) return rc;
+    transpose_kernel<<<grid_for((int64_t)KK * Co, cap), kT, 0, st>>>(t->dcol, KK, Co, dw, 0);
+    GN_LAUNCHED(t->h);
+    bias_grad_kernel<<<Co, kT, 0, st>>>(dy, n, Co, OHW, db);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+int conv_bwd_x_tc(gn_avm_trainer* t, const float* dy, const float* w, int n, int Ci, int H, int Co, int s, int pad, int OH,
+                  float* dx, cudaStream_t st) {
+    const int KK = Ci * 9, OHW = OH * OH, P = n * OHW, rows = pad_to(P, 128), cap = t->h->num_sms * 8;
+    transpose_kernel<<<grid_for((int64_t)KK * Co, cap), kT, 0, st>>>(w, Co, KK, t->col, 1);             // W^T[k][3*co]
+    GN_LAUNCHED(t->h);
+    nchw_to_pc_kernel<<<grid_for((int64_t)rows * Co, cap), kT, 0, st>>>(dy, n, Co, OHW, rows, t->opb);
+    GN_LAUNCHED(t->h);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * Co, 3 * Co, t->opb, rows, 3 * Co, t->dcol, st);     // dcol^T[k][rows]
+    if (rc) return rc;
+    col2im_t_kernel<<<grid_for((int64_t)n * Ci * H * H, cap), kT, 0, st>>>(t->dcol, n, Ci, H, H, s, pad, OH, OH, rows, dx);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
 }  // namespace
 
 #define TL(kern, total, ...)                                                             \
@@ -737,7 +907,9 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     // ---------------- forward: VisBl (utils.py:172-195) ----------------
     const float* x = d_visual;
     for (int i = 0; i < 3; ++i) {
-        int rc = conv_fwd_gemm(t, x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], t->y[i], st);
+        const bool tc = t->use_tc && i > 0;
+        int rc = (tc ? conv_fwd_tc : conv_fwd_gemm)(t, x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], C[i], stride[i],
+                                                    pad[i], OH[i], t->y[i], st);
         if (rc) return rc;
         TL(pool_fwd_kernel, (int64_t)n * C[i] * PH[i] * PH[i], t->y[i], n * C[i], OH[i], OH[i], t->p[i], t->arg[i]);
         bn_fwd_kernel<<<C[i], kT, 0, st>>>(t->p[i], n, C[i], PH[i] * PH[i], P + o[bw[i]], P + o[bb[i]], t->rmean[i],
@@ -822,10 +994,13 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
         float* dy = da;                  // reuse: da is dead now
         TL(pool_relu_bwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], dp, t->arg[i], t->y[i], n * C[i], OH[i], OH[i], dy);
         const float* xin = i ? t->a[i - 1] : d_visual;
-        int rc = conv_bwd_w_gemm(t, dy, xin, n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], G + o[cw[i]], G + o[cb[i]], st);
+        const bool tc = t->use_tc && i > 0;
+        int rc = (tc ? conv_bwd_w_tc : conv_bwd_w_gemm)(t, dy, xin, n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i],
+                                                        G + o[cw[i]], G + o[cb[i]], st);
         if (rc) return rc;
         if (i > 0) {
-            rc = conv_bwd_x_gemm(t, dy, P + o[cw[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i], dp, st);
+            rc = (tc ? conv_bwd_x_tc : conv_bwd_x_gemm)(t, dy, P + o[cw[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i],
+                                                        dp, st);
             if (rc) return rc;
             da = dp;
         }

@@ -132,6 +132,18 @@ def test_trainer_argument_errors():
 
 
 # ------------------------------------------------------------------ full-AVM train sub-step
+# Two arithmetic modes: the default runs the conv2/conv3 GEMMs on the tensor cores as error-compensated TF32
+# (3xTF32: every operand split into a TF32 head and its exact remainder, three products in one K-tripled GEMM),
+# GN_TRAIN_FP32=1 as plain fp32 SGEMMs.  Tolerances (SGEMM | 3xTF32):
+#   scores 2e-5 abs (values in [1,5]); loss 1e-5 relative;
+#   gradients per tensor, relative to the tensor's largest element: 5e-3 | 6e-2.  A weight gradient is a sum of ~1200
+#   cancelling terms; oneDNN, the SGEMM and the tensor core add them in different orders, and the tensor-core
+#   accumulator truncates instead of rounding, a bias that grows with the 456 chained MMAs of a K = 3 x 1216
+#   reduction (measured: <= 0.35 % | <= 4.1 %, worst on small, strongly cancelling tensors: BatchNorm biases downstream
+#   of two tensor-core dgrads, and the audio conv1 whose gradient hinges on p_i - mean(l) of the shifted scores).
+TOL = {True: dict(score=2e-5, loss=1e-5, loss2=2e-4, grad=5e-3), False: dict(score=2e-5, loss=1e-5, loss2=2e-3, grad=6e-2)}
+
+
 def _avm_case(n, audio_included, seed):
     rng = np.random.default_rng(seed)
     w = syn.make_weights(seed=1, audio_included=audio_included)
@@ -145,81 +157,107 @@ def _rel(a, b):
     return float(max(np.abs(a - b).max() - 1e-7, 0.0) / max(np.abs(b).max(), 1e-12))
 
 
-@pytest.mark.parametrize("audio_included,n,fixed", [(True, 10, False), (False, 7, False), (True, 4, True)])
-def test_avm_train_step_vs_oracle_no_dropout(cuda_device, audio_included, n, fixed):
-    from cvml_goalnet_b200 import utils as U
+def _grad_ok(got, ref, tol, exact):
+    """Element-wise bound; in tensor-core mode a ReLU unit whose pre-activation is within rounding of zero may switch
+    state against the oracle, which changes one whole row of a weight gradient: then require the tensor as a whole to
+    agree (cosine >= 0.995, relative L2 error <= 0.12)."""
+    if _rel(got, ref) <= tol:
+        return True
+    if exact:
+        return False
+    a, b = got.astype(np.float64).ravel(), ref.astype(np.float64).ravel()
+    cos = float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-300))
+    return cos >= 0.995 and np.linalg.norm(a - b) <= 0.12 * np.linalg.norm(b)
+
+
+def _trainer(monkeypatch, exact, model, **kw):
     from cvml_goalnet_b200.train import AVMTrainer
+    if exact:
+        monkeypatch.setenv("GN_TRAIN_FP32", "1")
+    else:
+        monkeypatch.delenv("GN_TRAIN_FP32", raising=False)
+    return AVMTrainer(model, **kw)
+
+
+@pytest.mark.parametrize("exact", [True, False])
+@pytest.mark.parametrize("audio_included,n,fixed", [(True, 10, False), (False, 7, False), (True, 4, True)])
+def test_avm_train_step_vs_oracle_no_dropout(cuda_device, monkeypatch, audio_included, n, fixed, exact):
+    from cvml_goalnet_b200 import utils as U
+    tol = TOL[exact]
     w, vis, aud, lab = _avm_case(n, audio_included, 5 + n)
     m = U.AVM(audio_included)
     m.load_state_dict(w)
-    tr = AVMTrainer(m, max_frames=16, dropout_p=0.0, fixed_loss=fixed)
+    tr = _trainer(monkeypatch, exact, m, max_frames=16, dropout_p=0.0, fixed_loss=fixed)
     losses, scores0, grads0, out = O.avm_train_steps(w, aud, vis, lab, steps=2, audio_included=audio_included,
                                                      fixed_loss=fixed)
     tr.forward_backward(aud, vis, lab)
-    assert abs(float(tr.loss.item()) - losses[0]) <= 1e-5 * abs(losses[0])
-    assert np.abs(tr.scores[:n].cpu().numpy() - scores0).max() <= 2e-5
+    assert abs(float(tr.loss.item()) - losses[0]) <= tol["loss"] * abs(losses[0])
+    assert np.abs(tr.scores[:n].cpu().numpy() - scores0).max() <= tol["score"]
     g = tr.grad_dict()
     for k, ref in grads0.items():
-        assert _rel(g[k].cpu().numpy(), ref) <= 5e-3, k           # fp32; sums of ~1200 cancelling terms in another order than oneDNN
+        assert _grad_ok(g[k].cpu().numpy(), ref, tol["grad"], exact), k
     tr.optimizer_step()
     loss2, _ = tr.step(aud, vis, lab)
-    assert abs(float(loss2.item()) - losses[1]) <= 2e-4 * abs(losses[1])
+    assert abs(float(loss2.item()) - losses[1]) <= tol["loss2"] * abs(losses[1])
     sd = tr.state_dict()
     for k, ref in out.items():
         got = sd[k].cpu().numpy()
         # Adam's first steps move every weight by ~lr * sign(gradient) whatever the gradient's size, so an element
         # whose gradient is rounding noise (e.g. a conv bias in front of a batch-statistics BatchNorm) may step the
-        # other way: bound the bulk tightly and the outliers by two full steps
+        # other way: bound the bulk and the outliers by two full steps
         err = np.abs(got - ref)
         assert np.median(err) <= 5e-5 and np.mean(err <= 2.5e-4) >= 0.5, k
         assert err.max() <= 2 * 2 * 1e-3 + 1e-4 * np.abs(ref).max(), k
 
 
-def test_avm_train_step_golden_reference_model(cuda_device, golden):
+@pytest.mark.parametrize("exact", [True, False])
+def test_avm_train_step_golden_reference_model(cuda_device, monkeypatch, golden, exact):
     """Against vectors produced by the REFERENCE AVM object in train mode (oracle/gen_golden.py: gen_train_avm)."""
     from cvml_goalnet_b200 import utils as U
-    from cvml_goalnet_b200.train import AVMTrainer
+    tol = TOL[exact]
     g = golden("train_avm")
     for tag, audio_included in (("av", True), ("v", False)):
         w = syn.make_weights(seed=1, audio_included=audio_included)
         m = U.AVM(audio_included)
         m.load_state_dict(w)
-        tr = AVMTrainer(m, max_frames=10, dropout_p=0.0)
+        tr = _trainer(monkeypatch, exact, m, max_frames=10, dropout_p=0.0)
         vis, aud, lab = g[f"{tag}_vis"], g[f"{tag}_aud"], g[f"{tag}_labels"]
         tr.forward_backward(aud, vis, lab)
-        assert abs(float(tr.loss.item()) - g[f"{tag}_losses"][0]) <= 1e-5 * g[f"{tag}_losses"][0]
-        assert np.abs(tr.scores[:len(lab)].cpu().numpy() - g[f"{tag}_pred"]).max() <= 2e-5
+        assert abs(float(tr.loss.item()) - g[f"{tag}_losses"][0]) <= tol["loss"] * g[f"{tag}_losses"][0]
+        assert np.abs(tr.scores[:len(lab)].cpu().numpy() - g[f"{tag}_pred"]).max() <= tol["score"]
         gd = tr.grad_dict()
         for k, v in gd.items():
             got = v.cpu().numpy()
             ref = g[f"{tag}_gs_{k}"]          # (a dead channel's gradient is rounding noise around 1e-9: absolute floor)
-            assert np.abs(got.ravel()[::997] - ref).max() <= 5e-3 * np.abs(ref).max() + 1e-7, k
+            assert np.abs(got.ravel()[::997] - ref).max() <= tol["grad"] * np.abs(ref).max() + 1e-7, k
             l2 = float(np.sqrt(np.sum(np.square(got.astype(np.float64)))))
-            assert abs(l2 - float(g[f"{tag}_gl2_{k}"])) <= 2e-3 * float(g[f"{tag}_gl2_{k}"]) + 1e-7, k
+            assert abs(l2 - float(g[f"{tag}_gl2_{k}"])) <= (2e-3 if exact else 1e-2) * float(g[f"{tag}_gl2_{k}"]) + 1e-7, k
         tr.optimizer_step()
         loss2, _ = tr.step(aud, vis, lab)
-        assert abs(float(loss2.item()) - g[f"{tag}_losses"][1]) <= 2e-4 * g[f"{tag}_losses"][1]
+        assert abs(float(loss2.item()) - g[f"{tag}_losses"][1]) <= tol["loss2"] * g[f"{tag}_losses"][1]
 
 
-def test_avm_train_step_dropout_masks_and_eval_after_sync(cuda_device):
+@pytest.mark.parametrize("exact", [True, False])
+def test_avm_train_step_dropout_masks_and_eval_after_sync(cuda_device, monkeypatch, exact):
     from cvml_goalnet_b200 import utils as U
-    from cvml_goalnet_b200.train import AVMTrainer, DROPOUT_WIDTHS
+    from cvml_goalnet_b200.train import DROPOUT_WIDTHS
+    tol = TOL[exact]
     n = 10
     w, vis, aud, lab = _avm_case(n, True, 99)
     rng = np.random.default_rng(7)
     masks = [[(rng.random((n, wd)) < 0.8).astype(np.uint8) for wd in DROPOUT_WIDTHS] for _ in range(2)]
     m = U.AVM(True)
     m.load_state_dict(w)
-    tr = AVMTrainer(m, max_frames=n, dropout_p=0.2)
+    tr = _trainer(monkeypatch, exact, m, max_frames=n, dropout_p=0.2)
     losses, scores0, grads0, out = O.avm_train_steps(w, aud, vis, lab, steps=2, masks=masks)
     tr.forward_backward(aud, vis, lab, masks=masks[0])
-    assert abs(float(tr.loss.item()) - losses[0]) <= 1e-5 * abs(losses[0])
+    assert abs(float(tr.loss.item()) - losses[0]) <= tol["loss"] * abs(losses[0])
     g = tr.grad_dict()
     for k, ref in grads0.items():
-        assert _rel(g[k].cpu().numpy(), ref) <= 5e-3, k
+        assert _grad_ok(g[k].cpu().numpy(), ref, tol["grad"], exact), k
     tr.optimizer_step()
     loss2, _ = tr.step(aud, vis, lab, masks=masks[1])
-    assert abs(float(loss2.item()) - losses[1]) <= 2e-4 * abs(losses[1])
+    assert abs(float(loss2.item()) - losses[1]) <= tol["loss2"] * abs(losses[1])
     # generated masks: the step runs and the keep rate is about 0.8 (loss stays finite, parameters move)
     loss3, _ = tr.step(aud, vis, lab)
     assert np.isfinite(float(loss3.item()))
