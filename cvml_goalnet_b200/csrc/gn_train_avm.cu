@@ -110,8 +110,17 @@ linear_fwd_kernel(const float* __restrict__ x, int ldx, const float* __restrict_
         const int n = (int)(o / O), j = (int)(o - (int64_t)n * O);
         const float* xr = x + (int64_t)n * ldx;
         const float* wr = w + (int64_t)j * K;
-        float acc = 0.f;
-        for (int k = lane; k < K; k += 32) acc = fmaf(xr[k], wr[k], acc);
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;            // four independent chains, loads batched by the unroll
+        int k = lane;
+#pragma unroll 2
+        for (; k + 96 < K; k += 128) {
+            a0 = fmaf(xr[k], wr[k], a0);
+            a1 = fmaf(xr[k + 32], wr[k + 32], a1);
+            a2 = fmaf(xr[k + 64], wr[k + 64], a2);
+            a3 = fmaf(xr[k + 96], wr[k + 96], a3);
+        }
+        for (; k < K; k += 32) a0 = fmaf(xr[k], wr[k], a0);
+        float acc = (a0 + a1) + (a2 + a3);
         for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
         if (lane == 0) {
             float v = acc + b[j];
@@ -188,9 +197,17 @@ linear_bwd_x_kernel(const float* __restrict__ dy, int ldy, int col_off, const fl
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         const int n = (int)(i / K), k = (int)(i - (int64_t)n * K);
         const float* d = dy + (int64_t)n * ldy + col_off;
-        float acc = 0.f;
-        for (int o = 0; o < O; ++o) acc = fmaf(d[o], w[(int64_t)o * K + k], acc);
-        dx[i] = acc;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        int o = 0;
+#pragma unroll 2
+        for (; o + 3 < O; o += 4) {
+            a0 = fmaf(d[o], w[(int64_t)o * K + k], a0);
+            a1 = fmaf(d[o + 1], w[(int64_t)(o + 1) * K + k], a1);
+            a2 = fmaf(d[o + 2], w[(int64_t)(o + 2) * K + k], a2);
+            a3 = fmaf(d[o + 3], w[(int64_t)(o + 3) * K + k], a3);
+        }
+        for (; o < O; ++o) a0 = fmaf(d[o], w[(int64_t)o * K + k], a0);
+        dx[i] = (a0 + a1) + (a2 + a3);
     }
 }
 
@@ -209,6 +226,85 @@ linear_bwd_w_kernel(const float* __restrict__ dy, int ldy, int col_off, const fl
         }
         dw[i] = acc;
         if (k == 0) db[o] = accb;
+    }
+}
+
+// Sub-batch versions (N <= kMaxRows): every weight is read ONCE and used for all rows, instead of once per row.
+constexpr int kMaxRows = 16;
+// y[n][o]: one warp per output feature o, all rows at once
+__global__ void __launch_bounds__(kT)
+linear_fwd_rows_kernel(const float* __restrict__ x, int ldx, const float* __restrict__ w, const float* __restrict__ b, int N,
+                       int K, int O, int relu, const uint8_t* __restrict__ mask, float scale, float* __restrict__ y, int ldy,
+                       int col_off) {
+    const int lane = threadIdx.x & 31;
+    const int gw = (int)((blockIdx.x * (int64_t)kT + threadIdx.x) >> 5), nw = (int)(((int64_t)gridDim.x * kT) >> 5);
+    for (int j = gw; j < O; j += nw) {
+        const float* wr = w + (int64_t)j * K;
+        float acc[kMaxRows];
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n) acc[n] = 0.f;
+#pragma unroll 4
+        for (int k = lane; k < K; k += 32) {
+            const float wv = wr[k];
+#pragma unroll
+            for (int n = 0; n < kMaxRows; ++n)
+                if (n < N) acc[n] = fmaf(x[(int64_t)n * ldx + k], wv, acc[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n) {
+            if (n >= N) break;
+            float v = acc[n];
+            for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+            if (lane == 0) {
+                v += b[j];
+                if (relu) v = fmaxf(v, 0.f);
+                if (mask) v = mask[(int64_t)n * O + j] ? v * scale : 0.f;
+                y[(int64_t)n * ldy + col_off + j] = v;
+            }
+        }
+    }
+}
+// dx[n][k]: one thread per input feature k, all rows at once
+__global__ void __launch_bounds__(kT)
+linear_bwd_x_rows_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ w, int N, int K, int O,
+                         float* __restrict__ dx) {
+    extern __shared__ float sd[];                    // dy[n][o] for the whole sub-batch
+    for (int i = threadIdx.x; i < N * O; i += kT) sd[i] = dy[(int64_t)(i / O) * ldy + col_off + i % O];
+    __syncthreads();
+    for (int k = blockIdx.x * kT + threadIdx.x; k < K; k += gridDim.x * kT) {
+        float acc[kMaxRows];
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n) acc[n] = 0.f;
+#pragma unroll 8
+        for (int o = 0; o < O; ++o) {
+            const float wv = w[(int64_t)o * K + k];
+#pragma unroll
+            for (int n = 0; n < kMaxRows; ++n)
+                if (n < N) acc[n] = fmaf(sd[n * O + o], wv, acc[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n)
+            if (n < N) dx[(int64_t)n * K + k] = acc[n];
+    }
+}
+// dw[o][k..k+3], db[o]: one thread per (o, 4 consecutive k), K % 4 == 0
+__global__ void __launch_bounds__(kT)
+linear_bwd_w_vec4_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ x, int ldx, int N, int K,
+                         int O, float* __restrict__ dw, float* __restrict__ db) {
+    const int K4 = K >> 2;
+    const int64_t total = (int64_t)O * K4;
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        const int o = (int)(i / K4), k4 = (int)(i - (int64_t)o * K4);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float accb = 0.f;
+        for (int n = 0; n < N; ++n) {
+            const float d = dy[(int64_t)n * ldy + col_off + o];
+            const float4 xv = *reinterpret_cast<const float4*>(x + (int64_t)n * ldx + 4 * k4);
+            acc.x = fmaf(d, xv.x, acc.x); acc.y = fmaf(d, xv.y, acc.y); acc.z = fmaf(d, xv.z, acc.z); acc.w = fmaf(d, xv.w, acc.w);
+            accb += d;
+        }
+        *reinterpret_cast<float4*>(dw + (int64_t)o * K + 4 * k4) = acc;
+        if (k4 == 0) db[o] = accb;
     }
 }
 
@@ -866,6 +962,40 @@ int conv_bwd_x_tc(gn_avm_trainer* t, const float* dy, const float* w, int n, int
 }
 }  // namespace
 
+namespace {
+// linear layers: sub-batch kernels (every weight read once for all rows) when the batch fits their register arrays
+int lin_fwd(gn_avm_trainer* t, cudaStream_t st, const float* x, int ldx, const float* w, const float* b, int N, int K, int O,
+            int relu, const uint8_t* mask, float scale, float* y, int ldy, int col_off) {
+    const int cap = t->h->num_sms * 8;
+    // (the all-rows kernel pays 16 strided activation loads per weight: only worth it for short reductions)
+    if (N <= kMaxRows && K <= 1024) linear_fwd_rows_kernel<<<grid_for((int64_t)O * 32, cap), kT, 0, st>>>(x, ldx, w, b, N, K, O, relu, mask, scale, y, ldy, col_off);
+    else linear_fwd_kernel<<<grid_for((int64_t)N * O * 32, cap), kT, 0, st>>>(x, ldx, w, b, N, K, O, relu, mask, scale, y, ldy, col_off);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+int lin_bwd_x(gn_avm_trainer* t, cudaStream_t st, const float* dy, int ldy, int col_off, const float* w, int N, int K, int O,
+              float* dx) {
+    const int cap = t->h->num_sms * 8;
+    if (N <= kMaxRows && (size_t)N * O * 4 <= 48 * 1024)
+        linear_bwd_x_rows_kernel<<<grid_for(K, cap), kT, (size_t)N * O * 4, st>>>(dy, ldy, col_off, w, N, K, O, dx);
+    else linear_bwd_x_kernel<<<grid_for((int64_t)N * K, cap), kT, 0, st>>>(dy, ldy, col_off, w, N, K, O, dx);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+int lin_bwd_w(gn_avm_trainer* t, cudaStream_t st, const float* dy, int ldy, int col_off, const float* x, int ldx, int N, int K,
+              int O, float* dw, float* db) {
+    const int cap = t->h->num_sms * 16;
+    const bool v4 = (K % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dw)) & 15) == 0;
+    if (v4) linear_bwd_w_vec4_kernel<<<grid_for((int64_t)O * (K / 4), cap), kT, 0, st>>>(dy, ldy, col_off, x, ldx, N, K, O, dw, db);
+    else linear_bwd_w_kernel<<<grid_for((int64_t)O * K, cap), kT, 0, st>>>(dy, ldy, col_off, x, ldx, N, K, O, dw, db);
+    GN_LAUNCHED(t->h);
+    return GN_OK;
+}
+}  // namespace
+#define LF(...) do { int rc_ = lin_fwd(t, st, __VA_ARGS__); if (rc_) return rc_; } while (0)
+#define LBX(...) do { int rc_ = lin_bwd_x(t, st, __VA_ARGS__); if (rc_) return rc_; } while (0)
+#define LBW(...) do { int rc_ = lin_bwd_w(t, st, __VA_ARGS__); if (rc_) return rc_; } while (0)
+
 #define TL(kern, total, ...)                                                             \
     do {                                                                                 \
         kern<<<grid_for((total), cap), kT, 0, st>>>(__VA_ARGS__);                        \
@@ -908,9 +1038,14 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     const float* x = d_visual;
     for (int i = 0; i < 3; ++i) {
         const bool tc = t->use_tc && i > 0;
-        int rc = (tc ? conv_fwd_tc : conv_fwd_gemm)(t, x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], C[i], stride[i],
-                                                    pad[i], OH[i], t->y[i], st);
-        if (rc) return rc;
+        if (i == 0) {     // K = 27: direct kernel (a GEMM tile would be mostly padding)
+            TL(conv_fwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], IH[i], C[i], 3,
+               3, stride[i], stride[i], pad[i], pad[i], OH[i], OH[i], 1, t->y[i]);
+        } else {
+            int rc = (tc ? conv_fwd_tc : conv_fwd_gemm)(t, x, P + o[cw[i]], P + o[cb[i]], n, Cin[i], IH[i], C[i], stride[i],
+                                                        pad[i], OH[i], t->y[i], st);
+            if (rc) return rc;
+        }
         TL(pool_fwd_kernel, (int64_t)n * C[i] * PH[i] * PH[i], t->y[i], n * C[i], OH[i], OH[i], t->p[i], t->arg[i]);
         bn_fwd_kernel<<<C[i], kT, 0, st>>>(t->p[i], n, C[i], PH[i] * PH[i], P + o[bw[i]], P + o[bb[i]], t->rmean[i],
                                            t->rvar[i], t->xh[i], t->istd[i], t->a[i]);
@@ -919,7 +1054,7 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     }
     const int aoff = t->audio ? 128 : 0;
     // linear5 + ReLU + Dropout -> columns [aoff, aoff+512) of the fusion input; NCHW flatten == the reference's order
-    TL(linear_fwd_kernel, (int64_t)n * 512 * 32, t->a[2], (int)t->K5, P + o[P_L5W], P + o[P_L5B], n, (int)t->K5, 512, 1, mk[0],
+    LF( t->a[2], (int)t->K5, P + o[P_L5W], P + o[P_L5B], n, (int)t->K5, 512, 1, mk[0],
        scale, t->fin_buf, t->fin, aoff);
     // ---------------- forward: AudBl (utils.py:214-227) ----------------
     if (t->audio) {
@@ -927,7 +1062,7 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
            1, t->L1, 1, t->ay1);
         TL(conv_fwd_kernel, (int64_t)n * 128 * t->L2, t->ay1, P + o[P_AC2W], P + o[P_AC2B], n, 64, 1, t->L1, 128, 1, 3, 1, 2, 0,
            1, 1, t->L2, 1, t->ay2);
-        TL(linear_fwd_kernel, (int64_t)n * 128 * 32, t->ay2, 128 * t->L2, P + o[P_AL3W], P + o[P_AL3B], n, 128 * t->L2, 128, 1,
+        LF( t->ay2, 128 * t->L2, P + o[P_AL3W], P + o[P_AL3B], n, 128 * t->L2, 128, 1,
            (const uint8_t*)nullptr, 1.f, t->fin_buf, t->fin, 0);
     }
     // ---------------- forward: fusion (utils.py:242-258) ----------------
@@ -935,24 +1070,24 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     const int fwi[4] = {P_F0W, P_F3W, P_F6W, P_F9W}, fbi[4] = {P_F0B, P_F3B, P_F6B, P_F9B};
     const float* hin = t->fin_buf;
     for (int i = 0; i < 4; ++i) {
-        TL(linear_fwd_kernel, (int64_t)n * fw[i] * 32, hin, fk[i], P + o[fwi[i]], P + o[fbi[i]], n, fk[i], fw[i], 1, mk[i + 1],
+        LF( hin, fk[i], P + o[fwi[i]], P + o[fbi[i]], n, fk[i], fw[i], 1, mk[i + 1],
            scale, t->f[i], fw[i], 0);
         hin = t->f[i];
     }
-    TL(linear_fwd_kernel, (int64_t)n * 32, t->f[3], 128, P + o[P_F12W], P + o[P_F12B], n, 128, 1, 0, (const uint8_t*)nullptr,
+    LF( t->f[3], 128, P + o[P_F12W], P + o[P_F12B], n, 128, 1, 0, (const uint8_t*)nullptr,
        1.f, t->z, 1, 0);
     loss_kernel<<<1, kT, 0, st>>>(t->z, d_labels, n, fixed_loss, d_scores, t->dz, d_loss);
     GN_LAUNCHED(t->h);
 
     // ---------------- backward: fusion ----------------
-    TL(linear_bwd_w_kernel, 128, t->dz, 1, 0, t->f[3], 128, n, 128, 1, G + o[P_F12W], G + o[P_F12B]);
-    TL(linear_bwd_x_kernel, (int64_t)n * 128, t->dz, 1, 0, P + o[P_F12W], n, 128, 1, t->d_f[3]);
+    LBW( t->dz, 1, 0, t->f[3], 128, n, 128, 1, G + o[P_F12W], G + o[P_F12B]);
+    LBX( t->dz, 1, 0, P + o[P_F12W], n, 128, 1, t->d_f[3]);
     for (int i = 3; i >= 0; --i) {
         TL(relu_drop_bwd_kernel, (int64_t)n * fw[i], t->d_f[i], t->f[i], mk[i + 1], scale, (int64_t)n * fw[i]);
         const float* xin = i ? t->f[i - 1] : t->fin_buf;
-        TL(linear_bwd_w_kernel, (int64_t)fw[i] * fk[i], t->d_f[i], fw[i], 0, xin, fk[i], n, fk[i], fw[i], G + o[fwi[i]],
+        LBW( t->d_f[i], fw[i], 0, xin, fk[i], n, fk[i], fw[i], G + o[fwi[i]],
            G + o[fbi[i]]);
-        TL(linear_bwd_x_kernel, (int64_t)n * fk[i], t->d_f[i], fw[i], 0, P + o[fwi[i]], n, fk[i], fw[i],
+        LBX( t->d_f[i], fw[i], 0, P + o[fwi[i]], n, fk[i], fw[i],
            i ? t->d_f[i - 1] : t->d_fin);
     }
     // d_fin = gradient w.r.t. [audio128 | visual512] (both are post-ReLU outputs; the visual half also post-dropout)
@@ -965,9 +1100,9 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
         GN_CUDA(cudaMemcpy2DAsync(al3, 128 * 4, t->fin_buf, (size_t)t->fin * 4, 128 * 4, n, cudaMemcpyDeviceToDevice, st));
         TL(relu_drop_bwd_kernel, (int64_t)n * 128, dl3, al3, (const uint8_t*)nullptr, 1.f, (int64_t)n * 128);
         const int K3 = 128 * t->L2;
-        TL(linear_bwd_w_kernel, (int64_t)128 * K3, dl3, 128, 0, t->ay2, K3, n, K3, 128, G + o[P_AL3W], G + o[P_AL3B]);
+        LBW( dl3, 128, 0, t->ay2, K3, n, K3, 128, G + o[P_AL3W], G + o[P_AL3B]);
         float* day2 = t->d_big1;         // [n][128][L2]  (al3 is dead after the gate)
-        TL(linear_bwd_x_kernel, (int64_t)n * K3, dl3, 128, 0, P + o[P_AL3W], n, K3, 128, day2);
+        LBX( dl3, 128, 0, P + o[P_AL3W], n, K3, 128, day2);
         TL(relu_drop_bwd_kernel, (int64_t)n * K3, day2, t->ay2, (const uint8_t*)nullptr, 1.f, (int64_t)n * K3);
         TL(conv_bwd_w_kernel, (int64_t)128 * 192 * 32, day2, t->ay1, n, 64, 1, t->L1, 128, 1, 3, 1, 2, 0, 1, 1, t->L2,
            G + o[P_AC2W], G + o[P_AC2B]);
@@ -983,9 +1118,9 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
     GN_CUDA(cudaMemcpy2DAsync(dh5, 512 * 4, t->d_fin + aoff, (size_t)t->fin * 4, 512 * 4, n, cudaMemcpyDeviceToDevice, st));
     GN_CUDA(cudaMemcpy2DAsync(t->h5, 512 * 4, t->fin_buf + aoff, (size_t)t->fin * 4, 512 * 4, n, cudaMemcpyDeviceToDevice, st));
     TL(relu_drop_bwd_kernel, (int64_t)n * 512, dh5, t->h5, mk[0], scale, (int64_t)n * 512);
-    TL(linear_bwd_w_kernel, 512 * t->K5, dh5, 512, 0, t->a[2], (int)t->K5, n, (int)t->K5, 512, G + o[P_L5W], G + o[P_L5B]);
+    LBW( dh5, 512, 0, t->a[2], (int)t->K5, n, (int)t->K5, 512, G + o[P_L5W], G + o[P_L5B]);
     float* da = t->d_big1;               // gradient w.r.t. the BN output of block i
-    TL(linear_bwd_x_kernel, (int64_t)n * t->K5, dh5, 512, 0, P + o[P_L5W], n, (int)t->K5, 512, da);
+    LBX( dh5, 512, 0, P + o[P_L5W], n, (int)t->K5, 512, da);
     for (int i = 2; i >= 0; --i) {
         float* dp = (da == t->d_big1) ? t->d_big0 : t->d_big1;
         bn_bwd_kernel<<<C[i], kT, 0, st>>>(da, t->xh[i], t->istd[i], P + o[bw[i]], n, C[i], PH[i] * PH[i], dp, G + o[bw[i]],
@@ -995,9 +1130,15 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
         TL(pool_relu_bwd_kernel, (int64_t)n * C[i] * OH[i] * OH[i], dp, t->arg[i], t->y[i], n * C[i], OH[i], OH[i], dy);
         const float* xin = i ? t->a[i - 1] : d_visual;
         const bool tc = t->use_tc && i > 0;
-        int rc = (tc ? conv_bwd_w_tc : conv_bwd_w_gemm)(t, dy, xin, n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i],
+        int rc = GN_OK;
+        if (i == 0) {
+            TL(conv_bwd_w_kernel, (int64_t)C[i] * Cin[i] * 9 * 32, dy, xin, n, Cin[i], IH[i], IH[i], C[i], 3, 3, stride[i],
+               stride[i], pad[i], pad[i], OH[i], OH[i], G + o[cw[i]], G + o[cb[i]]);
+        } else {
+            rc = (tc ? conv_bwd_w_tc : conv_bwd_w_gemm)(t, dy, xin, n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i],
                                                         G + o[cw[i]], G + o[cb[i]], st);
-        if (rc) return rc;
+            if (rc) return rc;
+        }
         if (i > 0) {
             rc = (tc ? conv_bwd_x_tc : conv_bwd_x_gemm)(t, dy, P + o[cw[i]], n, Cin[i], IH[i], C[i], stride[i], pad[i], OH[i],
                                                         dp, st);
