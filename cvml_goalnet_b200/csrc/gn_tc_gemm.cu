@@ -312,10 +312,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int vy = min(P, args.g.pfull - gy0), vx = min(P, args.g.pfull - gx0);   // valid outputs of an edge tile
                 __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + n0;
                 // BatchNorm affine + bf16 store of one pooled (pixel, 8-channel group)
-                auto emit = [&](int oy, int ox, int cg, uint4 m) {
-                    const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
-                    const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
-                    const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
+                auto emit = [&](int oy, int ox, int cg, uint4 m, const float4& sc0, const float4& sc1, const float4& sh0,
+                                const float4& sh1) {
                     const float2 f0 = bf2_to_f2(m.x), f1 = bf2_to_f2(m.y), f2 = bf2_to_f2(m.z), f3 = bf2_to_f2(m.w);
                     const uint4 o = make_uint4(pack_bf16(fmaf(f0.x, sc0.x, sh0.x), fmaf(f0.y, sc0.y, sh0.y)),
                                                pack_bf16(fmaf(f1.x, sc0.z, sh0.z), fmaf(f1.y, sc0.w, sh0.w)),
@@ -333,6 +331,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     // 3-wide horizontal max (3 loads), per pooled row the max of the last three of those
                     const int ox = et / CG, cg = et - ox * CG;
                     if (ox < vx) {
+                        // the thread's channel group is fixed: its BatchNorm parameters are loaded once per tile
+                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
+                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
+                        const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
                         const unsigned char* s0 = stg + (size_t)ox * C::kStgStride + cg * 16;
                         uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;
 #pragma unroll
@@ -342,7 +344,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 const uint4 h2 = hmax2_u4(hmax2_u4(*reinterpret_cast<const uint4*>(sr),
                                                                    *reinterpret_cast<const uint4*>(sr + C::kStgStride)),
                                                           *reinterpret_cast<const uint4*>(sr + 2 * C::kStgStride));
-                                if (r >= 2) emit(r - 2, ox, cg, hmax2_u4(hmax2_u4(h0, h1), h2));
+                                if (r >= 2) emit(r - 2, ox, cg, hmax2_u4(hmax2_u4(h0, h1), h2), sc0, sc1, sh0, sh1);
                                 h0 = h1;
                                 h1 = h2;
                             }
@@ -363,7 +365,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 if (dy == 0 && dx == 0) continue;
                                 m = hmax2_u4(m, *reinterpret_cast<const uint4*>(s0 + (size_t)(dy * OHT + dx) * C::kStgStride));
                             }
-                        emit(oy, ox, cg, m);
+                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
+                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
+                        emit(oy, ox, cg, m, sc[0], sc[1], sh[0], sh[1]);
                     }
                 }
                 if (args.g.out_pad && tiles_pf == 1) {   // zero border of the next conv's input (padding = 1);
