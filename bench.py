@@ -206,7 +206,8 @@ def native_arm(args, rank, world, local_rank):
     # ground-truth summaries: one postprocess per annotator (reference utils.py:102-118)
     ann = syn.make_annotator_importances(n_raw, N_USERS, seed=rank)
     gd = U.gt_summaries_array(np.stack(ann), SKIP, n_raw, cps, device=dev, return_device=True)
-    scorer = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev)
+    scorer = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev,
+                         h2d_chunks=int(os.environ.get("GN_H2D_CHUNKS", "16")))
     gathered = torch.empty((world, n, 1), dtype=torch.float32, device=dev) if world > 1 else None
 
     def step_device():

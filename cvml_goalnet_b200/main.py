@@ -24,7 +24,7 @@ class MatchScorer:
     """
 
     def __init__(self, model: U.AVM, n_frames: int, H: int, W: int, samples: int, sr: int, skip_frames: int,
-                 full_n_frames: int, bin_length: int = 30, device=None, h2d_chunks: int = 8):
+                 full_n_frames: int, bin_length: int = 30, device=None, h2d_chunks: int = 16):
         self.dev = U._device(device)
         self.model = model
         self.n, self.H, self.W = int(n_frames), int(H), int(W)
