@@ -90,7 +90,7 @@ struct gn_ws {
 };
 gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
 int gn_tc_gemm_tf32(gn_handle* h, const float* A, int64_t M, int K, int64_t lda, const float* B, int N, int64_t ldb,
-                    float* C, cudaStream_t st);   // gn_tc_gemm.cu: C[M][N] = A[M][K] . B[N][K]^T, TF32 tensor cores
+                    float* C, cudaStream_t st, int k_splits = 1);   // gn_tc_gemm.cu: C[split][M][N] = A[M][K range] . B[N][K range]^T, TF32 tensor cores
 int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, int C, cudaStream_t st);   // gn_tc_gemm.cu
 int gn_linear5_plan(const gn_model* m, int64_t n, int64_t* rows_direct);   // gn_tc_gemm.cu: rows run as whole tiles + K ranges of the rest
 

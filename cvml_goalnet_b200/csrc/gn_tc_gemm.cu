@@ -128,7 +128,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int n_blocks = args.N / BN;
     const int tiles_pf = (MODE == kConv) ? args.g.tiles * args.g.tiles : 1;      // spatial tiles per frame
     const int64_t m_blocks = (MODE == kConv) ? args.M * tiles_pf : (args.M + 127) / 128;
-    const int k_splits = (MODE == kSplitK) ? args.k_splits : 1;
+    const int k_splits = (MODE == kSplitK || MODE == kGemmTF32) ? (args.k_splits > 1 ? args.k_splits : 1) : 1;
     const int64_t num_tiles = m_blocks * n_blocks * k_splits;
     constexpr int kbk = (MODE == kGemmTF32) ? 32 : kBK;      // elements per 128-byte operand row
     const int k_total = args.K / kbk;
@@ -841,9 +841,13 @@ int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, 
 // C[M][N] (fp32, row-major) = A[M][K] . B[N][K]^T with fp32 operands multiplied as TF32 on the tensor cores; K % 32 == 0,
 // N % 128 == 0, lda/ldb in elements (multiples of 4).  Rows of A beyond M are zero-filled by TMA and never stored.
 int gn_tc_gemm_tf32(gn_handle* h, const float* A, int64_t M, int K, int64_t lda, const float* B, int N, int64_t ldb,
-                    float* C, cudaStream_t st) {
+                    float* C, cudaStream_t st, int k_splits) {
     constexpr int BN = 128;
-    if (K % 32 || N % BN || M <= 0 || (lda & 3) || (ldb & 3)) return GN_E_SHAPE;
+    if (K % 32 || N % BN || M <= 0 || (lda & 3) || (ldb & 3) || k_splits < 1) return GN_E_SHAPE;
+    {   // every K range non-empty
+        const int ksteps = K / 32, per = (ksteps + k_splits - 1) / k_splits;
+        k_splits = (ksteps + per - 1) / per;
+    }
     if (!h->encode_tiled) return GN_E_NODEVICE;
     CUtensorMap ta, tb;
     for (int which = 0; which < 2; ++which) {
@@ -858,12 +862,12 @@ int gn_tc_gemm_tf32(gn_handle* h, const float* A, int64_t M, int K, int64_t lda,
         if (r != CUDA_SUCCESS) return (int)r;
     }
     GemmArgs a{};
-    a.M = M; a.N = N; a.K = K; a.out_f32 = C;
-    return launch<1, BN, 4, kGemmTF32, 0>(h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
+    a.M = M; a.N = N; a.K = K; a.out_f32 = C; a.k_splits = k_splits; a.split_stride = M * N;
+    return launch<1, BN, 4, kGemmTF32, 0>(h, ta, tb, a, ((M + 127) / 128) * (N / BN) * k_splits, st);
 }
 
 extern "C" int gn_dbg_gemm_tf32(gn_handle* h, const float* d_a, int64_t M, int K, const float* d_b, int N, float* d_c,
                                 void* stream) {
     if (!h || !d_a || !d_b || !d_c) return GN_E_ARG;
-    return gn_tc_gemm_tf32(h, d_a, M, K, K, d_b, N, K, d_c, gn_stream(stream));
+    return gn_tc_gemm_tf32(h, d_a, M, K, K, d_b, N, K, d_c, gn_stream(stream), 1);
 }

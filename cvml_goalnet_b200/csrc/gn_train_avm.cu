@@ -264,19 +264,74 @@ linear_fwd_rows_kernel(const float* __restrict__ x, int ldx, const float* __rest
         }
     }
 }
+// Long reductions (linear5: K = 41 472): the K axis is cut into chunks of kLinCK, one CTA per (chunk, 64 features); the
+// chunk's activations sit in shared memory, every weight is read once and used for all rows; partial sums
+// part[chunk][n][o] are reduced (in chunk order: deterministic) by linear_fwd_reduce_kernel with bias / ReLU / dropout.
+constexpr int kLinCK = 512;
+__global__ void __launch_bounds__(kT)
+linear_fwd_chunk_kernel(const float* __restrict__ x, int ldx, const float* __restrict__ w, int N, int K, int O,
+                        float* __restrict__ part) {
+    extern __shared__ float xs[];                    // [N][kLinCK]
+    const int k0 = blockIdx.x * kLinCK, kc = min(kLinCK, K - k0);
+    for (int i = threadIdx.x; i < N * kLinCK; i += kT) {
+        const int n = i / kLinCK, k = i - n * kLinCK;
+        xs[i] = k < kc ? x[(int64_t)n * ldx + k0 + k] : 0.f;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int jj = warp; jj < 64; jj += kT / 32) {
+        const int j = blockIdx.y * 64 + jj;
+        if (j >= O) break;
+        const float* wr = w + (int64_t)j * K + k0;
+        float acc[kMaxRows];
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n) acc[n] = 0.f;
+#pragma unroll 4
+        for (int k = lane; k < kc; k += 32) {
+            const float wv = wr[k];
+#pragma unroll
+            for (int n = 0; n < kMaxRows; ++n)
+                if (n < N) acc[n] = fmaf(xs[n * kLinCK + k], wv, acc[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < kMaxRows; ++n) {
+            if (n >= N) break;
+            float v = acc[n];
+            for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+            if (lane == 0) part[((int64_t)blockIdx.x * N + n) * O + j] = v;
+        }
+    }
+}
+__global__ void __launch_bounds__(kT)
+linear_fwd_reduce_kernel(const float* __restrict__ part, int chunks, const float* __restrict__ b, int N, int O, int relu,
+                         const uint8_t* __restrict__ mask, float scale, float* __restrict__ y, int ldy, int col_off) {
+    for (int i = blockIdx.x * kT + threadIdx.x; i < N * O; i += gridDim.x * kT) {
+        const int n = i / O, j = i - n * O;
+        float v = b[j];
+        for (int c = 0; c < chunks; ++c) v += part[(int64_t)c * N * O + i];
+        if (relu) v = fmaxf(v, 0.f);
+        if (mask) v = mask[i] ? v * scale : 0.f;
+        y[(int64_t)n * ldy + col_off + j] = v;
+    }
+}
+
 // dx[n][k]: one thread per input feature k, all rows at once
+// (gridDim.y > 1: output features are cut into gridDim.y ranges whose partial sums go to dx[range][n][k]; the caller
+//  reduces them in range order)
 __global__ void __launch_bounds__(kT)
 linear_bwd_x_rows_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ w, int N, int K, int O,
                          float* __restrict__ dx) {
     extern __shared__ float sd[];                    // dy[n][o] for the whole sub-batch
     for (int i = threadIdx.x; i < N * O; i += kT) sd[i] = dy[(int64_t)(i / O) * ldy + col_off + i % O];
     __syncthreads();
+    const int per = (O + gridDim.y - 1) / gridDim.y, o_lo = blockIdx.y * per, o_hi = min(O, o_lo + per);
+    dx += (int64_t)blockIdx.y * N * K;
     for (int k = blockIdx.x * kT + threadIdx.x; k < K; k += gridDim.x * kT) {
         float acc[kMaxRows];
 #pragma unroll
         for (int n = 0; n < kMaxRows; ++n) acc[n] = 0.f;
 #pragma unroll 8
-        for (int o = 0; o < O; ++o) {
+        for (int o = o_lo; o < o_hi; ++o) {
             const float wv = w[(int64_t)o * K + k];
 #pragma unroll
             for (int n = 0; n < kMaxRows; ++n)
@@ -287,6 +342,16 @@ linear_bwd_x_rows_kernel(const float* __restrict__ dy, int ldy, int col_off, con
             if (n < N) dx[(int64_t)n * K + k] = acc[n];
     }
 }
+// out[i] = sum over r of part[r][i] (range order)
+__global__ void __launch_bounds__(kT)
+sum_ranges_kernel(const float* __restrict__ part, int ranges, int64_t total, float* __restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
+        float v = 0.f;
+        for (int r = 0; r < ranges; ++r) v += part[(int64_t)r * total + i];
+        out[i] = v;
+    }
+}
+
 // dw[o][k..k+3], db[o]: one thread per (o, 4 consecutive k), K % 4 == 0
 __global__ void __launch_bounds__(kT)
 linear_bwd_w_vec4_kernel(const float* __restrict__ dy, int ldy, int col_off, const float* __restrict__ x, int ldx, int N, int K,
@@ -601,23 +666,30 @@ nchw_to_pc_kernel(const float* __restrict__ t, int N, int C, int HW, int rows, f
         store3(out + (int64_t)p * 3 * C, C, c, p < P ? t[((int64_t)(p / HW) * C + c) * HW + p % HW] : 0.f, false);
     }
 }
+// The tensor-core GEMMs run K-split (few tiles, long K): their consumers add the `splits` partial slabs, `slab` floats apart.
+__device__ __forceinline__ float sum_slabs(const float* p, int splits, int64_t slab) {
+    float v = p[0];
+    for (int s = 1; s < splits; ++s) v += p[(int64_t)s * slab];
+    return v;
+}
 // y[n][c][pos] = relu(yT[p][c] + b[c])
 __global__ void __launch_bounds__(kT)
-pc_bias_relu_to_nchw_kernel(const float* __restrict__ yT, const float* __restrict__ b, int N, int C, int HW,
-                            float* __restrict__ y) {
+pc_bias_relu_to_nchw_kernel(const float* __restrict__ yT, int splits, int64_t slab, const float* __restrict__ b, int N, int C,
+                            int HW, float* __restrict__ y) {
     const int64_t total = (int64_t)N * C * HW;
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         const int pos = (int)(i % HW), c = (int)((i / HW) % C), n = (int)(i / ((int64_t)HW * C));
-        y[i] = fmaxf(yT[((int64_t)n * HW + pos) * C + c] + b[c], 0.f);
+        y[i] = fmaxf(sum_slabs(yT + ((int64_t)n * HW + pos) * C + c, splits, slab) + b[c], 0.f);
     }
 }
 // out[c][r] = in[r][c]  (split: rows of out are 3xTF32 A operands [hi | hi | lo])
 __global__ void __launch_bounds__(kT)
-transpose_kernel(const float* __restrict__ in, int R, int Cc, float* __restrict__ out, int split) {
+transpose_kernel(const float* __restrict__ in, int R, int Cc, float* __restrict__ out, int split, int splits = 1,
+                 int64_t slab = 0) {
     const int64_t total = (int64_t)R * Cc;
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         const int r = (int)(i % R), c = (int)(i / R);
-        const float v = in[(int64_t)r * Cc + c];
+        const float v = sum_slabs(in + (int64_t)r * Cc + c, splits, slab);
         if (split) store3(out + (int64_t)c * 3 * R, R, r, v, true);
         else out[i] = v;
     }
@@ -649,8 +721,8 @@ im2col_split_kernel(const float* __restrict__ x, int N, int Ci, int H, int W, in
 }
 // dx from the transposed column gradient dcolT[k][ld]
 __global__ void __launch_bounds__(kT)
-col2im_t_kernel(const float* __restrict__ dcolT, int N, int Ci, int H, int W, int s, int pad, int OH, int OW, int ld,
-                float* __restrict__ dx) {
+col2im_t_kernel(const float* __restrict__ dcolT, int splits, int64_t slab, int N, int Ci, int H, int W, int s, int pad, int OH,
+                int OW, int ld, float* __restrict__ dx) {
     const int64_t total = (int64_t)N * Ci * H * W;
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         const int ix = (int)(i % W), iy = (int)((i / W) % H), ci = (int)((i / ((int64_t)W * H)) % Ci);
@@ -662,7 +734,7 @@ col2im_t_kernel(const float* __restrict__ dcolT, int N, int Ci, int H, int W, in
             for (int kw = 0; kw < 3; ++kw) {
                 const int tx = ix + pad - kw;
                 if (tx < 0 || tx % s || tx / s >= OW) continue;
-                acc += dcolT[(int64_t)((ci * 3 + kh) * 3 + kw) * ld + ((int64_t)n * OH + ty / s) * OW + tx / s];
+                acc += sum_slabs(dcolT + (int64_t)((ci * 3 + kh) * 3 + kw) * ld + ((int64_t)n * OH + ty / s) * OW + tx / s, splits, slab);
             }
         }
         dx[i] = acc;
@@ -709,7 +781,10 @@ struct gn_avm_trainer {
     uint8_t* arg[3];
     float *h5, *ay1, *ay2, *fin_buf, *f[4], *z, *dz;
     float *d_big0, *d_big1;          // ping-pong gradient buffers sized for the largest activation
+    int64_t col_elems;               // capacity of col / dcol in floats
     float *col, *dcol, *opb;         // im2col of a conv input / gradient w.r.t. it (largest layer), transposed B operand
+    float* lin_part;                 // partial sums of the K-chunked linear5 forward
+    int64_t lin_part_elems;
     int use_tc;                      // conv2 / conv3 GEMMs on the tensor cores as TF32 (default) or the fp32 SGEMM
     float *d_fin, *d_f[4];
     uint8_t* masks[5];               // keep-masks: linear5 (512), fusion.0/3/6/9 (512, 512, 256, 128)
@@ -806,7 +881,10 @@ extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const g
             if (ce > colmax) colmax = ce;
             if (be > bmax) bmax = be;
         }
+        t->col_elems = colmax;
         t->col = (float*)take(colmax, 4); t->dcol = (float*)take(colmax, 4); t->opb = (float*)take(bmax, 4);
+        t->lin_part_elems = ((t->K5 + kLinCK - 1) / kLinCK) * (n < kMaxRows ? n : kMaxRows) * 512;
+        t->lin_part = (float*)take(t->lin_part_elems, 4);
         const int mw[5] = {512, 512, 512, 256, 128};
         for (int i = 0; i < 5; ++i) t->masks[i] = (uint8_t*)take(n * mw[i], 1);
         if (pass == 0) {
@@ -919,6 +997,16 @@ int conv_bwd_x_gemm(gn_avm_trainer* t, const float* dy, const float* w, int n, i
 }
 // ---- the same three products on the tensor cores (kind::tf32), for layers with Cin*9 % 32 == 0 and Cout % 128 == 0 ----
 inline int pad_to(int v, int m) { return (v + m - 1) / m * m; }
+// K ranges for a TF32 GEMM of M x N with K elements: fill the SMs, keep >= 16 k-steps per range, fit the output buffer
+int tf32_splits(const gn_avm_trainer* t, int64_t M, int N, int K) {
+    const int64_t tiles = ((M + 127) / 128) * (N / 128), ksteps = K / 32;
+    int64_t s = t->h->num_sms / tiles;
+    if (s > ksteps / 16) s = ksteps / 16;
+    while (s > 1 && s * M * N > t->col_elems) --s;
+    if (s < 1) s = 1;
+    const int64_t per = (ksteps + s - 1) / s;          // the same normalisation gn_tc_gemm_tf32 applies: no empty range
+    return (int)((ksteps + per - 1) / per);
+}
 int conv_fwd_tc(gn_avm_trainer* t, const float* x, const float* w, const float* b, int n, int Ci, int H, int Co, int s, int pad,
                 int OH, float* y, cudaStream_t st) {
     const int KK = Ci * 9, OHW = OH * OH, P = n * OHW, cap = t->h->num_sms * 8;
@@ -926,9 +1014,10 @@ int conv_fwd_tc(gn_avm_trainer* t, const float* x, const float* w, const float* 
     GN_LAUNCHED(t->h);
     split3_kernel<<<grid_for((int64_t)Co * KK, cap), kT, 0, st>>>(w, Co, KK, t->opb, 0);
     GN_LAUNCHED(t->h);
-    int rc = gn_tc_gemm_tf32(t->h, t->col, P, 3 * KK, 3 * KK, t->opb, Co, 3 * KK, t->dcol, st);        // yT[p][co]
+    const int sp = tf32_splits(t, P, Co, 3 * KK);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, P, 3 * KK, 3 * KK, t->opb, Co, 3 * KK, t->dcol, st, sp);    // yT[split][p][co]
     if (rc) return rc;
-    pc_bias_relu_to_nchw_kernel<<<grid_for((int64_t)P * Co, cap), kT, 0, st>>>(t->dcol, b, n, Co, OHW, y);
+    pc_bias_relu_to_nchw_kernel<<<grid_for((int64_t)P * Co, cap), kT, 0, st>>>(t->dcol, sp, (int64_t)P * Co, b, n, Co, OHW, y);
     GN_LAUNCHED(t->h);
     return GN_OK;
 }
@@ -939,9 +1028,10 @@ int conv_bwd_w_tc(gn_avm_trainer* t, const float* dy, const float* x, int n, int
     GN_LAUNCHED(t->h);
     nchw_to_cp_kernel<<<grid_for((int64_t)Co * ld, cap), kT, 0, st>>>(dy, n, Co, OHW, ld, t->opb);
     GN_LAUNCHED(t->h);
-    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * ld, 3 * ld, t->opb, Co, 3 * ld, t->dcol, st);       // dW^T[k][co]
+    const int sp = tf32_splits(t, KK, Co, 3 * ld);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * ld, 3 * ld, t->opb, Co, 3 * ld, t->dcol, st, sp);   // dW^T[split][k][co]
     if (rc) return rc;
-    transpose_kernel<<<grid_for((int64_t)KK * Co, cap), kT, 0, st>>>(t->dcol, KK, Co, dw, 0);
+    transpose_kernel<<<grid_for((int64_t)KK * Co, cap), kT, 0, st>>>(t->dcol, KK, Co, dw, 0, sp, (int64_t)KK * Co);
     GN_LAUNCHED(t->h);
     bias_grad_kernel<<<Co, kT, 0, st>>>(dy, n, Co, OHW, db);
     GN_LAUNCHED(t->h);
@@ -954,9 +1044,11 @@ int conv_bwd_x_tc(gn_avm_trainer* t, const float* dy, const float* w, int n, int
     GN_LAUNCHED(t->h);
     nchw_to_pc_kernel<<<grid_for((int64_t)rows * Co, cap), kT, 0, st>>>(dy, n, Co, OHW, rows, t->opb);
     GN_LAUNCHED(t->h);
-    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * Co, 3 * Co, t->opb, rows, 3 * Co, t->dcol, st);     // dcol^T[k][rows]
+    const int sp = tf32_splits(t, KK, rows, 3 * Co);
+    int rc = gn_tc_gemm_tf32(t->h, t->col, KK, 3 * Co, 3 * Co, t->opb, rows, 3 * Co, t->dcol, st, sp); // dcol^T[split][k][rows]
     if (rc) return rc;
-    col2im_t_kernel<<<grid_for((int64_t)n * Ci * H * H, cap), kT, 0, st>>>(t->dcol, n, Ci, H, H, s, pad, OH, OH, rows, dx);
+    col2im_t_kernel<<<grid_for((int64_t)n * Ci * H * H, cap), kT, 0, st>>>(t->dcol, sp, (int64_t)KK * rows, n, Ci, H, H, s, pad, OH,
+                                                                           OH, rows, dx);
     GN_LAUNCHED(t->h);
     return GN_OK;
 }
@@ -967,6 +1059,16 @@ namespace {
 int lin_fwd(gn_avm_trainer* t, cudaStream_t st, const float* x, int ldx, const float* w, const float* b, int N, int K, int O,
             int relu, const uint8_t* mask, float scale, float* y, int ldy, int col_off) {
     const int cap = t->h->num_sms * 8;
+    if (N <= kMaxRows && K >= 4096 && t->lin_part) {
+        const int chunks = (K + kLinCK - 1) / kLinCK;
+        if ((int64_t)chunks * N * O <= t->lin_part_elems) {
+            linear_fwd_chunk_kernel<<<dim3(chunks, (O + 63) / 64), kT, (size_t)N * kLinCK * 4, st>>>(x, ldx, w, N, K, O, t->lin_part);
+            GN_LAUNCHED(t->h);
+            linear_fwd_reduce_kernel<<<grid_for((int64_t)N * O, cap), kT, 0, st>>>(t->lin_part, chunks, b, N, O, relu, mask, scale, y, ldy, col_off);
+            GN_LAUNCHED(t->h);
+            return GN_OK;
+        }
+    }
     // (the all-rows kernel pays 16 strided activation loads per weight: only worth it for short reductions)
     if (N <= kMaxRows && K <= 1024) linear_fwd_rows_kernel<<<grid_for((int64_t)O * 32, cap), kT, 0, st>>>(x, ldx, w, b, N, K, O, relu, mask, scale, y, ldy, col_off);
     else linear_fwd_kernel<<<grid_for((int64_t)N * O * 32, cap), kT, 0, st>>>(x, ldx, w, b, N, K, O, relu, mask, scale, y, ldy, col_off);
@@ -976,8 +1078,21 @@ int lin_fwd(gn_avm_trainer* t, cudaStream_t st, const float* x, int ldx, const f
 int lin_bwd_x(gn_avm_trainer* t, cudaStream_t st, const float* dy, int ldy, int col_off, const float* w, int N, int K, int O,
               float* dx) {
     const int cap = t->h->num_sms * 8;
-    if (N <= kMaxRows && (size_t)N * O * 4 <= 48 * 1024)
-        linear_bwd_x_rows_kernel<<<grid_for(K, cap), kT, (size_t)N * O * 4, st>>>(dy, ldy, col_off, w, N, K, O, dx);
+    if (N <= kMaxRows && (size_t)N * O * 4 <= 48 * 1024) {
+        // long rows (linear5): cut the output features into 8 ranges so that the grid fills the GPU; partials in t->col
+        // (a 512-wide fusion layer alone would give 2-3 CTAs of 512 dependent steps)
+        const int gx = grid_for(K, cap);
+        int ranges = 592 / gx;
+        if (ranges > O / 16) ranges = O / 16;
+        if (ranges < 1 || (int64_t)ranges * N * K > t->col_elems) ranges = 1;
+        if (ranges > 1) {
+            linear_bwd_x_rows_kernel<<<dim3(grid_for(K, cap), ranges), kT, (size_t)N * O * 4, st>>>(dy, ldy, col_off, w, N, K, O, t->col);
+            GN_LAUNCHED(t->h);
+            sum_ranges_kernel<<<grid_for((int64_t)N * K, cap), kT, 0, st>>>(t->col, ranges, (int64_t)N * K, dx);
+        } else {
+            linear_bwd_x_rows_kernel<<<grid_for(K, cap), kT, (size_t)N * O * 4, st>>>(dy, ldy, col_off, w, N, K, O, dx);
+        }
+    }
     else linear_bwd_x_kernel<<<grid_for((int64_t)N * K, cap), kT, 0, st>>>(dy, ldy, col_off, w, N, K, O, dx);
     GN_LAUNCHED(t->h);
     return GN_OK;
@@ -1032,7 +1147,7 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
             }
         }
     }
-    GN_CUDA(cudaMemsetAsync(G, 0, t->n_params * 4, st));
+    // (no memset of G: every gradient element is written, not accumulated, by exactly one kernel of the backward)
 
     // ---------------- forward: VisBl (utils.py:172-195) ----------------
     const float* x = d_visual;
