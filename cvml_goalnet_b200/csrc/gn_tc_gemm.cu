@@ -74,12 +74,14 @@ struct GemmArgs {
     ConvGeom g;
 };
 
-template <int MT, int BN, int STAGES, int MODE>
+template <int MT, int BN, int STAGES, int MODE, int SUBC = BN>
 struct Cfg {
     static constexpr int kABytes = MT * 128 * 128;          // MT x 128 rows x 128 B
     static constexpr int kBBytes = BN * 128;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStgStride = BN * 2 + 16;          // padded bf16 row of the pooling stage
+    // conv: the pooling stage holds SUBC of the tile's BN channels at a time (the epilogue makes BN / SUBC passes);
+    // a narrow stage frees shared memory for one more operand stage, which is what hides the TMA round trip
+    static constexpr int kStgStride = SUBC * 2 + 16;        // padded bf16 row of the pooling stage
     static constexpr int kStgBytes = (MODE == kConv) ? (MT * 128 * kStgStride) : 0;
     static constexpr int kParamBytes = 3 * kMaxN * 4;       // bias | bn_scale | bn_shift (or bias | w_last)
     static constexpr int kSmemBytes = 1024 /*align slack*/ + STAGES * kStageBytes + kStgBytes + kParamBytes + 256 /*barriers*/;
@@ -103,11 +105,12 @@ __device__ __forceinline__ float2 bf2_to_f2(uint32_t v) {
     return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&v));
 }
 
-template <int MT, int BN, int STAGES, int MODE, int OHT>
+template <int MT, int BN, int STAGES, int MODE, int OHT, int SUBC = BN>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmArgs args) {
-    using C = Cfg<MT, BN, STAGES, MODE>;
+    using C = Cfg<MT, BN, STAGES, MODE, SUBC>;
+    static_assert(BN % SUBC == 0 && SUBC % 64 == 0, "channel passes are whole pairs of 32-column TMEM chunks");
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: SWIZZLE_128B atoms are 8 rows x 128 B and the swizzle is address based.
     // (offset arithmetic on the shared pointer keeps the address space known to the compiler)
@@ -267,17 +270,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
             if (MODE == kConv) {
                 constexpr int npix = OHT * OHT;
-                // ---- phase 1: TMEM -> (+bias, ReLU) -> bf16 staging tile [pixel][BN] ----
+                constexpr int kPasses = BN / SUBC;
+#pragma unroll 1
+                for (int pass = 0; pass < kPasses; ++pass) {
+                const int nsub = n0 + pass * SUBC;       // first channel of this pass
+                // ---- phase 1: TMEM -> (+bias, ReLU) -> bf16 staging tile [pixel][SUBC] ----
 #pragma unroll 1
                 for (int mt = 0; mt < MT; ++mt) {
                     const int pix = mt * 128 + row;
 #pragma unroll 1
-                    for (int c = half; c < BN / 32; c += 2) {
+                    for (int c = half; c < SUBC / 32; c += 2) {
                         uint32_t r[32];
-                        tmem_ld32(tbase + (uint32_t)(mt * BN + c * 32), r);
+                        tmem_ld32(tbase + (uint32_t)(mt * BN + pass * SUBC + c * 32), r);
                         tmem_ld_wait();
                         if (pix < npix) {
-                            const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+                            const float4* bp = reinterpret_cast<const float4*>(s_bias + nsub + c * 32);
                             uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)pix * C::kStgStride + c * 64);
 #pragma unroll
                             for (int v = 0; v < 4; ++v) {
@@ -292,13 +299,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         }
                     }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));      // TMEM buffer may be overwritten
+                if (pass == kPasses - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[ab]));  // TMEM buffer may be overwritten
+                }
                 asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile complete
                 // ---- phase 2: MaxPool(3, stride 1) over the ReLU'd tile, BatchNorm affine, bf16 NHWC store ----
                 constexpr int P = OHT - 2;
-                constexpr int CG = BN / 8;
+                constexpr int CG = SUBC / 8;
                 const int PW = args.g.pfull + 2 * args.g.out_pad;
                 int64_t frame = m_blk;
                 int gy0 = 0, gx0 = 0;                 // pooled coordinates of this tile's first output
@@ -310,7 +319,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     gx0 = (t - ty * args.g.tiles) * P;
                 }
                 const int vy = min(P, args.g.pfull - gy0), vx = min(P, args.g.pfull - gx0);   // valid outputs of an edge tile
-                __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + n0;
+                __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + nsub;
                 // BatchNorm affine + bf16 store of one pooled (pixel, 8-channel group)
                 auto emit = [&](int oy, int ox, int cg, uint4 m, const float4& sc0, const float4& sc1, const float4& sh0,
                                 const float4& sh1) {
@@ -321,7 +330,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                                pack_bf16(fmaf(f3.x, sc1.z, sh1.z), fmaf(f3.y, sc1.w, sh1.w)));
                     const int opix = (gy0 + oy + args.g.out_pad) * PW + gx0 + ox + args.g.out_pad;
                     if (args.g.blocked)
-                        *reinterpret_cast<uint4*>(args.out + gn_a3_off(frame, (int64_t)opix * args.g.cout + n0 + cg * 8,
+                        *reinterpret_cast<uint4*>(args.out + gn_a3_off(frame, (int64_t)opix * args.g.cout + nsub + cg * 8,
                                                                        (int64_t)PW * PW * args.g.cout / 64)) = o;
                     else
                         *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
@@ -332,8 +341,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const int ox = et / CG, cg = et - ox * CG;
                     if (ox < vx) {
                         // the thread's channel group is fixed: its BatchNorm parameters are loaded once per tile
-                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
-                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
+                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + nsub + cg * 8);
+                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + nsub + cg * 8);
                         const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
                         const unsigned char* s0 = stg + (size_t)ox * C::kStgStride + cg * 16;
                         uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;
@@ -365,8 +374,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 if (dy == 0 && dx == 0) continue;
                                 m = hmax2_u4(m, *reinterpret_cast<const uint4*>(s0 + (size_t)(dy * OHT + dx) * C::kStgStride));
                             }
-                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + n0 + cg * 8);
-                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + n0 + cg * 8);
+                        const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + nsub + cg * 8);
+                        const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + nsub + cg * 8);
                         emit(oy, ox, cg, m, sc[0], sc[1], sh[0], sh[1]);
                     }
                 }
@@ -384,6 +393,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile may be reused
+                }   // channel passes
             } else {
                 const int64_t grow = m_blk * 128 + row;
                 float dot = 0.f;
@@ -529,12 +539,12 @@ int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, i
     return make_tmap(h, m, base, 2, dims, str, box);
 }
 
-template <int MT, int BN, int STAGES, int MODE, int OHT>
+template <int MT, int BN, int STAGES, int MODE, int OHT, int SUBC = BN>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
-    using C = Cfg<MT, BN, STAGES, MODE>;
+    using C = Cfg<MT, BN, STAGES, MODE, SUBC>;
     if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32) return GN_E_SHAPE;
-    auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT>;
+    auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT, SUBC>;
     static bool attr = false;
     if (!attr) {
         GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -548,7 +558,7 @@ int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const Gem
 }
 
 // conv block: in = zero-bordered NHWC [n][OH+2][OW+2][Cin]; weights K-major [Cout][9*Cin]
-template <int MT, int BN, int STAGES, int OH>
+template <int MT, int BN, int STAGES, int OH, int SUBC = BN>
 int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __nv_bfloat16* wk, int Cout,
              const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad, cudaStream_t st) {
     CUtensorMap ta, tb;
@@ -566,7 +576,7 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __n
     a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
     a.g.tiles = 1; a.g.pfull = OH - 2; a.g.blocked = out_pad ? 0 : 1;
     if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
-    return launch<MT, BN, STAGES, kConv, OH>(m->h, ta, tb, a, n * (Cout / BN), st);
+    return launch<MT, BN, STAGES, kConv, OH, SUBC>(m->h, ta, tb, a, n * (Cout / BN), st);
 }
 
 // zero the one-pixel border of [n][PW][PW][C] bf16 (the padding the next conv reads); 16 bytes per thread
@@ -765,8 +775,10 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
         if (rc) return rc;
         GN_STAGE_MARK(m, 3, st);
         // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
-        rc = run_conv<1, 256, 3, 11>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
-                                     ws.a3, 0, st);
+        // (4 operand stages: with 3 the TMA round trip was exposed -- tensor pipe 83 % busy; the pooling stage shrinks
+        //  to 64 channels per pass to make room)
+        rc = run_conv<1, 256, 4, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
+                                         ws.a3, 0, st);
     } else {
         // any other frame size (e.g. 224x224: conv2 on 74x74, conv3 on 72x72): overlapping 16x16 spatial tiles
         rc = run_conv_tiled(m, n, ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],

@@ -27,7 +27,7 @@ def main():
     col = {h: i for i, h in enumerate(hdr)}
     samp = col.get("# Samples", col.get("Warp Stall Sampling (All Samples)"))
     stall_cols = [(h, i) for h, i in col.items() if h.startswith("stall_") and "Not Issued" not in h]
-    body = [r for r in rows[1:] if len(r) > samp]
+    body = [r for r in rows[1:] if len(r) > samp and (r[samp] or "0").isdigit()]
     total = sum(int(r[samp] or 0) for r in body)
     print("total samples", total, "instructions", len(body))
     agg = {}
