@@ -298,7 +298,7 @@ def native_arm(args, rank, world, local_rank):
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get("conv3_block_dram_bytes_per_launch")
-    roofline = {"kernel": "tc_gemm_kernel<1,256,3,conv> (conv3 block: implicit GEMM + ReLU + maxpool + BN)",
+    roofline = {"kernel": "tc_gemm_kernel<1,256,4,conv> (conv3 block: implicit GEMM + ReLU + maxpool + BN)",
                 "bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": achieved / peaks["tf_sustained"], "traffic": traffic,
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['src']}); kernel timed inside the step",

@@ -50,6 +50,8 @@ struct gn_model {
     float *aconv1_w, *aconv1_b, *aconv2_w, *aconv2_b, *alinear3_w, *alinear3_b;
     float *f_b[4];               // fusion.0/3/6/9 biases
     float *f12_w, *f12_b;        // [128], [1]
+    int n_cls;                   // 0/1 = regression head; 5 = classifier head (gn_model_set_classifier_head)
+    float *cls_w, *cls_b;        // [5][128], [5]  (one separate allocation at cls_w)
     // bf16 K-major GEMM operands: [N_out][K]
     __nv_bfloat16 *conv2_wk;     // [256][9*64]    k = (ky*3+kx)*64 + ci
     __nv_bfloat16 *conv3_wk;     // [512][9*256]

@@ -290,7 +290,30 @@ extern "C" int gn_model_destroy(gn_model* m) {
     if (m->ev[0])
         for (int i = 0; i <= GN_AVM_STAGES; ++i) cudaEventDestroy(m->ev[i]);
     cudaFree(m->arena);
+    if (m->cls_w) cudaFree(m->cls_w);
     free(m);
+    return GN_OK;
+}
+
+// Classifier variant of the fusion head (CAVM / CVM in the report's Table 1; in the reference it survives as the
+// commented lines utils.py:257 `nn.Softmax(dim = 1)`, main.py:69 `nn.CrossEntropyLoss()` and main.py:97
+// `torch.argmax(batch_predictions, axis = 1) + 1`): fusion.12 becomes Linear(128, 5) and Softmax replaces
+// Sigmoid and 4y+1.  After this call gn_avm_forward writes [n][5] class probabilities to d_scores.
+extern "C" int gn_model_set_classifier_head(gn_model* m, const float* weight, const float* bias, int n_classes,
+                                            void* stream) {
+    if (!m || !weight || !bias) return GN_E_ARG;
+    if (n_classes != 5) return GN_E_SHAPE;
+    cudaStream_t st = gn_stream(stream);
+    if (!m->cls_w) {
+        cudaError_t e = cudaMalloc(&m->cls_w, (size_t)(n_classes * 128 + 8) * sizeof(float));
+        if (e != cudaSuccess) { m->cls_w = nullptr; return (int)e; }
+        m->cls_b = m->cls_w + n_classes * 128;
+    }
+    cudaError_t e = cudaMemcpyAsync(m->cls_w, weight, (size_t)n_classes * 128 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(m->cls_b, bias, (size_t)n_classes * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    m->n_cls = n_classes;
     return GN_OK;
 }
 
@@ -359,6 +382,7 @@ extern "C" int gn_avm_forward(gn_model* m, const float* d_visual, const float* d
 extern "C" int gn_dbg_avm_forward_simt(gn_model* m, const float* d_visual, const float* d_audio, int64_t n,
                                        float* d_scores, float* d_visual_features, void* d_workspace,
                                        int64_t workspace_bytes, void* stream) {
+    if (m && m->n_cls > 1) return GN_E_ARG;       // the validation path has the regression head only
     return avm_forward_impl(m, d_visual, d_audio, n, d_scores, d_visual_features, d_workspace, workspace_bytes, stream,
                             true);
 }

@@ -25,6 +25,7 @@ constexpr int kThreads = 64 + kEpiThreads;
 constexpr int kBK = 64;                  // bf16 elements per k-step = one 128-byte swizzle row
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;            // columns per accumulator buffer (MT * BN)
+constexpr int kCls = 5;                  // classifier head: importance levels 1..5 (utils.py:257, main.py:69,97)
 constexpr int kMaxN = 512;               // widest layer: per-channel parameter vectors staged in shared memory
 
 enum Mode { kConv = 0, kLinear = 1, kScore = 2,
@@ -57,7 +58,8 @@ struct GemmArgs {
     float* out_f32;          // linear: optional fp32 copy [M][N]
     const float* w_last;     // score: fusion.12 weight [128]
     const float* b_last;     // score: fusion.12 bias [1]
-    float* scores;           // score: [M]
+    float* scores;           // score: [M] regression scores, or [M][kCls] class probabilities
+    int n_cls;               // score: 0/1 = sigmoid regression head (utils.py:255-256,270); kCls = softmax classifier head
     int a3d_rows;            // linear: 0 = A is a 2-D [M][K] map; else A is a 3-D (k, position, frame) map with this many
                              //         positions per frame (AudBl conv2: overlapping 192-element windows, 128/rows frames per tile)
     // training modes
@@ -155,6 +157,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             s_par[kMaxN + i] = __ldg(args.w_last + i);
         }
     }
+    if (MODE == kScore && args.n_cls == kCls)     // rows 1..4 of the [kCls][N] classifier weight (N = 128)
+        for (int i = args.N + threadIdx.x; i < kCls * args.N; i += kThreads) s_par[kMaxN + i] = __ldg(args.w_last + i);
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
         prefetch_tmap(&tmap_b);
@@ -397,6 +401,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             } else {
                 const int64_t grow = m_blk * 128 + row;
                 float dot = 0.f;
+                float dotc[kCls - 1];
+#pragma unroll
+                for (int k = 0; k < kCls - 1; ++k) dotc[k] = 0.f;
                 // kScore keeps the whole row in one warp (the last layer is a dot product over the row)
                 const int c_begin = (MODE == kScore) ? (half == 0 ? 0 : BN / 32) : half;
                 const int c_step = (MODE == kScore) ? 1 : 2;
@@ -458,6 +465,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         const float* wl = s_par + kMaxN + n0 + c * 32;
 #pragma unroll
                         for (int i = 0; i < 32; ++i) dot = fmaf(x[i], wl[i], dot);
+                        if (args.n_cls == kCls) {
+#pragma unroll
+                            for (int k = 1; k < kCls; ++k)
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) dotc[k - 1] = fmaf(x[i], wl[k * args.N + i], dotc[k - 1]);
+                        }
                     } else if (grow < args.M) {
                         if (MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32 && args.out) {
                             uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
@@ -492,8 +505,25 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                 }
                 if (MODE == kScore && half == 0 && grow < args.M) {
-                    const float zlin = dot + __ldg(args.b_last);
-                    args.scores[grow] = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;   // utils.py:256,270
+                    if (args.n_cls == kCls) {
+                        // classifier head: Linear(128, 5) + Softmax(dim = 1) (the reference's commented variant, utils.py:257)
+                        float z[kCls];
+                        z[0] = dot + __ldg(args.b_last);
+#pragma unroll
+                        for (int k = 1; k < kCls; ++k) z[k] = dotc[k - 1] + __ldg(args.b_last + k);
+                        float zmax = z[0];
+#pragma unroll
+                        for (int k = 1; k < kCls; ++k) zmax = fmaxf(zmax, z[k]);
+                        float sum = 0.f;
+#pragma unroll
+                        for (int k = 0; k < kCls; ++k) { z[k] = expf(z[k] - zmax); sum += z[k]; }
+                        const float inv = 1.f / sum;
+#pragma unroll
+                        for (int k = 0; k < kCls; ++k) args.scores[grow * kCls + k] = z[k] * inv;
+                    } else {
+                        const float zlin = dot + __ldg(args.b_last);
+                        args.scores[grow] = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;   // utils.py:256,270
+                    }
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -686,7 +716,7 @@ int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K,
 template <int BN, int STAGES, int MODE>
 int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, const __nv_bfloat16* wk, int N,
                const float* bias, __nv_bfloat16* out, int ld_out, int col_off, float* out_f32, const float* w_last,
-               const float* b_last, float* scores, cudaStream_t st, int kblocked = 0) {
+               const float* b_last, float* scores, cudaStream_t st, int kblocked = 0, int n_cls = 1) {
     if (K % kBK || N % BN) return GN_E_SHAPE;
     CUtensorMap ta, tb;
     int rc;
@@ -702,7 +732,7 @@ int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, c
     GemmArgs a{};
     a.kblocked = kblocked;
     a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = ld_out; a.col_off = col_off;
-    a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores;
+    a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores; a.n_cls = n_cls;
     return launch<1, BN, STAGES, MODE, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
 }
 
@@ -817,8 +847,10 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
                                      nullptr, nullptr, nullptr, st);
     if (rc) return rc;
     // fusion.9 + ReLU + fusion.12 + sigmoid + 4y+1 -> scores
+    // (classifier head, gn_model_set_classifier_head: fusion.12 is 128 -> 5 and softmax replaces sigmoid; d_scores is [n][5])
     rc = run_linear<128, 4, kScore>(m, n, ws.h3, 256, 256, m->f_wk[3], 128, m->f_b[3], nullptr, 0, 0, nullptr,
-                                    m->f12_w, m->f12_b, d_scores, st);
+                                    m->n_cls > 1 ? m->cls_w : m->f12_w, m->n_cls > 1 ? m->cls_b : m->f12_b, d_scores, st,
+                                    0, m->n_cls > 1 ? m->n_cls : 1);
     GN_STAGE_MARK(m, 6, st);
     return rc;
 }

@@ -299,9 +299,15 @@ class AVM(nn.Module):
         with torch.cuda.device(dev):
             _lib.check(lib.gn_model_create(_h(dev), C.byref(mptr), C.byref(st), int(self.audio_included), self.S,
                                            self.B, _stream(dev)), "gn_model_create")
+            self._after_create(lib, mptr, sd, dev)
         del keep
         self._native[dev.index] = (mptr, self._version)
         return mptr
+
+    OUT_COLS = 1          # columns of forward()'s result
+
+    def _after_create(self, lib, mptr, sd, dev):
+        """Hook for head variants (CAVM)."""
 
     def _ws(self, dev, mptr, n):
         """Workspace view for n frames, 1024-byte aligned (TMA / swizzle atoms), grown on demand."""
@@ -324,7 +330,9 @@ class AVM(nn.Module):
             assert tuple(aud.shape) == (n, 30, self.B), "E: Inconsistency in data loader definition"
         mptr = self._model(dev)
         ws, need = self._ws(dev, mptr, n)
-        scores = out if out is not None else torch.empty((n, 1), dtype=torch.float32, device=dev)
+        scores = out if out is not None else torch.empty((n, self.OUT_COLS), dtype=torch.float32, device=dev)
+        assert scores.is_cuda and scores.dtype == torch.float32 and scores.numel() == n * self.OUT_COLS and \
+            scores.is_contiguous(), "E: Invalid output buffer"
         feats = torch.empty((n, 512), dtype=torch.float32, device=dev) if return_features else None
         lib = _lib.load()
         fn = lib.gn_dbg_avm_forward_simt if _simt else lib.gn_avm_forward
@@ -365,6 +373,41 @@ class AVM(nn.Module):
 # --------------------------------------------------------------------------------------------------
 # (a6-a9) keyshot selection  -- reference utils.py:396-410, 445-510, 606-643
 # --------------------------------------------------------------------------------------------------
+class CAVM(AVM):
+    """Classifier variant of AVM ("CAVM" / "CVM" in the report's Table 1).
+
+    The reference keeps it as commented lines: `# nn.Softmax(dim = 1),` (utils.py:257), `# criterion =
+    nn.CrossEntropyLoss()` (main.py:69) and `# batch_predictions = torch.argmax(batch_predictions, axis = 1) + 1`
+    (main.py:97,112,190,224).  fusion.12 is Linear(128, 5), fusion.13 is Softmax(dim=1) and there is no 4y+1:
+    `forward` returns (N,5) class probabilities, `predict` the (N,1) importance argmax+1 that `postprocess` takes.
+    Same state_dict key names as AVM (fusion.12.weight is (5,128)).
+    """
+
+    OUT_COLS = 5
+
+    def __init__(self, audio_included: bool, S: int = 40, B: int = 30):
+        super().__init__(audio_included, S, B)
+        self.fusion[12] = nn.Linear(128, self.OUT_COLS)
+        self.fusion[13] = nn.Softmax(dim=1)
+
+    def _after_create(self, lib, mptr, sd, dev):
+        w = sd["fusion.12.weight"].detach().to(device=dev, dtype=torch.float32).contiguous()
+        b = sd["fusion.12.bias"].detach().to(device=dev, dtype=torch.float32).contiguous()
+        assert tuple(w.shape) == (self.OUT_COLS, 128) and tuple(b.shape) == (self.OUT_COLS,), "E: Invalid classifier head"
+        _lib.check(lib.gn_model_set_classifier_head(mptr, _ptr(w), _ptr(b), self.OUT_COLS, _stream(dev)),
+                   "gn_model_set_classifier_head")
+        torch.cuda.current_stream(dev).synchronize()      # w, b may be temporaries
+
+    def forward(self, audio_input, visual_input, out=None, return_features: bool = False, _simt: bool = False):
+        assert not _simt, "E: the validation path has the regression head only"
+        return super().forward(audio_input, visual_input, out=out, return_features=return_features)
+
+    def predict(self, audio_input, visual_input):
+        """argmax + 1 (main.py:97, commented) as float32 (N,1), the shape `postprocess` expects."""
+        probs = self.forward(audio_input, visual_input)
+        return (torch.argmax(probs, dim=1, keepdim=True) + 1).to(torch.float32)
+
+
 def expand_array(arr, expansion_rate, length):
     """utils.py:396-410 (list plumbing; on the hot path it is fused into gn_clip_information)."""
     if len(arr) == length:

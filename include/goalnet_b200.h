@@ -111,6 +111,15 @@ int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state* sd, int au
                     void* stream);
 int gn_model_destroy(gn_model* m);
 
+/* Classifier variant of the fusion head (CAVM / CVM in the report's Table 1).  In the reference it
+ * survives as commented lines: utils.py:257 `# nn.Softmax(dim = 1),`, main.py:69 `# criterion = nn.CrossEntropyLoss()`,
+ * main.py:97 `# batch_predictions = torch.argmax(batch_predictions, axis = 1) + 1`.  fusion.12 becomes
+ * Linear(128, 5) and Softmax(dim = 1) replaces Sigmoid and 4y+1.
+ *   weight : device float32 [5][128] (nn.Linear layout), bias : device float32 [5]; n_classes must be 5.
+ * After this call gn_avm_forward writes float32 [n][5] class probabilities to d_scores (the caller sizes it so); the
+ * predicted importance of a frame is argmax + 1.  The copy is ordered on `stream`. */
+int gn_model_set_classifier_head(gn_model* m, const float* weight, const float* bias, int n_classes, void* stream);
+
 /* Bytes of caller workspace gn_avm_forward needs for n frames. */
 int64_t gn_avm_workspace_bytes(const gn_model* m, int64_t n);
 

@@ -216,7 +216,8 @@ def extract_audio_features_array(y: np.ndarray, sr: int, n_frames: int, bin_leng
 # ----------------------------------------------------------------------------------------------
 
 
-def avm_forward(sd: dict, audio, visual, audio_included: bool = True, return_features: bool = False):
+def avm_forward(sd: dict, audio, visual, audio_included: bool = True, return_features: bool = False,
+                classifier: bool = False):
     """Functional fp32 restatement of AVM.forward (utils.py:260-272) in eval mode.
 
     sd: state_dict-keyed tensors/arrays.  audio (N,30,B), visual (N,3,S,S).  Dropout is identity
@@ -248,8 +249,13 @@ def avm_forward(sd: dict, audio, visual, audio_included: bool = True, return_fea
             h = vis
         for idx in (0, 3, 6, 9):                                                  # utils.py:242-254
             h = F.relu(F.linear(h, t(f"fusion.{idx}.weight"), t(f"fusion.{idx}.bias")))
-        h = torch.sigmoid(F.linear(h, t("fusion.12.weight"), t("fusion.12.bias")))
-        out = 4 * h + 1                                                           # utils.py:270
+        if classifier:
+            # the reference's commented classifier variant: utils.py:257 `# nn.Softmax(dim = 1),` in place of
+            # nn.Sigmoid() with a 5-wide fusion.12; no 4y+1 (the prediction is argmax + 1, main.py:97)
+            out = torch.softmax(F.linear(h, t("fusion.12.weight"), t("fusion.12.bias")), dim=1)
+        else:
+            h = torch.sigmoid(F.linear(h, t("fusion.12.weight"), t("fusion.12.bias")))
+            out = 4 * h + 1                                                       # utils.py:270
     if return_features:
         return out, feats
     return out

@@ -190,6 +190,45 @@ def test_model_other_frame_sizes_tiled_conv_and_splitk(U, S, n):
     torch.cuda.empty_cache()
 
 
+@pytest.mark.parametrize("audio_included,n", [(True, 300), (False, 129), (True, 1)])
+def test_classifier_head_cavm(U, weights, audio_included, n):
+    """Linear(128,5) + Softmax head (the reference's commented variant, utils.py:257, main.py:69,97).
+    Probabilities within 2e-3 abs of the fp32 oracle (bf16 operands upstream); argmax+1 equal wherever the oracle's
+    top-2 margin exceeds twice that tolerance."""
+    w = dict(weights)
+    rng = np.random.default_rng(55)
+    w["fusion.12.weight"] = (rng.standard_normal((5, 128)) * 0.15).astype(np.float32)
+    w["fusion.12.bias"] = (rng.standard_normal(5) * 0.1).astype(np.float32)
+    if not audio_included:
+        w = {k: v for k, v in w.items() if not k.startswith("audbl.")}
+        w["fusion.0.weight"] = np.ascontiguousarray(np.asarray(w["fusion.0.weight"])[:, 128:])
+    vis = O.extract_condensed_frame_tensor_array(syn.make_frames(n, 48, 48, seed=n + 1), 40)
+    aud = (25.0 * rng.standard_normal((n, 30, 30))).astype(np.float32)
+    m = U.CAVM(audio_included)
+    m.load_state_dict(w)
+    probs = m(aud, vis)
+    assert probs.shape == (n, 5) and probs.dtype == torch.float32 and probs.is_cuda
+    p = probs.cpu().numpy()
+    ref = O.avm_forward(w, aud, vis, audio_included=audio_included, classifier=True).numpy()
+    assert np.abs(p.sum(1) - 1).max() <= 1e-5
+    assert np.abs(p - ref).max() <= 2e-3
+    pred = m.predict(aud, vis).cpu().numpy()
+    assert pred.shape == (n, 1) and pred.min() >= 1 and pred.max() <= 5
+    top2 = np.sort(ref, axis=1)
+    sure = (top2[:, -1] - top2[:, -2]) > 4e-3
+    assert np.array_equal(pred[sure, 0], ref.argmax(1)[sure] + 1.0)
+    assert ref.max() < 0.999                  # not saturated: the 2e-3 comparison above is meaningful
+    # predictions feed the same selection path as the regression scores
+    nraw = n * 15
+    cps = syn.make_change_points(nraw, seed=3) if hasattr(syn, "make_change_points") else None
+    if cps is not None:
+        _, ind = U.postprocess_array(pred, 15, nraw, cps)
+        _, ind_ref = O.postprocess_array(pred, 15, nraw, cps)
+        assert np.array_equal(np.asarray(ind), np.asarray(ind_ref))
+    with pytest.raises(AssertionError):
+        m(aud, vis, _simt=True)
+
+
 def test_model_empty_and_shape_errors(U, weights):
     m = _model(U, weights)
     assert m(np.zeros((0, 30, 30), np.float32), np.zeros((0, 3, 40, 40), np.float32)).shape == (0, 1)

@@ -136,3 +136,29 @@ def test_avm_train_steps_match_reference_model(golden):
             np.testing.assert_allclose(v.ravel()[::997], g[f"{tag}_gs_{k}"], rtol=1e-4, atol=1e-9, err_msg=k)
         for k, v in out.items():
             np.testing.assert_allclose(v.ravel()[::997], g[f"{tag}_p2_{k}"], rtol=1e-5, atol=1e-6, err_msg=k)
+
+
+def test_classifier_head_restatement_matches_torch_modules():
+    """SURVEY 8f N3.  The classifier variant is commented out in the reference (utils.py:257, main.py:69,97), so there
+    is nothing of the reference to run ("parity unpinned" for this head): the oracle's functional form is checked
+    against the torch modules that un-commenting those lines would build (Linear(128,5) -> Softmax(dim=1), no 4y+1)."""
+    import torch
+    from torch import nn
+    w = syn.make_weights(seed=0)
+    rng = np.random.default_rng(1)
+    w["fusion.12.weight"] = rng.standard_normal((5, 128)).astype(np.float32) * 0.2
+    w["fusion.12.bias"] = rng.standard_normal(5).astype(np.float32) * 0.1
+    n = 6
+    vis = rng.random((n, 3, 40, 40), dtype=np.float32)
+    aud = rng.standard_normal((n, 30, 30)).astype(np.float32)
+    _, feats = O.avm_forward(syn.make_weights(seed=0), aud, vis, return_features=True)
+    fusion = nn.Sequential(nn.Linear(640, 512), nn.ReLU(), nn.Dropout(0.2), nn.Linear(512, 512), nn.ReLU(), nn.Dropout(0.2),
+                           nn.Linear(512, 256), nn.ReLU(), nn.Dropout(0.2), nn.Linear(256, 128), nn.ReLU(), nn.Dropout(0.2),
+                           nn.Linear(128, 5), nn.Softmax(dim=1)).eval()
+    fusion.load_state_dict({k[len("fusion."):]: torch.as_tensor(np.asarray(v)) for k, v in w.items() if k.startswith("fusion.")})
+    with torch.no_grad():
+        ref = fusion(torch.cat((feats["audio_features"], feats["visual_features"]), dim=-1)).numpy()
+    out = O.avm_forward(w, aud, vis, classifier=True).numpy()
+    assert out.shape == (n, 5)
+    assert np.abs(out - ref).max() <= 1e-6
+    assert np.abs(out.sum(1) - 1).max() <= 1e-6
