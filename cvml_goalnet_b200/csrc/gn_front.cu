@@ -45,18 +45,33 @@ visbl_block1_kernel(const float* __restrict__ vis, int64_t n, const float* __res
     const float2 scale = *reinterpret_cast<const float2*>(sc + 2 * lane);
     const float2 shift = *reinterpret_cast<const float2*>(sh + 2 * lane);
     constexpr int P = kC1 - 2;                                  // pooled size; the padded output is C1 x C1 again
-    for (int64_t f = blockIdx.x; f < n; f += gridDim.x) {
-        __syncthreads();
+    // the next frame's pixels travel to registers while this frame is convolved and pooled
+    constexpr int kVec = 3 * kS * kS / 4, kPre = (kVec + kVThreads - 1) / kVThreads;
+    float4 pre[kPre];
+    auto prefetch = [&](int64_t f) {
         const float4* src = reinterpret_cast<const float4*>(vis + f * 3 * kS * kS);
-        for (int i = tid; i < 3 * kS * kS / 4; i += kVThreads) {
-            const float4 v = __ldg(src + i);
-            const uint2 o = *reinterpret_cast<const uint2*>(dsto + 4 * i);
-            patch[o.x & 0xffffu] = v.x;
-            patch[o.x >> 16] = v.y;
-            patch[o.y & 0xffffu] = v.z;
-            patch[o.y >> 16] = v.w;
+#pragma unroll
+        for (int v = 0; v < kPre; ++v) {
+            const int i = tid + v * kVThreads;
+            if (i < kVec) pre[v] = __ldg(src + i);
         }
-        __syncthreads();
+    };
+    if ((int64_t)blockIdx.x < n) prefetch(blockIdx.x);
+    for (int64_t f = blockIdx.x; f < n; f += gridDim.x) {
+        // patch was last read by the previous frame's convolution, which every thread left at the barrier below
+#pragma unroll
+        for (int v = 0; v < kPre; ++v) {
+            const int i = tid + v * kVThreads;
+            if (i < kVec) {
+                const uint2 o = *reinterpret_cast<const uint2*>(dsto + 4 * i);
+                patch[o.x & 0xffffu] = pre[v].x;
+                patch[o.x >> 16] = pre[v].y;
+                patch[o.y & 0xffffu] = pre[v].z;
+                patch[o.y >> 16] = pre[v].w;
+            }
+        }
+        __syncthreads();          // patch complete; the previous frame's pooling is done with c1
+        if (f + gridDim.x < n) prefetch(f + gridDim.x);
         for (int p = warp; p < kC1 * kC1; p += kVThreads / 32) {
             const float4* pp = reinterpret_cast<const float4*>(patch + p * kPatch);
             float in[kPatch];
@@ -75,25 +90,35 @@ visbl_block1_kernel(const float* __restrict__ vis, int64_t n, const float* __res
         }
         __syncthreads();
         uint32_t* o = reinterpret_cast<uint32_t*>(a1p + f * (int64_t)kC1 * kC1 * 64);
-        for (int p = warp; p < kC1 * kC1; p += kVThreads / 32) {
-            const int y = p / kC1, x = p - y * kC1;
-            uint32_t r = 0u;                                     // zero border = conv2's padding
-            if (y >= 1 && y <= P && x >= 1 && x <= P) {
-                const float* base = c1 + ((y - 1) * kC1 + x - 1) * 64 + 2 * lane;
-                float2 m = *reinterpret_cast<const float2*>(base);
-#pragma unroll
-                for (int dy = 0; dy < 3; ++dy)
-#pragma unroll
-                    for (int dx = 0; dx < 3; ++dx) {
-                        if (dy == 0 && dx == 0) continue;
-                        const float2 t = *reinterpret_cast<const float2*>(base + (dy * kC1 + dx) * 64);
-                        m.x = fmaxf(m.x, t.x);
-                        m.y = fmaxf(m.y, t.y);
-                    }
-                const __nv_bfloat162 h = __floats2bfloat162_rn(fmaf(m.x, scale.x, shift.x), fmaf(m.y, scale.y, shift.y));
-                r = *reinterpret_cast<const uint32_t*>(&h);
+        // zero border = conv2's padding
+        for (int bi = warp; bi < 4 * kC1 - 4; bi += kVThreads / 32) {
+            int y, x;
+            if (bi < kC1) { y = 0; x = bi; }
+            else if (bi < 2 * kC1) { y = kC1 - 1; x = bi - kC1; }
+            else { const int t = bi - 2 * kC1; y = 1 + (t >> 1); x = (t & 1) ? kC1 - 1 : 0; }
+            o[(y * kC1 + x) * 32 + lane] = 0u;
+        }
+        // separable 3x3 max pool: a warp walks a third of one pooled column (lane = channel pair), keeping the
+        // horizontal maxima of the last three conv rows -- 3 shared loads per pooled pixel instead of 9
+        constexpr int kThirds = 3;
+        for (int item = warp; item < P * kThirds; item += kVThreads / 32) {
+            const int x = item / kThirds, t = item - x * kThirds;          // pooled column, row range
+            const int y0 = (t * P) / kThirds, y1 = ((t + 1) * P) / kThirds;
+            const float* col = c1 + x * 64 + 2 * lane;                     // conv columns x .. x+2
+            float2 h0 = make_float2(0.f, 0.f), h1 = h0;
+            for (int r = y0; r < y1 + 2; ++r) {
+                const float* rp = col + r * kC1 * 64;
+                const float2 u = *reinterpret_cast<const float2*>(rp), v = *reinterpret_cast<const float2*>(rp + 64),
+                             w2 = *reinterpret_cast<const float2*>(rp + 128);
+                const float2 h2 = make_float2(fmaxf(fmaxf(u.x, v.x), w2.x), fmaxf(fmaxf(u.y, v.y), w2.y));
+                if (r >= y0 + 2) {
+                    const float mx = fmaxf(fmaxf(h0.x, h1.x), h2.x), my = fmaxf(fmaxf(h0.y, h1.y), h2.y);
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(fmaf(mx, scale.x, shift.x), fmaf(my, scale.y, shift.y));
+                    o[((r - 1) * kC1 + x + 1) * 32 + lane] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                h0 = h1;
+                h1 = h2;
             }
-            o[p * 32 + lane] = r;
         }
     }
 }
