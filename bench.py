@@ -299,9 +299,14 @@ def native_arm(args, rank, world, local_rank):
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get("conv3_block_dram_bytes_per_launch")
     roofline = {"kernel": "tc_gemm_kernel<1,256,4,conv> (conv3 block: implicit GEMM + ReLU + maxpool + BN)",
-                "bound": "tensor", "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                "frac": achieved / peaks["tf_sustained"], "traffic": traffic,
-                "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['src']}); kernel timed inside the step",
+                "bound": "tensor", "achieved": achieved, "peak": peaks["tf_burst"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["tf_burst"], "traffic": traffic,
+                # the timed region is tens of ms at full SM clock (see "clocks"); the sustained cuBLAS figure
+                # was taken over 4 s at power-capped clocks, so the burst figure is the comparable (and
+                # stricter) denominator here.  Both ratios are reported.
+                "frac_vs_sustained": achieved / peaks["tf_sustained"], "peak_sustained": peaks["tf_sustained"],
+                "peak_source": f"MEASURED_PEAKS.json bf16_tflops burst ({peaks['src']}): kernel is 2 ms inside a "
+                               "6 ms step at un-capped SM clock; frac_vs_sustained uses bf16_tflops_sustained",
                 "flops_per_launch": conv3_flops, "ms_per_launch": acc["conv3_block"]}
     pre_bytes = n * (H * W * 3 + 40 * 40 * 3 * 4)
     stages = {k: round(v, 4) for k, v in acc.items()}

@@ -101,6 +101,24 @@ def test_audio_vs_oracle(U, n, spf, sr):
     np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
 
 
+def test_audio_matches_independent_mfcc_vectors(U, golden):
+    """The CUDA MFCC against vectors the oracle did not produce: torchaudio.transforms.MFCC configured with librosa
+    0.10's defaults (oracle/gen_mfcc_crosscheck.py).  One slot spanning the whole signal and B = q makes the cubic
+    resampling (utils.py:336-343) the identity, so the output is the raw MFCC matrix of utils.py:333."""
+    g = golden("mfcc_torchaudio")
+    checked = 0
+    for name in [k[:-5] for k in g.files if k.endswith("_mfcc")]:
+        y, sr, ref = g[f"{name}_y"], int(g[f"{name}_sr"]), g[f"{name}_mfcc"]
+        q = ref.shape[1]
+        if q < 4:                              # interp1d(kind='cubic') needs 4 columns (reference fails too)
+            continue
+        out = U.extract_audio_features_array(y, sr, 1, q, as_numpy=True)
+        assert out.shape == (1, 30, q)
+        np.testing.assert_allclose(out[0], ref, rtol=MFCC_RTOL, atol=MFCC_ATOL, err_msg=name)
+        checked += 1
+    assert checked >= 5
+
+
 def test_audio_silence_and_short_segment_errors(U):
     out = U.extract_audio_features_array(np.zeros(4 * 8000, np.float32), 16000, 4, 30, as_numpy=True)
     ref = O.extract_audio_features_array(np.zeros(4 * 8000, np.float32), 16000, 4, 30)

@@ -162,3 +162,17 @@ def test_classifier_head_restatement_matches_torch_modules():
     assert out.shape == (n, 5)
     assert np.abs(out - ref).max() <= 1e-6
     assert np.abs(out.sum(1) - 1).max() <= 1e-6
+
+
+def test_mfcc_restatement_matches_independent_implementation(golden):
+    """utils.py:333 — librosa is absent, so the oracle's MFCC restatement is cross-checked against vectors from an
+    independent implementation of the same definition (torchaudio.transforms.MFCC with librosa 0.10's defaults;
+    oracle/gen_mfcc_crosscheck.py).  MFCC values span roughly ±600; both sides are float32 pipelines."""
+    g = golden("mfcc_torchaudio")
+    names = [k[:-5] for k in g.files if k.endswith("_mfcc")]
+    assert len(names) >= 6
+    for name in names:
+        y, sr, ref = g[f"{name}_y"], int(g[f"{name}_sr"]), g[f"{name}_mfcc"]
+        out = O.mfcc(y, sr)
+        assert out.shape == ref.shape == (30, 1 + len(y) // 512), name
+        np.testing.assert_allclose(out, ref, rtol=1e-4, atol=5e-4, err_msg=name)
