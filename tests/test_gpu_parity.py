@@ -461,3 +461,47 @@ def test_match_scorer_chunked_host_path_equals_device_path(U, weights):
     assert np.abs(s_host - o_scores).max() / np.abs(o_scores).max() <= SCORE_RTOL
     if np.array_equal(np.round(s_host), np.round(o_scores)):
         np.testing.assert_array_equal(ind_host, o_ind)
+
+
+def test_full_size_config2_match(U, weights):
+    """BASELINE config 2 at full size (10 800 frames of 224x224, 86.4 M audio samples, 162 000 raw frames) through the
+    same MatchScorer.score_device call bench.py times.  The oracle cannot score 10 800 frames in seconds, so the match
+    repeats a 432-frame base (frames and their 8 000-sample audio slots) 25 times: every frame's score depends only on
+    that frame and its slot (utils.py:260-272, eval mode), hence
+      * all 10 800 scores must equal the oracle's scores of the base, whatever tile / wave / split-K tail they ran in;
+      * selection and F-score counts on those scores are bit-exact against the oracle's integer path at full size."""
+    from cvml_goalnet_b200.main import MatchScorer
+    base, reps, skip, sr, spf = 432, 25, 15, 16000, 8000
+    n = base * reps
+    n_raw = n * skip
+    frames = syn.make_frames(base, 224, 224, seed=9)
+    y = syn.make_audio(base, spf, sr, seed=9)
+    assert y.size == base * spf
+    cps = syn.make_change_points(n_raw, seed=9)
+    dev = torch.device("cuda", 0)
+    frames_dev = torch.from_numpy(frames).to(dev).repeat(reps, 1, 1, 1)
+    y_dev = torch.from_numpy(y).to(dev).repeat(reps)
+    m = _model(U, weights)
+    sc = MatchScorer(m, n, 224, 224, y_dev.numel(), sr, skip, n_raw)
+    scores, ind, _ = sc.score_device(frames_dev, y_dev, cps, None)
+    s = scores.cpu().numpy()
+    ind = ind.cpu().numpy()
+    assert s.shape == (n, 1) and ind.shape == (n_raw,) and ind.dtype == np.uint8
+
+    o_base = O.avm_forward(weights, O.extract_audio_features_array(y, sr, base, 30),
+                           O.extract_condensed_frame_tensor_array(frames, 40))
+    o_base = np.asarray(o_base, dtype=np.float32).reshape(base, 1)
+    o_full = np.tile(o_base, (reps, 1))
+    assert np.abs(s - o_full).max() / np.abs(o_full).max() <= SCORE_RTOL
+    # position independence: the same frame scores the same in every repetition (to fp32 reassociation of the
+    # K-split tail rows), far inside the parity tolerance
+    spread = np.abs(s.reshape(reps, base) - s.reshape(reps, base)[0]).max()
+    assert spread <= 1e-4 * np.abs(o_full).max(), spread
+
+    # integer path at full size, on the GPU's own scores: bit-exact
+    _, o_ind = O.postprocess_array(s, skip, n_raw, cps)
+    np.testing.assert_array_equal(ind, o_ind)
+    assert 0 < int(ind.sum()) <= int(0.15 * n_raw) + len(cps)     # budget (+1 frame per clip: get_clip_information is end-exclusive)
+    gd = np.stack([O.postprocess_array(a[:, None], skip, n_raw, cps)[1]
+                   for a in syn.make_annotator_importances(n_raw, 20, seed=9)])
+    assert U.get_fscore(gd, ind) == O.get_fscore(gd, o_ind)
