@@ -91,8 +91,36 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.proc, self.path = index, None, None
+        self.nvml, self.thread, self.rows, self.stop_flag = None, None, [], False
+
+    def _nvml_loop(self, nv, h):
+        # NVML bits: 0x4 sw_power_cap, 0x8 hw_slowdown, 0x20 sw_thermal_slowdown, 0x40 hw_thermal_slowdown
+        while not self.stop_flag:
+            try:
+                self.rows.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+                                  nv.nvmlDeviceGetCurrentClocksEventReasons(h)))
+            except Exception:
+                pass
+            time.sleep(0.004)
 
     def start(self):
+        # in-process NVML polling every 4 ms (the timed region is tens of ms: nvidia-smi -lms 100 gets 0-2 samples,
+        # none at all with 8 ranks starting it at once); nvidia-smi stays as the fallback
+        try:
+            import threading
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else self.index
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            self.nvml = nv
+            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -103,6 +131,16 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            sm = [float(r[0]) for r in self.rows]
+            bits = 0
+            for r in self.rows:
+                bits |= int(r[1])
+            names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.sm_max, "samples": len(sm),
+                    "reasons": sorted(v for k, v in names.items() if bits & k), "source": "nvml, 4 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
