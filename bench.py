@@ -101,10 +101,10 @@ class ClockSampler:
                                   nv.nvmlDeviceGetCurrentClocksEventReasons(h)))
             except Exception:
                 pass
-            time.sleep(0.004)
+            time.sleep(0.010)
 
     def start(self):
-        # in-process NVML polling every 4 ms (the timed region is tens of ms: nvidia-smi -lms 100 gets 0-2 samples,
+        # in-process NVML polling every 10 ms (the timed region is tens of ms: nvidia-smi -lms 100 gets 0-2 samples,
         # none at all with 8 ranks starting it at once); nvidia-smi stays as the fallback
         try:
             import threading
@@ -140,7 +140,7 @@ class ClockSampler:
                 bits |= int(r[1])
             names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
             return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.sm_max, "samples": len(sm),
-                    "reasons": sorted(v for k, v in names.items() if bits & k), "source": "nvml, 4 ms period"}
+                    "reasons": sorted(v for k, v in names.items() if bits & k), "source": "nvml, 10 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
