@@ -75,6 +75,11 @@ for _i in (1, 2, 3):
     STATE_KEYS[f"bn{_i}_m"] = f"visbl.bnorm{_i}.running_mean"
     STATE_KEYS[f"bn{_i}_v"] = f"visbl.bnorm{_i}.running_var"
 
+class gn_score_sink(C.Structure):
+    _fields_ = [("n_dst", C.c_int32), ("reserved", C.c_int32), ("dst", C.c_void_p * 16), ("rows_per_match", C.c_int64),
+                ("dst_match_stride", C.c_int64), ("dst_offset", C.c_int64), ("row0", C.c_int64)]
+
+
 class gn_fusion_state(C.Structure):
     _fields_ = [("weight", C.c_void_p * 5), ("bias", C.c_void_p * 5)]
 
@@ -97,6 +102,8 @@ SIGNATURES = {
     "gn_model_set_classifier_head": (_I, [_P, _P, _P, _I, _P]),
     "gn_avm_workspace_bytes": (_L, [_P, _L]),
     "gn_avm_forward": (_I, [_P, _P, _P, _L, _P, _P, _P, _L, _P]),
+    "gn_avm_forward_scatter": (_I, [_P, _P, _P, _L, C.POINTER(gn_score_sink), _P, _L, _P]),
+    "gn_unshard_rows": (_I, [_P, _P, _I, _L, _L, _L, _P, _P]),
     "gn_model_set_timing": (_I, [_P, _I]),
     "gn_model_get_timing": (_I, [_P, C.POINTER(C.c_float), _I]),
     "gn_clip_information": (_I, [_P, _P, _L, _I, _L, _P, _I, _P, _P, _P]),

@@ -16,7 +16,19 @@ struct gn_handle {
     // link against libcuda (it must load, and export its symbols, on a box without a driver).
     void* encode_tiled;
     void* pre_plans;             // gn_preprocess.cu: cached tap plans per (H, W, S)
+    // kernels whose function attributes (dynamic shared memory limit, non-portable cluster size) have been set for
+    // THIS handle's device: the attributes are per device, so the record lives in the handle, not in the process
+    const void* attr_done[96];
+    int n_attr_done;
 };
+
+// true exactly once per (handle, kernel): the caller then sets the kernel's function attributes on the handle's device
+static inline bool gn_attr_first(gn_handle* h, const void* fn) {
+    for (int i = 0; i < h->n_attr_done; ++i)
+        if (h->attr_done[i] == fn) return false;
+    if (h->n_attr_done < 96) h->attr_done[h->n_attr_done++] = fn;
+    return true;      // (a full table only costs a repeated, idempotent cudaFuncSetAttribute)
+}
 void gn_preprocess_free_plans(gn_handle* h);
 
 #define GN_CUDA(expr)                                   \
@@ -52,13 +64,16 @@ struct gn_model {
     float *f12_w, *f12_b;        // [128], [1]
     int n_cls;                   // 0/1 = regression head; 5 = classifier head (gn_model_set_classifier_head)
     float *cls_w, *cls_b;        // [5][128], [5]  (one separate allocation at cls_w)
-    // bf16 K-major GEMM operands: [N_out][K]
+    // bf16 K-major GEMM operands of the visual backbone (99 % of the FLOPs): [N_out][K]
     __nv_bfloat16 *conv2_wk;     // [256][9*64]    k = (ky*3+kx)*64 + ci
     __nv_bfloat16 *conv3_wk;     // [512][9*256]
     __nv_bfloat16 *linear5_wk;   // K-blocked (gn_w5_off), k = p*512 + c   (reference flatten is c*P3^2 + p)
-    __nv_bfloat16 *f_wk[4];      // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
-    __nv_bfloat16 *aconv2_wk;    // [128][3*64]    k = tap*64 + ci
-    __nv_bfloat16 *alinear3_wk;  // [128][L2*128]  k = l*128 + c   (reference flatten is c*L2 + l)
+    // TF32 K-major GEMM operands of the "head" (AudBl conv2 / linear3 and the fusion MLP: 0.6 % of the FLOPs, but the
+    // layers whose bf16 rounding dominated the score error -- raw MFCCs span +-600 and the last layers amplify):
+    // fp32 storage, values rounded to TF32 (cvt.rna) when packed so that the tensor core's truncation is a no-op
+    float *f_wk[4];              // fusion.0 [512][fin], .3 [512][512], .6 [256][512], .9 [128][256]
+    float *aconv2_wk;            // [128][3*64]    k = tap*64 + ci
+    float *alinear3_wk;          // [128][L2*128]  k = l*128 + c   (reference flatten is c*L2 + l)
     void* arena;                 // one allocation backing everything above
     int timing;                  // record per-stage events in gn_avm_forward
     cudaEvent_t ev[GN_AVM_STAGES + 1];
@@ -76,31 +91,41 @@ __host__ __device__ __forceinline__ int64_t gn_w5_off(int64_t row, int64_t k) {
     return (((k >> 6) << 9) + row) * 64 + (k & 63);
 }
 
-// Workspace layout for n frames (all bf16 unless noted); offsets are computed by gn_ws_layout().
+// Workspace layout for n frames; offsets are computed by gn_ws_layout().  The visual backbone's activations are bf16,
+// the head's (AudBl, fusion input, fusion hidden layers) are fp32 holding TF32-rounded values.
 struct gn_ws {
     __nv_bfloat16* a1p;   // [n][15][15][64]   block-1 output, zero border (conv2 input)
     __nv_bfloat16* a2p;   // [n][13][13][256]  block-2 output, zero border (conv3 input)
     __nv_bfloat16* a3;    // block-3 output, k = p*512 + c, K-blocked (gn_a3_off): linear5 input
-    __nv_bfloat16* ac1;   // [n][L1+2][64]     AudBl conv1 output, (l, c) order, zero rows at l = -1 and l = L1
-    __nv_bfloat16* ac2;   // [n][L2][128]      AudBl conv2 output, (l, c) order (linear3 input)
-    __nv_bfloat16* h0;    // [n][fin]          [audio128 | visual512]
-    __nv_bfloat16* h1;    // [n][512]
-    __nv_bfloat16* h2;    // [n][512]
-    __nv_bfloat16* h3;    // [n][256]
-    float* part;          // [splits][rows][512] fp32 partial sums of the K-split part of linear5 (gn_linear5_plan)
+    float* ac1;           // [n][L1+2][64]     AudBl conv1 output, (l, c) order, zero rows at l = -1 and l = L1
+    float* ac2;           // [n][L2][128]      AudBl conv2 output, (l, c) order (linear3 input)
+    float* h0;            // [n][fin]          [audio128 | visual512]
+    float* h1;            // [n][512]
+    float* h2;            // [n][512]
+    float* h3;            // [n][256]
+    float* part;          // [splits][n][512] fp32 partial sums of linear5's K ranges (gn_linear5_splits)
     int64_t bytes;
 };
+
+#if defined(__CUDACC__)
+// value rounded to TF32 (10-bit mantissa, round to nearest, ties away): what the head's GEMM operands hold
+__device__ __forceinline__ float gn_round_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+#endif
 gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base);
 int gn_tc_gemm_tf32(gn_handle* h, const float* A, int64_t M, int K, int64_t lda, const float* B, int N, int64_t ldb,
                     float* C, cudaStream_t st, int k_splits = 1);   // gn_tc_gemm.cu: C[split][M][N] = A[M][K range] . B[N][K range]^T, TF32 tensor cores
 int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, int C, cudaStream_t st);   // gn_tc_gemm.cu
-int gn_linear5_plan(const gn_model* m, int64_t n, int64_t* rows_direct);   // gn_tc_gemm.cu: rows run as whole tiles + K ranges of the rest
+int gn_linear5_splits(const gn_model* m);   // gn_tc_gemm.cu: number of K ranges of linear5 (a function of K only: batch-invariant sums)
 
 // ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);
 int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt);
 int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st);   // conv2 + linear3 on tensor cores
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
-                          cudaStream_t st);
+                          cudaStream_t st, const gn_score_sink* sink = nullptr);
 int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
                             cudaStream_t st);

@@ -3,7 +3,7 @@
 //   * VisBl block 1: conv1 3->64 k3 s3 p3 + ReLU + MaxPool(3,1) + BatchNorm(eval)  (utils.py:174-177)
 //     -> bf16 NHWC with a zero border (the padding=1 input of conv2);
 //   * AudBl: conv1d 30->64 s2, conv1d 64->128 s2, linear -> 128, ReLUs             (utils.py:216-225)
-//     -> bf16 columns [0,128) of the fusion input (audio first, utils.py:266).
+//     -> TF32 columns [0,128) of the fusion input (audio first, utils.py:266).
 #include "gn_common.cuh"
 
 namespace {
@@ -220,7 +220,7 @@ constexpr int kAFrames = 4;    // frames per CTA pass: every weight fetched from
 __global__ void __launch_bounds__(kAThreads)
 audbl_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, int L2, const float* __restrict__ w1,
              const float* __restrict__ b1, const float* __restrict__ w2, const float* __restrict__ b2,
-             const float* __restrict__ w3, const float* __restrict__ b3, __nv_bfloat16* __restrict__ h0, int ld) {
+             const float* __restrict__ w3, const float* __restrict__ b3, float* __restrict__ h0, int ld) {
     extern __shared__ __align__(16) float sm[];
     float* in = sm;                              // [F][30][B]
     float* c1 = in + kAFrames * 30 * B;          // [F][64][L1]
@@ -287,7 +287,7 @@ audbl_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, int L2, co
                 float v = acc[f];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if (lane == 0 && f < nf) h0[(f0 + f) * ld + j] = __float2bfloat16(fmaxf(v + b3[j], 0.f));
+                if (lane == 0 && f < nf) h0[(f0 + f) * ld + j] = gn_round_tf32(fmaxf(v + b3[j], 0.f));
             }
         }
     }
@@ -302,7 +302,7 @@ constexpr int kCF = 4;
 
 __global__ void __launch_bounds__(kCThreads, 2)
 audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, const float* __restrict__ w1,
-                   const float* __restrict__ b1, __nv_bfloat16* __restrict__ ac1) {
+                   const float* __restrict__ b1, float* __restrict__ ac1) {
     extern __shared__ __align__(16) float sm[];            // [kCF][B+2][32]
     const int tid = threadIdx.x, co = tid & 63, g = tid >> 6;
     const int rows = B + 2;
@@ -320,8 +320,8 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
         }
         __syncthreads();
         for (int f = 0; f < nf; ++f) {
-            __nv_bfloat16* o = ac1 + (f0 + f) * (int64_t)(L1 + 2) * 64;
-            if (g == 0) { o[co] = __float2bfloat16(0.f); o[(L1 + 1) * 64 + co] = __float2bfloat16(0.f); }
+            float* o = ac1 + (f0 + f) * (int64_t)(L1 + 2) * 64;
+            if (g == 0) { o[co] = 0.f; o[(L1 + 1) * 64 + co] = 0.f; }
             for (int l = g; l < L1; l += kCThreads / 64) {
                 float acc = bias;
 #pragma unroll
@@ -338,7 +338,7 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
                         }
                     }
                 }
-                o[(l + 1) * 64 + co] = __float2bfloat16(fmaxf(acc, 0.f));
+                o[(l + 1) * 64 + co] = gn_round_tf32(fmaxf(acc, 0.f));
             }
         }
     }
@@ -348,12 +348,9 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
 
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
     if (m->S != kS || m->C1 != kC1) {
-        static bool attr_t = false;
         const size_t smem_t = sizeof(float) * kT1 * kT1 * (64 + kPatch);
-        if (!attr_t) {
+        if (gn_attr_first(m->h, reinterpret_cast<const void*>(visbl_block1_tiled_kernel)))
             GN_CUDA(cudaFuncSetAttribute(visbl_block1_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
-            attr_t = true;
-        }
         const int P1 = m->C1 - 2, tiles = (P1 + kT1P - 1) / kT1P;
         int rc = gn_launch_zero_border(m->h, ws.a1p, n, m->C1, 64, st);
         if (rc) return rc;
@@ -364,11 +361,8 @@ int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const g
         return GN_OK;
     }
     const size_t smem = sizeof(float) * (size_t)(kC1 * kC1 * (kPatch + 64)) + sizeof(unsigned short) * 3 * kS * kS;
-    static bool attr = false;
-    if (!attr) {
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(visbl_block1_kernel)))
         GN_CUDA(cudaFuncSetAttribute(visbl_block1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        attr = true;
-    }
     const int64_t cap = (int64_t)m->h->num_sms * 2;
     const int grid = (int)(n < cap ? n : cap);
     visbl_block1_kernel<<<grid, kVThreads, smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0],

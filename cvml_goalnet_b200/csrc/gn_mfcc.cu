@@ -226,11 +226,8 @@ extern "C" int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_sampl
     if (dct_smem) smem += dct_bytes;
     const int w_smem = (w_bytes <= 16 * 1024 && smem + w_bytes <= kSmemMax) ? 1 : 0;
     if (w_smem) smem += w_bytes;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gn_attr_first(h, reinterpret_cast<const void*>(mfcc_kernel)))
         GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax));
-        attr_set = true;
-    }
     // persistent: one 8-warp CTA per SM (the register-resident transforms need ~all of the register file)
     const int grid = (int)(n < (int64_t)h->num_sms ? n : (int64_t)h->num_sms);
     mfcc_kernel<<<grid, kThreads, smem, gn_stream(stream)>>>(

@@ -127,26 +127,26 @@ __global__ void pack_linear5(const float* __restrict__ w, int C, int PP, __nv_bf
         out[gn_w5_off(o, k)] = __float2bfloat16(w[o * K + (int64_t)c * PP + p]);
     }
 }
-// AudBl conv2 weight [128][64][3] -> bf16 [128][tap*64 + ci]
-__global__ void pack_aconv2(const float* __restrict__ w, __nv_bfloat16* __restrict__ out) {
+// AudBl conv2 weight [128][64][3] -> TF32 [128][tap*64 + ci]
+__global__ void pack_aconv2(const float* __restrict__ w, float* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 128 * 192) {
         const int co = i / 192, k = i - co * 192, tap = k / 64, ci = k - tap * 64;
-        out[i] = __float2bfloat16(w[(co * 64 + ci) * 3 + tap]);
+        out[i] = gn_round_tf32(w[(co * 64 + ci) * 3 + tap]);
     }
 }
-// AudBl linear3 weight [128][128*L2] with column c*L2 + l -> bf16 [128][l*128 + c]
-__global__ void pack_alinear3(const float* __restrict__ w, int L2, __nv_bfloat16* __restrict__ out) {
+// AudBl linear3 weight [128][128*L2] with column c*L2 + l -> TF32 [128][l*128 + c]
+__global__ void pack_alinear3(const float* __restrict__ w, int L2, float* __restrict__ out) {
     const int K = 128 * L2;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 128 * K) {
         const int j = i / K, k = i - j * K, l = k / 128, c = k - l * 128;
-        out[i] = __float2bfloat16(w[j * K + c * L2 + l]);
+        out[i] = gn_round_tf32(w[j * K + c * L2 + l]);
     }
 }
-__global__ void cast_bf16(const float* __restrict__ w, int64_t total, __nv_bfloat16* __restrict__ out) {
+__global__ void cast_tf32(const float* __restrict__ w, int64_t total, float* __restrict__ out) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
-        out[i] = __float2bfloat16(w[i]);
+        out[i] = gn_round_tf32(w[i]);
 }
 __global__ void copy_f32(const float* __restrict__ w, int64_t total, float* __restrict__ out) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
@@ -199,8 +199,9 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
     m->C1 = C1; m->P1 = P1; m->P2 = P2; m->P3 = P3; m->L1 = L1; m->L2 = L2;
     m->fin = 512 + (audio_included ? 128 : 0);
     const int64_t K5 = 512LL * P3 * P3;
-    const size_t cap = (size_t)(512 * K5 + 512 * 2304 + 256 * 576 + 512 * 640 + 512 * 512 + 256 * 512 + 128 * 256) * 2 +
-                       (size_t)(64 * 90 + 128 * 192 + 128 * 128 * L2) * 6 + (1 << 20);
+    const size_t cap = (size_t)(512 * K5 + 512 * 2304 + 256 * 576) * 2 +
+                       (size_t)(512 * 640 + 512 * 512 + 256 * 512 + 128 * 256) * 4 +
+                       (size_t)(64 * 90 + 128 * 192 + 128 * 128 * L2) * 8 + (1 << 20);
     cudaError_t e = cudaMalloc(&m->arena, cap);
     if (e != cudaSuccess) { free(m); return (int)e; }
     Arena A{reinterpret_cast<char*>(m->arena), 0, cap};
@@ -242,9 +243,9 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
         m->aconv2_b = copyf(sd->aconv2_b, 128);
         m->alinear3_w = copyf(sd->alinear3_w, 128LL * 128 * L2);
         m->alinear3_b = copyf(sd->alinear3_b, 128);
-        m->aconv2_wk = A.take<__nv_bfloat16>(128 * 192);
+        m->aconv2_wk = A.take<float>(128 * 192);
         pack_aconv2<<<(128 * 192 + T - 1) / T, T, 0, st>>>(sd->aconv2_w, m->aconv2_wk);
-        m->alinear3_wk = A.take<__nv_bfloat16>((size_t)128 * 128 * L2);
+        m->alinear3_wk = A.take<float>((size_t)128 * 128 * L2);
         pack_alinear3<<<(128 * 128 * L2 + T - 1) / T, T, 0, st>>>(sd->alinear3_w, L2, m->alinear3_wk);
     }
     const float* fw[4] = {sd->f0_w, sd->f3_w, sd->f6_w, sd->f9_w};
@@ -252,8 +253,8 @@ extern "C" int gn_model_create(gn_handle* h, gn_model** out, const gn_avm_state*
     const int fo[4] = {512, 512, 256, 128};
     const int fi[4] = {m->fin, 512, 512, 256};
     for (int i = 0; i < 4; ++i) {
-        m->f_wk[i] = A.take<__nv_bfloat16>((size_t)fo[i] * fi[i]);
-        cast_bf16<<<blocks((int64_t)fo[i] * fi[i]), T, 0, st>>>(fw[i], (int64_t)fo[i] * fi[i], m->f_wk[i]);
+        m->f_wk[i] = A.take<float>((size_t)fo[i] * fi[i]);
+        cast_tf32<<<blocks((int64_t)fo[i] * fi[i]), T, 0, st>>>(fw[i], (int64_t)fo[i] * fi[i], m->f_wk[i]);
         m->f_b[i] = copyf(fb[i], fo[i]);
     }
     m->f12_w = copyf(sd->f12_w, 128);
@@ -329,19 +330,18 @@ gn_ws gn_ws_layout(const gn_model* m, int64_t n, void* base) {
         off += elems * sizeof(__nv_bfloat16);
         return p;
     };
+    auto takef = [&](size_t elems) { return reinterpret_cast<float*>(take(elems * 2)); };
     const size_t nn = (size_t)(n > 0 ? n : 1);
     w.a1p = take(nn * m->C1 * m->C1 * 64);
     w.a2p = take(nn * m->P1 * m->P1 * 256);
     w.a3 = take(((nn + 127) / 128 * 128) * m->P3 * m->P3 * 512);
-    w.ac1 = take(nn * (m->L1 + 2) * 64);
-    w.ac2 = take(nn * m->L2 * 128);
-    w.h0 = take(nn * m->fin);
-    w.h1 = take(nn * 512);
-    w.h2 = take(nn * 512);
-    w.h3 = take(nn * 256);
-    int64_t rows_direct = 0;
-    const int splits = gn_linear5_plan(m, (int64_t)nn, &rows_direct);
-    w.part = splits > 1 ? reinterpret_cast<float*>(take((size_t)splits * (nn - (size_t)rows_direct) * 512 * 2)) : nullptr;
+    w.ac1 = takef(nn * (m->L1 + 2) * 64);
+    w.ac2 = takef(nn * m->L2 * 128);
+    w.h0 = takef(nn * m->fin);
+    w.h1 = takef(nn * 512);
+    w.h2 = takef(nn * 512);
+    w.h3 = takef(nn * 256);
+    w.part = takef((size_t)gn_linear5_splits(m) * nn * 512);
     w.bytes = (int64_t)((off + 1023) & ~size_t(1023));
     return w;
 }
@@ -352,10 +352,11 @@ extern "C" int64_t gn_avm_workspace_bytes(const gn_model* m, int64_t n) {
 }
 
 static int avm_forward_impl(gn_model* m, const float* d_visual, const float* d_audio, int64_t n, float* d_scores,
-                            float* d_visfeat, void* d_ws, int64_t ws_bytes, void* stream, bool simt) {
+                            float* d_visfeat, void* d_ws, int64_t ws_bytes, void* stream, bool simt,
+                            const gn_score_sink* sink = nullptr) {
     if (!m || n < 0) return GN_E_ARG;
     if (n == 0) return GN_OK;
-    if (!d_visual || !d_scores || !d_ws) return GN_E_ARG;
+    if (!d_visual || (!d_scores && !sink) || !d_ws) return GN_E_ARG;
     if (m->audio_included && !d_audio) return GN_E_ARG;
     if ((reinterpret_cast<uintptr_t>(d_ws) & 1023) != 0) return GN_E_ARG;
     if (n > (1LL << 31) / 256) return GN_E_RANGE;   // TMA coordinates are int32
@@ -370,7 +371,18 @@ static int avm_forward_impl(gn_model* m, const float* d_visual, const float* d_a
     if (rc) return rc;
     GN_STAGE_MARK(m, 2, st);
     return simt ? gn_launch_simt_backbone(m, n, ws, d_scores, d_visfeat, st)
-                : gn_launch_tc_backbone(m, n, ws, d_scores, d_visfeat, st);
+                : gn_launch_tc_backbone(m, n, ws, d_scores, d_visfeat, st, sink);
+}
+
+extern "C" int gn_avm_forward_scatter(gn_model* m, const float* d_visual, const float* d_audio, int64_t n,
+                                      const gn_score_sink* sink, void* d_workspace, int64_t workspace_bytes,
+                                      void* stream) {
+    if (!m || !sink) return GN_E_ARG;
+    if (m->n_cls > 1) return GN_E_ARG;             // regression head only
+    if (sink->n_dst < 1 || sink->n_dst > GN_MAX_PEERS || sink->rows_per_match < 1 || sink->dst_match_stride < 1 ||
+        sink->dst_offset < 0 || sink->row0 < 0) return GN_E_ARG;
+    for (int p = 0; p < sink->n_dst; ++p) if (!sink->dst[p]) return GN_E_ARG;
+    return avm_forward_impl(m, d_visual, d_audio, n, nullptr, nullptr, d_workspace, workspace_bytes, stream, false, sink);
 }
 
 extern "C" int gn_avm_forward(gn_model* m, const float* d_visual, const float* d_audio, int64_t n, float* d_scores,
@@ -432,10 +444,15 @@ simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __n
     }
 }
 
-// out[r][col_off + j] = relu(A[r] . W[j] + b[j]); one warp per (row, j), lanes stride K
+__device__ __forceinline__ float ldf(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float ldf(const float* p) { return *p; }
+
+// out[r][col_off + j] = tf32(relu(A[r] . W[j] + b[j])); one warp per (row, j), lanes stride K.  T = bf16 (linear5) or
+// float (head layers: TF32-rounded values, whose products are exact in fp32 -- the same products the tensor core forms)
+template <typename T>
 __global__ void __launch_bounds__(256)
-simt_linear(const __nv_bfloat16* __restrict__ A, int64_t M, int K, int lda, const __nv_bfloat16* __restrict__ W, int N,
-            const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int ld_out, int col_off,
+simt_linear(const T* __restrict__ A, int64_t M, int K, int lda, const T* __restrict__ W, int N,
+            const float* __restrict__ bias, float* __restrict__ out, int ld_out, int col_off,
             float* __restrict__ out_f32, int blocked) {
     const int lane = threadIdx.x & 31;
     const int64_t gw = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
@@ -443,26 +460,26 @@ simt_linear(const __nv_bfloat16* __restrict__ A, int64_t M, int K, int lda, cons
     for (int64_t o = gw; o < M * N; o += nw) {
         const int64_t r = o / N;
         const int j = (int)(o - r * N);
-        const __nv_bfloat16* a = A + r * lda;
-        const __nv_bfloat16* w = W + (size_t)j * K;
+        const T* a = A + r * lda;
+        const T* w = W + (size_t)j * K;
         float acc = 0.f;
         if (blocked) {   // linear5 operands (gn_a3_off / gn_w5_off)
             for (int k = lane; k < K; k += 32)
-                acc = fmaf(__bfloat162float(A[gn_a3_off(r, k, K / 64)]), __bfloat162float(W[gn_w5_off(j, k)]), acc);
+                acc = fmaf(ldf(A + gn_a3_off(r, k, K / 64)), ldf(W + gn_w5_off(j, k)), acc);
         } else
-        for (int k = lane; k < K; k += 32) acc = fmaf(__bfloat162float(a[k]), __bfloat162float(w[k]), acc);
+        for (int k = lane; k < K; k += 32) acc = fmaf(ldf(a + k), ldf(w + k), acc);
         for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
         if (lane == 0) {
-            const __nv_bfloat16 v = __float2bfloat16(fmaxf(acc + bias[j], 0.f));
+            const float v = gn_round_tf32(fmaxf(acc + bias[j], 0.f));
             out[r * ld_out + col_off + j] = v;
-            if (out_f32) out_f32[r * N + j] = __bfloat162float(v);
+            if (out_f32) out_f32[r * N + j] = v;
         }
     }
 }
 
 // fusion.9 + ReLU + fusion.12 + sigmoid + 4y+1; one warp per row
 __global__ void __launch_bounds__(256)
-simt_score(const __nv_bfloat16* __restrict__ A, int64_t M, int K, const __nv_bfloat16* __restrict__ W,
+simt_score(const float* __restrict__ A, int64_t M, int K, const float* __restrict__ W,
            const float* __restrict__ bias, const float* __restrict__ wl, const float* __restrict__ bl,
            float* __restrict__ scores) {
     const int lane = threadIdx.x & 31;
@@ -473,7 +490,7 @@ simt_score(const __nv_bfloat16* __restrict__ A, int64_t M, int K, const __nv_bfl
         for (int j = 0; j < 128; ++j) {
             float acc = 0.f;
             for (int k = lane; k < K; k += 32)
-                acc = fmaf(__bfloat162float(A[r * K + k]), __bfloat162float(W[(size_t)j * K + k]), acc);
+                acc = fmaf(A[r * K + k], W[(size_t)j * K + k], acc);
             for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
             dot = fmaf(fmaxf(acc + bias[j], 0.f), wl[j], dot);
         }
@@ -494,9 +511,9 @@ __global__ void read_act_nchw(const __nv_bfloat16* __restrict__ in, int64_t n, i
         else out[i] = __bfloat162float(in[((f * PW + y + pad) * PW + x + pad) * C + c]);
     }
 }
-__global__ void read_act_flat(const __nv_bfloat16* __restrict__ in, int64_t total, float* __restrict__ out) {
+__global__ void read_act_flat(const float* __restrict__ in, int64_t total, float* __restrict__ out) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
-        out[i] = __bfloat162float(in[i]);
+        out[i] = in[i];
 }
 
 }  // namespace
@@ -505,11 +522,8 @@ int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_sc
                             cudaStream_t st) {
     if (n > 65535 * 16) return GN_E_SHAPE;
     if (m->P1 * m->P1 * 64 * 4 > 64 * 1024) return GN_E_SHAPE;   // validation path: one frame's conv tile in shared memory
-    static bool attr = false;
-    if (!attr) {
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(simt_conv_block)))
         GN_CUDA(cudaFuncSetAttribute(simt_conv_block, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-        attr = true;
-    }
     simt_conv_block<<<dim3((unsigned)n, 4), 256, m->P1 * m->P1 * 64 * 4, st>>>(
         ws.a1p, m->P1, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1], ws.a2p, 1, 0);
     GN_LAUNCHED(m->h);
@@ -521,14 +535,14 @@ int gn_launch_simt_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_sc
     const int K5 = m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     const int grid = m->h->num_sms * 8;
-    simt_linear<<<grid, 256, 0, st>>>(ws.a3, n, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff, d_visfeat, 1);
+    simt_linear<__nv_bfloat16><<<grid, 256, 0, st>>>(ws.a3, n, K5, K5, m->linear5_wk, 512, m->linear5_b, ws.h0, m->fin, aoff, d_visfeat, 1);
     GN_LAUNCHED(m->h);
     GN_STAGE_MARK(m, 5, st);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h0, n, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr, 0);
+    simt_linear<float><<<grid, 256, 0, st>>>(ws.h0, n, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h1, n, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr, 0);
+    simt_linear<float><<<grid, 256, 0, st>>>(ws.h1, n, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
-    simt_linear<<<grid, 256, 0, st>>>(ws.h2, n, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr, 0);
+    simt_linear<float><<<grid, 256, 0, st>>>(ws.h2, n, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr, 0);
     GN_LAUNCHED(m->h);
     simt_score<<<grid, 256, 0, st>>>(ws.h3, n, 256, m->f_wk[3], m->f_b[3], m->f12_w, m->f12_b, d_scores);
     GN_LAUNCHED(m->h);

@@ -526,7 +526,9 @@ extern "C" int64_t gn_knapsack_workspace_bytes(int n_items, int64_t capacity_col
     if (n_items < 0 || capacity_columns < 0) return GN_E_ARG;
     const int64_t words = knap_words(capacity_columns);
     int64_t bytes = (int64_t)n_items * words * 4;                 // decision bits
-    if (2 * words * 32 * 4 > kKnapSmemLimit) bytes += 2 * words * 32 * 4;   // rows do not fit shared memory
+    // two table rows for knapsack_kernel (the fallback when the cluster kernels' shared-memory need -- which also grows
+    // with n_items -- exceeds the limit): always reserved, so that no item count can make the fallback write past the end
+    bytes = ((bytes + 15) & ~15LL) + 2 * words * 32 * 4;
     return ((bytes + 255) & ~255LL) + 256;                        // + status word of the multi-row kernel
 }
 
@@ -585,13 +587,11 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
             auto k4 = knapsack_multirow_kernel<kMT, 4, kMCPT>;
             auto k2 = knapsack_multirow_kernel<kMT, 2, kMCPT>;
             cfg.blockDim = dim3(kMT);
-            static bool mattr = false;
-            if (!mattr) {
+            if (gn_attr_first(h, reinterpret_cast<const void*>(k4))) {
                 GN_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
                 GN_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
                 GN_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
                 GN_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-                mattr = true;
             }
             cfg.dynamicSmemBytes = (size_t)mr_smem;
             GN_CUDA(cudaLaunchKernelEx(&cfg, rows_per_step == 4 ? k4 : k2, d_values, d_weights, n_items, (int)capacity,
@@ -602,11 +602,9 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
             cfg.blockDim = dim3(kT);
         }
         auto kern = knapsack_cluster_kernel<kT>;
-        static bool cattr = false;
-        if (!cattr) {
+        if (gn_attr_first(h, reinterpret_cast<const void*>(kern))) {
             GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKnapSmemLimit));
             GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-            cattr = true;
         }
         cfg.dynamicSmemBytes = (size_t)cl_smem;
         GN_CUDA(cudaLaunchKernelEx(&cfg, kern, d_values, d_weights, n_items, (int)capacity,
@@ -618,6 +616,30 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
     knapsack_kernel<<<batch, kKnapThreads, 0, gn_stream(stream)>>>(
         d_values, d_weights, n_items, capacity, capacity_rem == 0 ? 1 : 0, d_selected, d_best, bits, words, rows,
         0);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}
+
+// d_dst[m][r * per + j] = d_src[r][m][j] (see goalnet_b200.h): the layout change after an all-gather of frame shards
+__global__ void __launch_bounds__(256)
+unshard_rows_kernel(const float* __restrict__ src, int world, int64_t n_matches, int64_t per, int64_t n,
+                    float* __restrict__ dst) {
+    const int64_t total = n_matches * n;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t mt = i / n, f = i - mt * n;
+        const int64_t r = f / per, j = f - r * per;
+        dst[i] = src[(r * n_matches + mt) * per + j];
+    }
+}
+
+extern "C" int gn_unshard_rows(gn_handle* h, const float* d_src, int world, int64_t n_matches, int64_t per, int64_t n,
+                               float* d_dst, void* stream) {
+    if (!h || world < 1 || n_matches < 0 || per < 0 || n < 0 || n > (int64_t)world * per) return GN_E_ARG;
+    if (n_matches == 0 || n == 0) return GN_OK;
+    if (!d_src || !d_dst) return GN_E_ARG;
+    const int64_t blocks = (n_matches * n + 255) / 256, cap = (int64_t)h->num_sms * 8;
+    unshard_rows_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, gn_stream(stream)>>>(d_src, world, n_matches, per, n,
+                                                                                          d_dst);
     GN_LAUNCHED(h);
     return GN_OK;
 }

@@ -4,9 +4,12 @@
 //     BatchNorm(eval) block fused into the epilogue;
 //   * K-major GEMM  C = relu(A . W^T + b)  (linear5, fusion.0/3/6), and the same with the last
 //     layer (fusion.12), the sigmoid and 4y+1 folded in (fusion.9 -> scores).
-// Operands are bf16, staged by TMA into 128B-swizzled shared memory, multiplied by
-// tcgen05.mma (cta_group::1, M=128) into fp32 accumulators in TMEM (two 256-column buffers so that
-// the epilogue of tile i overlaps the MMAs of tile i+1), and read back with tcgen05.ld.
+// Operands are staged by TMA into 128B-swizzled shared memory, multiplied by tcgen05.mma
+// (cta_group::1, M=128) into fp32 accumulators in TMEM (two 256-column buffers so that the epilogue of
+// tile i overlaps the MMAs of tile i+1), and read back with tcgen05.ld.  The visual backbone (conv2,
+// conv3, linear5: 99 % of the FLOPs) multiplies bf16 operands (kind::f16); the head (AudBl conv2 /
+// linear3, fusion MLP) multiplies fp32 operands holding TF32-rounded values (kind::tf32), because its
+// bf16 rounding dominated the score error (raw MFCCs span +-600; the last layers amplify).
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
 // warps 2..9 = epilogue (TMEM lane quarter = warp_id % 4; the two warps of a quarter split the
@@ -28,7 +31,7 @@ constexpr int kAccCols = 256;            // columns per accumulator buffer (MT *
 constexpr int kCls = 5;                  // classifier head: importance levels 1..5 (utils.py:257, main.py:69,97)
 constexpr int kMaxN = 512;               // widest layer: per-channel parameter vectors staged in shared memory
 
-enum Mode { kConv = 0, kLinear = 1, kScore = 2,
+enum Mode { kConv = 0, kLinear = 1, kScore = 2,    // kLinear / kScore: TF32 operands, fp32 (TF32-rounded) out
             // training GEMMs of the fusion MLP (gn_train.cu): all are C = A . B^T with K-major bf16 operands
             kTrainFwd = 3,   // relu(acc + bias), dropout, bf16 out [M][N] and its transpose [N][ld_t]
             kDgrad = 4,      // acc * scale * [gate > 0], bf16 out [M][N] and its transpose
@@ -53,13 +56,15 @@ struct GemmArgs {
     const float* bias;       // [N]
     const float* bn_scale;   // conv: [N]
     const float* bn_shift;   // conv: [N]
-    __nv_bfloat16* out;      // conv: activation buffer; linear: [M][ld_out]
+    __nv_bfloat16* out;      // conv: activation buffer; training modes: [M][ld_out]
+    float* out_f;            // kLinear: [M][ld_out] fp32, values rounded to TF32 (the next GEMM's operand)
     int ld_out, col_off;     // linear: leading dimension and first column of the output
     float* out_f32;          // linear: optional fp32 copy [M][N]
     const float* w_last;     // score: fusion.12 weight [128]
     const float* b_last;     // score: fusion.12 bias [1]
     float* scores;           // score: [M] regression scores, or [M][kCls] class probabilities
     int n_cls;               // score: 0/1 = sigmoid regression head (utils.py:255-256,270); kCls = softmax classifier head
+    gn_score_sink sink;      // score: n_dst > 0 -> store each score into every destination (peer-mapped) instead of `scores`
     int a3d_rows;            // linear: 0 = A is a 2-D [M][K] map; else A is a 3-D (k, position, frame) map with this many
                              //         positions per frame (AudBl conv2: overlapping 192-element windows, 128/rows frames per tile)
     // training modes
@@ -135,7 +140,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int64_t m_blocks = (MODE == kConv) ? args.M * tiles_pf : (args.M + 127) / 128;
     const int k_splits = (MODE == kSplitK || MODE == kGemmTF32) ? (args.k_splits > 1 ? args.k_splits : 1) : 1;
     const int64_t num_tiles = m_blocks * n_blocks * k_splits;
-    constexpr int kbk = (MODE == kGemmTF32) ? 32 : kBK;      // elements per 128-byte operand row
+    constexpr bool T32 = (MODE == kGemmTF32 || MODE == kLinear || MODE == kScore);   // fp32 (TF32) operands
+    constexpr int kbk = T32 ? 32 : kBK;                      // elements per 128-byte operand row
     const int k_total = args.K / kbk;
     const int k_per = (k_total + k_splits - 1) / k_splits;
     // tile -> (m_blk, n_blk, split): split fastest, then n_blk, so that CTAs running side by side share A and W in L2
@@ -209,7 +215,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     } else {
                         mbar_expect_tx(fb, (uint32_t)(C::kABytes + C::kBBytes));
                         if (args.kblocked)      tma_load_2d(sa, &tmap_a, fb, 0, (int)((m_blk * k_total + kt) * 128));
-                        else if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kBK, 0, (int)(m_blk * (128 / args.a3d_rows)));
+                        else if (args.a3d_rows) tma_load_3d(sa, &tmap_a, fb, kt * kbk, 0, (int)(m_blk * (128 / args.a3d_rows)));
                         else                    tma_load_2d(sa, &tmap_a, fb, kt * kbk, (int)(m_blk * 128));
                     }
                     if (MODE != kConv && args.kblocked) tma_load_2d(sb, &tmap_b, fb, 0, kt * args.N + n_blk * BN);
@@ -220,7 +226,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = (MODE == kGemmTF32) ? make_idesc_tf32(128, BN) : make_idesc_bf16(128, BN);
+        constexpr uint32_t idesc = T32 ? make_idesc_tf32(128, BN) : make_idesc_bf16(128, BN);
         int stage = 0;
         uint32_t phase = 0;
         int ab = 0;
@@ -243,7 +249,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         for (int k4 = 0; k4 < kBK / 16; ++k4) {
                             const uint64_t ad = make_desc_sw128(sa + mt * (128 * 128) + k4 * 32);
                             const uint64_t bd = make_desc_sw128(sb + k4 * 32);
-                            if (MODE == kGemmTF32) umma_tf32(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                            if (T32) umma_tf32(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
                             else                   umma_bf16(d, ad, bd, idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
                         }
                     }
@@ -472,7 +478,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 for (int i = 0; i < 32; ++i) dotc[k - 1] = fmaf(x[i], wl[k * args.N + i], dotc[k - 1]);
                         }
                     } else if (grow < args.M) {
-                        if (MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32 && args.out) {
+                        if (MODE == kLinear) {
+                            float4* dst = reinterpret_cast<float4*>(args.out_f + (size_t)grow * args.ld_out + args.col_off +
+                                                                    n0 + c * 32);
+#pragma unroll
+                            for (int v = 0; v < 8; ++v)
+                                dst[v] = make_float4(gn_round_tf32(x[v * 4]), gn_round_tf32(x[v * 4 + 1]),
+                                                     gn_round_tf32(x[v * 4 + 2]), gn_round_tf32(x[v * 4 + 3]));
+                        } else if (MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32 && args.out) {
                             uint4* dst = reinterpret_cast<uint4*>(args.out + (size_t)grow * args.ld_out + args.col_off +
                                                                   n0 + c * 32);
 #pragma unroll
@@ -522,7 +535,18 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         for (int k = 0; k < kCls; ++k) args.scores[grow * kCls + k] = z[k] * inv;
                     } else {
                         const float zlin = dot + __ldg(args.b_last);
-                        args.scores[grow] = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;   // utils.py:256,270
+                        const float sc = 4.f * (1.f / (1.f + expf(-zlin))) + 1.f;      // utils.py:256,270
+                        if (args.sink.n_dst > 0) {
+                            // all-gather fused into the epilogue: the score goes straight into every rank's (M, n) score
+                            // matrix (lanes hold consecutive rows -> 128-byte runs per destination over NVLink)
+                            const int64_t i = args.sink.row0 + grow;
+                            const int64_t mt = i / args.sink.rows_per_match;
+                            const int64_t idx = mt * args.sink.dst_match_stride + args.sink.dst_offset +
+                                                (i - mt * args.sink.rows_per_match);
+                            for (int p = 0; p < args.sink.n_dst; ++p) args.sink.dst[p][idx] = sc;
+                        } else {
+                            args.scores[grow] = sc;
+                        }
                     }
                 }
                 tc_fence_before();
@@ -548,25 +572,27 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 int make_tmap(gn_handle* h, CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
-              const uint64_t* strides_bytes, const uint32_t* box) {
+              const uint64_t* strides_bytes, const uint32_t* box, bool f32 = false) {
     if (!h->encode_tiled) return GN_E_NODEVICE;
     cuuint64_t gdim[5], gstr[4];
     cuuint32_t bx[5], es[5];
     for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
     for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
     CUresult r = reinterpret_cast<EncodeTiledFn>(h->encode_tiled)(
-        m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+        m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+        const_cast<void*>(base), gdim, gstr, bx, es,
         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? GN_OK : (int)r;
 }
 
-// [rows][K] bf16 row-major -> 2-D map, box (64, box_rows)
-int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, int64_t K, int64_t ld, int box_rows) {
+// [rows][K] row-major -> 2-D map whose box is one 128-byte swizzle row wide: (64 bf16 | 32 fp32, box_rows)
+int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, int64_t K, int64_t ld, int box_rows,
+                 bool f32 = false) {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
-    const uint64_t str[1] = {(uint64_t)ld * 2};
-    const uint32_t box[2] = {(uint32_t)kBK, (uint32_t)box_rows};
-    return make_tmap(h, m, base, 2, dims, str, box);
+    const uint64_t str[1] = {(uint64_t)ld * (f32 ? 4 : 2)};
+    const uint32_t box[2] = {(uint32_t)(f32 ? 32 : kBK), (uint32_t)box_rows};
+    return make_tmap(h, m, base, 2, dims, str, box, f32);
 }
 
 template <int MT, int BN, int STAGES, int MODE, int OHT, int SUBC = BN>
@@ -575,11 +601,8 @@ int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     using C = Cfg<MT, BN, STAGES, MODE, SUBC>;
     if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32) return GN_E_SHAPE;
     auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT, SUBC>;
-    static bool attr = false;
-    if (!attr) {
+    if (gn_attr_first(h, reinterpret_cast<const void*>(kern)))
         GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-        attr = true;
-    }
     const int grid = (int)(tiles < h->num_sms ? tiles : h->num_sms);
     if (grid <= 0) return GN_OK;
     kern<<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, a);
@@ -656,10 +679,11 @@ int run_conv_tiled(gn_model* m, int64_t n, const __nv_bfloat16* in, int OHF, int
     return launch<2, BN, 3, kConv, kTileOH>(m->h, ta, tb, a, n * a.g.tiles * a.g.tiles * (Cout / BN), st);
 }
 
-// out[r][col_off + j] = bf16(relu(sum_s part[s][r][j] + bias[j])) (+ fp32 copy of the rounded value); 4 columns / thread
+// out[r][col_off + j] = tf32(relu(sum_s part[s][r][j] + bias[j])) (+ a dense copy of the same values); 4 columns / thread.
+// The ranges are added in a fixed order (s = 0, 1, ...), so a row's result does not depend on the batch it is in.
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int N, const float* __restrict__ bias,
-                     __nv_bfloat16* __restrict__ out, int ld_out, int col_off, float* __restrict__ out_f32) {
+                     float* __restrict__ out, int ld_out, int col_off, float* __restrict__ out_f32) {
     const int64_t total = M * N / 4;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = (i * 4) / N;
@@ -669,15 +693,10 @@ splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int 
             const float4 v = __ldcs(reinterpret_cast<const float4*>(part + (size_t)s * M * N) + i);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
         }
-        const __nv_bfloat162 lo = __floats2bfloat162_rn(fmaxf(acc.x, 0.f), fmaxf(acc.y, 0.f));
-        const __nv_bfloat162 hi = __floats2bfloat162_rn(fmaxf(acc.z, 0.f), fmaxf(acc.w, 0.f));
-        uint2 pk;
-        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
-        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(out + r * ld_out + col_off + j) = pk;
-        if (out_f32)
-            *reinterpret_cast<float4*>(out_f32 + r * N + j) =
-                make_float4(__bfloat162float(lo.x), __bfloat162float(lo.y), __bfloat162float(hi.x), __bfloat162float(hi.y));
+        const float4 o = make_float4(gn_round_tf32(fmaxf(acc.x, 0.f)), gn_round_tf32(fmaxf(acc.y, 0.f)),
+                                     gn_round_tf32(fmaxf(acc.z, 0.f)), gn_round_tf32(fmaxf(acc.w, 0.f)));
+        *reinterpret_cast<float4*>(out + r * ld_out + col_off + j) = o;
+        if (out_f32) *reinterpret_cast<float4*>(out_f32 + r * N + j) = o;
     }
 }
 
@@ -691,11 +710,14 @@ int make_tmaps_kblocked(gn_handle* h, CUtensorMap* ta, CUtensorMap* tb, const __
     return make_tmap_2d(h, tb, wk, rows_b, kBK, kBK, BN);
 }
 
-// relu(A . W^T + b) with the reduction split into `splits` K ranges, one (tile, range) unit per CTA visit: used when
-// the (M/128) x (N/256) tiles alone would leave SMs idle (few frames, or linear5 at large frame sizes where
-// K = 512 * P3^2 is in the millions).  Deterministic: partial sums go to fp32 slabs, then one reduction pass.
+// linear5: relu(A . W^T + b) with the reduction split into `splits` K ranges, one (tile, range) unit per CTA visit.
+// K = 512 * P3^2 is 41 472 at the reference's 40x40 frames and in the millions at large frame sizes, so the
+// (M/128) x (N/256) tiles alone rarely fill the GPU in whole waves.  EVERY row takes this path with the SAME ranges
+// (gn_linear5_splits depends on K only): partial sums go to fp32 slabs and one reduction pass adds them in a fixed
+// order, so a frame's features -- hence its score -- are bit-identical whatever batch, chunk or GPU shard it is
+// scored in (what lets the frame-sharded multi-GPU path reproduce the single-GPU bits).
 int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K, const __nv_bfloat16* wk, int N,
-                      const float* bias, int splits, float* part, __nv_bfloat16* out, int ld_out, int col_off,
+                      const float* bias, int splits, float* part, float* out, int ld_out, int col_off,
                       float* out_f32, cudaStream_t st) {
     constexpr int BN = 256;
     if (K % kBK || N % BN || K > (1LL << 31) - 64 || splits < 1 || !part) return GN_E_SHAPE;
@@ -713,26 +735,23 @@ int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K,
     return GN_OK;
 }
 
+// head layers: out = tf32(relu(A . W^T + b)) (kLinear) or the score epilogue (kScore); A [M][K] and W [N][K] are fp32
+// arrays of TF32-rounded values
 template <int BN, int STAGES, int MODE>
-int run_linear(gn_model* m, int64_t M, const __nv_bfloat16* A, int K, int lda, const __nv_bfloat16* wk, int N,
-               const float* bias, __nv_bfloat16* out, int ld_out, int col_off, float* out_f32, const float* w_last,
-               const float* b_last, float* scores, cudaStream_t st, int kblocked = 0, int n_cls = 1) {
-    if (K % kBK || N % BN) return GN_E_SHAPE;
+int run_linear(gn_model* m, int64_t M, const float* A, int K, int lda, const float* wk, int N, const float* bias,
+               float* out, int ld_out, int col_off, const float* w_last, const float* b_last, float* scores,
+               cudaStream_t st, int n_cls = 1, const gn_score_sink* sink = nullptr) {
+    static_assert(MODE == kLinear || MODE == kScore, "head layers only");
+    if (K % 32 || N % BN || (lda & 3)) return GN_E_SHAPE;
     CUtensorMap ta, tb;
-    int rc;
-    if (kblocked) {
-        rc = make_tmaps_kblocked(m->h, &ta, &tb, A, M, K, wk, N, BN);
-        if (rc) return rc;
-    } else {
-        rc = make_tmap_2d(m->h, &ta, A, M, K, lda, 128);
-        if (rc) return rc;
-        rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN);
-        if (rc) return rc;
-    }
+    int rc = make_tmap_2d(m->h, &ta, A, M, K, lda, 128, true);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, N, K, K, BN, true);
+    if (rc) return rc;
     GemmArgs a{};
-    a.kblocked = kblocked;
-    a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = ld_out; a.col_off = col_off;
-    a.out_f32 = out_f32; a.w_last = w_last; a.b_last = b_last; a.scores = scores; a.n_cls = n_cls;
+    a.M = M; a.N = N; a.K = K; a.bias = bias; a.out_f = out; a.ld_out = ld_out; a.col_off = col_off;
+    a.w_last = w_last; a.b_last = b_last; a.scores = scores; a.n_cls = n_cls;
+    if (sink) a.sink = *sink;
     return launch<1, BN, STAGES, MODE, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN), st);
 }
 
@@ -747,24 +766,15 @@ int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, i
     return GN_OK;
 }
 
-// Work plan for linear5 (N = 512 -> two 256-wide column tiles per 128 rows) on a persistent grid of num_sms CTAs:
-// rows [0, *rows_direct) run as whole tiles in full waves; the remaining rows -- a partial last wave, or everything
-// when there are fewer tiles than SMs -- have their reduction split into the returned number of K ranges so that the
-// tail also fills the GPU.  Returns 1 (and *rows_direct = n) when splitting does not pay.
-int gn_linear5_plan(const gn_model* m, int64_t n, int64_t* rows_direct) {
-    const int sms = m->h->num_sms;
-    const int64_t mb = (n + 127) / 128, tiles = mb * 2;
+// Number of K ranges linear5's reduction is cut into (see run_linear_splitk).  A function of the model only -- never of
+// the batch -- so that every frame is summed the same way: about 108 k-steps (of 64) per range, at most 32 ranges.
+// 40x40 frames: K = 41 472 = 648 k-steps -> 6 ranges (10 800 frames: 85 x 2 x 6 = 1 020 units over 148 CTAs).
+int gn_linear5_splits(const gn_model* m) {
     const int64_t k_total = (int64_t)m->P3 * m->P3 * 512 / kBK;
-    *rows_direct = n;
-    if (n <= 0 || k_total < 16) return 1;
-    const int64_t waves = (sms % 2 == 0) ? tiles / sms : 0;
-    const int64_t rem_tiles = tiles - waves * sms;
-    if (rem_tiles == 0 || rem_tiles * 4 > (int64_t)sms * 3) return 1;     // last wave already >= 75 % full
-    int64_t s = sms / rem_tiles;
-    if (s > k_total / 8) s = k_total / 8;          // at least 8 k-steps per range
-    if (s <= 1) return 1;
+    int64_t s = (k_total + 107) / 108;
+    if (s > 32) s = 32;
+    if (s < 1) s = 1;
     const int64_t k_per = (k_total + s - 1) / s;
-    *rows_direct = waves * (sms / 2) * 128;
     return (int)((k_total + k_per - 1) / k_per);   // every range non-empty
 }
 
@@ -777,25 +787,25 @@ int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st)
     if (128 % L2) return GN_E_SHAPE;
     CUtensorMap ta, tb;
     const uint64_t dims[3] = {192, (uint64_t)L2, (uint64_t)n};
-    const uint64_t str[2] = {128 * 2, (uint64_t)rows * 64 * 2};
-    const uint32_t box[3] = {(uint32_t)kBK, (uint32_t)L2, (uint32_t)(128 / L2)};
-    int rc = make_tmap(m->h, &ta, ws.ac1, 3, dims, str, box);
+    const uint64_t str[2] = {128 * 4, (uint64_t)rows * 64 * 4};
+    const uint32_t box[3] = {32u, (uint32_t)L2, (uint32_t)(128 / L2)};
+    int rc = make_tmap(m->h, &ta, ws.ac1, 3, dims, str, box, true);
     if (rc) return rc;
-    rc = make_tmap_2d(m->h, &tb, m->aconv2_wk, 128, 192, 192, 128);
+    rc = make_tmap_2d(m->h, &tb, m->aconv2_wk, 128, 192, 192, 128, true);
     if (rc) return rc;
     GemmArgs a{};
-    a.M = n * L2; a.N = 128; a.K = 192; a.bias = m->aconv2_b; a.out = ws.ac2; a.ld_out = 128; a.col_off = 0;
+    a.M = n * L2; a.N = 128; a.K = 192; a.bias = m->aconv2_b; a.out_f = ws.ac2; a.ld_out = 128; a.col_off = 0;
     a.a3d_rows = L2;
-    rc = launch<1, 128, 3, kLinear, 0>(m->h, ta, tb, a, (a.M + 127) / 128, st);
+    rc = launch<1, 128, 4, kLinear, 0>(m->h, ta, tb, a, (a.M + 127) / 128, st);
     if (rc) return rc;
     // linear3 + ReLU -> columns [0,128) of the fusion input (audio first, utils.py:266)
     return run_linear<128, 4, kLinear>(m, n, ws.ac2, 128 * L2, 128 * L2, m->alinear3_wk, 128, m->alinear3_b, ws.h0,
-                                       m->fin, 0, nullptr, nullptr, nullptr, nullptr, st);
+                                       m->fin, 0, nullptr, nullptr, nullptr, st);
 }
 
 // conv2 -> conv3 -> linear5 -> fusion MLP -> scores, all on the tensor cores.
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
-                          cudaStream_t st) {
+                          cudaStream_t st, const gn_score_sink* sink) {
     int rc;
     if (m->P1 == 13 && m->P2 == 11) {
         // the reference's 40x40 frames: one frame per tile
@@ -823,34 +833,24 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
     const int64_t K5 = (int64_t)m->P3 * m->P3 * 512;
     const int aoff = m->audio_included ? 128 : 0;
     // linear5 + ReLU -> columns [aoff, aoff+512) of the fusion input (audio features occupy [0,128))
-    int64_t rows_direct = n;
-    const int splits = gn_linear5_plan(m, n, &rows_direct);
-    if (rows_direct > 0) {
-        rc = run_linear<256, 4, kLinear>(m, rows_direct, ws.a3, (int)K5, (int)K5, m->linear5_wk, 512, m->linear5_b, ws.h0,
-                                         m->fin, aoff, d_visfeat, nullptr, nullptr, nullptr, st, 1);
-        if (rc) return rc;
-    }
-    if (rows_direct < n) {
-        rc = run_linear_splitk(m, n - rows_direct, ws.a3 + rows_direct * K5, K5, m->linear5_wk, 512, m->linear5_b, splits,
-                               ws.part, ws.h0 + rows_direct * m->fin, m->fin, aoff,
-                               d_visfeat ? d_visfeat + rows_direct * 512 : nullptr, st);
-        if (rc) return rc;
-    }
+    rc = run_linear_splitk(m, n, ws.a3, K5, m->linear5_wk, 512, m->linear5_b, gn_linear5_splits(m), ws.part, ws.h0,
+                           m->fin, aoff, d_visfeat, st);
+    if (rc) return rc;
     GN_STAGE_MARK(m, 5, st);
     rc = run_linear<256, 4, kLinear>(m, n, ws.h0, m->fin, m->fin, m->f_wk[0], 512, m->f_b[0], ws.h1, 512, 0, nullptr,
-                                     nullptr, nullptr, nullptr, st);
+                                     nullptr, nullptr, st);
     if (rc) return rc;
     rc = run_linear<256, 4, kLinear>(m, n, ws.h1, 512, 512, m->f_wk[1], 512, m->f_b[1], ws.h2, 512, 0, nullptr,
-                                     nullptr, nullptr, nullptr, st);
+                                     nullptr, nullptr, st);
     if (rc) return rc;
     rc = run_linear<256, 4, kLinear>(m, n, ws.h2, 512, 512, m->f_wk[2], 256, m->f_b[2], ws.h3, 256, 0, nullptr,
-                                     nullptr, nullptr, nullptr, st);
+                                     nullptr, nullptr, st);
     if (rc) return rc;
     // fusion.9 + ReLU + fusion.12 + sigmoid + 4y+1 -> scores
     // (classifier head, gn_model_set_classifier_head: fusion.12 is 128 -> 5 and softmax replaces sigmoid; d_scores is [n][5])
-    rc = run_linear<128, 4, kScore>(m, n, ws.h3, 256, 256, m->f_wk[3], 128, m->f_b[3], nullptr, 0, 0, nullptr,
+    rc = run_linear<128, 4, kScore>(m, n, ws.h3, 256, 256, m->f_wk[3], 128, m->f_b[3], nullptr, 0, 0,
                                     m->n_cls > 1 ? m->cls_w : m->f12_w, m->n_cls > 1 ? m->cls_b : m->f12_b, d_scores, st,
-                                    0, m->n_cls > 1 ? m->n_cls : 1);
+                                    m->n_cls > 1 ? m->n_cls : 1, sink);
     GN_STAGE_MARK(m, 6, st);
     return rc;
 }

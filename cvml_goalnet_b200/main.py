@@ -24,7 +24,7 @@ class MatchScorer:
     """
 
     def __init__(self, model: U.AVM, n_frames: int, H: int, W: int, samples: int, sr: int, skip_frames: int,
-                 full_n_frames: int, bin_length: int = 30, device=None, h2d_chunks: int = 16):
+                 full_n_frames: int, bin_length: int = 30, device=None, h2d_chunks: int = 16, copy_streams: int = 2):
         self.dev = U._device(device)
         self.model = model
         self.n, self.H, self.W = int(n_frames), int(H), int(W)
@@ -36,15 +36,21 @@ class MatchScorer:
         self.vis = torch.empty((self.n, 3, model.S, model.S), dtype=torch.float32, device=d)
         self.aud = torch.empty((self.n, 30, self.B), dtype=torch.float32, device=d)
         self.scores = torch.empty((self.n, 1), dtype=torch.float32, device=d)
-        self.copy_stream = torch.cuda.Stream(device=d)
+        self.features = None
+        # two copy streams: alternate chunks, so that one chunk's descriptor/setup latency hides under the other's transfer
+        self.copy_streams = [torch.cuda.Stream(device=d) for _ in range(max(1, int(copy_streams)))]
         self.h2d_chunks = max(1, min(int(h2d_chunks), self.n))
         self.scores_host = torch.empty((self.n, 1), dtype=torch.float32).pin_memory()
         self.ind_host = torch.empty(self.n_raw, dtype=torch.uint8).pin_memory()
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._sel = {}            # clip count -> SelectBuffers (allocated on first use, reused by every later step)
+        self._counts = {}         # annotators -> int64 (2U+1,) device counts
+        self._chunk_events = [torch.cuda.Event() for _ in range(self.h2d_chunks)]
         # audio samples each H2D chunk must bring along (slot boundaries of utils.py:322-330); consecutive
         # chunks may share a boundary sample, so each range starts where the previous one ended at the latest
         bounds = np.linspace(0, self.n, self.h2d_chunks + 1).astype(np.int64)
+        self._bounds = [(int(bounds[i]), int(bounds[i + 1])) for i in range(self.h2d_chunks)]
         self._audio_ranges, prev_hi = [], 0
         for i in range(self.h2d_chunks):
             lo, hi = U.audio_slot_sample_range(self.samples, self.n, int(bounds[i]), int(bounds[i + 1]))
@@ -52,17 +58,36 @@ class MatchScorer:
             self._audio_ranges.append((lo, max(hi, lo)))
             prev_hi = max(hi, prev_hi)
 
+    def _select(self, change_points):
+        """Selection + indicator on self.scores with preallocated buffers (no allocation / library fill per step)."""
+        n_clips = int(change_points.shape[0]) if hasattr(change_points, "shape") else len(change_points)
+        bufs = self._sel.get(n_clips)
+        if bufs is None:
+            bufs = self._sel[n_clips] = U.SelectBuffers(n_clips, self.n_raw, 1, self.dev)
+        _, ind = U.postprocess_array(self.scores, self.skip, self.n_raw, change_points, device=self.dev,
+                                     return_device=True, bufs=bufs)
+        return ind
+
+    def _fscore(self, gd_dev, ind):
+        users = int(gd_dev.shape[0])
+        c = self._counts.get(users)
+        if c is None:
+            c = self._counts[users] = torch.empty(2 * users + 1, dtype=torch.int64, device=self.dev)
+        counts = U.fscore_counts_device(gd_dev, ind, device=self.dev, out=c).cpu().tolist()      # D2H read: synchronises
+        return U.fscore_from_counts(counts[:users], counts[users:2 * users], counts[2 * users])
+
     # ---- device-resident path (inputs already in HBM) ------------------------------------------------
-    def score_device(self, frames_dev, audio_dev, change_points_dev_or_host, gd_dev=None):
+    def score_device(self, frames_dev, audio_dev, change_points_dev_or_host, gd_dev=None, return_features: bool = False):
         """frames_dev uint8 (N,H,W,3) and audio_dev float32 (samples,) on the device.  Returns
-        (scores (N,1) cuda, indicator (N_raw,) uint8 cuda, (f_avg, f_max) | None)."""
+        (scores (N,1) cuda, indicator (N_raw,) uint8 cuda, (f_avg, f_max) | None); with `return_features` the
+        (N,512) VisBl features of utils.py:191-192 are left in `self.features`."""
         U.extract_condensed_frame_tensor_array(frames_dev, self.model.S, out=self.vis)
         if self.model.audio_included:
             U.extract_audio_features_array(audio_dev, self.sr, self.n, self.B, out=self.aud)
-        self.model(self.aud, self.vis, out=self.scores)
-        _, ind = U.postprocess_array(self.scores, self.skip, self.n_raw, change_points_dev_or_host, device=self.dev,
-                                     return_device=True)
-        fs = U.get_fscore(gd_dev, ind, device=self.dev) if gd_dev is not None else None
+        self.model(self.aud, self.vis, out=self.scores, return_features=return_features)
+        self.features = self.model.last_visual_features if return_features else None
+        ind = self._select(change_points_dev_or_host)
+        fs = self._fscore(gd_dev, ind) if gd_dev is not None else None
         return self.scores, ind, fs
 
     # ---- host path: what a user of the reference calls with decoded arrays ----------------------------
@@ -76,36 +101,262 @@ class MatchScorer:
         assert tuple(fh.shape) == (self.n, self.H, self.W, 3), "E: Inconsistency in data loader definition"
         assert ah.numel() == self.samples, "E: Inconsistency in data loader definition"
         main = torch.cuda.current_stream(d)
-        cs = self.copy_stream
-        cs.wait_stream(main)                       # previous step's readers of the staging buffers are done
+        for cs in self.copy_streams:
+            cs.wait_stream(main)                   # previous step's readers of the staging buffers are done
         ah = ah.reshape(-1)
-        bounds = np.linspace(0, self.n, self.h2d_chunks + 1).astype(np.int64)
-        events = []
-        with torch.cuda.stream(cs):
-            for i in range(self.h2d_chunks):
-                a, b = int(bounds[i]), int(bounds[i + 1])
+        for i, (a, b) in enumerate(self._bounds):
+            cs = self.copy_streams[i % len(self.copy_streams)]
+            with torch.cuda.stream(cs):
                 if self.model.audio_included:
                     lo, hi = self._audio_ranges[i]
                     self.audio_dev[lo:hi].copy_(ah[lo:hi], non_blocking=True)
                 self.frames_dev[a:b].copy_(fh[a:b], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(cs)
-                events.append((a, b, ev))
+                self._chunk_events[i].record(cs)
         # chunk i is preprocessed and scored while chunk i+1 is still crossing PCIe
-        for a, b, ev in events:
-            main.wait_event(ev)
+        for i, (a, b) in enumerate(self._bounds):
+            main.wait_event(self._chunk_events[i])
             if self.model.audio_included:
                 U.extract_audio_features_array(self.audio_dev, self.sr, self.n, self.B, out=self.aud, slots=(a, b))
             U.extract_condensed_frame_tensor_array(self.frames_dev[a:b], self.model.S, out=self.vis[a:b])
             self.model(self.aud[a:b], self.vis[a:b], out=self.scores[a:b])
-        _, ind = U.postprocess_array(self.scores, self.skip, self.n_raw, change_points, device=d, return_device=True)
+        ind = self._select(change_points)
         self.scores_host.copy_(self.scores, non_blocking=True)
         self.ind_host.copy_(ind, non_blocking=True)
-        fs = U.get_fscore(gd, ind, device=d) if gd is not None else None     # synchronises (reads the counts)
+        fs = self._fscore(U._to_dev(gd, torch.uint8, d), ind) if gd is not None else None     # synchronises (reads the counts)
         main.synchronize()
         self.h2d_bytes = fh.numel() + ah.numel() * 4
         self.d2h_bytes = self.scores_host.numel() * 4 + self.ind_host.numel()
         return self.scores_host.numpy(), self.ind_host.numpy(), fs
+
+
+class ShardedBatchScorer:
+    """BASELINE config 3: a batch of `n_matches` matches of one shape scored on all ranks of a process group with the
+    FRAMES of every match sharded (rank r holds frames [a_r, b_r) = `distributed.shard_bounds(n, P)[r]` of each match
+    and the audio samples of those frame slots).
+
+    One step = (1) each rank preprocesses / extracts MFCCs / runs the AVM forward over its (match, local frame) rows in
+    big chunks; (2) the scores reach every rank -- by default straight from the last GEMM's epilogue into each peer's
+    (M, n) score matrix through NVLink-mapped pointers (`exchange="peer"`: symmetric memory + one cross-rank barrier,
+    no collective launch), or with an NCCL all-gather + layout kernel (`exchange="nccl"`); (3) selection is sequential
+    per match (utils.py:466-510), so MATCHES are distributed over ranks (match m belongs to rank m % P) and a rank runs
+    its matches' knapsacks as ONE batched DP launch (a thread-block cluster per match); (4) the uint8 indicators
+    (and F-score counts) of all matches are all-gathered.  The reference scores a whole video in one forward
+    (main.py:95,331) and its selection needs every frame's score (utils.py:627-631), which is what makes (2) the
+    path's one real exchange step.  With a one-rank group the same code runs without any exchange.
+    """
+
+    def __init__(self, model: U.AVM, n_matches: int, n_frames: int, H: int, W: int, samples: int, sr: int,
+                 skip_frames: int, full_n_frames: int, max_clips: int, n_users: int = 0, bin_length: int = 30,
+                 device=None, group=None, exchange: str = "peer", chunk_frames: int = 21600):
+        import torch.distributed as dist
+        from . import distributed as D
+        self.dev = U._device(device)
+        self.model, self.group = model, group
+        self.rank, self.world = D._world(group)
+        self.M, self.n, self.H, self.W = int(n_matches), int(n_frames), int(H), int(W)
+        self.samples, self.sr, self.skip, self.n_raw, self.B = int(samples), int(sr), int(skip_frames), \
+            int(full_n_frames), int(bin_length)
+        self.a, self.b = D.shard_bounds(self.n, self.world)[self.rank]
+        self.n_loc = self.b - self.a
+        self.per = -(-self.n // self.world)
+        assert self.world == 1 or self.n == self.per * self.world, \
+            "E: frames per match must divide evenly over the ranks"      # (ragged shards: pad the match)
+        d = self.dev
+        # slot bounds of this rank's frames inside its local audio buffer [M][samples_loc] (utils.py:322-330 on the
+        # whole track, shifted to the shard)
+        st, ln = U.dsp.segment_bounds(self.samples, self.n)
+        self.sample_lo = int(st[self.a]) if self.n_loc else 0
+        self.sample_hi = int((st[self.a:self.b] + ln[self.a:self.b]).max()) if self.n_loc else 0
+        self.samples_loc = self.sample_hi - self.sample_lo
+        starts = np.concatenate([m * self.samples_loc + (st[self.a:self.b] - self.sample_lo) for m in range(self.M)]) \
+            if self.M and self.n_loc else np.zeros(0, np.int64)
+        self.plan = U.segment_plan_from_bounds(starts, np.tile(ln[self.a:self.b], self.M), self.B, d)
+        self.rows = self.M * self.n_loc
+        self.chunk = max(1, min(int(chunk_frames), max(self.rows, 1)))
+        self.vis = torch.empty((self.chunk, 3, model.S, model.S), dtype=torch.float32, device=d)
+        self.aud = torch.empty((self.chunk, 30, self.B), dtype=torch.float32, device=d)
+        self.exchange = exchange if self.world > 1 else "none"
+        self.hdl = None
+        if self.exchange == "peer":
+            import torch.distributed._symmetric_memory as symm
+            self.scores_all = symm.empty((self.M, self.n), dtype=torch.float32, device=d)
+            g = group if group is not None else dist.group.WORLD
+            self.hdl = symm.rendezvous(self.scores_all, g.group_name)
+            self.dst_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        else:
+            self.scores_all = torch.empty((self.M, self.n), dtype=torch.float32, device=d)
+            self.dst_ptrs = [self.scores_all.data_ptr()]
+            if self.exchange == "nccl":
+                self.scores_loc = torch.empty((self.M, self.per), dtype=torch.float32, device=d)
+                self.gathered = torch.empty((self.world, self.M, self.per), dtype=torch.float32, device=d)
+                self.dst_ptrs = [self.scores_loc.data_ptr()]
+        self.mine = D.matches_of_rank(self.M, self.rank, self.world)
+        self.mo = -(-self.M // self.world)                     # matches per rank, padded
+        self.sel = U.SelectBuffers(int(max_clips), self.n_raw, max(self.mo, 1), d)
+        self.users = int(n_users)
+        self.counts_own = torch.zeros((max(self.mo, 1), 2 * self.users + 1), dtype=torch.int64, device=d)
+        if self.world > 1:
+            self.ind_all = torch.empty((self.world, self.mo, self.n_raw), dtype=torch.uint8, device=d)
+            self.counts_all = torch.empty((self.world, self.mo, 2 * self.users + 1), dtype=torch.int64, device=d)
+        else:
+            self.ind_all = self.sel.ind.view(1, max(self.mo, 1), self.n_raw)
+            self.counts_all = self.counts_own.view(1, max(self.mo, 1), 2 * self.users + 1)
+        self.counts_host = torch.empty(tuple(self.counts_all.shape), dtype=torch.int64).pin_memory()
+        self._cps = None
+        # host path staging: a ring of chunk-sized device buffers filled by two copy streams
+        self._stage = None
+
+    # -- clips --------------------------------------------------------------------------------------------
+    def set_change_points(self, cps_list):
+        """KTS change points (n_clips_m, 2) of ALL matches (a rank only uses its own, m % P == rank).  Uploaded once;
+        scoring steps reuse them."""
+        assert len(cps_list) == self.M, "E: Inconsistency in data loader definition"
+        self._cps = {}
+        self.sel.values.zero_()
+        self.sel.lengths.zero_()
+        for m in self.mine:
+            c = cps_list[m]
+            c = c if torch.is_tensor(c) else torch.from_numpy(np.ascontiguousarray(np.asarray(c).reshape(-1, 2).astype(np.int32)))
+            assert c.shape[0] <= self.sel.n_clips, "E: more clips than max_clips"
+            self._cps[m] = c.to(self.dev, dtype=torch.int32).contiguous()
+
+    # -- steps ---------------------------------------------------------------------------------------------
+    def _forward_rows(self, frames_flat, audio_flat, r0, r1):
+        """rows [r0, r1) of the rank's (match, local frame) list: preprocess -> MFCC -> forward with scattered scores."""
+        k = r1 - r0
+        vis, aud = self.vis[:k], self.aud[:k]
+        U.extract_condensed_frame_tensor_array(frames_flat[r0:r1], self.model.S, out=vis)
+        if self.model.audio_included:
+            U.extract_audio_features_array(audio_flat, self.sr, self.rows, self.B, out=self._aud_rows(r0, r1), slots=(r0, r1),
+                                           plan=self.plan)
+        if self.exchange == "nccl":
+            self.model.forward_scatter(aud, vis, self.dst_ptrs, self.n_loc, self.per, 0, r0)
+        else:
+            self.model.forward_scatter(aud, vis, self.dst_ptrs, self.n_loc, self.n, self.a, r0)
+
+    def _aud_rows(self, r0, r1):
+        # extract_audio_features_array writes rows a..b-1 of `out`: give it a view whose row r0 is self.aud[0]
+        return _OffsetRows(self.aud, r0)
+
+    def _exchange_and_select(self, gd_list):
+        import torch.distributed as dist
+        lib, h = U._lib.load(), U._h(self.dev)
+        if self.exchange == "peer":
+            self.hdl.barrier()                                   # every rank's stores have landed in every score matrix
+        elif self.exchange == "nccl":
+            dist.all_gather_into_tensor(self.gathered, self.scores_loc, group=self.group)
+            with torch.cuda.device(self.dev):
+                U._lib.check(lib.gn_unshard_rows(h, U._ptr(self.gathered), self.world, self.M, self.per, self.n,
+                                                 U._ptr(self.scores_all), U._stream(self.dev)), "gn_unshard_rows")
+        nb = len(self.mine)
+        if nb:
+            assert self._cps is not None, "E: set_change_points() first"
+            with torch.cuda.device(self.dev):
+                for k, m in enumerate(self.mine):
+                    c = self._cps[m]
+                    U._lib.check(lib.gn_clip_information(h, U._ptr(self.scores_all[m]), self.n, self.skip, self.n_raw, U._ptr(c),
+                                                         int(c.shape[0]), U._ptr(self.sel.values[k]), U._ptr(self.sel.lengths[k]),
+                                                         U._stream(self.dev)), "gn_clip_information")
+            U._knapsack_device(self.sel.values, self.sel.lengths, self.sel.n_clips, self.sel.cap, 0, nb, self.dev, self.sel)
+            with torch.cuda.device(self.dev):
+                for k, m in enumerate(self.mine):
+                    c = self._cps[m]
+                    U._lib.check(lib.gn_summary_indicator(h, U._ptr(c), U._ptr(self.sel.sel[k]), int(c.shape[0]), self.n_raw,
+                                                          U._ptr(self.sel.ind[k]), U._stream(self.dev)), "gn_summary_indicator")
+                    if gd_list is not None:
+                        U.fscore_counts_device(gd_list[m], self.sel.ind[k], device=self.dev, out=self.counts_own[k])
+        if self.world > 1:
+            # also the write-after-read fence of the score matrices: a rank's part of this gather is sent after its
+            # selection has read them, so nobody's next forward can overwrite scores a peer still needs
+            dist.all_gather_into_tensor(self.ind_all, self.sel.ind[:self.mo], group=self.group)
+            if gd_list is not None:
+                dist.all_gather_into_tensor(self.counts_all, self.counts_own[:self.mo], group=self.group)
+        if gd_list is not None:
+            self.counts_host.copy_(self.counts_all, non_blocking=True)
+
+    def score_device(self, frames_loc, audio_loc, gd_list=None):
+        """frames_loc uint8 (M, n_loc, H, W, 3), audio_loc float32 (M, samples_loc) on this rank's device.
+        Returns (scores (M, n) cuda, indicators view(m) -> (N_raw,) uint8 cuda via `indicator(m)`); F-score counts of
+        all matches are in `self.counts_host` (pinned) after the stream is synchronised."""
+        assert tuple(frames_loc.shape) == (self.M, self.n_loc, self.H, self.W, 3), "E: Inconsistency in data loader definition"
+        ff = frames_loc.view(self.rows, self.H, self.W, 3)
+        af = audio_loc.reshape(-1)
+        assert af.numel() == self.M * self.samples_loc, "E: Inconsistency in data loader definition"
+        for r0 in range(0, self.rows, self.chunk):
+            self._forward_rows(ff, af, r0, min(r0 + self.chunk, self.rows))
+        self._exchange_and_select(gd_list)
+        return self.scores_all
+
+    def score_host(self, frames_host, audio_host, gd_list=None, copy_streams: int = 2, ring: int = 3):
+        """The same step from PINNED HOST shards (uint8 (M, n_loc, H, W, 3), float32 (M, samples_loc)): chunks cross
+        PCIe on two copy streams into a small ring of device staging buffers while earlier chunks are scored."""
+        d = self.dev
+        fh = frames_host.view(self.rows, self.H, self.W, 3)
+        ah = audio_host.view(self.M, self.samples_loc)
+        if self._stage is None:
+            self._stage = dict(
+                frames=[torch.empty((self.chunk, self.H, self.W, 3), dtype=torch.uint8, device=d) for _ in range(ring)],
+                audio=torch.empty(self.M * self.samples_loc, dtype=torch.float32, device=d),
+                streams=[torch.cuda.Stream(device=d) for _ in range(copy_streams)],
+                filled=[torch.cuda.Event() for _ in range(ring)], freed=[torch.cuda.Event() for _ in range(ring)])
+        sg = self._stage
+        main = torch.cuda.current_stream(d)
+        for cs in sg["streams"]:
+            cs.wait_stream(main)
+        af = sg["audio"]
+        st, ln = self.plan["start_host"], self.plan["length_host"]
+        chunks = [(r0, min(r0 + self.chunk, self.rows)) for r0 in range(0, self.rows, self.chunk)]
+        for i, (r0, r1) in enumerate(chunks):
+            slot = i % ring
+            cs = sg["streams"][i % len(sg["streams"])]
+            with torch.cuda.stream(cs):
+                if i >= ring:
+                    cs.wait_event(sg["freed"][slot])               # the forward that read this slot has finished
+                if self.model.audio_included:
+                    lo, hi = int(st[r0]), int((st[r0:r1] + ln[r0:r1]).max())
+                    af[lo:hi].copy_(ah.view(-1)[lo:hi], non_blocking=True)
+                sg["frames"][slot][: r1 - r0].copy_(fh[r0:r1], non_blocking=True)
+                sg["filled"][slot].record(cs)
+            # enqueue the compute of the PREVIOUS chunk after this copy has been issued, so both queues stay fed
+            main.wait_event(sg["filled"][slot])
+            k = r1 - r0
+            vis, aud = self.vis[:k], self.aud[:k]
+            U.extract_condensed_frame_tensor_array(sg["frames"][slot][:k], self.model.S, out=vis)
+            sg["freed"][slot].record(main)
+            if self.model.audio_included:
+                U.extract_audio_features_array(af, self.sr, self.rows, self.B, out=_OffsetRows(self.aud, r0), slots=(r0, r1),
+                                               plan=self.plan)
+            if self.exchange == "nccl":
+                self.model.forward_scatter(aud, vis, self.dst_ptrs, self.n_loc, self.per, 0, r0)
+            else:
+                self.model.forward_scatter(aud, vis, self.dst_ptrs, self.n_loc, self.n, self.a, r0)
+        self._exchange_and_select(gd_list)
+        self.h2d_bytes = fh.numel() + ah.numel() * 4
+        return self.scores_all
+
+    def indicator(self, m: int):
+        """uint8 (N_raw,) summary indicator of match m (valid on every rank after a step)."""
+        return self.ind_all[m % self.world, m // self.world]
+
+    def counts(self, m: int):
+        """F-score counts (overlap[U], gsum[U], ssum) of match m from the last step with ground truth (synchronise first)."""
+        c = self.counts_host[m % self.world, m // self.world].tolist()
+        return c[:self.users], c[self.users:2 * self.users], c[2 * self.users]
+
+
+class _OffsetRows:
+    """`out[a:]` view helper: behaves like a tensor whose row a is `base[0]` (extract_audio_features_array slices
+    `out[a:]` to find where slot a goes; the chunk buffer only holds the rows of the current chunk)."""
+
+    def __init__(self, base, row0):
+        self.base, self.row0 = base, row0
+
+    def __getitem__(self, sl):
+        assert isinstance(sl, slice) and sl.stop is None and sl.step is None
+        return self.base[sl.start - self.row0:]
+
+    def cpu(self):  # pragma: no cover - as_numpy is never used with this helper
+        raise AssertionError("E: chunk view")
 
 
 def infer_arrays(frames_u8, y, sr, skip_frames, full_n_frames, change_points, model: U.AVM, full_frames=None,

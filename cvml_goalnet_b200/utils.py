@@ -133,7 +133,7 @@ def _segment_plan(n_samples: int, n_frames: int, B: int, dev_index: int):
     start, length = dsp.segment_bounds(n_samples, n_frames)
     q = 1 + length // dsp.HOP
     assert n_frames == 0 or int(q.min()) >= 4, "E: Shape mismatch"   # interp1d(kind='cubic') needs >= 4 columns
-    assert n_frames == 0 or int(q.max()) <= 64, "E: audio segment too long for one frame slot (q > 64)"
+    assert n_frames == 0 or int(q.max()) <= dsp.MAX_Q, "E: audio segment too long for one frame slot"
     offs, mats, table = np.zeros(n_frames, np.int32), [], {}
     pos = 0
     for qq in np.unique(q):
@@ -156,18 +156,45 @@ def audio_slot_sample_range(n_samples: int, n_frames: int, a: int, b: int):
     return int(start[a]), int((start[a:b] + length[a:b]).max())
 
 
+def segment_plan_from_bounds(start, length, B: int, device=None):
+    """Device tables for `extract_audio_features_array(..., plan=...)` from explicit slot bounds (sample index of the
+    first sample and sample count of every frame slot inside the buffer that will be passed as `y`).  Used where the
+    buffer is not one whole track: e.g. a rank's shard of several matches laid end to end."""
+    dev = _device(device)
+    start = np.ascontiguousarray(start, dtype=np.int64)
+    length = np.ascontiguousarray(length, dtype=np.int32)
+    n_frames = int(start.shape[0])
+    q = 1 + length // dsp.HOP
+    assert n_frames == 0 or int(q.min()) >= 4, "E: Shape mismatch"
+    assert n_frames == 0 or int(q.max()) <= dsp.MAX_Q, "E: audio segment too long for one frame slot"
+    table, mats, pos = {}, [], 0
+    for qq in np.unique(q):
+        table[int(qq)] = pos
+        mats.append(dsp.cubic_resample_matrix(int(qq), B).reshape(-1))
+        pos += mats[-1].size
+    offs = np.asarray([table[int(v)] for v in q], dtype=np.int32) if n_frames else np.zeros(0, np.int32)
+    wcat = np.concatenate(mats) if mats else np.zeros(1, np.float32)
+    return dict(start=torch.from_numpy(start).to(dev), length=torch.from_numpy(length).to(dev),
+                w_offset=torch.from_numpy(offs).to(dev), w=torch.from_numpy(wcat).to(dev),
+                max_q=int(q.max()) if n_frames else 4, start_host=start, length_host=length)
+
+
 def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, device=None, out=None,
-                                 as_numpy: bool = False, slots=None):
+                                 as_numpy: bool = False, slots=None, plan=None):
     """Array twin of `extract_audio_features` (utils.py:313-349) with `(y, sr)` replacing librosa.load:
     float32 (N,30,B) MFCC features, cubic-resampled to B columns per frame slot.
-    `slots=(a, b)` computes only the frame slots a..b-1 (rows a..b-1 of `out`), for chunked pipelines."""
+    `slots=(a, b)` computes only the frame slots a..b-1 (rows a..b-1 of `out`), for chunked pipelines.
+    `plan` (from `segment_plan_from_bounds`) replaces the slot bounds utils.py:322-330 derives from len(y)."""
     dev = _device(device if device is not None else (y.device if torch.is_tensor(y) and y.is_cuda else None))
     yd = _to_dev(y, torch.float32, dev).reshape(-1)
     B = int(bin_length)
     if int(n_frames) == 0:
         out = torch.empty((0, dsp.N_MFCC, B), dtype=torch.float32, device=dev)
         return out.cpu().numpy() if as_numpy else out
-    plan = _segment_plan(int(yd.numel()), int(n_frames), B, dev.index)
+    if plan is None:
+        plan = _segment_plan(int(yd.numel()), int(n_frames), B, dev.index)
+    else:
+        assert int(plan["start"].shape[0]) == int(n_frames), "E: Shape mismatch"
     tab = _audio_tables(int(sr), dev.index)
     if out is None:
         out = torch.empty((n_frames, dsp.N_MFCC, B), dtype=torch.float32, device=dev)
@@ -342,6 +369,32 @@ class AVM(nn.Module):
         self.last_visual_features = feats
         return scores
 
+    def forward_scatter(self, audio_input, visual_input, dst_ptrs, rows_per_match: int, dst_match_stride: int,
+                        dst_offset: int, row0: int = 0):
+        """Forward whose scores are stored straight into the (M, n) score matrix of every rank from the last GEMM's
+        epilogue (`gn_avm_forward_scatter`; BASELINE config 3 / SURVEY 8e).  `dst_ptrs`: device addresses of the
+        destination matrices (peer-mapped for other GPUs).  Inputs must already be float32 CUDA tensors."""
+        dev = visual_input.device
+        n = int(visual_input.shape[0])
+        assert visual_input.is_cuda and visual_input.dtype == torch.float32 and visual_input.is_contiguous() and \
+            tuple(visual_input.shape[1:]) == (3, self.S, self.S), "E: Invalid shape for visual input"
+        if self.audio_included:
+            assert audio_input.is_cuda and audio_input.dtype == torch.float32 and audio_input.is_contiguous() and \
+                tuple(audio_input.shape) == (n, 30, self.B), "E: Inconsistency in data loader definition"
+        assert 1 <= len(dst_ptrs) <= 16, "E: too many score destinations"
+        mptr = self._model(dev)
+        ws, need = self._ws(dev, mptr, n)
+        sink = _lib.gn_score_sink()
+        sink.n_dst = len(dst_ptrs)
+        for i, p in enumerate(dst_ptrs):
+            sink.dst[i] = int(p)
+        sink.rows_per_match, sink.dst_match_stride = int(rows_per_match), int(dst_match_stride)
+        sink.dst_offset, sink.row0 = int(dst_offset), int(row0)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().gn_avm_forward_scatter(mptr, _ptr(visual_input), _ptr(audio_input if self.audio_included else None),
+                                                          n, C.byref(sink), _ptr(ws), need, _stream(dev)),
+                       "gn_avm_forward_scatter")
+
     STAGES = ("visbl_block1", "audbl", "conv2_block", "conv3_block", "linear5", "fusion_mlp")
 
     def set_timing(self, enable: bool, device=None):
@@ -418,10 +471,11 @@ def expand_array(arr, expansion_rate, length):
     return expanded_arr + [expanded_arr[-1]] * (length - len(expanded_arr))
 
 
-def _clip_information_device(scores_dev, n, skip_frames, n_raw, clips_dev, dev):
+def _clip_information_device(scores_dev, n, skip_frames, n_raw, clips_dev, dev, values=None, lengths=None):
     n_clips = clips_dev.shape[0]
-    values = torch.empty(n_clips, dtype=torch.int32, device=dev)
-    lengths = torch.empty(n_clips, dtype=torch.int32, device=dev)
+    if values is None:
+        values = torch.empty(n_clips, dtype=torch.int32, device=dev)
+        lengths = torch.empty(n_clips, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         _lib.check(_lib.load().gn_clip_information(_h(dev), _ptr(scores_dev), n, skip_frames, n_raw, _ptr(clips_dev),
                                                    n_clips, _ptr(values), _ptr(lengths), _stream(dev)),
@@ -445,16 +499,42 @@ def get_clip_information(clip_intervals, importances, device=None):
     return v.cpu().tolist(), l.cpu().tolist(), clip_intervals
 
 
-def _knapsack_device(values_dev, weights_dev, n_items, cap_cols, cap_rem, batch, dev):
+class SelectBuffers:
+    """Preallocated device buffers of the selection stage for `batch` problems of up to `n_clips` clips over `n_raw`
+    raw frames: with these, `postprocess_array` allocates nothing and launches no library fill inside a scoring step.
+    Problems with fewer clips are padded with (value 0, weight 0) items, which the reference's table never selects
+    (utils.py:487-492: K[i][w] = max(0 + K[i-1][w], K[i-1][w]); the backtrack at :500 skips them)."""
+
+    def __init__(self, n_clips: int, n_raw: int, batch: int = 1, device=None):
+        dev = _device(device)
+        self.dev, self.n_clips, self.n_raw, self.batch = dev, int(n_clips), int(n_raw), int(batch)
+        nc = max(self.n_clips, 1)
+        self.values = torch.zeros((batch, nc), dtype=torch.int32, device=dev)
+        self.lengths = torch.zeros((batch, nc), dtype=torch.int32, device=dev)
+        self.sel = torch.zeros((batch, nc), dtype=torch.uint8, device=dev)
+        self.best = torch.zeros(batch, dtype=torch.int32, device=dev)
+        self.cap = int(0.15 * self.n_raw)                                          # utils.py:629
+        self.ws_bytes = int(_lib.load().gn_knapsack_workspace_bytes(self.n_clips, self.cap)) * batch
+        self.ws = torch.empty(max(self.ws_bytes, 256), dtype=torch.uint8, device=dev)
+        self.ind = torch.zeros((batch, self.n_raw), dtype=torch.uint8, device=dev)
+        self.counts = None
+
+
+def _knapsack_device(values_dev, weights_dev, n_items, cap_cols, cap_rem, batch, dev, bufs: "SelectBuffers" = None):
     lib = _lib.load()
     need = int(lib.gn_knapsack_workspace_bytes(n_items, cap_cols)) * batch
-    ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
-    sel = torch.empty((batch, max(n_items, 1)), dtype=torch.uint8, device=dev)
-    best = torch.empty(batch, dtype=torch.int32, device=dev)
+    if bufs is not None:
+        assert bufs.ws_bytes >= need and bufs.sel.shape[0] >= batch and bufs.sel.shape[1] == max(n_items, 1), \
+            "E: selection buffers do not fit this problem"
+        ws, sel, best = bufs.ws, bufs.sel, bufs.best
+    else:
+        ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        sel = torch.empty((batch, max(n_items, 1)), dtype=torch.uint8, device=dev)
+        best = torch.empty(batch, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         _lib.check(lib.gn_knapsack(_h(dev), _ptr(values_dev), _ptr(weights_dev), n_items, cap_cols, cap_rem, batch,
                                    _ptr(sel), _ptr(best), _ptr(ws), need, _stream(dev)), "gn_knapsack")
-    return sel[:, :n_items], best
+    return sel[:batch, :n_items], best
 
 
 def _scale_problem(weights, capacity, scale_factor):
@@ -491,11 +571,12 @@ def knapsack(values, weights, capacity, scale_factor=5, device=None):
 
 
 def postprocess_array(batch_importances, skip_frames, full_n_frames, change_points, full_frames=None, device=None,
-                      return_device: bool = False):
+                      return_device: bool = False, bufs: SelectBuffers = None):
     """HDF5-free `postprocess` (utils.py:608-613,627-643): scores (N,1)|(N,) -> (summarized_video|None,
     uint8 indicator over the raw frames).  `change_points` is the (n_clips,2) inclusive KTS array the
     reference reads from the h5 file (utils.py:625).  Everything from the rounding on is integer work on
-    the GPU and bit-exact with the reference."""
+    the GPU and bit-exact with the reference.  `bufs` (a `SelectBuffers` for exactly this clip count and
+    N_raw) makes the call allocation-free; the returned indicator is then `bufs.ind[0]`."""
     dev = _device(device if device is not None else
                   (batch_importances.device if torch.is_tensor(batch_importances) and batch_importances.is_cuda else None))
     sc = _to_dev(batch_importances, torch.float32, dev)
@@ -510,18 +591,25 @@ def postprocess_array(batch_importances, skip_frames, full_n_frames, change_poin
         cps = _to_dev(np.asarray(change_points).reshape(-1, 2).astype(np.int32), torch.int32, dev)
     n_clips = int(cps.shape[0])
     lib = _lib.load()
-    ind = torch.zeros(n_raw, dtype=torch.uint8, device=dev)
-    sel = torch.zeros(max(n_clips, 1), dtype=torch.uint8, device=dev)
+    if bufs is not None:
+        assert bufs.n_clips == n_clips and bufs.n_raw == n_raw and bufs.dev == dev, "E: selection buffers do not fit"
+        ind, sel = bufs.ind[0], bufs.sel[0]
+    else:
+        ind = torch.zeros(n_raw, dtype=torch.uint8, device=dev)
+        sel = torch.zeros(max(n_clips, 1), dtype=torch.uint8, device=dev)
     if n_clips > 0 and n > 0:
-        values, lengths = _clip_information_device(sc, n, int(skip_frames), n_raw, cps, dev)
+        values, lengths = _clip_information_device(sc, n, int(skip_frames), n_raw, cps, dev,
+                                                   bufs.values[0] if bufs else None, bufs.lengths[0] if bufs else None)
         # weights = int(len * 5), capacity = int(int(0.15 * N_raw) * 5) (utils.py:478-479, 629): both are
         # multiples of 5, so the table compresses exactly to int(0.15 * N_raw) + 1 columns (unit = 5).
         cap = int(0.15 * n_raw)
-        sel2, _ = _knapsack_device(values, lengths, n_clips, cap, 0, 1, dev)
+        sel2, _ = _knapsack_device(values, lengths, n_clips, cap, 0, 1, dev, bufs)
         sel = sel2[0].contiguous()
         with torch.cuda.device(dev):
             _lib.check(lib.gn_summary_indicator(_h(dev), _ptr(cps), _ptr(sel), n_clips, n_raw, _ptr(ind), _stream(dev)),
                        "gn_summary_indicator")
+    elif bufs is not None:
+        ind.zero_()
     summarized_video = None
     if full_frames is not None:
         cps_host = cps.cpu().numpy()
@@ -599,25 +687,31 @@ def postprocess(video_id, h5_file_path, mat_file_path, batch_importances, skip_f
 # --------------------------------------------------------------------------------------------------
 # (a10) evaluation  -- reference utils.py:552-604
 # --------------------------------------------------------------------------------------------------
-def fscore_counts(gd_summary_indices, predicted_summary_indices, device=None):
-    """Device counts behind utils.py:571-573: (overlap[u], sum(G_u)[u], sum(S)) as Python ints."""
+def fscore_counts_device(gd_summary_indices, predicted_summary_indices, device=None, out=None):
+    """Device counts behind utils.py:571-573 as an int64 (2U+1,) CUDA tensor {overlap[u].., sum(G_u).., sum(S)};
+    no host synchronisation (`out` = a preallocated tensor to fill)."""
     dev = _device(device)
     G = _to_dev(gd_summary_indices, torch.uint8, dev)
     S = _to_dev(predicted_summary_indices, torch.uint8, dev)
     assert G.dim() == 2 and G.shape[1] == S.shape[0]
     n_users, n_raw = int(G.shape[0]), int(G.shape[1])
-    counts = torch.empty(2 * n_users + 1, dtype=torch.int64, device=dev)
+    counts = out if out is not None else torch.empty(2 * n_users + 1, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
         _lib.check(_lib.load().gn_fscore_counts(_h(dev), _ptr(S), _ptr(G), n_users, n_raw, _ptr(counts), _stream(dev)),
                    "gn_fscore_counts")
+    return counts
+
+
+def fscore_counts(gd_summary_indices, predicted_summary_indices, device=None):
+    """Device counts behind utils.py:571-573: (overlap[u], sum(G_u)[u], sum(S)) as Python ints."""
+    counts = fscore_counts_device(gd_summary_indices, predicted_summary_indices, device)
+    n_users = (counts.numel() - 1) // 2
     c = counts.cpu().tolist()
     return c[:n_users], c[n_users:2 * n_users], c[2 * n_users]
 
 
-def get_fscore(gd_summary_indices, predicted_summary_indices, device=None):
-    """utils.py:552-580: (mean, max) F-score over the annotators.  Counts are integer sums on the GPU
-    (NumPy-1 semantics, SURVEY.md quirk Q6); the float64 tail follows the reference's operation order."""
-    overlap, gsum, ssum = fscore_counts(gd_summary_indices, predicted_summary_indices, device)
+def fscore_from_counts(overlap, gsum, ssum):
+    """The float64 tail of utils.py:571-580 on integer counts: (mean, max) F-score over the annotators."""
     f_scores = []
     for ov, sg in zip(overlap, gsum):
         precision = ov / ssum if ssum != 0 else 0
@@ -627,6 +721,13 @@ def get_fscore(gd_summary_indices, predicted_summary_indices, device=None):
     for f in f_scores:          # plain left-to-right adds, like sum() over np.float64 scalars (utils.py:580)
         acc = acc + f
     return acc / len(f_scores), max(f_scores)
+
+
+def get_fscore(gd_summary_indices, predicted_summary_indices, device=None):
+    """utils.py:552-580: (mean, max) F-score over the annotators.  Counts are integer sums on the GPU
+    (NumPy-1 semantics, SURVEY.md quirk Q6); the float64 tail follows the reference's operation order."""
+    overlap, gsum, ssum = fscore_counts(gd_summary_indices, predicted_summary_indices, device)
+    return fscore_from_counts(overlap, gsum, ssum)
 
 
 def postprocess_and_get_fscores_array(batch_predictions, full_n_batch_frames, gd_summarized_video_frame_indices,

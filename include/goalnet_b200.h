@@ -126,9 +126,41 @@ int64_t gn_avm_workspace_bytes(const gn_model* m, int64_t n);
 /* d_visual : float32 [n][3][S][S] (the tensor `extract_condensed_frame_tensor` returns)
  * d_audio  : float32 [n][30][B]  (ignored / may be NULL when the model has no audio branch)
  * d_scores : float32 [n]  (the reference's (n,1) output of utils.py:270, values in [1,5])
- * d_visual_features : optional bf16-rounded float32 [n][512] copy of VisBl's output, or NULL. */
+ * d_visual_features : optional float32 [n][512] copy of VisBl's output (the TF32-rounded values the fusion network
+ *            consumes), or NULL.
+ * A frame's score does not depend on the batch it is scored in (no data-dependent work split anywhere in the
+ * forward): chunked, sharded and whole-video calls give bit-identical scores. */
 int gn_avm_forward(gn_model* m, const float* d_visual, const float* d_audio, int64_t n, float* d_scores,
                    float* d_visual_features, void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* Frame-sharded scoring of a batch of matches on several GPUs (BASELINE config 3; SURVEY 8e: "scores written straight
+ * into peers from the fusion-MLP epilogue").  The reference scores a whole video in one forward (main.py:95,331) and
+ * its selection needs every frame's score (utils.py:627-631); here rank r scores frames [a_r, b_r) of each of M
+ * matches, and the LAST GEMM'S EPILOGUE stores each score into the (M, n) score matrix of EVERY rank through
+ * peer-mapped pointers (NVLink stores; no separate all-gather launch -- only a cross-rank barrier before the
+ * selection reads).  Local row i (rows are [match][local frame], rows_per_match = b_r - a_r) of a forward that
+ * starts at local row `row0` goes to element
+ *     ((row0 + i) / rows_per_match) * dst_match_stride + dst_offset + (row0 + i) % rows_per_match
+ * of each dst[p], p < n_dst.  dst_match_stride = n (frames per match), dst_offset = a_r. */
+typedef struct gn_score_sink {
+    int32_t n_dst;              /* 1..GN_MAX_PEERS destinations (all ranks incl. this one) */
+    int32_t reserved;
+    float* dst[16];             /* device pointers, peer-mapped where they belong to another GPU */
+    int64_t rows_per_match;
+    int64_t dst_match_stride;
+    int64_t dst_offset;
+    int64_t row0;
+} gn_score_sink;
+#define GN_MAX_PEERS 16
+/* gn_avm_forward with the scores scattered through `sink` instead of written to a local [n] vector (regression head
+ * only). */
+int gn_avm_forward_scatter(gn_model* m, const float* d_visual, const float* d_audio, int64_t n,
+                           const gn_score_sink* sink, void* d_workspace, int64_t workspace_bytes, void* stream);
+/* The same exchange after a library all-gather (the NCCL variant of the path above): d_src float32
+ * [world][n_matches][per] (rank-major, what all_gather_into_tensor of [n_matches][per] rows produces, per =
+ * ceil(n / world) padded rows) -> d_dst float32 [n_matches][n], d_dst[m][r * per + j] = d_src[r][m][j]. */
+int gn_unshard_rows(gn_handle* h, const float* d_src, int world, int64_t n_matches, int64_t per, int64_t n,
+                    float* d_dst, void* stream);
 
 /* Per-stage device timing of gn_avm_forward (CUDA events recorded on the forward's stream).
  * GN_AVM_STAGES stages: 0 VisBl block 1 (conv1), 1 AudBl, 2 conv2 block, 3 conv3 block, 4 linear5,
