@@ -1,19 +1,29 @@
 #!/usr/bin/env python
 """Benchmark of the per-frame scoring path (BASELINE.json metric: frames/s scored end to end).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload ...]
 
-A "step" is one pass of the hot path over one synthetic 90-minute match (BASELINE config 2: 10 800
-frames of 224x224 BGR uint8 at 2 fps + 16 kHz mono audio, skip_frames 15 -> 162 000 raw frames):
-frame preprocessing -> MFCC features -> AVM forward -> clip statistics -> 0/1 knapsack -> summary
-indicator -> F-score counts against 20 synthetic annotators.  With N > 1 every rank scores its own match
-(weak scaling) and the per-frame scores are all-gathered over NCCL before the selection step.
+The hot path over one synthetic 90-minute match (10 800 frames of 224x224 BGR uint8 at 2 fps + 16 kHz mono audio,
+skip_frames 15 -> 162 000 raw frames): frame preprocessing -> MFCC features -> AVM forward -> clip statistics ->
+0/1 knapsack -> summary indicator -> F-score counts against 20 synthetic annotators.
+
+N = 1  : BASELINE config 2 -- one step = one match on one GPU.
+N > 1  : BASELINE config 3 -- one step = a batch of 64 such matches with the FRAMES of every match sharded over the
+         N ranks: local frames -> local scores -> the scores reach every rank (stored straight into each peer's score
+         matrix from the last GEMM's epilogue over NVLink, then one cross-rank barrier; `--exchange nccl` uses an NCCL
+         all-gather instead) -> per-match knapsacks distributed over the ranks and run as one batched DP launch per
+         rank -> indicators and F-score counts all-gathered.  Strong scaling: the same 691 200 frames at every N.
+         After the timed region every rank re-scores its own matches on its GPU alone and the gathered scores and
+         indicators must equal that single-GPU result bit for bit ("multi_gpu_parity").
+         `--workload replicas` is the old arm (one independent match per rank, no exchange).
 
 `value`  : device-resident inputs (already in HBM when the timed region starts).
-`e2e`    : the same step through the public host API (MatchScorer.score_match) with pinned HOST buffers,
-           host->device copies and the device->host read of scores + indicator inside the timed region.
-`--impl reference` times the CPU oracle port of the reference (oracle/goalnet_oracle.py; the reference is
-pure Python and cannot travel to the GPU box) on a bounded sample of the same workload.
+`e2e`    : the same step through the public host API (MatchScorer.score_match / ShardedBatchScorer.score_host) with
+           pinned HOST buffers: host->device copies and the device->host read of the results inside the timed region;
+           the bare pinned-H2D rate of the same bytes on the same ranks is measured beside it (`h2d_ceiling_gbs`).
+`--impl reference` / `cpu_baseline`: BASELINE config 1 (2-minute clip, 240 frames, 3 600 raw frames) IN FULL on the host
+           cores, per stage, with the reference's own AVM / expand_array / get_clip_information / knapsack (the literal
+           pure-Python table) / get_fscore when its utils.py has been staged under oracle/_ref/ by build().
 """
 from __future__ import annotations
 
@@ -36,7 +46,6 @@ UNIT = "frames/s"
 FRAMES, H, W = 10800, 224, 224
 SR, SPF, SKIP = 16000, 8000, 15
 N_USERS = 20
-CPU_SAMPLE_FRAMES = 120
 
 
 def load_peaks():
@@ -168,106 +177,29 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU oracle leg (cpu_baseline and --impl reference)
+# shared timing harness (barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks)
 # ------------------------------------------------------------------------------------------------
-def cpu_sample_inputs(n):
-    from cvml_goalnet_b200 import synthetic as syn
-    frames = syn.make_frames(n, H, W, seed=0)
-    y = syn.make_audio(n, SPF, SR, seed=0)
-    cps = syn.make_change_points(n * SKIP, seed=0)
-    return syn.make_weights(seed=0), frames, y, cps
+class Harness:
+    def __init__(self, dev, world, local_rank):
+        self.dev, self.world, self.local_rank = dev, world, local_rank
 
-
-def cpu_step(O, w, frames, y, cps, gd):
-    n = len(frames)
-    return O.score_and_summarize(w, frames, y, SR, SKIP, n * SKIP, cps, gd=gd)
-
-
-def run_cpu(steps, warmup):
-    """Oracle port of the reference path on all host threads; returns (frames/s, ms/step, cores, sample)."""
-    from oracle import goalnet_oracle as O
-    from cvml_goalnet_b200 import synthetic as syn
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    n = CPU_SAMPLE_FRAMES
-    w, frames, y, cps = cpu_sample_inputs(n)
-    gd = np.stack([O.postprocess_array(a[:, None], SKIP, n * SKIP, cps)[1]
-                   for a in syn.make_annotator_importances(n * SKIP, N_USERS, seed=0)])
-    for _ in range(warmup):
-        cpu_step(O, w, frames, y, cps, gd)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        cpu_step(O, w, frames, y, cps, gd)
-    dt = time.perf_counter() - t0
-    sample = (f"{n} frames ({n // 2} s of the config-2 match: {H}x{W} source, 2 fps, 16 kHz audio, "
-              f"{n * SKIP} raw frames) per step, {steps} steps; torch threads {torch.get_num_threads()}")
-    return n * steps / dt, 1e3 * dt / steps, cores, sample
-
-
-def reference_arm(args, rank):
-    if rank != 0:
-        return
-    steps = max(1, min(args.steps, 20))
-    warm = max(0, min(args.warmup, 3))
-    v, ms, cores, sample = run_cpu(steps, warm)
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "config-2 90-min match, bounded CPU sample", "frames_per_step": CPU_SAMPLE_FRAMES,
-                       "source": f"{H}x{W}", "fps": 2, "audio_hz": SR, "skip_frames": SKIP},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
-
-
-# ------------------------------------------------------------------------------------------------
-# native arm
-# ------------------------------------------------------------------------------------------------
-def native_arm(args, rank, world, local_rank):
-    import torch.distributed as dist
-    from cvml_goalnet_b200 import _lib, synthetic as syn, utils as U
-    from cvml_goalnet_b200.main import MatchScorer
-
-    peaks = load_peaks()
-    dev = torch.device("cuda", local_rank)
-    torch.cuda.set_device(dev)
-    n, n_raw = args.frames, args.frames * SKIP
-    samples = n * SPF
-
-    model = U.AVM(True)
-    model.load_state_dict(syn.make_weights(seed=0))
-    frames = device_frames(n, H, W, seed=rank, dev=dev)
-    audio = device_audio(n, SPF, SR, seed=rank, dev=dev)
-    cps_host = syn.make_change_points(n_raw, seed=rank)
-    cps = torch.from_numpy(cps_host).to(dev)
-    # ground-truth summaries: one postprocess per annotator (reference utils.py:102-118)
-    ann = syn.make_annotator_importances(n_raw, N_USERS, seed=rank)
-    gd = U.gt_summaries_array(np.stack(ann), SKIP, n_raw, cps, device=dev, return_device=True)
-    scorer = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev,
-                         h2d_chunks=int(os.environ.get("GN_H2D_CHUNKS", "16")))
-    gathered = torch.empty((world, n, 1), dtype=torch.float32, device=dev) if world > 1 else None
-
-    def step_device():
-        scores, ind, fs = scorer.score_device(frames, audio, cps, None)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, scores)       # exchange step: every rank sees all scores
-        counts = U.fscore_counts(gd, ind, device=dev)            # D2H read of the step's result
-        return counts
-
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
+    def barrier(self):
+        torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            import torch.distributed as dist
             dist.barrier()
-        torch.cuda.synchronize(dev)
+        torch.cuda.synchronize(self.dev)
 
-    def timed(fn, steps, warmup, profile=False):
+    def timed(self, fn, steps, warmup, profile=False):
+        """W untimed warm-up steps, then EXACTLY `steps` steps between two barrier+synchronize pairs.  Returns
+        (ms for all steps, max over ranks; launches of this library's kernels on this rank; clock record)."""
+        from cvml_goalnet_b200 import _lib
         for _ in range(warmup):
             fn()
-        barrier()
-        sampler = ClockSampler(local_rank)
+        self.barrier()
+        sampler = ClockSampler(self.local_rank)
         sampler.start()
-        l0 = _lib.launch_count(dev.index)
+        l0 = _lib.launch_count(self.dev.index)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         if profile:
             torch.cuda.profiler.start()      # `ncu --profile-from-start off` captures exactly the timed steps
@@ -275,36 +207,268 @@ def native_arm(args, rank, world, local_rank):
         for _ in range(steps):
             fn()
         e1.record()
-        barrier()
+        self.barrier()
         if profile:
             torch.cuda.profiler.stop()
         ms = e0.elapsed_time(e1)
-        launches = _lib.launch_count(dev.index) - l0
+        launches = _lib.launch_count(self.dev.index) - l0
         clocks = sampler.stop()
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if self.world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], device=self.dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
         return ms, launches, clocks
 
-    ms, launches, clocks = timed(step_device, args.steps, args.warmup, profile=True)
+
+def h2d_ceiling(h: Harness, host_buf, dev_buf, chunks=16, reps=3):
+    """Bare pinned host -> device copy of `host_buf` (uint8, pinned) in `chunks` cudaMemcpyAsync calls, on every rank at
+    the same time: GB/s of this rank (best of `reps`) and the list over ranks.  Nothing else runs: this is the ceiling
+    the e2e leg is measured against."""
+    n = host_buf.numel()
+    b = np.linspace(0, n, chunks + 1).astype(np.int64)
+    hv, dv = host_buf.view(-1), dev_buf.view(-1)
+    best = None
+    for _ in range(reps + 1):
+        h.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(chunks):
+            dv[int(b[i]):int(b[i + 1])].copy_(hv[int(b[i]):int(b[i + 1])], non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize(h.dev)
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+    gbs = n / (best * 1e-3) / 1e9
+    per_rank = [gbs]
+    if h.world > 1:
+        import torch.distributed as dist
+        t = torch.zeros(h.world, device=h.dev, dtype=torch.float64)
+        t[dist.get_rank()] = gbs
+        dist.all_reduce(t)
+        per_rank = [float(x) for x in t.tolist()]
+    return gbs, per_rank
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU leg (cpu_baseline and --impl reference): BASELINE config 1 in full, per stage
+# ------------------------------------------------------------------------------------------------
+CFG1_FRAMES = 240           # 2 minutes at 2 fps; 3 600 raw frames (30 fps source, skip_frames 15)
+
+
+def _cpu_reference_module():
+    """The reference's own utils module (unmodified; /root/reference or the copy build() staged under oracle/_ref/), or
+    None when neither exists -- the CPU leg then times the oracle's restatement of the same functions (kind "port")."""
+    try:
+        from oracle import ref_import
+        if ref_import.reference_available():
+            return ref_import.import_reference_utils()
+    except Exception as e:  # noqa: BLE001
+        print(f"[bench] reference module not importable ({e!r}); timing the oracle port", file=sys.stderr)
+    return None
+
+
+def run_cpu(steps, warmup):
+    """BASELINE config 1 (240 frames of 224x224 + 16 kHz audio -> scores -> keyshots -> F-score) in full on all host
+    threads, per stage.  Returns a dict with frames/s, ms per step, per-stage ms, what ran, and the config-2 knapsack
+    cost (measured vectorised + the literal table extrapolated from the config-1 literal run)."""
+    import warnings
+    from oracle import goalnet_oracle as O
+    from cvml_goalnet_b200 import synthetic as syn
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n, n_raw = CFG1_FRAMES, CFG1_FRAMES * SKIP
+    frames = syn.make_frames(n, H, W, seed=0)
+    y = syn.make_audio(n, SPF, SR, seed=0)
+    cps = syn.make_change_points(n_raw, seed=0)
+    w = syn.make_weights(seed=0, score_gain=syn.SPREAD_GAIN)
+    R = _cpu_reference_module()
+    kind = "reference" if R is not None else "port"
+    # ground truth (setup, untimed): one postprocess per annotator, utils.py:102-118
+    gd = np.stack([O.postprocess_array(a[:, None], SKIP, n_raw, cps)[1]
+                   for a in syn.make_annotator_importances(n_raw, N_USERS, seed=0)])
+    clip_intervals = [[int(a), int(b)] for a, b in cps]
+
+    model = None
+    if R is not None:
+        model = R.AVM(audio_included=True)
+        model.eval()                                        # parity is defined in eval mode (SURVEY quirk Q4)
+        with torch.no_grad():
+            model(torch.zeros((1, 30, 30)), torch.zeros((1, 3, 40, 40)))      # materialise the Lazy* layers
+        model.load_state_dict({k: torch.as_tensor(np.asarray(v)) for k, v in w.items()})
+
+    def forward(aud, vis):
+        if model is not None:
+            with torch.no_grad():                           # main.py:94,108: evaluation runs under no_grad
+                return model(torch.as_tensor(aud, dtype=torch.float32), torch.as_tensor(vis, dtype=torch.float32))
+        return O.avm_forward(w, aud, vis)
+
+    def select(scores):
+        if R is None:
+            return O.postprocess_array(scores, SKIP, n_raw, cps, fast=False)[1]     # the literal pure-Python table
+        # utils.py:608-613,627-641 with the reference's own functions; change points passed in instead of the HDF5 reads
+        imp = torch.round(scores[:, 0]).type(torch.int8).tolist()
+        imp = R.expand_array(arr=imp, expansion_rate=SKIP, length=n_raw)
+        vals, lens, ci = R.get_clip_information(clip_intervals=clip_intervals, importances=imp)
+        sel = R.knapsack(values=vals, weights=lens, capacity=int(0.15 * n_raw))
+        ind = np.zeros(shape=(n_raw,), dtype=np.uint8)
+        for c in (ci[j] for j in sel):
+            for f in range(c[0], c[1] + 1):
+                ind[f] = 1
+        return ind
+
+    def fscore(ind):
+        if R is None:
+            return O.get_fscore(gd, ind)
+        with warnings.catch_warnings(), np.errstate(all="ignore"):
+            warnings.simplefilter("ignore")               # NumPy-2 uint8 wrap-around of utils.py:572-573 (quirk Q6): timing only
+            return R.get_fscore(gd, ind)
+
+    centred = [False]
+    stages = {"preprocess": 0.0, "audio_features": 0.0, "avm_forward": 0.0, "select": 0.0, "fscore": 0.0}
+
+    def step(record):
+        nonlocal w
+        t0 = time.perf_counter()
+        vis = O.extract_condensed_frame_tensor_array(frames, 40, literal=True)         # utils.py:284-285,292 through cv2
+        t1 = time.perf_counter()
+        aud = O.extract_audio_features_array(y, SR, n, 30).astype(np.float32)          # librosa restated + literal interp1d
+        t2 = time.perf_counter()
+        scores = forward(aud, vis)
+        t3 = time.perf_counter()
+        if not centred[0]:                                   # once, untimed steps only: scores straddle a rounding boundary
+            w = syn.center_scores(w, np.asarray(scores))
+            if model is not None:
+                model.load_state_dict({k: torch.as_tensor(np.asarray(v)) for k, v in w.items()})
+            centred[0] = True
+        ind = select(scores if torch.is_tensor(scores) else torch.as_tensor(np.asarray(scores)))
+        t4 = time.perf_counter()
+        fscore(ind)
+        t5 = time.perf_counter()
+        if record:
+            for k, dt in zip(stages, (t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4)):
+                stages[k] += 1e3 * dt / steps
+
+    for _ in range(max(warmup, 1)):
+        step(False)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step(True)
+    dt = time.perf_counter() - t0
+
+    # config-2 selection cost on the host: 984 clips x (5 * 24 300 + 1) columns
+    n2_raw = FRAMES * SKIP
+    cps2 = syn.make_change_points(n2_raw, seed=0)
+    sc2 = syn.make_scores(FRAMES, seed=0)
+    imp2 = O.expand_array(O.round_importances(sc2), SKIP, n2_raw)
+    v2, l2, _ = O.get_clip_information([[int(a), int(b)] for a, b in cps2], imp2)
+    t0 = time.perf_counter()
+    O.knapsack_rows(v2, l2, int(0.15 * n2_raw))
+    vec_s = time.perf_counter() - t0
+    cells1 = len(cps) * (5 * int(0.15 * n_raw) + 1)
+    cells2 = len(cps2) * (5 * int(0.15 * n2_raw) + 1)
+    literal_us_per_cell = stages["select"] * 1e3 / cells1
+    what = ("reference's own AVM (eval, no_grad), expand_array, get_clip_information, knapsack (pure-Python table), "
+            "get_fscore from oracle/_ref/utils.py" if R is not None else
+            "oracle restatement of the same functions (reference utils.py not staged on this box)")
+    sample = (f"BASELINE config 1 in full: {n} frames {H}x{W} at 2 fps + {SR} Hz audio, {n_raw} raw frames, {len(cps)} clips, "
+              f"{N_USERS} annotators, {steps} steps, {torch.get_num_threads()} torch threads; {what}; preprocess = the literal "
+              f"utils.py:284-285 expression through cv2 on decoded frames; MFCC = librosa 0.10 restated in NumPy (librosa is "
+              f"not in the image) + the literal interp1d loop")
+    return {"value": n * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": cores, "kind": kind, "sample": sample,
+            "stages_ms": {k: round(v, 3) for k, v in stages.items()}, "frames_per_step": n,
+            "config2_knapsack": {"cells": cells2, "vectorised_numpy_s": round(vec_s, 3),
+                                 "literal_python_s_extrapolated": round(literal_us_per_cell * cells2 * 1e-6, 1),
+                                 "literal_us_per_cell_measured_on_config1": round(literal_us_per_cell, 4)}}
+
+
+def reference_arm(args, rank):
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 10))
+    warm = max(1, min(args.warmup, 2))
+    r = run_cpu(steps, warm)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "config-1: synthetic 2-min 224x224 clip at 2 fps + 16 kHz mono audio through the reference "
+                                   "scoring path on CPU, in full (a 2-minute sample of the config-2 match)",
+                       "frames_per_step": r["frames_per_step"], "source": f"{H}x{W}", "fps": 2, "audio_hz": SR,
+                       "skip_frames": SKIP},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+                             "stages_ms": r["stages_ms"], "config2_knapsack": r["config2_knapsack"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# native arm, N = 1: BASELINE config 2
+# ------------------------------------------------------------------------------------------------
+def spread_model(U, syn, run_scores):
+    """AVM with the score-spreading synthetic head: last-layer gain syn.SPREAD_GAIN and a bias centred so that the median
+    frame scores 3.5 on THIS workload (`run_scores(model)` returns the scores the un-centred model gives), which makes
+    the keyshot knapsack a real instance instead of one long tie (every default-init score rounds to 3)."""
+    w = syn.make_weights(seed=0, score_gain=syn.SPREAD_GAIN)
+    model = U.AVM(True)
+    model.load_state_dict(w)
+    s0 = run_scores(model)
+    w = syn.center_scores(w, s0.float().cpu().numpy())
+    model.load_state_dict(w)
+    return model
+
+
+def native_arm(args, rank, world, local_rank):
+    from cvml_goalnet_b200 import synthetic as syn, utils as U
+    from cvml_goalnet_b200.main import MatchScorer, ShardedBatchScorer
+
+    peaks = load_peaks()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    hz = Harness(dev, world, local_rank)
+    n, n_raw = args.frames, args.frames * SKIP
+    samples = n * SPF
+
+    frames = device_frames(n, H, W, seed=rank, dev=dev)
+    audio = device_audio(n, SPF, SR, seed=rank, dev=dev)
+    cps_host = syn.make_change_points(n_raw, seed=rank)
+    cps = torch.from_numpy(cps_host).to(dev)
+    # ground-truth summaries: one postprocess per annotator (reference utils.py:102-118)
+    ann = syn.make_annotator_importances(n_raw, N_USERS, seed=rank)
+    gd = U.gt_summaries_array(np.stack(ann), SKIP, n_raw, cps, device=dev, return_device=True)
+    holder = {}
+
+    def first_scores(model):
+        holder["scorer"] = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev,
+                                       h2d_chunks=int(os.environ.get("GN_H2D_CHUNKS", "16")))
+        return holder["scorer"].score_device(frames, audio, cps, None)[0]
+
+    model = spread_model(U, syn, first_scores)
+    scorer = holder["scorer"]
+
+    def step_device():
+        return scorer.score_device(frames, audio, cps, gd)[2]       # (f_avg, f_max): D2H read of the step's result
+
+    ms, launches, clocks = hz.timed(step_device, args.steps, args.warmup, profile=True)
     value = world * n * args.steps / (ms * 1e-3)
+    scores_now = scorer.scores.float().cpu().numpy().reshape(-1)
+    ind_now = scorer._select(cps)
+    classes, counts_cls = np.unique(np.round(scores_now), return_counts=True)
 
     # ---- e2e: pinned host inputs, H2D + D2H inside the timed region ------------------------------
     frames_host = torch.empty(frames.shape, dtype=torch.uint8).pin_memory()
     audio_host = torch.empty(audio.shape, dtype=torch.float32).pin_memory()
     frames_host.copy_(frames)
     audio_host.copy_(audio)
-    gd_host_dev = gd
 
     def step_host():
-        scores, ind, fs = scorer.score_match(frames_host, audio_host, cps, gd_host_dev)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, scorer.scores)
-        return fs
+        return scorer.score_match(frames_host, audio_host, cps, gd)[2]
 
-    ms_e2e, _, _ = timed(step_host, args.steps, args.warmup)
+    ms_e2e, _, _ = hz.timed(step_host, args.steps, args.warmup)
     e2e_value = world * n * args.steps / (ms_e2e * 1e-3)
+    ceil_gbs, ceil_ranks = h2d_ceiling(hz, frames_host, scorer.frames_dev, chunks=scorer.h2d_chunks)
+    h2d_bytes = int(scorer.h2d_bytes)
+    e2e_gbs = h2d_bytes / (ms_e2e / args.steps * 1e-3) / 1e9
 
     # ---- per-stage device time (CUDA events on the launching stream), same workload ---------------
     model.set_timing(True, dev)
@@ -318,7 +482,7 @@ def native_arm(args, rank, world, local_rank):
         ev[2].record()
         model(scorer.aud, scorer.vis, out=scorer.scores)
         ev[3].record()
-        U.postprocess_array(scorer.scores, SKIP, n_raw, cps, device=dev, return_device=True)
+        scorer._select(cps)
         ev[4].record()
         torch.cuda.synchronize(dev)
         st = model.stage_ms(dev)
@@ -327,6 +491,36 @@ def native_arm(args, rank, world, local_rank):
         for k, v in st.items():
             acc[k] = acc.get(k, 0.0) + v / args.steps
     model.set_timing(False, dev)
+
+    # ---- config-3 share: the work one rank does per step at N = 8 (8 whole matches, batched selection), on this GPU
+    # alone and without any exchange -- the strong-scaling reference point for the 8-GPU line
+    share = None
+    if n == FRAMES and not args.no_share:
+        mb = 8
+        fr8 = torch.empty((mb, n, H, W, 3), dtype=torch.uint8, device=dev)
+        au8 = torch.empty((mb, samples), dtype=torch.float32, device=dev)
+        cps8, gd8 = [], []
+        for mi in range(mb):
+            fr8[mi] = frames if mi == 0 else device_frames(n, H, W, seed=100 + mi, dev=dev)
+            au8[mi] = audio if mi == 0 else device_audio(n, SPF, SR, seed=100 + mi, dev=dev)
+            c = syn.make_change_points(n_raw, seed=rank if mi == 0 else 100 + mi)
+            cps8.append(c)
+            a8 = syn.make_annotator_importances(n_raw, N_USERS, seed=rank if mi == 0 else 100 + mi)
+            gd8.append(U.gt_summaries_array(np.stack(a8), SKIP, n_raw, c, device=dev, return_device=True))
+        bs = ShardedBatchScorer(model, mb, n, H, W, samples, SR, SKIP, n_raw, max(len(c) for c in cps8), N_USERS, device=dev)
+        bs.set_change_points(cps8)
+
+        def step_share():
+            bs.score_device(fr8, au8, gd8)
+            torch.cuda.current_stream(dev).synchronize()      # the pinned counts are the step's result
+        ms_share, l_share, _ = hz.timed(step_share, max(2, args.steps // 2), 3)
+        k_share = max(2, args.steps // 2)
+        ok = bool(torch.equal(bs.scores_all[0], scorer.scores.reshape(-1))) and bool(torch.equal(bs.indicator(0), ind_now))
+        share = {"workload": "config-3 share of one rank at N=8: 8 whole matches per step, batched selection, no exchange",
+                 "matches_per_step": mb, "ms_per_step": ms_share / k_share, "value": mb * n * k_share / (ms_share * 1e-3),
+                 "unit": UNIT, "gpu_launches_per_step": l_share / k_share,
+                 "match0_equals_single_match_path_bit_for_bit": ok}
+        del fr8, au8, bs, gd8
 
     if rank != 0:
         return
@@ -354,28 +548,179 @@ def native_arm(args, rank, world, local_rank):
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        v, cms, cores, sample = run_cpu(steps=3, warmup=1)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        r = run_cpu(steps=2, warmup=1)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+               "stages_ms": r["stages_ms"], "config2_knapsack": r["config2_knapsack"]}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "config-2: synthetic 90-min match at 2 fps + audio, end-to-end summary"
-                                   if n == FRAMES else f"reduced match of {n} frames",
+            "config": {"workload": ("config-2: synthetic 90-min match at 2 fps + audio, end-to-end summary"
+                                    if n == FRAMES else f"reduced match of {n} frames") +
+                                   ("" if world == 1 else " (replicas: one independent match per rank, no exchange)"),
                        "frames_per_match": n, "matches_per_step": world, "source": f"{H}x{W} BGR uint8",
                        "model_input": "40x40 (reference utils.py:285)", "audio": f"{SR} Hz mono, {SPF} samples/frame",
                        "skip_frames": SKIP, "raw_frames": n_raw, "clips": int(cps_host.shape[0]), "annotators": N_USERS,
-                       "parallelism": f"dp{world} (one match per rank, NCCL all-gather of scores)",
+                       "weights": f"synthetic, last-layer gain {syn.SPREAD_GAIN:g}, bias centred on the median score",
+                       "score_classes": {str(int(c)): int(k) for c, k in zip(classes, counts_cls)},
+                       "score_range": [float(scores_now.min()), float(scores_now.max())],
+                       "selected_raw_frames": int(ind_now.sum().item()),
+                       "arithmetic": "visual backbone bf16 x bf16 -> fp32 (tcgen05 kind::f16); AudBl GEMMs + fusion MLP TF32 "
+                                     "(kind::tf32); preprocess / MFCC / conv1 fp32; selection and F-score counts integer",
+                       "parallelism": f"dp{world}" + (" (replicas)" if world > 1 else ""),
                        "l2": f"inputs are {(frames.numel() + audio.numel() * 4) / 1e9:.2f} GB per step (> 126 MB L2); no flush needed"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": int(scorer.h2d_bytes), "d2h_bytes_per_step": int(scorer.d2h_bytes) + 8 * (2 * N_USERS + 1)},
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(scorer.d2h_bytes) + 8 * (2 * N_USERS + 1),
+                    "h2d_gbs_achieved": round(e2e_gbs, 2), "h2d_ceiling_gbs": round(ceil_gbs, 2),
+                    "h2d_ceiling_gbs_per_rank": [round(x, 2) for x in ceil_ranks],
+                    "frac_of_h2d_ceiling": round(e2e_gbs / ceil_gbs, 3),
+                    "h2d_ceiling_how": f"bare pinned cudaMemcpyAsync of the step's {frames_host.numel() / 1e9:.2f} GB of frames in "
+                                       f"{scorer.h2d_chunks} chunks on every rank at once, best of 3"},
             "gpu_launches": int(launches),
             "roofline": roofline, "stages_ms": stages}
+    if share is not None:
+        line["config3_share"] = share
     if cpu is not None:
         line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)
 
+
+# ------------------------------------------------------------------------------------------------
+# native arm, N > 1: BASELINE config 3 (a batch of matches, frames sharded, scores exchanged, selection distributed)
+# ------------------------------------------------------------------------------------------------
+def config3_arm(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import distributed as D, synthetic as syn, utils as U
+    from cvml_goalnet_b200.main import MatchScorer, ShardedBatchScorer
+
+    peaks = load_peaks()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    hz = Harness(dev, world, local_rank)
+    n, n_raw, M = args.frames, args.frames * SKIP, args.matches
+    samples = n * SPF
+    a, b = D.shard_bounds(n, world)[rank]
+    n_loc = b - a
+    mine = D.matches_of_rank(M, rank, world)
+
+    # every rank generates each match in full (deterministic per match seed) and keeps its frame shard
+    frames_loc = torch.empty((M, n_loc, H, W, 3), dtype=torch.uint8, device=dev)
+    audio_loc = torch.empty((M, n_loc * SPF), dtype=torch.float32, device=dev)
+    cps_all = [syn.make_change_points(n_raw, seed=1000 + m) for m in range(M)]
+    gd_list = [None] * M
+    for m in range(M):
+        full = device_frames(n, H, W, seed=1000 + m, dev=dev)
+        frames_loc[m] = full[a:b]
+        del full
+        audio_loc[m] = device_audio(n, SPF, SR, seed=1000 + m, dev=dev)[a * SPF:b * SPF]
+        if m in mine:
+            ann = syn.make_annotator_importances(n_raw, N_USERS, seed=1000 + m)
+            gd_list[m] = U.gt_summaries_array(np.stack(ann), SKIP, n_raw, cps_all[m], device=dev, return_device=True)
+    max_clips = max(len(c) for c in cps_all)
+    holder = {}
+
+    def first_scores(model):
+        bs = ShardedBatchScorer(model, M, n, H, W, samples, SR, SKIP, n_raw, max_clips, N_USERS, device=dev,
+                                exchange=args.exchange, chunk_frames=args.chunk_frames)
+        bs.set_change_points(cps_all)
+        holder["bs"] = bs
+        s = bs.score_device(frames_loc, audio_loc, None)
+        torch.cuda.synchronize(dev)
+        return s
+
+    model = spread_model(U, syn, first_scores)
+    bs = holder["bs"]
+
+    def step_device():
+        bs.score_device(frames_loc, audio_loc, gd_list)
+        torch.cuda.current_stream(dev).synchronize()          # D2H read of the step's result (F-score counts of all matches)
+
+    ms, launches, clocks = hz.timed(step_device, args.steps, args.warmup, profile=True)
+    value = M * n * args.steps / (ms * 1e-3)
+
+    # ---- multi-GPU parity, outside the timed region: this rank's matches re-scored on this GPU ALONE must give the
+    # gathered scores, indicators and F-score counts bit for bit -------------------------------------------------
+    single = MatchScorer(model, n, H, W, samples, SR, SKIP, n_raw, device=dev)
+    ok, checked = True, 0
+    scores_all = bs.scores_all.clone()
+    for m in mine:
+        full = device_frames(n, H, W, seed=1000 + m, dev=dev)
+        au = device_audio(n, SPF, SR, seed=1000 + m, dev=dev)
+        s1, i1, _ = single.score_device(full, au, cps_all[m], None)
+        c1 = U.fscore_counts(gd_list[m], i1, device=dev)
+        ok = ok and bool(torch.equal(s1.reshape(-1), scores_all[m])) and bool(torch.equal(i1, bs.indicator(m))) and \
+            (tuple(c1[0]), tuple(c1[1]), c1[2]) == tuple((tuple(x) if isinstance(x, list) else x) for x in bs.counts(m))
+        checked += 1
+        del full, au
+    # a foreign match too (the gathered row of a match this rank did not select): scores must still be identical everywhere
+    t = torch.tensor([1.0 if ok else 0.0, float(checked)], device=dev, dtype=torch.float64)
+    digest = scores_all.double().sum().reshape(1)
+    dlist = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(dlist, digest)
+    same_everywhere = all(bool(torch.equal(dlist[0], d)) for d in dlist)
+    dist.all_reduce(t[:1], op=dist.ReduceOp.MIN)
+    dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+    parity = "ok" if (t[0].item() == 1.0 and same_everywhere and int(t[1].item()) == M) else "FAILED"
+    s_host = scores_all.float().cpu().numpy().reshape(-1)
+    classes, counts_cls = np.unique(np.round(s_host), return_counts=True)
+    del single
+
+    # ---- e2e: pinned host shards of a smaller batch (bounded pinned memory), H2D + D2H inside the timed region ----
+    Me = min(M, args.e2e_matches)
+    be = ShardedBatchScorer(model, Me, n, H, W, samples, SR, SKIP, n_raw, max_clips, N_USERS, device=dev,
+                            exchange=args.exchange, chunk_frames=min(args.chunk_frames, 5400))
+    be.set_change_points(cps_all[:Me])
+    # ground truth of the e2e batch's matches this rank owns (ownership is by match index: the same as in the big batch)
+    gd_e = [gd_list[m] if (m % world == rank) else None for m in range(Me)]
+    fh = torch.empty((Me, n_loc, H, W, 3), dtype=torch.uint8).pin_memory()
+    ah = torch.empty((Me, n_loc * SPF), dtype=torch.float32).pin_memory()
+    fh.copy_(frames_loc[:Me])
+    ah.copy_(audio_loc[:Me])
+
+    def step_host():
+        be.score_host(fh, ah, gd_e)
+        torch.cuda.current_stream(dev).synchronize()
+
+    e2e_steps = max(2, args.steps // 2)
+    ms_e2e, _, _ = hz.timed(step_host, e2e_steps, 2)
+    e2e_value = Me * n * e2e_steps / (ms_e2e * 1e-3)
+    e2e_ok = bool(torch.equal(be.scores_all, scores_all[:Me]))
+    stage = torch.empty(fh.numel(), dtype=torch.uint8, device=dev)
+    ceil_gbs, ceil_ranks = h2d_ceiling(hz, fh, stage, chunks=16)
+    del stage
+    h2d_bytes = int(fh.numel() + ah.numel() * 4)
+    e2e_gbs = h2d_bytes / (ms_e2e / e2e_steps * 1e-3) / 1e9
+    if rank != 0:
+        return
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic", "multi_gpu_parity": parity,
+            "config": {"workload": f"config-3: batch of {M} synthetic 90-min matches, frames sharded across {world} B200 with score "
+                                   f"exchange ({'stores into every peer from the fusion epilogue + barrier' if args.exchange == 'peer' else 'NCCL all-gather'}), "
+                                   "per-match knapsacks distributed over ranks, indicators all-gathered",
+                       "matches_per_step": M, "frames_per_match": n, "frames_per_step": M * n, "frames_per_rank_per_step": M * n_loc,
+                       "source": f"{H}x{W} BGR uint8", "model_input": "40x40 (reference utils.py:285)",
+                       "audio": f"{SR} Hz mono, {SPF} samples/frame", "skip_frames": SKIP, "raw_frames": n_raw,
+                       "clips_max": max_clips, "annotators": N_USERS, "exchange": args.exchange,
+                       "weights": f"synthetic, last-layer gain {syn.SPREAD_GAIN:g}, bias centred on the median score",
+                       "score_classes": {str(int(c)): int(k) for c, k in zip(classes, counts_cls)},
+                       "parity_check": f"all {M} matches re-scored on one GPU each after the timed region: scores, indicators "
+                                       f"and F-score counts bit-equal; score matrix identical on all ranks",
+                       "parallelism": f"frames of every match sharded {world}-way; matches round-robin for selection",
+                       "l2": f"inputs are {(frames_loc.numel() + audio_loc.numel() * 4) / 1e9:.1f} GB per rank per step (> 126 MB L2); no flush needed"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / e2e_steps, "matches_per_step": Me,
+                    "h2d_bytes_per_step": h2d_bytes * world, "d2h_bytes_per_step": int(be.counts_host.numel() * 8),
+                    "h2d_gbs_achieved_per_rank": round(e2e_gbs, 2), "h2d_ceiling_gbs": round(float(np.min(ceil_ranks)), 2),
+                    "h2d_ceiling_gbs_per_rank": [round(x, 2) for x in ceil_ranks],
+                    "h2d_ceiling_gbs_aggregate": round(float(np.sum(ceil_ranks)), 1),
+                    "frac_of_h2d_ceiling": round(e2e_gbs / float(np.min(ceil_ranks)), 3),
+                    "scores_equal_device_path": e2e_ok,
+                    "h2d_ceiling_how": "bare pinned cudaMemcpyAsync of this rank's frame shards in 16 chunks on every rank at "
+                                       "once, best of 3 (slowest rank quoted)"},
+            "gpu_launches": int(launches)}
+    print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -405,33 +750,7 @@ def train_arm(args, rank, world, local_rank):
     x_in = torch.empty_like(x); lab_in = torch.empty_like(lab)
     loss_host = torch.empty(1, dtype=torch.float64).pin_memory()
 
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        barrier()
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        l0 = _lib.launch_count(dev.index)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        ms = e0.elapsed_time(e1)
-        launches = _lib.launch_count(dev.index) - l0
-        clocks = sampler.stop()
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, launches, clocks
+    hz = Harness(dev, world, local_rank)
 
     def step_device():
         tr.step(x, lab)
@@ -444,8 +763,8 @@ def train_arm(args, rank, world, local_rank):
         torch.cuda.current_stream(dev).synchronize()
 
     steps = max(args.steps, 20)
-    ms, launches, clocks = timed(step_device, steps, args.warmup)
-    ms_e2e, _, _ = timed(step_host, steps, args.warmup)
+    ms, launches, clocks = hz.timed(step_device, steps, args.warmup)
+    ms_e2e, _, _ = hz.timed(step_host, steps, args.warmup)
     if rank != 0:
         return
     flops = 3 * 2.0 * (640 * 512 + 512 * 512 + 512 * 256 + 256 * 128 + 128) * n      # fwd + dgrad + wgrad per rank
@@ -531,35 +850,7 @@ def stress_arm(args, rank, world, local_rank):
     model(aud, vis, out=scores)          # packs the weights
     torch.cuda.synchronize(dev)
 
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        barrier()
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        l0 = _lib.launch_count(dev.index)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.profiler.start()
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        torch.cuda.profiler.stop()
-        ms = e0.elapsed_time(e1)
-        launches = _lib.launch_count(dev.index) - l0
-        clocks = sampler.stop()
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, launches, clocks
+    hz = Harness(dev, world, local_rank)
 
     def step_device():
         U.extract_condensed_frame_tensor_array(frames, S, out=vis)
@@ -573,8 +864,8 @@ def stress_arm(args, rank, world, local_rank):
         scores_host.copy_(scores, non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()
 
-    ms, launches, clocks = timed(step_device, args.steps, args.warmup)
-    ms_e2e, _, _ = timed(step_host, max(1, args.steps // 2), 1)
+    ms, launches, clocks = hz.timed(step_device, args.steps, args.warmup, profile=True)
+    ms_e2e, _, _ = hz.timed(step_host, max(1, args.steps // 2), 1)
     e2e_steps = max(1, args.steps // 2)
 
     model.set_timing(True, dev)
@@ -649,35 +940,7 @@ def avm_train_arm(args, rank, world, local_rank):
     tr = AVMTrainer(model, max_frames=n, dropout_p=0.2, device=dev)
     loss_host = torch.empty(1, dtype=torch.float64).pin_memory()
 
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        barrier()
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        l0 = _lib.launch_count(dev.index)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.profiler.start()
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        torch.cuda.profiler.stop()
-        ms = e0.elapsed_time(e1)
-        launches = _lib.launch_count(dev.index) - l0
-        clocks = sampler.stop()
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, launches, clocks
+    hz = Harness(dev, world, local_rank)
 
     def step_device():
         tr.step(aud, vis, lab)
@@ -689,8 +952,8 @@ def avm_train_arm(args, rank, world, local_rank):
         torch.cuda.current_stream(dev).synchronize()
 
     steps = args.steps if args.steps < 10 else max(args.steps, 20)      # (a short run is for profilers)
-    ms, launches, clocks = timed(step_device, steps, args.warmup)
-    ms_e2e, _, _ = timed(step_host, steps, args.warmup)
+    ms, launches, clocks = hz.timed(step_device, steps, args.warmup)
+    ms_e2e, _, _ = hz.timed(step_host, steps, args.warmup)
     if rank != 0:
         return
     cpu = None
@@ -727,6 +990,21 @@ def avm_train_arm(args, rank, world, local_rank):
     print(json.dumps(line), flush=True)
 
 
+def h2d_arm(args, rank, world, local_rank):
+    """Bare pinned host -> device ceiling on every rank at once (what bounds the e2e legs): one config-2 match worth of
+    frames (1.63 GB) per rank in 16 chunks."""
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    hz = Harness(dev, world, local_rank)
+    nbytes = FRAMES * H * W * 3
+    hb = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    db = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    gbs, ranks = h2d_ceiling(hz, hb, db, chunks=16, reps=5)
+    if rank == 0:
+        print(json.dumps({"metric": "pinned_h2d_GBps", "n_gpus": world, "per_rank": [round(x, 2) for x in ranks],
+                          "aggregate": round(float(np.sum(ranks)), 1), "bytes_per_rank": nbytes, "chunks": 16}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -735,9 +1013,16 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--frames", type=int, default=FRAMES, help="frames per match (default: config 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="match", choices=["match", "fusion_train", "stress", "avm_train"],
-                    help="match = BASELINE config 2 (the headline, default); fusion_train = config 4 "
-                         "(fusion-network forward/backward/Adam step, 4096 rows per GPU, data parallel)")
+    ap.add_argument("--workload", default="match", choices=["match", "replicas", "fusion_train", "stress", "avm_train", "h2d"],
+                    help="match = the headline: BASELINE config 2 at N = 1, config 3 (64 matches, frames sharded, score "
+                         "exchange) at N > 1; replicas = one independent config-2 match per rank; fusion_train = config 4; "
+                         "stress = config 5; avm_train = SURVEY 8f N1; h2d = bare pinned host->device ceiling")
+    ap.add_argument("--matches", type=int, default=64, help="config 3: matches per step")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="config 3 score exchange: stores into every peer from the fusion epilogue (default) or NCCL all-gather")
+    ap.add_argument("--chunk-frames", type=int, default=21600, help="config 3: frames per forward chunk on a rank")
+    ap.add_argument("--e2e-matches", type=int, default=16, help="config 3: matches per step of the pinned-host e2e leg")
+    ap.add_argument("--no-share", action="store_true", help="N = 1: skip the config-3 share sub-measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -758,6 +1043,10 @@ def main():
             stress_arm(args, rank, world, local_rank)
         elif args.workload == "avm_train":
             avm_train_arm(args, rank, world, local_rank)
+        elif args.workload == "h2d":
+            h2d_arm(args, rank, world, local_rank)
+        elif world > 1 and args.workload == "match":
+            config3_arm(args, rank, world, local_rank)
         else:
             native_arm(args, rank, world, local_rank)
     finally:

@@ -58,6 +58,73 @@ def _worker(rank, world, port, out_dir):
         dist.destroy_process_group()
 
 
+def _batch_worker(rank, world, port, out_dir):
+    """BASELINE config 3 in small: 5 matches (not a multiple of the rank count: padded ownership), frames sharded,
+    both score-exchange variants, device and pinned-host entry points -- all against the single-GPU MatchScorer."""
+    import torch.distributed as dist
+    from cvml_goalnet_b200 import distributed as D, synthetic as syn, utils as U
+    from cvml_goalnet_b200.main import MatchScorer, ShardedBatchScorer
+    from oracle import goalnet_oracle as O
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        M, n, skip, sr, spf, Hh, Ww, users = 5, 100, 15, 16000, 8000, 48, 64, 20
+        n_raw, samples = n * skip, n * spf
+        a, b = D.shard_bounds(n, world)[rank]
+        fr = [syn.make_frames(n, Hh, Ww, seed=20 + m) for m in range(M)]
+        au = [syn.make_audio(n, spf, sr, seed=20 + m) for m in range(M)]
+        cps = [syn.make_change_points(n_raw, seed=20 + m, lo=10, hi=80) for m in range(M)]
+        gd = [np.stack([O.postprocess_array(x[:, None], skip, n_raw, cps[m])[1]
+                        for x in syn.make_annotator_importances(n_raw, users, seed=20 + m)]) for m in range(M)]
+        w = syn.make_weights(seed=0, score_gain=syn.SPREAD_GAIN)
+        model = U.AVM(True)
+        model.load_state_dict(w)
+        single = MatchScorer(model, n, Hh, Ww, samples, sr, skip, n_raw, device=dev, h2d_chunks=2)
+        ref = []
+        for m in range(M):
+            s1, i1, f1 = single.score_device(torch.from_numpy(fr[m]).to(dev), torch.from_numpy(au[m]).to(dev), cps[m],
+                                             torch.from_numpy(gd[m]).to(dev))
+            ref.append((s1.reshape(-1).clone(), i1.clone(), f1))
+        frames_loc = torch.from_numpy(np.stack([f[a:b] for f in fr])).to(dev)
+        audio_loc = torch.from_numpy(np.stack([x[a * spf:b * spf] for x in au])).to(dev)
+        gd_dev = [torch.from_numpy(g).to(dev) for g in gd]
+        oks = []
+        for exchange in ("peer", "nccl"):
+            bs = ShardedBatchScorer(model, M, n, Hh, Ww, samples, sr, skip, n_raw, max(len(c) for c in cps), users,
+                                    device=dev, exchange=exchange, chunk_frames=130)      # ragged chunks across matches
+            bs.set_change_points(cps)
+            for entry in ("device", "host", "device"):
+                if entry == "device":
+                    S = bs.score_device(frames_loc, audio_loc, gd_dev)
+                else:
+                    S = bs.score_host(frames_loc.cpu().pin_memory(), audio_loc.cpu().pin_memory(), gd_dev)
+                torch.cuda.synchronize(dev)
+                ok = True
+                for m in range(M):
+                    ok = ok and bool(torch.equal(S[m], ref[m][0])) and bool(torch.equal(bs.indicator(m), ref[m][1]))
+                    ov, gs, ss = bs.counts(m)
+                    ok = ok and U.fscore_from_counts(ov, gs, ss) == ref[m][2]
+                oks.append(ok)
+            del bs
+        np.save(os.path.join(out_dir, f"batch_{rank}.npy"), np.array(oks))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_config3_frame_sharded_batch(tmp_path):
+    """ShardedBatchScorer (frames sharded, scores stored into the peer from the fusion epilogue or NCCL-gathered,
+    selection distributed, indicators gathered) reproduces the single-GPU bits for every match on every rank."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    import torch.multiprocessing as mp
+    mp.spawn(_batch_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        assert np.load(tmp_path / f"batch_{r}.npy").all(), (r, np.load(tmp_path / f"batch_{r}.npy"))
+
+
 def test_two_gpu_sharded_paths_match_single_gpu(tmp_path):
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs two CUDA devices")
