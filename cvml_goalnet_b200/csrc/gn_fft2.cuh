@@ -1,0 +1,215 @@
+// 2048-point complex FFT for the MFCC kernel, computed by a 128-thread CTA, TWO transforms at a time in the two
+// lanes of Blackwell's packed fp32 instructions (add/sub/mul/fma .f32x2 -> FADD2 / FMUL2 / FFMA2: the only way to
+// reach the SM's full fp32 rate; a scalar FFMA issues every other cycle).
+//
+//   N = 16 x 16 x 8,  n = 128 n1 + 8 n2 + n3,  k = k1 + 16 k2 + 256 k3:
+//     W_N^(nk) = W_16^(n1 k1) . W_2048^((8 n2 + n3) k1) . W_16^(n2 k2) . W_128^(n3 k2) . W_8^(n3 k3)
+//   pass 1: thread t = 8 n2 + n3 holds x[t + 128 n1] (coalesced loads), DFT-16 over n1, twiddle W_2048^(t k1)
+//   exchange through shared memory, layout [k1][n2][n3]
+//   pass 2: thread t = 8 k1 + n3, DFT-16 over n2, twiddle W_128^(n3 k2)
+//   exchange, layout [k1][k2][n3 ^ (k2 & 7)]
+//   pass 3: thread u handles the pairs p = u and u + 128, p = 16 k1 + k2: DFT-8 over n3 -> X[k1 + 16 k2 + 256 k3],
+//           written in natural order at k ^ ((k >> 4) & 7)
+// Every shared-memory element is a float4 {re(A), re(B), im(A), im(B)} of the two transforms A and B, and every access
+// pattern above is conflict-free for 16-byte accesses (8 lanes of a quarter-warp hit 8 different 16-byte bank groups).
+//
+// Everything is __host__ __device__: tests/native/fft2_host_check.cu runs the same code for the 128 "threads"
+// sequentially on the CPU (packed operations emulated lane by lane) against a direct DFT in double.
+#pragma once
+#include <cuda_runtime.h>
+
+#if defined(__CUDACC__)
+#define GNF2_UNROLL _Pragma("unroll")
+#else
+#define GNF2_UNROLL
+#endif
+#define GNF2_HD __host__ __device__ __forceinline__
+
+namespace gnfft2 {
+
+constexpr int kN = 2048;
+constexpr int kThreads = 128;
+
+// two fp32 lanes: x = transform A, y = transform B
+struct __align__(8) V2 { float x, y; };
+
+GNF2_HD V2 mk(float a, float b) { V2 r; r.x = a; r.y = b; return r; }
+GNF2_HD V2 bc(float a) { return mk(a, a); }
+
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ unsigned long long as_u64(V2 a) { return *reinterpret_cast<unsigned long long*>(&a); }
+__device__ __forceinline__ V2 as_v2(unsigned long long a) { return *reinterpret_cast<V2*>(&a); }
+__device__ __forceinline__ V2 add2(V2 a, V2 b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(as_u64(a)), "l"(as_u64(b)));
+    return as_v2(d);
+}
+__device__ __forceinline__ V2 sub2(V2 a, V2 b) {
+    unsigned long long d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(as_u64(a)), "l"(as_u64(b)));
+    return as_v2(d);
+}
+__device__ __forceinline__ V2 mul2(V2 a, V2 b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(as_u64(a)), "l"(as_u64(b)));
+    return as_v2(d);
+}
+__device__ __forceinline__ V2 fma2(V2 a, V2 b, V2 c) {      // a * b + c
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(as_u64(a)), "l"(as_u64(b)), "l"(as_u64(c)));
+    return as_v2(d);
+}
+#else
+inline V2 add2(V2 a, V2 b) { return mk(a.x + b.x, a.y + b.y); }
+inline V2 sub2(V2 a, V2 b) { return mk(a.x - b.x, a.y - b.y); }
+inline V2 mul2(V2 a, V2 b) { return mk(a.x * b.x, a.y * b.y); }
+inline V2 fma2(V2 a, V2 b, V2 c) { return mk(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+#endif
+GNF2_HD V2 neg2(V2 a) { return mk(-a.x, -a.y); }      // sign flips: integer pipe, not the fp32 pipe
+
+// a complex value of both transforms
+struct C2 { V2 re, im; };
+GNF2_HD C2 cadd(C2 a, C2 b) { C2 r; r.re = add2(a.re, b.re); r.im = add2(a.im, b.im); return r; }
+GNF2_HD C2 csub(C2 a, C2 b) { C2 r; r.re = sub2(a.re, b.re); r.im = sub2(a.im, b.im); return r; }
+// (re + i im) * (wr + i wi), the factor given as broadcast pairs
+GNF2_HD C2 cmul(C2 a, V2 wr, V2 wi) {
+    C2 r;
+    r.re = fma2(a.re, wr, mul2(a.im, neg2(wi)));
+    r.im = fma2(a.re, wi, mul2(a.im, wr));
+    return r;
+}
+
+// forward DFT-4, natural order in and out: 16 packed adds
+GNF2_HD void dft4(C2& x0, C2& x1, C2& x2, C2& x3) {
+    const C2 a0 = cadd(x0, x2), a1 = csub(x0, x2), b0 = cadd(x1, x3), d = csub(x1, x3);
+    // b1 = d * (-i) = (d.im, -d.re)
+    x0 = cadd(a0, b0);
+    x2 = csub(a0, b0);
+    x1.re = add2(a1.re, d.im); x1.im = sub2(a1.im, d.re);
+    x3.re = sub2(a1.re, d.im); x3.im = add2(a1.im, d.re);
+}
+
+// v * W_16^m (m compile-time after unrolling); W_16 = exp(-2 pi i / 16)
+GNF2_HD C2 mul_w16(C2 v, int m) {
+    m &= 15;
+    const float c1 = 0.92387953251128675613f, s1 = 0.38268343236508977173f, h = 0.70710678118654752440f;
+    switch (m) {
+        case 0: return v;
+        case 4: { C2 r; r.re = v.im; r.im = neg2(v.re); return r; }                  // -i
+        case 8: { C2 r; r.re = neg2(v.re); r.im = neg2(v.im); return r; }            // -1
+        case 12: { C2 r; r.re = neg2(v.im); r.im = v.re; return r; }                 // +i
+        case 2: { C2 r; r.re = mul2(add2(v.re, v.im), bc(h)); r.im = mul2(sub2(v.im, v.re), bc(h)); return r; }      // (1 - i)/sqrt2
+        case 6: { C2 r; r.re = mul2(sub2(v.im, v.re), bc(h)); r.im = mul2(add2(v.re, v.im), bc(-h)); return r; }     // (-1 - i)/sqrt2
+        case 10: { C2 r; r.re = mul2(add2(v.re, v.im), bc(-h)); r.im = mul2(sub2(v.re, v.im), bc(h)); return r; }    // (-1 + i)/sqrt2
+        case 14: { C2 r; r.re = mul2(sub2(v.re, v.im), bc(h)); r.im = mul2(add2(v.re, v.im), bc(h)); return r; }     // (1 + i)/sqrt2
+        case 1: return cmul(v, bc(c1), bc(-s1));
+        case 3: return cmul(v, bc(s1), bc(-c1));
+        case 5: return cmul(v, bc(-s1), bc(-c1));
+        case 7: return cmul(v, bc(-c1), bc(-s1));
+        case 9: return cmul(v, bc(-c1), bc(s1));
+        case 11: return cmul(v, bc(-s1), bc(c1));
+        case 13: return cmul(v, bc(s1), bc(c1));
+        default: return cmul(v, bc(c1), bc(s1));   // 15
+    }
+}
+
+// In-register DFT-16 (n = 4a + b, k = c + 4d).  Output is permuted: z[4c + d] = X[c + 4d].
+GNF2_HD constexpr int perm16(int p) { return (p >> 2) + 4 * (p & 3); }      // index in z -> frequency
+GNF2_HD void dft16(C2 (&z)[16]) {
+    GNF2_UNROLL
+    for (int b = 0; b < 4; ++b) {
+        dft4(z[b], z[4 + b], z[8 + b], z[12 + b]);                           // over a: z[4c + b] = t[b][c]
+        GNF2_UNROLL
+        for (int c = 1; c < 4; ++c) z[4 * c + b] = mul_w16(z[4 * c + b], b * c);
+    }
+    GNF2_UNROLL
+    for (int c = 0; c < 4; ++c) dft4(z[4 * c], z[4 * c + 1], z[4 * c + 2], z[4 * c + 3]);   // over b: z[4c + d]
+}
+
+// In-register DFT-8, natural order in and out
+GNF2_HD void dft8(C2 (&v)[8]) {
+    C2 e0 = v[0], e1 = v[2], e2 = v[4], e3 = v[6];
+    C2 o0 = v[1], o1 = v[3], o2 = v[5], o3 = v[7];
+    dft4(e0, e1, e2, e3);
+    dft4(o0, o1, o2, o3);
+    o1 = mul_w16(o1, 2);
+    o2 = mul_w16(o2, 4);
+    o3 = mul_w16(o3, 6);
+    v[0] = cadd(e0, o0); v[4] = csub(e0, o0);
+    v[1] = cadd(e1, o1); v[5] = csub(e1, o1);
+    v[2] = cadd(e2, o2); v[6] = csub(e2, o2);
+    v[3] = cadd(e3, o3); v[7] = csub(e3, o3);
+}
+
+GNF2_HD float4 pack4(C2 v) { return make_float4(v.re.x, v.re.y, v.im.x, v.im.y); }
+GNF2_HD C2 unpack4(float4 f) { C2 v; v.re = mk(f.x, f.y); v.im = mk(f.z, f.w); return v; }
+
+// ---- tables (built on the host in double, see gn_fft2_fill_tables) --------------------------------------------
+//   tw1[(k1 - 1) * 128 + t] = {wr, wr, wi, wi} of W_2048^(t k1),  k1 = 1..15
+//   tw2[(k2 - 1) * 8 + n3]  = {wr, wr, wi, wi} of W_128^(n3 k2),  k2 = 1..15
+constexpr int kTw1 = 15 * 128, kTw2 = 15 * 8;
+
+// pass 1 for thread t: z[n1] = x[t + 128 n1] on entry; results to the exchange buffer
+GNF2_HD void pass1(int t, C2 (&z)[16], const float4* tw1, float4* xbuf) {
+    dft16(z);
+    const int n2 = t >> 3, n3 = t & 7;
+    GNF2_UNROLL
+    for (int p = 0; p < 16; ++p) {
+        const int k1 = perm16(p);
+        C2 v = z[p];
+        if (k1 != 0) {
+            const float4 w = tw1[(k1 - 1) * 128 + t];
+            v = cmul(v, mk(w.x, w.y), mk(w.z, w.w));
+        }
+        xbuf[(k1 * 16 + n2) * 8 + n3] = pack4(v);
+    }
+}
+
+// pass 2 for thread t = 8 k1 + n3
+GNF2_HD void pass2(int t, const float4* tw2, float4* xbuf_in, float4* xbuf_out) {
+    const int k1 = t >> 3, n3 = t & 7;
+    C2 z[16];
+    GNF2_UNROLL
+    for (int n2 = 0; n2 < 16; ++n2) z[n2] = unpack4(xbuf_in[(k1 * 16 + n2) * 8 + n3]);
+    dft16(z);
+    GNF2_UNROLL
+    for (int p = 0; p < 16; ++p) {
+        const int k2 = perm16(p);
+        C2 v = z[p];
+        if (k2 != 0) {
+            const float4 w = tw2[(k2 - 1) * 8 + n3];
+            v = cmul(v, mk(w.x, w.y), mk(w.z, w.w));
+        }
+        xbuf_out[(k1 * 16 + k2) * 8 + (n3 ^ (k2 & 7))] = pack4(v);
+    }
+}
+
+// where frequency k lives in the spectrum buffer
+GNF2_HD int spec_index(int k) { return k ^ ((k >> 4) & 7); }
+
+// pass 3 for thread u: pairs p = u and u + 128 (p = 16 k1 + k2); writes X[k] at spec_index(k)
+GNF2_HD void pass3(int u, const float4* xbuf_in, float4* spec) {
+    GNF2_UNROLL
+    for (int h = 0; h < 2; ++h) {
+        const int p = u + 128 * h, k1 = p >> 4, k2 = p & 15;
+        C2 v[8];
+        GNF2_UNROLL
+        for (int n3 = 0; n3 < 8; ++n3) v[n3] = unpack4(xbuf_in[p * 8 + (n3 ^ (k2 & 7))]);
+        dft8(v);
+        GNF2_UNROLL
+        for (int k3 = 0; k3 < 8; ++k3) spec[spec_index(k1 + 16 * k2 + 256 * k3)] = pack4(v[k3]);
+    }
+}
+
+// Power spectra of the two real sequences packed as z = x1 + i x2 in EACH transform, bin k (0..1024):
+//   X1 = (Z[k] + conj Z[N-k]) / 2,  X2 = (Z[k] - conj Z[N-k]) / (2i)
+// returns {|X1|^2 (A), |X1|^2 (B), |X2|^2 (A), |X2|^2 (B)}
+GNF2_HD float4 split_power(const float4* spec, int k) {
+    const C2 zk = unpack4(spec[spec_index(k)]), zn = unpack4(spec[spec_index((kN - k) & (kN - 1))]);
+    const V2 ar = add2(zk.re, zn.re), ai = sub2(zk.im, zn.im), br = add2(zk.im, zn.im), bi = sub2(zk.re, zn.re);
+    const V2 q = bc(0.25f);
+    const V2 p1 = mul2(fma2(ar, ar, mul2(ai, ai)), q), p2 = mul2(fma2(br, br, mul2(bi, bi)), q);
+    return make_float4(p1.x, p1.y, p2.x, p2.y);
+}
+
+}  // namespace gnfft2

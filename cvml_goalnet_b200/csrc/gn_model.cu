@@ -417,15 +417,16 @@ simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __n
     const __nv_bfloat16* wr = wk + (size_t)co * K;
     for (int p = pg; p < OH * OH; p += 4) {
         const int oy = p / OH, ox = p - oy * OH;
-        float acc = bias[co];
+        float acc = 0.f;
         for (int tap = 0; tap < 9; ++tap) {
             const int ky = tap / 3, kx = tap - ky * 3;
             const __nv_bfloat16* ip = fin + ((size_t)(oy + ky) * IW + ox + kx) * Cin;
             const __nv_bfloat16* wp = wr + tap * Cin;
             for (int ci = 0; ci < Cin; ++ci) acc = fmaf(__bfloat162float(ip[ci]), __bfloat162float(wp[ci]), acc);
         }
-        // the tensor-core epilogue rounds conv+ReLU to bf16 before pooling; do the same
-        cs[p * 64 + (threadIdx.x & 63)] = __bfloat162float(__float2bfloat16(fmaxf(acc, 0.f)));
+        // the tensor-core epilogue rounds the raw conv sum to bf16, pools, then adds the bias and applies ReLU (max
+        // commutes with the monotone x -> relu(x + b)); do the same
+        cs[p * 64 + (threadIdx.x & 63)] = __bfloat162float(__float2bfloat16(acc));
     }
     __syncthreads();
     const int P = OH - 2, PW = P + 2 * out_pad;
@@ -437,7 +438,7 @@ simt_conv_block(const __nv_bfloat16* __restrict__ in, int OH, int Cin, const __n
             float mx = -INFINITY;
             for (int dy = 0; dy < 3; ++dy)
                 for (int dx = 0; dx < 3; ++dx) mx = fmaxf(mx, cs[((y + dy) * OH + x + dx) * 64 + (threadIdx.x & 63)]);
-            r = fmaf(mx, sc[co], sh[co]);
+            r = fmaf(fmaxf(mx + bias[co], 0.f), sc[co], sh[co]);
         }
         if (blocked) out[gn_a3_off(f, (int64_t)p * Cout + co, (int64_t)PW * PW * Cout / 64)] = __float2bfloat16(r);
         else o[(size_t)p * Cout + co] = __float2bfloat16(r);

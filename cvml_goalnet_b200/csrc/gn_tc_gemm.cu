@@ -81,7 +81,7 @@ struct GemmArgs {
     ConvGeom g;
 };
 
-template <int MT, int BN, int STAGES, int MODE, int SUBC = BN>
+template <int MT, int BN, int STAGES, int MODE, int SUBC = BN, int STG_ROWS = MT * 128>
 struct Cfg {
     static constexpr int kABytes = MT * 128 * 128;          // MT x 128 rows x 128 B
     static constexpr int kBBytes = BN * 128;
@@ -89,7 +89,7 @@ struct Cfg {
     // conv: the pooling stage holds SUBC of the tile's BN channels at a time (the epilogue makes BN / SUBC passes);
     // a narrow stage frees shared memory for one more operand stage, which is what hides the TMA round trip
     static constexpr int kStgStride = SUBC * 2 + 16;        // padded bf16 row of the pooling stage
-    static constexpr int kStgBytes = (MODE == kConv) ? (MT * 128 * kStgStride) : 0;
+    static constexpr int kStgBytes = (MODE == kConv) ? (((STG_ROWS * kStgStride) + 127) & ~127) : 0;   // one row per conv pixel of the tile
     static constexpr int kParamBytes = 3 * kMaxN * 4;       // bias | bn_scale | bn_shift (or bias | w_last)
     static constexpr int kSmemBytes = 1024 /*align slack*/ + STAGES * kStageBytes + kStgBytes + kParamBytes + 256 /*barriers*/;
     static_assert(MT * BN <= kAccCols, "an accumulator buffer is at most 256 TMEM columns");
@@ -116,7 +116,7 @@ template <int MT, int BN, int STAGES, int MODE, int OHT, int SUBC = BN>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmArgs args) {
-    using C = Cfg<MT, BN, STAGES, MODE, SUBC>;
+    using C = Cfg<MT, BN, STAGES, MODE, SUBC, (MODE == kConv ? OHT * OHT : MT * 128)>;
     static_assert(BN % SUBC == 0 && SUBC % 64 == 0, "channel passes are whole pairs of 32-column TMEM chunks");
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: SWIZZLE_128B atoms are 8 rows x 128 B and the swizzle is address based.
@@ -284,27 +284,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll 1
                 for (int pass = 0; pass < kPasses; ++pass) {
                 const int nsub = n0 + pass * SUBC;       // first channel of this pass
-                // ---- phase 1: TMEM -> (+bias, ReLU) -> bf16 staging tile [pixel][SUBC] ----
+                // ---- phase 1: TMEM -> bf16 staging tile [pixel][SUBC] ----
+                // (bias + ReLU are applied AFTER the pool: x -> relu(x + b) is monotone per channel, so
+                //  max_window relu(x + b) = relu(max_window x + b); 121 pooled pixels instead of 169 conv pixels, and the
+                //  per-thread channel group of phase 2 keeps its bias in registers)
 #pragma unroll 1
                 for (int mt = 0; mt < MT; ++mt) {
                     const int pix = mt * 128 + row;
+                    if (mt * 128 + q * 32 >= npix) continue;      // (warp-uniform) this warp's 32 rows are all padding
 #pragma unroll 1
                     for (int c = half; c < SUBC / 32; c += 2) {
                         uint32_t r[32];
                         tmem_ld32(tbase + (uint32_t)(mt * BN + pass * SUBC + c * 32), r);
                         tmem_ld_wait();
                         if (pix < npix) {
-                            const float4* bp = reinterpret_cast<const float4*>(s_bias + nsub + c * 32);
                             uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)pix * C::kStgStride + c * 64);
 #pragma unroll
                             for (int v = 0; v < 4; ++v) {
-                                const float4 b0 = bp[2 * v], b1 = bp[2 * v + 1];
                                 const int i = v * 8;
-                                dst[v] = make_uint4(
-                                    pack_bf16(fmaxf(__uint_as_float(r[i]) + b0.x, 0.f), fmaxf(__uint_as_float(r[i + 1]) + b0.y, 0.f)),
-                                    pack_bf16(fmaxf(__uint_as_float(r[i + 2]) + b0.z, 0.f), fmaxf(__uint_as_float(r[i + 3]) + b0.w, 0.f)),
-                                    pack_bf16(fmaxf(__uint_as_float(r[i + 4]) + b1.x, 0.f), fmaxf(__uint_as_float(r[i + 5]) + b1.y, 0.f)),
-                                    pack_bf16(fmaxf(__uint_as_float(r[i + 6]) + b1.z, 0.f), fmaxf(__uint_as_float(r[i + 7]) + b1.w, 0.f)));
+                                dst[v] = make_uint4(pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1])),
+                                                    pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])),
+                                                    pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5])),
+                                                    pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7])));
                             }
                         }
                     }
@@ -328,16 +329,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     gy0 = ty * P;
                     gx0 = (t - ty * args.g.tiles) * P;
                 }
-                const int vy = min(P, args.g.pfull - gy0), vx = min(P, args.g.pfull - gx0);   // valid outputs of an edge tile
+                // valid outputs of this tile: the whole P x P when the tile is the frame (compile-time: the walk below is then
+                // fully unrolled and its loads scheduled ahead), fewer for an edge tile of a tiled frame
+                constexpr bool kWhole = (OHT != 16);
+                const int vy = kWhole ? P : min(P, args.g.pfull - gy0), vx = kWhole ? P : min(P, args.g.pfull - gx0);
                 __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + nsub;
-                // BatchNorm affine + bf16 store of one pooled (pixel, 8-channel group)
-                auto emit = [&](int oy, int ox, int cg, uint4 m, const float4& sc0, const float4& sc1, const float4& sh0,
-                                const float4& sh1) {
+                // bias + ReLU + BatchNorm affine + bf16 store of one pooled (pixel, 8-channel group)
+                auto emit = [&](int oy, int ox, int cg, uint4 m, const float4& b0, const float4& b1, const float4& sc0,
+                                const float4& sc1, const float4& sh0, const float4& sh1) {
                     const float2 f0 = bf2_to_f2(m.x), f1 = bf2_to_f2(m.y), f2 = bf2_to_f2(m.z), f3 = bf2_to_f2(m.w);
-                    const uint4 o = make_uint4(pack_bf16(fmaf(f0.x, sc0.x, sh0.x), fmaf(f0.y, sc0.y, sh0.y)),
-                                               pack_bf16(fmaf(f1.x, sc0.z, sh0.z), fmaf(f1.y, sc0.w, sh0.w)),
-                                               pack_bf16(fmaf(f2.x, sc1.x, sh1.x), fmaf(f2.y, sc1.y, sh1.y)),
-                                               pack_bf16(fmaf(f3.x, sc1.z, sh1.z), fmaf(f3.y, sc1.w, sh1.w)));
+                    const uint4 o = make_uint4(
+                        pack_bf16(fmaf(fmaxf(f0.x + b0.x, 0.f), sc0.x, sh0.x), fmaf(fmaxf(f0.y + b0.y, 0.f), sc0.y, sh0.y)),
+                        pack_bf16(fmaf(fmaxf(f1.x + b0.z, 0.f), sc0.z, sh0.z), fmaf(fmaxf(f1.y + b0.w, 0.f), sc0.w, sh0.w)),
+                        pack_bf16(fmaf(fmaxf(f2.x + b1.x, 0.f), sc1.x, sh1.x), fmaf(fmaxf(f2.y + b1.y, 0.f), sc1.y, sh1.y)),
+                        pack_bf16(fmaf(fmaxf(f3.x + b1.z, 0.f), sc1.z, sh1.z), fmaf(fmaxf(f3.y + b1.w, 0.f), sc1.w, sh1.w)));
                     const int opix = (gy0 + oy + args.g.out_pad) * PW + gx0 + ox + args.g.out_pad;
                     if (args.g.blocked)
                         *reinterpret_cast<uint4*>(args.out + gn_a3_off(frame, (int64_t)opix * args.g.cout + nsub + cg * 8,
@@ -354,18 +359,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + nsub + cg * 8);
                         const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + nsub + cg * 8);
                         const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1];
+                        const float4* bb = reinterpret_cast<const float4*>(s_bias + nsub + cg * 8);
+                        const float4 b0 = bb[0], b1 = bb[1];
                         const unsigned char* s0 = stg + (size_t)ox * C::kStgStride + cg * 16;
                         uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;
+                        // the three taps of the NEXT conv row are loaded before this row's maxima are combined and stored
+                        uint4 t0 = *reinterpret_cast<const uint4*>(s0), t1 = *reinterpret_cast<const uint4*>(s0 + C::kStgStride),
+                              t2 = *reinterpret_cast<const uint4*>(s0 + 2 * C::kStgStride);
 #pragma unroll
                         for (int r = 0; r < OHT; ++r) {
                             if (r < vy + 2) {
-                                const unsigned char* sr = s0 + (size_t)(r * OHT) * C::kStgStride;
-                                const uint4 h2 = hmax2_u4(hmax2_u4(*reinterpret_cast<const uint4*>(sr),
-                                                                   *reinterpret_cast<const uint4*>(sr + C::kStgStride)),
-                                                          *reinterpret_cast<const uint4*>(sr + 2 * C::kStgStride));
-                                if (r >= 2) emit(r - 2, ox, cg, hmax2_u4(hmax2_u4(h0, h1), h2), sc0, sc1, sh0, sh1);
+                                uint4 n0 = t0, n1 = t1, n2 = t2;
+                                if (r + 1 < OHT && r + 1 < vy + 2) {
+                                    const unsigned char* sr = s0 + (size_t)((r + 1) * OHT) * C::kStgStride;
+                                    n0 = *reinterpret_cast<const uint4*>(sr);
+                                    n1 = *reinterpret_cast<const uint4*>(sr + C::kStgStride);
+                                    n2 = *reinterpret_cast<const uint4*>(sr + 2 * C::kStgStride);
+                                }
+                                const uint4 h2 = hmax2_u4(hmax2_u4(t0, t1), t2);
+                                if (r >= 2) emit(r - 2, ox, cg, hmax2_u4(hmax2_u4(h0, h1), h2), b0, b1, sc0, sc1, sh0, sh1);
                                 h0 = h1;
                                 h1 = h2;
+                                t0 = n0; t1 = n1; t2 = n2;
                             }
                         }
                     }
@@ -386,7 +401,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             }
                         const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + nsub + cg * 8);
                         const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + nsub + cg * 8);
-                        emit(oy, ox, cg, m, sc[0], sc[1], sh[0], sh[1]);
+                        const float4* bb = reinterpret_cast<const float4*>(s_bias + nsub + cg * 8);
+                        emit(oy, ox, cg, m, bb[0], bb[1], sc[0], sc[1], sh[0], sh[1]);
                     }
                 }
                 if (args.g.out_pad && tiles_pf == 1) {   // zero border of the next conv's input (padding = 1);
@@ -598,7 +614,7 @@ int make_tmap_2d(gn_handle* h, CUtensorMap* m, const void* base, int64_t rows, i
 template <int MT, int BN, int STAGES, int MODE, int OHT, int SUBC = BN>
 int launch(gn_handle* h, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& a, int64_t tiles,
            cudaStream_t st) {
-    using C = Cfg<MT, BN, STAGES, MODE, SUBC>;
+    using C = Cfg<MT, BN, STAGES, MODE, SUBC, (MODE == kConv ? OHT * OHT : MT * 128)>;
     if (a.N > kMaxN && MODE != kDgrad && MODE != kWgrad && MODE != kSplitK && MODE != kGemmTF32) return GN_E_SHAPE;
     auto kern = tc_gemm_kernel<MT, BN, STAGES, MODE, OHT, SUBC>;
     if (gn_attr_first(h, reinterpret_cast<const void*>(kern)))
