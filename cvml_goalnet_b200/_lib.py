@@ -96,7 +96,7 @@ SIGNATURES = {
     "gn_destroy": (_I, [_P]),
     "gn_launch_count": (_L, [_P]),
     "gn_preprocess_u8_bgr": (_I, [_P, _P, _L, _I, _I, _I, _P, _P, _P]),
-    "gn_mfcc_resampled": (_I, [_P, _P, _L, _P, _P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    "gn_mfcc_resampled": (_I, [_P, _P, _L, _P, _P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _I, _P, _P, _P]),
     "gn_model_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_avm_state), _I, _I, _I, _P]),
     "gn_model_destroy": (_I, [_P]),
     "gn_model_set_classifier_head": (_I, [_P, _P, _P, _I, _P]),

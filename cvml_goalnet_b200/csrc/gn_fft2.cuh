@@ -145,12 +145,13 @@ GNF2_HD float4 pack4(C2 v) { return make_float4(v.re.x, v.re.y, v.im.x, v.im.y);
 GNF2_HD C2 unpack4(float4 f) { C2 v; v.re = mk(f.x, f.y); v.im = mk(f.z, f.w); return v; }
 
 // ---- tables (built on the host in double, see gn_fft2_fill_tables) --------------------------------------------
-//   tw1[(k1 - 1) * 128 + t] = {wr, wr, wi, wi} of W_2048^(t k1),  k1 = 1..15
-//   tw2[(k2 - 1) * 8 + n3]  = {wr, wr, wi, wi} of W_128^(n3 k2),  k2 = 1..15
+//   tw1[(k1 - 1) * 128 + t] = {wr, wi} of W_2048^(t k1),  k1 = 1..15
+//   tw2[(k2 - 1) * 8 + n3]  = {wr, wi} of W_128^(n3 k2),  k2 = 1..15
+// (scalars: the packed instructions broadcast a 32-bit operand to both lanes for free)
 constexpr int kTw1 = 15 * 128, kTw2 = 15 * 8;
 
 // pass 1 for thread t: z[n1] = x[t + 128 n1] on entry; results to the exchange buffer
-GNF2_HD void pass1(int t, C2 (&z)[16], const float4* tw1, float4* xbuf) {
+GNF2_HD void pass1(int t, C2 (&z)[16], const float2* tw1, float4* xbuf) {
     dft16(z);
     const int n2 = t >> 3, n3 = t & 7;
     GNF2_UNROLL
@@ -158,15 +159,15 @@ GNF2_HD void pass1(int t, C2 (&z)[16], const float4* tw1, float4* xbuf) {
         const int k1 = perm16(p);
         C2 v = z[p];
         if (k1 != 0) {
-            const float4 w = tw1[(k1 - 1) * 128 + t];
-            v = cmul(v, mk(w.x, w.y), mk(w.z, w.w));
+            const float2 w = tw1[(k1 - 1) * 128 + t];
+            v = cmul(v, bc(w.x), bc(w.y));
         }
         xbuf[(k1 * 16 + n2) * 8 + n3] = pack4(v);
     }
 }
 
 // pass 2 for thread t = 8 k1 + n3
-GNF2_HD void pass2(int t, const float4* tw2, float4* xbuf_in, float4* xbuf_out) {
+GNF2_HD void pass2(int t, const float2* tw2, float4* xbuf_in, float4* xbuf_out) {
     const int k1 = t >> 3, n3 = t & 7;
     C2 z[16];
     GNF2_UNROLL
@@ -177,8 +178,8 @@ GNF2_HD void pass2(int t, const float4* tw2, float4* xbuf_in, float4* xbuf_out) 
         const int k2 = perm16(p);
         C2 v = z[p];
         if (k2 != 0) {
-            const float4 w = tw2[(k2 - 1) * 8 + n3];
-            v = cmul(v, mk(w.x, w.y), mk(w.z, w.w));
+            const float2 w = tw2[(k2 - 1) * 8 + n3];
+            v = cmul(v, bc(w.x), bc(w.y));
         }
         xbuf_out[(k1 * 16 + k2) * 8 + (n3 ^ (k2 & 7))] = pack4(v);
     }

@@ -2,26 +2,29 @@
 // 10 log10 with an 80 dB floor under the segment max -> DCT-II ortho (30 rows) -> cubic time
 // resampling W (B x q).  Replaces reference utils.py:322-349 (librosa.feature.mfcc + interp1d loop).
 //
-// One CTA (8 warps) per slot, one warp per pair of STFT columns.  Two columns share one complex
-// 2048-point FFT (column j in the real part, column j+1 in the imaginary part) that the warp computes
-// with the points in registers (gn_fft.cuh: 64-point DFTs, one transpose through a private
-// shared-memory tile, 32-point DFTs); X[k] and X[N-k] land in the same lane, so the two power spectra
-// are formed in registers and only then written to the warp's tile for the mel filterbank.  No block
-// barrier inside the transform; HBM traffic is the slot's samples in and 30*B floats out.
+// One 128-thread CTA per slot, several CTAs per SM (so that one CTA's barriers and latencies hide under
+// another's arithmetic).  The transform is the stage's cost (8 complex FFT-2048 per slot: ~1 MFLOP of
+// 1.1): FOUR STFT columns go through the butterflies at once -- two real columns share one complex
+// transform (column j in the real part, j+1 in the imaginary part), and two such transforms ride in
+// the two lanes of the packed fp32 instructions (gn_fft2.cuh: FADD2 / FMUL2 / FFMA2).  The samples of
+// four consecutive columns overlap (hop 512 = 4 rows of 128), so a thread loads 28 values instead of
+// 64.  One 32 KB shared-memory buffer serves the two exchanges, the spectrum and the power spectra;
+// the tables (twiddles, window, mel weights, DCT rows, W) are read through L1.  HBM traffic is the
+// slot's samples in and 30*B floats out.  Every sum is formed in a fixed order: a slot's features do
+// not depend on the launch it is part of.
 #include "gn_common.cuh"
-#include "gn_fft.cuh"
+#include "gn_fft2.cuh"
 
 namespace {
+
+using namespace gnfft2;
 
 constexpr int kFFT = 2048;
 constexpr int kHop = 512;
 constexpr int kMels = 128;
 constexpr int kMfcc = 30;
-constexpr int kWarps = 8;
-constexpr int kThreads = kWarps * 32;
-constexpr int kMelWMax = 2304;              // >= 2 * 1025: every FFT bin feeds at most two triangular filters
-constexpr int kPw2 = 1056;                  // offset (floats) of the second power spectrum inside a warp tile
-static_assert(kPw2 >= kFFT / 2 + 1 && kPw2 + kFFT / 2 + 1 <= 2 * gnfft::kTile, "power spectra alias the tile");
+constexpr int kT = 128;                     // threads per CTA == gnfft2::kThreads
+constexpr int kXBytes = kFFT * 16;          // exchange / spectrum / power buffer
 
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
@@ -29,210 +32,240 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kT, 4)
 mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, const int32_t* __restrict__ seg_len,
-            const int32_t* __restrict__ w_offset, const float* __restrict__ w_all, int64_t n, int B, int max_q,
+            const int32_t* __restrict__ w_offset, const float* __restrict__ w_all, int64_t n, int B, int mq,
             const int32_t* __restrict__ mel_start, const int32_t* __restrict__ mel_count,
-            const int32_t* __restrict__ mel_offset, const float* __restrict__ mel_w,
-            const float* __restrict__ dct, const float2* __restrict__ twiddle, const float* __restrict__ hann,
-            float* __restrict__ out, int dct_smem, int w_smem) {
+            const int32_t* __restrict__ mel_offset, const float* __restrict__ mel_w, int n_mel_w,
+            const float* __restrict__ dctT /*[128][32]*/, const float2* __restrict__ tw1, const float2* __restrict__ tw2,
+            const float* __restrict__ hann, float* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* tiles = reinterpret_cast<float2*>(smem_raw);                  // [kWarps][kTile] transpose tiles
-    float2* tw = tiles + kWarps * gnfft::kTile;                           // [64][32] lane-major twiddles
-    float* hw = reinterpret_cast<float*>(tw + gnfft::kTwLane);            // [2048] hann window
-    float* melw = hw + kFFT;                                              // [kMelWMax] mel filter weights
-    int* mst = reinterpret_cast<int*>(melw + kMelWMax);                   // [128] first bin of each filter
-    int* mcn = mst + kMels;                                               // [128] bins per filter
-    int* mof = mcn + kMels;                                               // [128] offset into melw
-    float* mel = reinterpret_cast<float*>(mof + kMels);                   // [128][max_q] log-mel
-    float* cep = mel + kMels * max_q;                                     // [30][max_q]
-    float* dctT = cep + kMfcc * max_q;                                    // [128][32] DCT rows, transposed (if dct_smem)
-    float* wsm = dctT + (dct_smem ? kMels * 32 : 0);                      // [B][max_q + 4] this slot's W (if w_smem)
-    __shared__ float red[kWarps];
+    float4* xb = reinterpret_cast<float4*>(smem_raw);                      // [2048] exchange / spectrum / power
+    float* mel = reinterpret_cast<float*>(smem_raw + kXBytes);             // [128][mq]  (mq = max_q rounded up to 4)
+    float* cepT = mel + kMels * mq;                                        // [mq][32]   cepstra, transposed (row = column j)
+    float* mws = cepT + 32 * mq;                                           // [n_mel_w]  mel filter weights (CSR order)
+    __shared__ float red[kT / 32];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < gnfft::kTwLane; i += kThreads) tw[i] = twiddle[i];
-    for (int i = tid; i < kFFT; i += kThreads) hw[i] = hann[i];
-    const int n_mel_w = mel_offset[kMels - 1] + mel_count[kMels - 1];
-    const bool melw_fits = n_mel_w <= kMelWMax;
-    if (melw_fits)
-        for (int i = tid; i < n_mel_w; i += kThreads) melw[i] = mel_w[i];
-    if (tid < kMels) { mst[tid] = mel_start[tid]; mcn[tid] = mel_count[tid]; mof[tid] = mel_offset[tid]; }
-    if (dct_smem)
-        for (int i = tid; i < kMels * 32; i += kThreads) {
-            const int m = i >> 5, c = i & 31;
-            dctT[i] = c < kMfcc ? dct[c * kMels + m] : 0.f;
-        }
-    const float* mw = melw_fits ? melw : mel_w;
-    float2* tile = tiles + warp * gnfft::kTile;
-    float* pw1 = reinterpret_cast<float*>(tile);
-    float* pw2 = pw1 + kPw2;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    // this thread's mel band: contiguous bins [mst, mst + mcn), weights mw[0..mcn); the weights are staged once per CTA
+    const int mst = __ldg(mel_start + t), mcn = __ldg(mel_count + t);
+    const float* mw = mws + __ldg(mel_offset + t);
+    for (int i = t; i < n_mel_w; i += kT) mws[i] = __ldg(mel_w + i);
+    __syncthreads();
 
     for (int64_t slot = blockIdx.x; slot < n; slot += gridDim.x) {
         const int64_t s0 = seg_start[slot];
         const int L = seg_len[slot];
         const int q = 1 + L / kHop;
         const float* seg = y + s0;
-        const float* W = w_all + w_offset[slot];
-        const int wq = q + 4;                                  // padded row of the staged W: conflict-free 16-byte reads
-        __syncthreads();          // tables loaded; previous slot's resampling is done with cep / wsm
-        if (w_smem)
-            for (int i = tid; i < B * q; i += kThreads) {
-                const int bb = i / q;
-                wsm[bb * wq + (i - bb * q)] = __ldg(W + i);
-            }
-        float emax = 0.f;                                      // largest mel energy seen by this lane
-        for (int j = 2 * warp; j < q; j += 2 * kWarps) {
-            const bool two = (j + 1 < q);
-            {
-                // windowed columns j (re) and j+1 (im); samples outside [0,L) are the centre zero padding.
-                // Column j+1 is column j shifted by one hop = 16 rows of 32 samples, so 80 rows feed both.
-                float2 z[64];
-                const int base = j * kHop - kFFT / 2 + lane;
-                float raw[16];
+        float emax = 0.f;                                      // largest mel energy seen by this thread
+        // sample rows of 128: row m of a group holds samples j0*512 - 1024 + 128 m + t; column j0+c starts at row 4c.
+        // Samples outside [0, L) are the centre zero padding; interior groups skip the bounds checks.  The rows of group
+        // g+1 are requested while group g is between its passes (they are only consumed one group later).
+        float raw[28];
+        auto load_rows = [&](int j0) {
+            const int base = j0 * kHop - kFFT / 2 + t;
+            if (base - t >= 0 && base - t + 28 * 128 <= L) {
+                const float* p = seg + base;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) {
-                    const int i = base + 32 * r;
-                    raw[r] = ((unsigned)i < (unsigned)L) ? __ldg(seg + i) : 0.f;
-                }
+                for (int m = 0; m < 28; ++m) raw[m] = __ldg(p + 128 * m);
+            } else {
 #pragma unroll
-                for (int n1 = 0; n1 < 64; ++n1) {
-                    const int i = base + 32 * (n1 + 16);
-                    const float nxt = ((unsigned)i < (unsigned)L) ? __ldg(seg + i) : 0.f;
-                    const float h = hw[32 * n1 + lane];
-                    z[n1] = make_float2(raw[n1 & 15] * h, two ? nxt * h : 0.f);
-                    raw[n1 & 15] = nxt;
+                for (int m = 0; m < 28; ++m) {
+                    const int i = base + 128 * m;
+                    raw[m] = ((unsigned)i < (unsigned)L) ? __ldg(seg + i) : 0.f;
                 }
-                gnfft::warp_fft_stage1(lane, z, tw, tile);
             }
-            __syncwarp();
+        };
+        load_rows(0);
+        for (int j0 = 0; j0 < q; j0 += 4) {
+            // ---- windowed columns j0..j0+3: transform A = (j0, j0+1), transform B = (j0+2, j0+3) ----
             {
-                float2 a[32], b[32];
-                gnfft::warp_fft_stage2(lane, tile, a, b);
-                __syncwarp();                                  // every lane has read its rows: the tile becomes pw1 / pw2
-                gnfft::warp_fft_power(lane, a, b, pw1, pw2);
-            }
-            __syncwarp();
-            // mel filterbank: lane owns bands lane, lane + 32, ... (a band's bins are contiguous)
-#pragma unroll 1
-            for (int band = lane; band < kMels; band += 32) {
-                const int st = mst[band], cnt = mcn[band];
-                const float* wv = mw + mof[band];
-                float a0 = 0.f, a1 = 0.f;
-                for (int i = 0; i < cnt; ++i) {
-                    const float wgt = wv[i];
-                    a0 = fmaf(wgt, pw1[st + i], a0);
-                    a1 = fmaf(wgt, pw2[st + i], a1);
+                C2 z[16];
+                {
+                    const float c1 = (j0 + 1 < q) ? 1.f : 0.f, c2 = (j0 + 2 < q) ? 1.f : 0.f, c3 = (j0 + 3 < q) ? 1.f : 0.f;
+#pragma unroll
+                    for (int n1 = 0; n1 < 16; ++n1) {
+                        const float h = __ldg(hann + t + 128 * n1);
+                        z[n1].re = mk(raw[n1] * h, raw[n1 + 8] * (h * c2));
+                        z[n1].im = mk(raw[n1 + 4] * (h * c1), raw[n1 + 12] * (h * c3));
+                    }
                 }
-                mel[band * max_q + j] = a0;
-                emax = fmaxf(emax, a0);
-                if (two) { mel[band * max_q + j + 1] = a1; emax = fmaxf(emax, a1); }
+                if (j0 + 4 < q) load_rows(j0 + 4);
+                pass1(t, z, tw1, xb);                          // (the previous group's readers left at the barrier below)
             }
-            __syncwarp();                                      // pw reads done before the next pair reuses the tile
+            __syncthreads();
+            {
+                // pass 2 in place: a quarter-warp (same k1) reads and writes the same 128 elements
+                const int k1 = t >> 3, n3 = t & 7;
+                C2 z[16];
+#pragma unroll
+                for (int n2 = 0; n2 < 16; ++n2) z[n2] = unpack4(xb[(k1 * 16 + n2) * 8 + n3]);
+                __syncwarp();
+                dft16(z);
+#pragma unroll
+                for (int p = 0; p < 16; ++p) {
+                    const int k2 = perm16(p);
+                    C2 v = z[p];
+                    if (k2 != 0) {
+                        const float2 w = __ldg(tw2 + (k2 - 1) * 8 + n3);
+                        v = cmul(v, bc(w.x), bc(w.y));
+                    }
+                    xb[(k1 * 16 + k2) * 8 + (n3 ^ (k2 & 7))] = pack4(v);
+                }
+            }
+            __syncthreads();
+            {
+                // pass 3 in place: all reads, barrier, then the spectrum in natural (swizzled) order
+                C2 va[8], vb[8];
+                const int ka = t & 15;                         // k2 of both pairs (p = t and t + 128 share p & 15)
+#pragma unroll
+                for (int n3 = 0; n3 < 8; ++n3) {
+                    va[n3] = unpack4(xb[t * 8 + (n3 ^ (ka & 7))]);
+                    vb[n3] = unpack4(xb[(t + 128) * 8 + (n3 ^ (ka & 7))]);
+                }
+                __syncthreads();
+                dft8(va);
+                dft8(vb);
+                const int kba = (t >> 4) + 16 * ka, kbb = ((t + 128) >> 4) + 16 * ka;
+#pragma unroll
+                for (int k3 = 0; k3 < 8; ++k3) {
+                    xb[spec_index(kba + 256 * k3)] = pack4(va[k3]);
+                    xb[spec_index(kbb + 256 * k3)] = pack4(vb[k3]);
+                }
+            }
+            __syncthreads();
+            {
+                // power spectra of the four real columns, bins k = t + 128 r (r < 8) and k = 1024 (thread 0):
+                // to registers, barrier, then over the spectrum as pw[k] = {col j0, col j0+2, col j0+1, col j0+3}
+                float4 pw[8], pwn = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int r = 0; r < 8; ++r) pw[r] = split_power(xb, t + 128 * r);
+                if (t == 0) pwn = split_power(xb, 1024);
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < 8; ++r) xb[t + 128 * r] = pw[r];
+                if (t == 0) xb[1024] = pwn;
+            }
+            __syncthreads();
+            {
+                // mel filterbank: thread = band (its bins are contiguous); four independent accumulator pairs
+                V2 a02 = bc(0.f), a13 = bc(0.f), b02 = bc(0.f), b13 = bc(0.f);
+                int i = 0;
+                for (; i + 1 < mcn; i += 2) {
+                    const float w0 = mw[i], w1 = mw[i + 1];
+                    const float4 p0 = xb[mst + i], p1 = xb[mst + i + 1];
+                    a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
+                    a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
+                    b02 = fma2(bc(w1), mk(p1.x, p1.y), b02);
+                    b13 = fma2(bc(w1), mk(p1.z, p1.w), b13);
+                }
+                if (i < mcn) {
+                    const float w0 = mw[i];
+                    const float4 p0 = xb[mst + i];
+                    a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
+                    a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
+                }
+                a02 = add2(a02, b02);
+                a13 = add2(a13, b13);
+                // columns j0, j0+1, j0+2, j0+3 (columns >= q were transformed as zeros: 0 energy, within the padded row)
+                *reinterpret_cast<float4*>(mel + t * mq + j0) = make_float4(a02.x, a13.x, a02.y, a13.y);
+                emax = fmaxf(emax, fmaxf(fmaxf(a02.x, a13.x), fmaxf(a02.y, a13.y)));
+            }
+            __syncthreads();                                   // pw reads done before the next group's pass 1 writes
         }
         emax = warp_max(emax);
         if (lane == 0) red[warp] = emax;
         __syncthreads();
         // power_to_db: 10 log10(max(1e-10, S)), floored at (segment max - 80 dB); log10 is monotone, so the
         // segment max of the log is the log of the largest energy
-        float smax = red[0];
-#pragma unroll
-        for (int w = 1; w < kWarps; ++w) smax = fmaxf(smax, red[w]);
+        const float smax = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
         const float floor_db = 10.f * log10f(fmaxf(1e-10f, smax)) - 80.f;
-        // every warp finishes its own columns: log + floor in place, then the DCT-II (ortho) over the mel axis,
-        // cep[c][j] = sum_m dct[c][m] * logmel[m][j], lane = cepstral row c
-        for (int j = 2 * warp; j < q; j += 2 * kWarps) {
-            const bool two = (j + 1 < q);
-            for (int band = lane; band < kMels; band += 32) {
-                float* mp = mel + band * max_q + j;
-                mp[0] = fmaxf(10.f * log10f(fmaxf(1e-10f, mp[0])), floor_db);
-                if (two) mp[1] = fmaxf(10.f * log10f(fmaxf(1e-10f, mp[1])), floor_db);
-            }
-            __syncwarp();
-            if (lane < kMfcc) {
-                float c0 = 0.f, c1 = 0.f;
-                const float* mp = mel + j;
-                const int j1 = two ? 1 : 0;
-                if (dct_smem) {
+        const int qp = (q + 3) & ~3;
+        for (int idx = t; idx < kMels * (qp >> 2); idx += kT) {
+            const int band = idx / (qp >> 2), jq = idx - band * (qp >> 2);
+            float4* mp = reinterpret_cast<float4*>(mel + band * mq + 4 * jq);
+            float4 v = *mp;
+            v.x = fmaxf(3.0102999566398120f * __log2f(fmaxf(1e-10f, v.x)), floor_db);
+            v.y = fmaxf(3.0102999566398120f * __log2f(fmaxf(1e-10f, v.y)), floor_db);
+            v.z = fmaxf(3.0102999566398120f * __log2f(fmaxf(1e-10f, v.z)), floor_db);
+            v.w = fmaxf(3.0102999566398120f * __log2f(fmaxf(1e-10f, v.w)), floor_db);
+            *mp = v;
+        }
+        __syncthreads();
+        // DCT-II (ortho) over the mel axis: cep[c][j] = sum_m dct[c][m] * logmel[m][j]; lane = row c, warp = column quad.
+        // The table is transposed ([m][32]) so that a warp's 32 coefficients are one 128-byte line.
+        {
+            for (int jq = warp; jq < (qp >> 2); jq += kT / 32) {
+                V2 a01 = bc(0.f), a23 = bc(0.f);
+                const float* mp = mel + 4 * jq;
 #pragma unroll 8
-                    for (int m = 0; m < kMels; ++m) {
-                        const float d = dctT[m * 32 + lane];
-                        c0 = fmaf(d, mp[m * max_q], c0);
-                        c1 = fmaf(d, mp[m * max_q + j1], c1);
-                    }
-                } else {
-                    const float* dg = dct + lane * kMels;
-#pragma unroll 8
-                    for (int m = 0; m < kMels; ++m) {
-                        const float d = __ldg(dg + m);
-                        c0 = fmaf(d, mp[m * max_q], c0);
-                        c1 = fmaf(d, mp[m * max_q + j1], c1);
-                    }
+                for (int m = 0; m < kMels; ++m) {
+                    const float d = __ldg(dctT + m * 32 + lane);
+                    const float4 v = *reinterpret_cast<const float4*>(mp + m * mq);      // broadcast
+                    a01 = fma2(bc(d), mk(v.x, v.y), a01);
+                    a23 = fma2(bc(d), mk(v.z, v.w), a23);
                 }
-                cep[lane * max_q + j] = c0;
-                if (two) cep[lane * max_q + j + 1] = c1;
+                float* cp = cepT + (4 * jq) * 32 + lane;
+                cp[0] = a01.x; cp[32] = a01.y; cp[64] = a23.x; cp[96] = a23.y;
             }
         }
         __syncthreads();
-        // cubic time resampling (utils.py:336-343) as the linear operator W (B x q)
-        float* o = out + slot * (int64_t)(kMfcc * B);
-        if (w_smem && (q & 3) == 0 && (max_q & 3) == 0) {
-            for (int i = tid; i < kMfcc * B; i += kThreads) {
-                const int c = i / B, bb = i - c * B;
-                const float4* wr = reinterpret_cast<const float4*>(wsm + bb * wq);
-                const float4* cr = reinterpret_cast<const float4*>(cep + c * max_q);
+        // cubic time resampling (utils.py:336-343) as the linear operator W (B x q): warp = output column b (its W row is
+        // one broadcast line), lane = cepstral row c; results are staged row-major in the exchange buffer and stored as
+        // whole lines
+        {
+            const float* W = w_all + w_offset[slot];
+            float* stage = reinterpret_cast<float*>(xb);
+            for (int bb = warp; bb < B; bb += kT / 32) {
+                const float* wr = W + bb * q;
                 float acc = 0.f;
-                for (int j4 = 0; j4 < (q >> 2); ++j4) {
-                    const float4 wv = wr[j4], cv = cr[j4];
-                    acc = fmaf(wv.x, cv.x, acc); acc = fmaf(wv.y, cv.y, acc);
-                    acc = fmaf(wv.z, cv.z, acc); acc = fmaf(wv.w, cv.w, acc);
-                }
-                o[i] = acc;
+                for (int j = 0; j < q; ++j) acc = fmaf(__ldg(wr + j), cepT[j * 32 + lane], acc);
+                if (lane < kMfcc) stage[lane * B + bb] = acc;
             }
-        } else {
-            for (int i = tid; i < kMfcc * B; i += kThreads) {
-                const int c = i / B, bb = i - c * B;
-                float acc = 0.f;
-                if (w_smem) for (int j = 0; j < q; ++j) acc = fmaf(wsm[bb * wq + j], cep[c * max_q + j], acc);
-                else        for (int j = 0; j < q; ++j) acc = fmaf(__ldg(W + bb * q + j), cep[c * max_q + j], acc);
-                o[i] = acc;
-            }
+            __syncthreads();
+            float* o = out + slot * (int64_t)(kMfcc * B);
+            for (int i = t; i < kMfcc * B; i += kT) o[i] = stage[i];
         }
+        // (the next slot's first pass-1 store is behind that slot's loads; cep / mel are rewritten only after barriers)
+        __syncthreads();
     }
 }
 
 }  // namespace
 
-struct gn_mfcc_tables { const float2* twiddle; const float* hann; };
+struct gn_mfcc_tables { const float2* tw1; const float2* tw2; const float* hann; };
 gn_mfcc_tables gn_get_mfcc_tables(gn_handle* h);   // gn_model.cu
 
 extern "C" int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_samples, const int64_t* d_seg_start,
                                  const int32_t* d_seg_len, const int32_t* d_w_offset, const float* d_w, int64_t n,
                                  int B, int max_q, const int32_t* d_mel_start, const int32_t* d_mel_count,
-                                 const int32_t* d_mel_offset, const float* d_mel_w, const float* d_dct,
-                                 float* d_out, void* stream) {
+                                 const int32_t* d_mel_offset, const float* d_mel_w, int n_mel_w_given,
+                                 const float* d_dct, float* d_out, void* stream) {
     if (!h || n < 0 || n_samples < 0 || B <= 0) return GN_E_ARG;
     if (max_q < 1 || max_q > GN_MFCC_MAX_Q || B > 4096) return GN_E_SHAPE;
+    if (n_mel_w_given < 0 || n_mel_w_given > 2 * (kFFT / 2 + 1) + 64) return GN_E_SHAPE;
     if (n == 0) return GN_OK;
     if (!d_y || !d_seg_start || !d_seg_len || !d_w_offset || !d_w || !d_mel_start || !d_mel_count ||
         !d_mel_offset || !d_mel_w || !d_dct || !d_out) return GN_E_ARG;
     const gn_mfcc_tables t = gn_get_mfcc_tables(h);
-    size_t smem = sizeof(float2) * (size_t)(kWarps * gnfft::kTile + gnfft::kTwLane) + sizeof(float) * (kFFT + kMelWMax) +
-                  sizeof(int) * 3 * kMels + sizeof(float) * (size_t)(kMels + kMfcc) * max_q;
-    constexpr size_t kSmemMax = 220 * 1024;
-    // optional staging (dropped for very long segments): the DCT rows and the slot's resampling operator
-    const size_t dct_bytes = sizeof(float) * kMels * 32, w_bytes = sizeof(float) * (size_t)B * (max_q + 4);
-    const int dct_smem = smem + dct_bytes <= kSmemMax ? 1 : 0;
-    if (dct_smem) smem += dct_bytes;
-    const int w_smem = (w_bytes <= 16 * 1024 && smem + w_bytes <= kSmemMax) ? 1 : 0;
-    if (w_smem) smem += w_bytes;
+    const int mq = (max_q + 3) & ~3;
+    if (B * kMfcc * 4 > kXBytes) return GN_E_SHAPE;       // the output rows are staged in the exchange buffer
+    const int n_mel_w = 2 * (kFFT / 2 + 1) + 64;           // upper bound the caller's CSR must respect (two filters per bin)
+    const size_t smem = (size_t)kXBytes + sizeof(float) * ((size_t)(kMels + 32) * mq + n_mel_w);
     if (gn_attr_first(h, reinterpret_cast<const void*>(mfcc_kernel)))
-        GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax));
-    // persistent: one 8-warp CTA per SM (the register-resident transforms need ~all of the register file)
-    const int grid = (int)(n < (int64_t)h->num_sms ? n : (int64_t)h->num_sms);
-    mfcc_kernel<<<grid, kThreads, smem, gn_stream(stream)>>>(
-        d_y, d_seg_start, d_seg_len, d_w_offset, d_w, n, B, max_q, d_mel_start, d_mel_count, d_mel_offset,
-        d_mel_w, d_dct, t.twiddle, t.hann, d_out, dct_smem, w_smem);
+        GN_CUDA(cudaFuncSetAttribute(mfcc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    // persistent: as many CTAs as are resident at once (4 per SM at 16 columns per slot), slots strided over them
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mfcc_kernel, kT, smem) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        per_sm = 1;
+    }
+    const int64_t cap = (int64_t)h->num_sms * per_sm;
+    const int grid = (int)(n < cap ? n : cap);
+    mfcc_kernel<<<grid, kT, smem, gn_stream(stream)>>>(
+        d_y, d_seg_start, d_seg_len, d_w_offset, d_w, n, B, mq, d_mel_start, d_mel_count, d_mel_offset,
+        d_mel_w, n_mel_w_given, d_dct, t.tw1, t.tw2, t.hann, d_out);
     GN_LAUNCHED(h);
     return GN_OK;
 }

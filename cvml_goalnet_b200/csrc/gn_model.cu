@@ -10,15 +10,16 @@
 // handle
 // ================================================================================================
 struct gn_handle_tables {
-    float2* twiddle;   // [64][32] lane-major: tw[k1 * 32 + n2] = exp(-2 pi i k1 n2 / 2048)  (gn_fft.cuh)
+    float2* tw1;       // [15][128] {wr, wi} of W_2048^(t k1), k1 = 1..15   (gn_fft2.cuh, pass 1)
+    float2* tw2;       // [15][8]   {wr, wi} of W_128^(n3 k2), k2 = 1..15   (pass 2)
     float* hann;       // [2048] periodic hann
 };
 static gn_handle_tables* tables_of(gn_handle* h) { return reinterpret_cast<gn_handle_tables*>(h + 1); }
 
-struct gn_mfcc_tables { const float2* twiddle; const float* hann; };
+struct gn_mfcc_tables { const float2* tw1; const float2* tw2; const float* hann; };
 gn_mfcc_tables gn_get_mfcc_tables(gn_handle* h) {
     gn_handle_tables* t = tables_of(h);
-    return gn_mfcc_tables{t->twiddle, t->hann};
+    return gn_mfcc_tables{t->tw1, t->tw2, t->hann};
 }
 
 extern "C" int gn_abi_version(void) { return GN_ABI_VERSION; }
@@ -61,23 +62,38 @@ extern "C" int gn_create(gn_handle** out, int device) {
         return GN_E_NODEVICE;
     }
     h->encode_tiled = fn;
-    // FFT tables, computed in double on the host
+    // FFT tables, computed in double on the host (one allocation: tw1 | tw2 | hann)
     gn_handle_tables* t = tables_of(h);
-    float2* tw = reinterpret_cast<float2*>(malloc(sizeof(float2) * 2048));
-    float* hn = reinterpret_cast<float*>(malloc(sizeof(float) * 2048));
-    for (int k1 = 0; k1 < 64; ++k1)
-        for (int n2 = 0; n2 < 32; ++n2) {
-            const double a = -2.0 * M_PI * (double)(k1 * n2) / 2048.0;
-            tw[k1 * 32 + n2] = make_float2((float)cos(a), (float)sin(a));
+    const int n1 = 15 * 128, n2 = 15 * 8;
+    float* host = reinterpret_cast<float*>(malloc(sizeof(float) * (size_t)(2 * (n1 + n2) + 2048)));
+    if (!host) { free(h); return GN_E_ARG; }
+    float* p1 = host;
+    float* p2 = host + 2 * n1;
+    float* hn = host + 2 * (n1 + n2);
+    for (int k1 = 1; k1 < 16; ++k1)
+        for (int tt = 0; tt < 128; ++tt) {
+            const double a = -2.0 * M_PI * (double)(tt * k1) / 2048.0;
+            float* e = p1 + 2 * ((k1 - 1) * 128 + tt);
+            e[0] = (float)cos(a);
+            e[1] = (float)sin(a);
+        }
+    for (int k2 = 1; k2 < 16; ++k2)
+        for (int n3 = 0; n3 < 8; ++n3) {
+            const double a = -2.0 * M_PI * (double)(n3 * k2) / 128.0;
+            float* e = p2 + 2 * ((k2 - 1) * 8 + n3);
+            e[0] = (float)cos(a);
+            e[1] = (float)sin(a);
         }
     for (int i = 0; i < 2048; ++i) hn[i] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * (double)i / 2048.0));
-    cudaError_t e = cudaMalloc(&t->twiddle, sizeof(float2) * 2048);
-    if (e == cudaSuccess) e = cudaMalloc(&t->hann, sizeof(float) * 2048);
-    if (e == cudaSuccess) e = cudaMemcpy(t->twiddle, tw, sizeof(float2) * 2048, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(t->hann, hn, sizeof(float) * 2048, cudaMemcpyHostToDevice);
-    free(tw);
-    free(hn);
-    if (e != cudaSuccess) { free(h); return (int)e; }
+    float* dev = nullptr;
+    const size_t bytes = sizeof(float) * (size_t)(2 * (n1 + n2) + 2048);
+    cudaError_t e = cudaMalloc(&dev, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(dev, host, bytes, cudaMemcpyHostToDevice);
+    free(host);
+    if (e != cudaSuccess) { if (dev) cudaFree(dev); free(h); return (int)e; }
+    t->tw1 = reinterpret_cast<float2*>(dev);
+    t->tw2 = reinterpret_cast<float2*>(dev + 2 * n1);
+    t->hann = dev + 2 * (n1 + n2);
     *out = h;
     return GN_OK;
 }
@@ -85,8 +101,7 @@ extern "C" int gn_create(gn_handle** out, int device) {
 extern "C" int gn_destroy(gn_handle* h) {
     if (!h) return GN_OK;
     gn_handle_tables* t = tables_of(h);
-    cudaFree(t->twiddle);
-    cudaFree(t->hann);
+    cudaFree(t->tw1);          // tw1 | tw2 | hann are one allocation
     gn_preprocess_free_plans(h);
     free(h);
     return GN_OK;

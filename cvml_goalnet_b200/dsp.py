@@ -14,7 +14,7 @@ N_FFT = 2048
 HOP = 512
 N_MELS = 128
 N_MFCC = 30
-MAX_Q = 64          # GN_MFCC_MAX_Q: STFT columns per frame slot the kernel's shared-memory tiles are sized for
+MAX_Q = 128         # GN_MFCC_MAX_Q: STFT columns per frame slot the kernel sizes its shared-memory tiles for
 
 
 def _hz_to_mel(f):

@@ -122,9 +122,11 @@ def get_frame_tensor(fp: str):
 def _audio_tables(sr: int, dev_index: int):
     dev = torch.device("cuda", dev_index)
     start, count, offset, w = dsp.mel_filterbank_csr(int(sr))
+    dct_t = np.zeros((dsp.N_MELS, 32), np.float32)              # transposed + padded: a warp's 32 coefficients are one line
+    dct_t[:, :dsp.N_MFCC] = dsp.dct_matrix().T
     return dict(start=torch.from_numpy(start).to(dev), count=torch.from_numpy(count).to(dev),
-                offset=torch.from_numpy(offset).to(dev), w=torch.from_numpy(w).to(dev),
-                dct=torch.from_numpy(dsp.dct_matrix()).to(dev))
+                offset=torch.from_numpy(offset).to(dev), w=torch.from_numpy(w).to(dev), n_w=int(w.size),
+                dct=torch.from_numpy(dct_t).to(dev))
 
 
 @lru_cache(maxsize=32)
@@ -205,7 +207,8 @@ def extract_audio_features_array(y, sr: int, n_frames: int, bin_length: int, dev
             _lib.check(_lib.load().gn_mfcc_resampled(
                 _h(dev), _ptr(yd), yd.numel(), _ptr(plan["start"][a:]), _ptr(plan["length"][a:]),
                 _ptr(plan["w_offset"][a:]), _ptr(plan["w"]), b - a, B, plan["max_q"], _ptr(tab["start"]),
-                _ptr(tab["count"]), _ptr(tab["offset"]), _ptr(tab["w"]), _ptr(tab["dct"]), _ptr(out[a:]), _stream(dev)),
+                _ptr(tab["count"]), _ptr(tab["offset"]), _ptr(tab["w"]), tab["n_w"], _ptr(tab["dct"]), _ptr(out[a:]),
+                _stream(dev)),
                 "gn_mfcc_resampled")
     return out.cpu().numpy() if as_numpy else out
 

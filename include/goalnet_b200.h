@@ -71,16 +71,17 @@ int gn_preprocess_u8_bgr(gn_handle* h, const uint8_t* d_frames, int64_t n, int H
  *              (q_i = 1 + len_i/512 STFT columns, 4 <= q_i <= GN_MFCC_MAX_Q)
  * d_w_offset : int32 [n]  offset (in floats) of slot i's row-major W (B x q_i) inside d_w
  * d_mel_*    : the mel filterbank in CSR-like form: for mel m, bins [start[m], start[m]+count[m])
- *              with weights d_mel_w[offset[m] ...]  (128 entries each)
- * d_dct      : float32 [30][128] DCT-II ortho rows
+ *              with weights d_mel_w[offset[m] ...]  (128 entries each); n_mel_w = length of d_mel_w (<= 2114: a bin
+ *              feeds at most two triangular filters)
+ * d_dct_t    : float32 [128][32] DCT-II ortho rows TRANSPOSED (element [m][c] = row c, mel m; columns 30, 31 zero)
  * d_out      : float32 [n][30][B]
  * ------------------------------------------------------------------------------------------- */
-#define GN_MFCC_MAX_Q 64
+#define GN_MFCC_MAX_Q 128
 int gn_mfcc_resampled(gn_handle* h, const float* d_y, int64_t n_samples, const int64_t* d_seg_start,
                       const int32_t* d_seg_len, const int32_t* d_w_offset, const float* d_w, int64_t n,
                       int B, int max_q, const int32_t* d_mel_start, const int32_t* d_mel_count,
-                      const int32_t* d_mel_offset, const float* d_mel_w, const float* d_dct, float* d_out,
-                      void* stream);
+                      const int32_t* d_mel_offset, const float* d_mel_w, int n_mel_w, const float* d_dct_t,
+                      float* d_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * (a3-a5) AVM forward, eval mode -- replaces utils.py:172-195 (VisBl), 214-227 (AudBl),

@@ -103,7 +103,8 @@ def test_expand_array_host():
 
 
 def test_fft_passes_host_check(tmp_path):
-    """gn_fft.cuh (the MFCC kernel's 2048-point Stockham FFT) run on the CPU against a direct DFT in double."""
+    """gn_fft2.cuh (the MFCC kernel's 2048-point FFT: 128 threads, 16 x 16 x 8, two transforms in the packed fp32 lanes)
+    run for every thread on the CPU against a direct DFT in double."""
     import shutil
     import subprocess
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
@@ -111,6 +112,6 @@ def test_fft_passes_host_check(tmp_path):
         pytest.skip("nvcc not available")
     exe = str(tmp_path / "fft_host_check")
     subprocess.run([nvcc, "-std=c++17", "-O2", "-Wno-deprecated-gpu-targets", "-o", exe,
-                    os.path.join(ROOT, "tests", "native", "fft_host_check.cu")], check=True)
+                    os.path.join(ROOT, "tests", "native", "fft2_host_check.cu")], check=True)
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
