@@ -112,6 +112,7 @@ SIGNATURES = {
     "gn_summary_indicator": (_I, [_P, _P, _P, _I, _L, _P, _P]),
     "gn_fscore_counts": (_I, [_P, _P, _P, _I, _L, _P, _P]),
     "gn_fusion_trainer_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_fusion_state), _I, _L, _P]),
+    "gn_fusion_trainer_create_head": (_I, [_P, C.POINTER(_P), C.POINTER(gn_fusion_state), _I, _L, _I, _P]),
     "gn_fusion_trainer_destroy": (_I, [_P]),
     "gn_fusion_param_count": (_L, [_P]),
     "gn_fusion_set_hyper": (_I, [_P, C.c_float, C.c_float, C.c_float, C.c_float]),

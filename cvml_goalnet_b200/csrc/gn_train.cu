@@ -32,10 +32,12 @@ struct gn_fusion_trainer {
     __nv_bfloat16 *a[5];           // a[k] = input of layer k, [max_n][kin[k]]
     __nv_bfloat16 *aT[4];          // a[k]^T, [kin[k]][max_n]
     __nv_bfloat16 *dz[4], *dzT[4]; // gradient w.r.t. the pre-activation of layer k: [max_n][nout[k]] and transposed
-    float *y, *dz4;                // sigmoid output and gradient of the last pre-activation, [max_n]
+    float *y, *dz4;                // sigmoid output and gradient of the last pre-activation, [max_n] ([max_n][5] classifier)
     double* sums;                  // [8] sum p, p^2, l, l^2, p*l
-    float* partial;                // [blocks][132] per-block partial sums of dW_4 / db_4
+    float* partial;                // [blocks][kPartStride] per-block partial sums of dW_4 / db_4
+    double* lpart;                 // [blocks] per-block partial sums of the classifier loss
     int partial_blocks;
+    int n_cls;                     // 1 = regression head (fusion.12 = Linear(128,1) + Sigmoid, 4y+1); 5 = classifier head
     long long step;
     float lr, beta1, beta2, eps;
     void* arena;
@@ -44,6 +46,8 @@ struct gn_fusion_trainer {
 namespace {
 
 constexpr int kLastThreads = 256;
+constexpr int kCls = 5;                       // importance levels 1..5 (utils.py:257, main.py:69,96-97)
+constexpr int kPartStride = 656;              // >= 5 * 128 + 5 partial sums per block (regression uses the first 129)
 
 // fp32 [n][K] -> bf16 [n][K] and bf16 [K][ld_t] (32 x 32 tiles through shared memory)
 __global__ void __launch_bounds__(256)
@@ -154,7 +158,133 @@ last_backward_kernel(const __nv_bfloat16* __restrict__ a4, const float* __restri
     if (threadIdx.x < 129) {
         float t = 0.f;
         for (int w = 0; w < kLastThreads / 32; ++w) t += s_part[w][threadIdx.x];
-        partial[(size_t)blockIdx.x * 132 + threadIdx.x] = t;
+        partial[(size_t)blockIdx.x * kPartStride + threadIdx.x] = t;
+    }
+}
+
+// Classifier head (the training half): fusion.12 = Linear(128, 5) + Softmax(dim = 1) (utils.py:257,
+// commented) trained with nn.CrossEntropyLoss (main.py:69,96: `criterion(batch_predictions, (batch_labels-1).long())`).
+//   loss_kind 2 -- AS WRITTEN: the criterion receives the model's OUTPUT, i.e. the softmax probabilities p, so the loss is
+//                  L_i = -log softmax(p_i)[y_i] (a second softmax inside CrossEntropyLoss);
+//                  dL/dp = (softmax(p) - onehot) / N, then through the model's softmax: dz_j = p_j (g_j - sum_k p_k g_k)
+//   loss_kind 3 -- cross-entropy on the logits: L_i = -log p_i[y_i], dz = (p - onehot) / N
+// One warp per row (4 features per lane); forward, loss, last-layer backward and layer 3's pre-activation gradient in
+// one pass; per-block partial sums of dW_4 [5][128], db_4 [5] and the loss, reduced in a fixed order afterwards.
+__global__ void __launch_bounds__(kLastThreads)
+cls_forward_backward_kernel(const __nv_bfloat16* __restrict__ a4, const float* __restrict__ w4, const float* __restrict__ b4,
+                            const float* __restrict__ labels, int64_t n, int loss_kind, float scale,
+                            float* __restrict__ probs, __nv_bfloat16* __restrict__ dz3, __nv_bfloat16* __restrict__ dzT3,
+                            int64_t ld_t, float* __restrict__ partial, double* __restrict__ lpart) {
+    __shared__ float s_w[kCls][128];
+    __shared__ float s_part[kLastThreads / 32][kCls * 128 + 8];
+    __shared__ double s_loss[kLastThreads / 32];
+    for (int i = threadIdx.x; i < kCls * 128; i += kLastThreads) s_w[i / 128][i % 128] = w4[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float inv_n = 1.f / (float)n;
+    float gw[kCls][4], gb[kCls];
+#pragma unroll
+    for (int k = 0; k < kCls; ++k) { gb[k] = 0.f; gw[k][0] = gw[k][1] = gw[k][2] = gw[k][3] = 0.f; }
+    double loss = 0.0;
+    for (int64_t row = (int64_t)blockIdx.x * (kLastThreads / 32) + warp; row < n; row += (int64_t)gridDim.x * (kLastThreads / 32)) {
+        const uint2 hv = *reinterpret_cast<const uint2*>(a4 + row * 128 + lane * 4);
+        const float2 h01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&hv.x));
+        const float2 h23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&hv.y));
+        const float hx[4] = {h01.x, h01.y, h23.x, h23.y};
+        float z[kCls];
+#pragma unroll
+        for (int k = 0; k < kCls; ++k) {
+            float d = hx[0] * s_w[k][lane * 4] + hx[1] * s_w[k][lane * 4 + 1] + hx[2] * s_w[k][lane * 4 + 2] +
+                      hx[3] * s_w[k][lane * 4 + 3];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+            z[k] = d + b4[k];
+        }
+        float zmax = z[0];
+#pragma unroll
+        for (int k = 1; k < kCls; ++k) zmax = fmaxf(zmax, z[k]);
+        float p[kCls], sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < kCls; ++k) { p[k] = expf(z[k] - zmax); sum += p[k]; }
+        const float inv = 1.f / sum;
+#pragma unroll
+        for (int k = 0; k < kCls; ++k) p[k] *= inv;
+        int yk = (int)labels[row] - 1;
+        yk = yk < 0 ? 0 : (yk > kCls - 1 ? kCls - 1 : yk);
+        float dz[kCls];
+        if (loss_kind == 2) {
+            // CrossEntropyLoss applied to the probabilities (values in [0,1]: no max subtraction needed)
+            float s2[kCls], sum2 = 0.f, py = 0.f;
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) { s2[k] = expf(p[k]); sum2 += s2[k]; py = (k == yk) ? p[k] : py; }
+            const float inv2 = 1.f / sum2;
+            float dot = 0.f, g[kCls];
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) {
+                g[k] = (s2[k] * inv2 - (k == yk ? 1.f : 0.f)) * inv_n;
+                dot = fmaf(p[k], g[k], dot);
+            }
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) dz[k] = p[k] * (g[k] - dot);
+            if (lane == 0) loss += (double)(logf(sum2) - py);
+        } else {
+            float zy = 0.f;
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) { dz[k] = (p[k] - (k == yk ? 1.f : 0.f)) * inv_n; zy = (k == yk) ? z[k] : zy; }
+            if (lane == 0) loss += (double)(logf(sum) + zmax - zy);
+        }
+        if (lane == 0 && probs)
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) probs[row * kCls + k] = p[k];
+        __nv_bfloat16 o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float back = 0.f;
+#pragma unroll
+            for (int k = 0; k < kCls; ++k) {
+                gw[k][i] = fmaf(dz[k], hx[i], gw[k][i]);
+                back = fmaf(dz[k], s_w[k][lane * 4 + i], back);
+            }
+            o[i] = __float2bfloat16(hx[i] > 0.f ? back * scale : 0.f);
+            dzT3[(int64_t)(lane * 4 + i) * ld_t + row] = o[i];
+        }
+        *reinterpret_cast<uint2*>(dz3 + row * 128 + lane * 4) = *reinterpret_cast<const uint2*>(o);
+#pragma unroll
+        for (int k = 0; k < kCls; ++k) gb[k] += dz[k];
+    }
+#pragma unroll
+    for (int k = 0; k < kCls; ++k) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s_part[warp][k * 128 + lane * 4 + i] = gw[k][i];
+        if (lane == 0) s_part[warp][kCls * 128 + k] = gb[k];
+    }
+    if (lane == 0) s_loss[warp] = loss;
+    __syncthreads();
+    for (int j = threadIdx.x; j < kCls * 128 + kCls; j += kLastThreads) {
+        float t = 0.f;
+        for (int w = 0; w < kLastThreads / 32; ++w) t += s_part[w][j];
+        partial[(size_t)blockIdx.x * kPartStride + j] = t;
+    }
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < kLastThreads / 32; ++w) t += s_loss[w];
+        lpart[blockIdx.x] = t;
+    }
+}
+
+// deterministic reduction of the classifier head's per-block partials into grads[W_4 | b_4]; mean loss
+__global__ void __launch_bounds__(256)
+cls_finalize_kernel(const float* __restrict__ partial, const double* __restrict__ lpart, int blocks, int64_t n,
+                    float* __restrict__ g_w4, float* __restrict__ g_b4, double* __restrict__ loss) {
+    for (int j = threadIdx.x; j < kCls * 128 + kCls; j += 256) {
+        float t = 0.f;
+        for (int b = 0; b < blocks; ++b) t += partial[(size_t)b * kPartStride + j];
+        if (j < kCls * 128) g_w4[j] = t; else g_b4[j - kCls * 128] = t;
+    }
+    if (threadIdx.x == 255 && loss) {
+        double t = 0.0;
+        for (int b = 0; b < blocks; ++b) t += lpart[b];
+        *loss = t / (double)n;
     }
 }
 
@@ -165,7 +295,7 @@ last_finalize_kernel(const float* __restrict__ partial, int blocks, const double
     const int j = threadIdx.x;
     if (j < 129) {
         float t = 0.f;
-        for (int b = 0; b < blocks; ++b) t += partial[(size_t)b * 132 + j];
+        for (int b = 0; b < blocks; ++b) t += partial[(size_t)b * kPartStride + j];
         if (j < 128) g_w4[j] = t; else g_b4[0] = t;
     }
     if (j == 159 && loss) {
@@ -253,16 +383,22 @@ int repack_all(gn_fusion_trainer* t, cudaStream_t st) {
 // ================================================================================================
 extern "C" int gn_fusion_trainer_create(gn_handle* h, gn_fusion_trainer** out, const gn_fusion_state* sd, int fin,
                                         int64_t max_rows, void* stream) {
+    return gn_fusion_trainer_create_head(h, out, sd, fin, max_rows, 1, stream);
+}
+
+extern "C" int gn_fusion_trainer_create_head(gn_handle* h, gn_fusion_trainer** out, const gn_fusion_state* sd, int fin,
+                                             int64_t max_rows, int n_classes, void* stream) {
     if (!h || !out || !sd || max_rows <= 0) return GN_E_ARG;
     if (fin != 640 && fin != 512) return GN_E_SHAPE;
+    if (n_classes != 1 && n_classes != kCls) return GN_E_SHAPE;
     *out = nullptr;
     for (int k = 0; k < 5; ++k)
         if (!sd->weight[k] || !sd->bias[k]) return GN_E_ARG;
     gn_fusion_trainer* t = reinterpret_cast<gn_fusion_trainer*>(calloc(1, sizeof(gn_fusion_trainer)));
     if (!t) return GN_E_ARG;
-    t->h = h; t->fin = fin;
+    t->h = h; t->fin = fin; t->n_cls = n_classes;
     t->max_n = (max_rows + 127) / 128 * 128;
-    const int kin[5] = {fin, 512, 512, 256, 128}, nout[5] = {512, 512, 256, 128, 1};
+    const int kin[5] = {fin, 512, 512, 256, 128}, nout[5] = {512, 512, 256, 128, n_classes};
     int64_t off = 0;
     for (int k = 0; k < 5; ++k) {
         t->kin[k] = kin[k]; t->nout[k] = nout[k];
@@ -284,7 +420,8 @@ extern "C" int gn_fusion_trainer_create(gn_handle* h, gn_fusion_trainer** out, c
         o_dz[k] = take((size_t)t->max_n * nout[k] * 2);
         o_dzT[k] = take((size_t)t->max_n * nout[k] * 2);
     }
-    const size_t o_y = take(t->max_n * 4), o_dz4 = take(t->max_n * 4), o_sums = take(64), o_part = take((size_t)t->partial_blocks * 132 * 4);
+    const size_t o_y = take(t->max_n * 4 * kCls), o_dz4 = take(t->max_n * 4), o_sums = take(64),
+                 o_part = take((size_t)t->partial_blocks * kPartStride * 4), o_lpart = take((size_t)t->partial_blocks * 8);
     cudaError_t e = cudaMalloc(&t->arena, bytes);
     if (e != cudaSuccess) { free(t); return (int)e; }
     char* base = reinterpret_cast<char*>(t->arena);
@@ -306,6 +443,7 @@ extern "C" int gn_fusion_trainer_create(gn_handle* h, gn_fusion_trainer** out, c
     t->dz4 = reinterpret_cast<float*>(base + o_dz4);
     t->sums = reinterpret_cast<double*>(base + o_sums);
     t->partial = reinterpret_cast<float*>(base + o_part);
+    t->lpart = reinterpret_cast<double*>(base + o_lpart);
     for (int k = 0; k < 5 && e == cudaSuccess; ++k) {
         e = cudaMemcpyAsync(t->params + t->off_w[k], sd->weight[k], (size_t)nout[k] * kin[k] * 4, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess)
@@ -346,6 +484,9 @@ extern "C" int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_f
     if (!t || n <= 0 || !d_features || !d_labels || !d_grads) return GN_E_ARG;
     if (n > t->max_n) return GN_E_WORKSPACE;
     if (dropout_p < 0.f || dropout_p >= 1.f) return GN_E_ARG;
+    // fixed_loss doubles as the loss kind: 0 = MSE as written (N x N broadcast), 1 = element-wise MSE (regression head);
+    // 2 = CrossEntropyLoss on the softmax output as written, 3 = cross-entropy on the logits (classifier head)
+    if (t->n_cls == 1 ? (fixed_loss != 0 && fixed_loss != 1) : (fixed_loss != 2 && fixed_loss != 3)) return GN_E_ARG;
     gn_handle* h = t->h;
     cudaStream_t st = gn_stream(stream);
     const float keep = 1.f - dropout_p;
@@ -369,6 +510,15 @@ extern "C" int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_f
     GN_CUDA(cudaMemsetAsync(t->sums, 0, 64, st));
     int blocks = (int)((n + kLastThreads / 32 - 1) / (kLastThreads / 32));
     if (blocks > t->partial_blocks) blocks = t->partial_blocks;
+    if (t->n_cls == kCls) {
+        cls_forward_backward_kernel<<<blocks, kLastThreads, 0, st>>>(
+            t->a[4], t->params + t->off_w[4], t->params + t->off_b[4], d_labels, n, fixed_loss, scale, d_scores,
+            t->dz[3], t->dzT[3], ld, t->partial, t->lpart);
+        GN_LAUNCHED(h);
+        cls_finalize_kernel<<<1, 256, 0, st>>>(t->partial, t->lpart, blocks, n, d_grads + t->off_w[4],
+                                               d_grads + t->off_b[4], d_loss);
+        GN_LAUNCHED(h);
+    } else {
     last_forward_kernel<<<blocks, kLastThreads, 0, st>>>(t->a[4], t->params + t->off_w[4], t->params + t->off_b[4],
                                                         d_labels, n, t->y, d_scores, t->sums);
     GN_LAUNCHED(h);
@@ -378,6 +528,7 @@ extern "C" int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_f
     last_finalize_kernel<<<1, 160, 0, st>>>(t->partial, blocks, t->sums, n, fixed_loss, d_grads + t->off_w[4],
                                             d_grads + t->off_b[4], d_loss);
     GN_LAUNCHED(h);
+    }
     // the weight-gradient GEMMs reduce over K = n rounded up to 64: zero the pad columns of the transposed operands
     // (a previous call with a larger n may have left values there)
     const int64_t kred = (n + 63) / 64 * 64;

@@ -29,6 +29,9 @@ class FusionTrainer:
 
     fixed_loss=False reproduces the reference's loss as written: MSELoss(pred (N,1), labels (N,)) broadcasts to
     N x N (quirk Q5).  dropout_p is the reference's 0.2 (utils.py:245-254); 0 disables it.
+    With a `CAVM` model (fusion.12 = Linear(128,5) + Softmax, the reference's commented classifier variant) the loss is
+    nn.CrossEntropyLoss: fixed_loss=False applies it to the model's softmax OUTPUT with target labels-1, exactly what
+    un-commenting main.py:69,96 computes; fixed_loss=True applies it to the logits.  `scores` is then (N,5).
     process_group: torch.distributed group for data-parallel training (None = the default group when
     torch.distributed is initialised, False = never reduce); gradients are averaged over its ranks.
     """
@@ -38,6 +41,7 @@ class FusionTrainer:
         self.dev = _device(device)
         self.model = model
         self.fin = 640 if model.audio_included else 512
+        self.n_cls = int(getattr(model, "OUT_COLS", 1))
         self.fixed_loss = bool(fixed_loss)
         self.dropout_p = float(dropout_p)
         self.group = process_group
@@ -56,14 +60,15 @@ class FusionTrainer:
             st.bias[k] = b.data_ptr()
         p = C.c_void_p()
         with torch.cuda.device(self.dev):
-            _lib.check(lib.gn_fusion_trainer_create(_lib.handle(self.dev.index), C.byref(p), C.byref(st), self.fin,
-                                                    self.max_rows, _stream(self.dev)), "gn_fusion_trainer_create")
+            _lib.check(lib.gn_fusion_trainer_create_head(_lib.handle(self.dev.index), C.byref(p), C.byref(st), self.fin,
+                                                         self.max_rows, self.n_cls, _stream(self.dev)),
+                       "gn_fusion_trainer_create_head")
             torch.cuda.current_stream(self.dev).synchronize()      # `keep` may be freed after this
         self._t = p
         _lib.check(lib.gn_fusion_set_hyper(self._t, lr, betas[0], betas[1], eps), "gn_fusion_set_hyper")
         self.n_params = int(lib.gn_fusion_param_count(self._t))
         self.grads = torch.zeros(self.n_params, dtype=torch.float32, device=self.dev)
-        self.scores = torch.empty(self.max_rows, dtype=torch.float32, device=self.dev)
+        self.scores = torch.empty(self.max_rows * self.n_cls, dtype=torch.float32, device=self.dev)
         self.loss = torch.zeros(1, dtype=torch.float64, device=self.dev)
 
     def __del__(self):
@@ -95,7 +100,8 @@ class FusionTrainer:
         seed = (self.seed + 0x9E3779B97F4A7C15 * (self.steps + 1)) & 0xFFFFFFFFFFFFFFFF
         with torch.cuda.device(self.dev):
             _lib.check(_lib.load().gn_fusion_forward_backward(
-                self._t, _ptr(x), _ptr(lab), n, int(self.fixed_loss), self.dropout_p, marg, seed, _ptr(self.grads),
+                self._t, _ptr(x), _ptr(lab), n, int(self.fixed_loss) + (2 if self.n_cls > 1 else 0), self.dropout_p, marg,
+                seed, _ptr(self.grads),
                 _ptr(self.scores), _ptr(self.loss), _stream(self.dev)), "gn_fusion_forward_backward")
         return n
 
@@ -118,7 +124,7 @@ class FusionTrainer:
         """One train step (main.py:187-193).  Returns (loss tensor float64[1] on the device, predictions (N,1))."""
         n = self.forward_backward(features, labels, masks)
         self.optimizer_step()
-        return self.loss, self.scores[:n].reshape(n, 1)
+        return self.loss, self.scores[:n * self.n_cls].reshape(n, self.n_cls)
 
     # ------------------------------------------------------------------------------------------------
     def flat_params(self) -> torch.Tensor:

@@ -237,15 +237,24 @@ typedef struct gn_fusion_state {
 /* fin = 640 (audio included) or 512; max_rows = largest batch a step will be called with. */
 int gn_fusion_trainer_create(gn_handle* h, gn_fusion_trainer** out, const gn_fusion_state* sd, int fin,
                              int64_t max_rows, void* stream);
+/* The same with a choice of head: n_classes = 1 is the regression head above (fusion.12 = Linear(128,1)
+ * + Sigmoid + 4y+1); n_classes = 5 is the classifier head the reference keeps as commented lines (utils.py:257
+ * `nn.Softmax(dim = 1)`, main.py:69 `nn.CrossEntropyLoss()`, main.py:96 `criterion(batch_predictions,
+ * (batch_labels-1).long())`): fusion.12 = Linear(128,5) ([5][128] weight, [5] bias) + Softmax. */
+int gn_fusion_trainer_create_head(gn_handle* h, gn_fusion_trainer** out, const gn_fusion_state* sd, int fin,
+                                  int64_t max_rows, int n_classes, void* stream);
 int gn_fusion_trainer_destroy(gn_fusion_trainer* t);
 int64_t gn_fusion_param_count(const gn_fusion_trainer* t);
 /* torch.optim.Adam hyper-parameters; defaults lr 1e-3, betas (0.9, 0.999), eps 1e-8. */
 int gn_fusion_set_hyper(gn_fusion_trainer* t, float lr, float beta1, float beta2, float eps);
 /* Copy the float32 master parameters (flat, order above) to d_out. */
 int gn_fusion_get_params(gn_fusion_trainer* t, float* d_out, void* stream);
-/* d_features float32 [n][fin]; d_labels float32 [n]; d_grads float32 [param_count] (out);
- * d_scores float32 [n] predictions in [1,5] (out, may be NULL); d_loss double[1] on the device (out,
- * may be NULL); d_masks: NULL or 4 device pointers. */
+/* d_features float32 [n][fin]; d_labels float32 [n] (importance 1..5); d_grads float32 [param_count] (out);
+ * d_scores float32 [n] predictions in [1,5] -- or [n][5] class probabilities with the classifier head -- (out, may be
+ * NULL); d_loss double[1] on the device (out, may be NULL); d_masks: NULL or 4 device pointers.
+ * fixed_loss selects the loss: regression head 0 = nn.MSELoss as written (pred (N,1) vs labels (N,) broadcast to N x N,
+ * SURVEY quirk Q5), 1 = element-wise MSE; classifier head 2 = nn.CrossEntropyLoss as written (applied to the model's
+ * softmax OUTPUT with target labels-1, main.py:96), 3 = cross-entropy on the logits. */
 int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_features, const float* d_labels, int64_t n,
                                int fixed_loss, float dropout_p, const uint8_t* const* d_masks,
                                unsigned long long seed, float* d_grads, float* d_scores, double* d_loss,

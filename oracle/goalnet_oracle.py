@@ -449,12 +449,17 @@ def fusion_flat(sd: dict) -> np.ndarray:
 
 
 def fusion_train_steps(sd: dict, features, labels, steps: int = 1, fixed_loss: bool = False, masks=None,
-                       dropout_p: float = 0.2, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+                       dropout_p: float = 0.2, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                       classifier: bool = False):
     """`steps` iterations of  optimizer.zero_grad(); pred = fusion(x); loss = MSELoss()(pred, labels);
     loss.backward(); optimizer.step()  (main.py:187-193) with optim.Adam(lr) (main.py:70) in float32 on the CPU.
     As written pred is (N,1) and labels (N,), so MSELoss broadcasts to N x N (quirk Q5); fixed_loss
     compares element-wise.  Dropout(0.2) (utils.py:245-254): `masks` = per step a list of four uint8
     keep-masks applied as x * mask / (1 - p); None = dropout off (eval-mode forward).
+    classifier=True is the reference's commented classifier variant: fusion.12 = Linear(128,5) followed by
+    nn.Softmax(dim=1) (utils.py:257) and `criterion = nn.CrossEntropyLoss()` (main.py:69) called as
+    `criterion(batch_predictions, (batch_labels-1).long())` (main.py:96), i.e. ON THE SOFTMAX OUTPUT as written;
+    fixed_loss then applies the criterion to the logits instead.  Predictions are the (N,5) probabilities.
     Returns (losses [steps], grads of the FIRST step (flat), predictions of the first step, final flat params)."""
     import torch
     import warnings
@@ -462,7 +467,7 @@ def fusion_train_steps(sd: dict, features, labels, steps: int = 1, fixed_loss: b
     bs = [torch.tensor(np.asarray(sd[k + ".bias"], np.float32), requires_grad=True) for k in FUSION_KEYS]
     params = [p for pair in zip(ws, bs) for p in pair]
     opt = torch.optim.Adam(params, lr=lr, betas=betas, eps=eps)
-    crit = torch.nn.MSELoss()
+    crit = torch.nn.CrossEntropyLoss() if classifier else torch.nn.MSELoss()
     x0 = torch.as_tensor(np.asarray(features, np.float32))
     lab = torch.as_tensor(np.asarray(labels, np.float32))
     losses, grads0, pred0 = [], None, None
@@ -473,14 +478,19 @@ def fusion_train_steps(sd: dict, features, labels, steps: int = 1, fixed_loss: b
             h = torch.relu(h @ ws[k].T + bs[k])
             if masks is not None:
                 h = h * torch.as_tensor(np.asarray(masks[s][k], np.float32)) / (1.0 - dropout_p)
-        pred = 4 * torch.sigmoid(h @ ws[4].T + bs[4]) + 1            # (N,1), utils.py:256,270
-        with warnings.catch_warnings():
-            warnings.simplefilter("ignore")                          # the reference's broadcasting UserWarning
-            loss = crit(pred, lab) if not fixed_loss else crit(pred[:, 0], lab)
+        if classifier:
+            logits = h @ ws[4].T + bs[4]
+            pred = torch.softmax(logits, dim=1)                      # nn.Softmax(dim = 1), utils.py:257
+            loss = crit(logits if fixed_loss else pred, (lab - 1).long())     # main.py:96
+        else:
+            pred = 4 * torch.sigmoid(h @ ws[4].T + bs[4]) + 1        # (N,1), utils.py:256,270
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")                      # the reference's broadcasting UserWarning
+                loss = crit(pred, lab) if not fixed_loss else crit(pred[:, 0], lab)
         loss.backward()
         if s == 0:
             grads0 = np.concatenate([p.grad.detach().numpy().ravel() for p in params])
-            pred0 = pred.detach().numpy()[:, 0].copy()
+            pred0 = pred.detach().numpy().copy() if classifier else pred.detach().numpy()[:, 0].copy()
         opt.step()
         losses.append(float(loss.item()))
     flat = np.concatenate([p.detach().numpy().ravel() for p in params])

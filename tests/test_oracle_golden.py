@@ -176,3 +176,38 @@ def test_mfcc_restatement_matches_independent_implementation(golden):
         out = O.mfcc(y, sr)
         assert out.shape == ref.shape == (30, 1 + len(y) // 512), name
         np.testing.assert_allclose(out, ref, rtol=1e-4, atol=5e-4, err_msg=name)
+
+
+def test_classifier_training_oracle_is_the_uncommented_reference_lines():
+    """The oracle's classifier train step against the torch modules the reference's commented lines name:
+    nn.Softmax(dim = 1) as the last layer of the Sequential (utils.py:257), nn.CrossEntropyLoss() (main.py:69) applied to
+    the model output with target (labels - 1).long() (main.py:96), optim.Adam(lr = 0.001) (main.py:70)."""
+    import torch
+    import torch.nn as nn
+    from cvml_goalnet_b200 import synthetic as syn
+    rng = np.random.default_rng(5)
+    w = dict(syn.make_weights(seed=0))
+    w["fusion.12.weight"] = (rng.standard_normal((5, 128)) * 0.3).astype(np.float32)
+    w["fusion.12.bias"] = (rng.standard_normal(5) * 0.1).astype(np.float32)
+    x = np.abs(rng.standard_normal((40, 640))).astype(np.float32)
+    lab = rng.integers(1, 6, 40).astype(np.float32)
+    seq = nn.Sequential(nn.Linear(640, 512), nn.ReLU(), nn.Dropout(0.2), nn.Linear(512, 512), nn.ReLU(), nn.Dropout(0.2),
+                        nn.Linear(512, 256), nn.ReLU(), nn.Dropout(0.2), nn.Linear(256, 128), nn.ReLU(), nn.Dropout(0.2),
+                        nn.Linear(128, 5), nn.Softmax(dim=1))
+    seq.load_state_dict({k[len("fusion."):]: torch.as_tensor(v) for k, v in w.items() if k.startswith("fusion.")})
+    seq.eval()                                   # dropout off: the vectors must be reproducible
+    opt = torch.optim.Adam(seq.parameters(), lr=0.001)
+    crit = nn.CrossEntropyLoss()
+    losses = []
+    for _ in range(2):
+        opt.zero_grad()
+        pred = seq(torch.as_tensor(x))
+        loss = crit(pred, (torch.as_tensor(lab) - 1).long())
+        loss.backward()
+        opt.step()
+        losses.append(float(loss.item()))
+    o_losses, _, o_pred, o_flat = O.fusion_train_steps(w, x, lab, steps=2, classifier=True, masks=None)
+    assert np.allclose(o_losses, losses, rtol=1e-6)
+    flat = np.concatenate([p.detach().numpy().ravel() for p in seq.parameters()])
+    # Adam divides by sqrt(v): parameters whose gradient is ~0 move by up to lr whatever the summation order of the matmul
+    assert np.abs(o_flat - flat).max() <= 1e-4 and np.mean(np.abs(o_flat - flat)) <= 1e-7

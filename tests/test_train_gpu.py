@@ -98,6 +98,58 @@ def test_train_step_vs_oracle(n, fixed, drop):
     assert np.allclose([l0, l1], ref_losses, rtol=5e-3, atol=1e-5)
 
 
+@pytest.mark.parametrize("n,fixed,drop", [(256, False, False), (300, True, False), (130, False, True), (2048, True, True)])
+def test_classifier_head_cross_entropy_step_vs_oracle(n, fixed, drop):
+    """SURVEY 8f N3, training half: CAVM (fusion.12 = Linear(128,5) + Softmax, utils.py:257) trained with
+    nn.CrossEntropyLoss (main.py:69,96).  fixed=False is the loss AS WRITTEN -- the criterion applied to the model's softmax
+    output with target labels-1 --, fixed=True the criterion on the logits.  Probabilities <= 5e-3 abs, loss <= 5e-3
+    relative; per-tensor gradient error <= 0.15 and overall cosine >= 0.99: like the element-wise MSE, the per-sample terms
+    (p - onehot) have mixed signs and largely cancel over the batch, which amplifies the bf16 rounding of the hidden
+    layers' operands (module docstring); two Adam steps."""
+    from cvml_goalnet_b200 import utils as U
+    from cvml_goalnet_b200.train import FusionTrainer
+    w = dict(syn.make_weights(seed=0))
+    rng = np.random.default_rng(900 + n)
+    w["fusion.12.weight"] = (rng.standard_normal((5, 128)) * 0.3).astype(np.float32)
+    w["fusion.12.bias"] = (rng.standard_normal(5) * 0.1).astype(np.float32)
+    m = U.CAVM(True)
+    m.load_state_dict(w)
+    x = np.abs(rng.standard_normal((n, 640))).astype(np.float32)
+    lab = rng.integers(1, 6, n).astype(np.float32)
+    masks = [[(rng.random((n, wd)) < 0.8).astype(np.uint8) for wd in (512, 512, 256, 128)] for _ in range(2)] if drop else None
+    tr = FusionTrainer(m, max_rows=2048, fixed_loss=fixed, dropout_p=0.2 if drop else 0.0, process_group=False)
+    assert tr.n_params == 640 * 512 + 512 + 512 * 512 + 512 + 256 * 512 + 256 + 128 * 256 + 128 + 5 * 128 + 5
+    ref_losses, ref_grads, ref_pred, ref_flat = O.fusion_train_steps(w, x, lab, steps=2, fixed_loss=fixed, masks=masks,
+                                                                     classifier=True)
+    nn = tr.forward_backward(x, lab, masks[0] if drop else None)
+    probs = tr.scores[:nn * 5].reshape(nn, 5).cpu().numpy()
+    assert np.abs(probs.sum(1) - 1).max() <= 1e-5
+    assert np.abs(probs - ref_pred).max() <= 5e-3
+    grads = tr.grads.cpu().numpy()
+    sizes = [512 * 640, 512, 512 * 512, 512, 256 * 512, 256, 128 * 256, 128, 5 * 128, 5]
+    off = 0
+    for sz in sizes:
+        g, r = grads[off:off + sz].astype(np.float64), ref_grads[off:off + sz].astype(np.float64)
+        assert np.linalg.norm(g - r) <= 0.15 * max(np.linalg.norm(r), 1e-12), (off, np.linalg.norm(g - r) / np.linalg.norm(r))
+        off += sz
+    assert off == grads.size
+    assert float(np.dot(grads, ref_grads) / (np.linalg.norm(grads) * np.linalg.norm(ref_grads))) >= 0.99
+    tr.optimizer_step()
+    l0 = float(tr.loss.item())
+    _, pred = tr.step(x, lab, masks[1] if drop else None)
+    l1 = float(tr.loss.item())
+    assert pred.shape == (n, 5)
+    assert np.allclose([l0, l1], ref_losses, rtol=5e-3, atol=1e-5)
+    # the trained head goes back into the scoring model: predictions are argmax + 1 (main.py:97)
+    tr.sync_model()
+    assert tuple(m.state_dict()["fusion.12.weight"].shape) == (5, 128)
+    p_after = tr.flat_params().cpu().numpy()
+    # two Adam steps move every parameter by at most ~2 lr = 2e-3; where a gradient is ~0 its bf16 sign can differ, so two
+    # runs may end 4e-3 apart there -- but only there: the mean distance is a small fraction of one step
+    d = np.abs(p_after - ref_flat)
+    assert d.max() <= 4.2e-3 and d.mean() <= 3e-4, (d.max(), d.mean())
+
+
 def test_smaller_batch_after_larger_one_and_internal_dropout():
     """pad columns of the transposed operands are re-zeroed; the built-in dropout generator keeps ~80 %."""
     from cvml_goalnet_b200.train import FusionTrainer
