@@ -743,7 +743,7 @@ def train_arm(args, rank, world, local_rank):
     g.manual_seed(12344321 + rank)
     x = torch.randn((n, 640), generator=g, device=dev)
     lab = torch.randint(1, 6, (n,), generator=g, device=dev).float()
-    tr = FusionTrainer(model, max_rows=n, dropout_p=0.2, device=dev)
+    tr = FusionTrainer(model, max_rows=n, dropout_p=0.2, device=dev, use_graph=not args.no_graph)
     x_host = torch.empty(x.shape, dtype=torch.float32).pin_memory()
     lab_host = torch.empty(lab.shape, dtype=torch.float32).pin_memory()
     x_host.copy_(x); lab_host.copy_(lab)
@@ -937,7 +937,7 @@ def avm_train_arm(args, rank, world, local_rank):
     lab_h = torch.from_numpy(rng.integers(1, 6, n).astype(np.float32)).pin_memory()
     vis, aud, lab = vis_h.to(dev), aud_h.to(dev), lab_h.to(dev)
     vis_in, aud_in, lab_in = torch.empty_like(vis), torch.empty_like(aud), torch.empty_like(lab)
-    tr = AVMTrainer(model, max_frames=n, dropout_p=0.2, device=dev)
+    tr = AVMTrainer(model, max_frames=n, dropout_p=0.2, device=dev, use_graph=not args.no_graph)
     loss_host = torch.empty(1, dtype=torch.float64).pin_memory()
 
     hz = Harness(dev, world, local_rank)
@@ -1023,6 +1023,7 @@ def main():
     ap.add_argument("--chunk-frames", type=int, default=21600, help="config 3: frames per forward chunk on a rank")
     ap.add_argument("--e2e-matches", type=int, default=16, help="config 3: matches per step of the pinned-host e2e leg")
     ap.add_argument("--no-share", action="store_true", help="N = 1: skip the config-3 share sub-measurement")
+    ap.add_argument("--no-graph", action="store_true", help="training workloads: issue every launch instead of replaying a CUDA graph")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -177,5 +177,14 @@ def handle(device_index: int = 0):
     return h
 
 
+_graph_launches = {}      # device index -> kernel launches executed by CUDA-graph replays (not seen by the library)
+
+
+def add_graph_launches(device_index: int, n: int):
+    _graph_launches[device_index] = _graph_launches.get(device_index, 0) + int(n)
+
+
 def launch_count(device_index: int = 0) -> int:
-    return int(load().gn_launch_count(handle(device_index)))
+    """Kernel launches of this library on the device: issued directly (counted by the library) plus those executed by
+    replays of captured CUDA graphs (counted per replay from the number of launches recorded during the capture)."""
+    return int(load().gn_launch_count(handle(device_index))) + _graph_launches.get(device_index, 0)

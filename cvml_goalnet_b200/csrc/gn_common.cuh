@@ -46,6 +46,16 @@ void gn_preprocess_free_plans(gn_handle* h);
 
 static inline cudaStream_t gn_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// Per-trainer optimizer state that lives ON THE DEVICE so that a whole train step can be captured once in a CUDA graph
+// and replayed: the Adam step count with its bias corrections, and the bump added to the dropout seed each step
+// (a value baked into a captured kernel's arguments would repeat the same step forever).
+struct gn_step_state {
+    unsigned long long seed_bump;   // added to every dropout seed of the step; advanced by gn_launch_step_advance
+    long long step;                 // Adam step count t
+    float bc1, bc2;                 // 1 - beta1^t, 1 - beta2^t
+};
+int gn_launch_step_advance(gn_handle* h, gn_step_state* d_state, float beta1, float beta2, cudaStream_t st);   // gn_train.cu
+
 // ---- model object ------------------------------------------------------------------------------
 // Geometry of VisBl at S=40 (reference utils.py:151-164): conv1 k3 s3 p3 -> 15x15, pool -> 13x13,
 // conv2 p1 -> 13x13, pool -> 11x11, conv3 p1 -> 11x11, pool -> 9x9, flatten 512*81 = 41472.

@@ -75,6 +75,7 @@ struct GemmArgs {
     float scale;             // dropout scale 1/(1-p) (1 = no dropout)
     float keep_prob;         // kTrainFwd without mask: P(keep); >= 1 disables dropout
     unsigned long long seed;
+    const gn_step_state* step_state;   // kTrainFwd without mask: device-side seed bump (CUDA-graph replay), or null
     int kblocked;            // linear modes: A and W are K-blocked (gn_a3_off / gn_w5_off): every TMA box is contiguous
     int k_splits;            // kSplitK: number of K ranges (1 otherwise)
     int64_t split_stride;    // kSplitK: elements between the partial-sum slabs (M * N)
@@ -457,10 +458,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                     x[v * 16 + i] = ((w4[i >> 2] >> ((i & 3) * 8)) & 0xFFu) ? x[v * 16 + i] * args.scale : 0.f;
                             }
                         } else {
+                            const unsigned long long seed_now = args.seed + (args.step_state ? args.step_state->seed_bump : 0ull);
 #pragma unroll
                             for (int i = 0; i < 32; ++i) {
                                 // splitmix64 of (seed, element index) -> 24 uniform bits
-                                unsigned long long zz = args.seed + (unsigned long long)(e0 + i) * 0x9E3779B97F4A7C15ull;
+                                unsigned long long zz = seed_now + (unsigned long long)(e0 + i) * 0x9E3779B97F4A7C15ull;
                                 zz = (zz ^ (zz >> 30)) * 0xBF58476D1CE4E5B9ull;
                                 zz = (zz ^ (zz >> 27)) * 0x94D049BB133111EBull;
                                 zz ^= zz >> 31;
@@ -878,7 +880,8 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
 int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, int K, int64_t lda,
                      const __nv_bfloat16* B, int N, int64_t ldb, const float* bias, __nv_bfloat16* out,
                      __nv_bfloat16* out_t, int64_t ld_t, float* out_f32, const __nv_bfloat16* gate,
-                     const uint8_t* mask, float scale, float keep_prob, unsigned long long seed, cudaStream_t st) {
+                     const uint8_t* mask, float scale, float keep_prob, unsigned long long seed, cudaStream_t st,
+                     const gn_step_state* step_state) {
     constexpr int BN = 128;
     if (K % kBK || N % BN || M <= 0) return GN_E_SHAPE;
     CUtensorMap ta, tb;
@@ -889,6 +892,7 @@ int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, 
     GemmArgs a{};
     a.M = M; a.N = N; a.K = K; a.bias = bias; a.out = out; a.ld_out = N; a.col_off = 0; a.out_f32 = out_f32;
     a.out_t = out_t; a.ld_t = ld_t; a.gate = gate; a.mask = mask; a.scale = scale; a.keep_prob = keep_prob; a.seed = seed;
+    a.step_state = step_state;
     const int64_t tiles = ((M + 127) / 128) * (N / BN);
     switch (mode) {
         case kTrainFwd: return launch<1, BN, 4, kTrainFwd, 0>(h, ta, tb, a, tiles, st);

@@ -19,7 +19,8 @@
 int gn_tc_train_gemm(gn_handle* h, int mode, const __nv_bfloat16* A, int64_t M, int K, int64_t lda,
                      const __nv_bfloat16* B, int N, int64_t ldb, const float* bias, __nv_bfloat16* out,
                      __nv_bfloat16* out_t, int64_t ld_t, float* out_f32, const __nv_bfloat16* gate,
-                     const uint8_t* mask, float scale, float keep_prob, unsigned long long seed, cudaStream_t st);
+                     const uint8_t* mask, float scale, float keep_prob, unsigned long long seed, cudaStream_t st,
+                     const gn_step_state* step_state = nullptr);
 
 struct gn_fusion_trainer {
     gn_handle* h;
@@ -38,10 +39,25 @@ struct gn_fusion_trainer {
     double* lpart;                 // [blocks] per-block partial sums of the classifier loss
     int partial_blocks;
     int n_cls;                     // 1 = regression head (fusion.12 = Linear(128,1) + Sigmoid, 4y+1); 5 = classifier head
-    long long step;
+    long long step;                // host copy of the count (the arithmetic uses the device copy in `state`)
+    gn_step_state* state;          // device: Adam step count, bias corrections, dropout seed bump (CUDA-graph safe)
     float lr, beta1, beta2, eps;
     void* arena;
 };
+
+__global__ void step_advance_kernel(gn_step_state* s, float b1, float b2) {
+    const long long t = s->step + 1;
+    s->step = t;
+    s->bc1 = (float)(1.0 - pow((double)b1, (double)t));
+    s->bc2 = (float)(1.0 - pow((double)b2, (double)t));
+    s->seed_bump += 0x9E3779B97F4A7C15ull;
+}
+
+int gn_launch_step_advance(gn_handle* h, gn_step_state* d_state, float beta1, float beta2, cudaStream_t st) {
+    step_advance_kernel<<<1, 1, 0, st>>>(d_state, beta1, beta2);
+    GN_LAUNCHED(h);
+    return GN_OK;
+}
 
 namespace {
 
@@ -331,9 +347,10 @@ rowsum_kernel(const __nv_bfloat16* __restrict__ xt, int rows, int64_t n, int64_t
 // torch.optim.Adam (no weight decay, no amsgrad) on the flat parameter vector
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
-            int64_t count, float grad_scale, float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt) {
+            int64_t count, float grad_scale, float lr, float b1, float b2, float eps, const gn_step_state* __restrict__ state) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
+    const float bc1 = state->bc1, bc2_sqrt = sqrtf(state->bc2);
     const float gi = g[i] * grad_scale;
     const float mi = b1 * m[i] + (1.f - b1) * gi;
     const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
@@ -420,6 +437,7 @@ extern "C" int gn_fusion_trainer_create_head(gn_handle* h, gn_fusion_trainer** o
         o_dz[k] = take((size_t)t->max_n * nout[k] * 2);
         o_dzT[k] = take((size_t)t->max_n * nout[k] * 2);
     }
+    const size_t o_state = take(sizeof(gn_step_state));
     const size_t o_y = take(t->max_n * 4 * kCls), o_dz4 = take(t->max_n * 4), o_sums = take(64),
                  o_part = take((size_t)t->partial_blocks * kPartStride * 4), o_lpart = take((size_t)t->partial_blocks * 8);
     cudaError_t e = cudaMalloc(&t->arena, bytes);
@@ -444,6 +462,7 @@ extern "C" int gn_fusion_trainer_create_head(gn_handle* h, gn_fusion_trainer** o
     t->sums = reinterpret_cast<double*>(base + o_sums);
     t->partial = reinterpret_cast<float*>(base + o_part);
     t->lpart = reinterpret_cast<double*>(base + o_lpart);
+    t->state = reinterpret_cast<gn_step_state*>(base + o_state);       // zeroed with the arena: step 0, no seed bump
     for (int k = 0; k < 5 && e == cudaSuccess; ++k) {
         e = cudaMemcpyAsync(t->params + t->off_w[k], sd->weight[k], (size_t)nout[k] * kin[k] * 4, cudaMemcpyDeviceToDevice, st);
         if (e == cudaSuccess)
@@ -504,7 +523,7 @@ extern "C" int gn_fusion_forward_backward(gn_fusion_trainer* t, const float* d_f
         const uint8_t* mask = (d_masks && dropout_p > 0.f) ? d_masks[k] : nullptr;
         rc = gn_tc_train_gemm(h, 3, t->a[k], n, t->kin[k], t->kin[k], t->wk[k], t->nout[k], t->kin[k],
                               t->params + t->off_b[k], t->a[k + 1], k < 3 ? t->aT[k + 1] : nullptr, ld, nullptr, nullptr,
-                              mask, scale, keep, seed + 0x632BE59BD9B4E019ull * (unsigned long long)(k + 1), st);
+                              mask, scale, keep, seed + 0x632BE59BD9B4E019ull * (unsigned long long)(k + 1), st, t->state);
         if (rc) return rc;
     }
     GN_CUDA(cudaMemsetAsync(t->sums, 0, 64, st));
@@ -558,10 +577,11 @@ extern "C" int gn_fusion_adam_step(gn_fusion_trainer* t, const float* d_grads, f
     if (!t || !d_grads) return GN_E_ARG;
     cudaStream_t st = gn_stream(stream);
     t->step += 1;
-    const float bc1 = 1.f - powf(t->beta1, (float)t->step);
-    const float bc2 = 1.f - powf(t->beta2, (float)t->step);
+    // step count, bias corrections and the next step's dropout seed advance ON THE DEVICE (a captured graph replays them)
+    int rc0 = gn_launch_step_advance(t->h, t->state, t->beta1, t->beta2, st);
+    if (rc0) return rc0;
     adam_kernel<<<(unsigned)((t->n_params + 255) / 256), 256, 0, st>>>(t->params, t->m, t->v, d_grads, t->n_params, grad_scale,
-                                                                       t->lr, t->beta1, t->beta2, t->eps, bc1, sqrtf(bc2));
+                                                                       t->lr, t->beta1, t->beta2, t->eps, t->state);
     GN_LAUNCHED(t->h);
     return repack_all(t, st);
 }

@@ -133,7 +133,9 @@ linear_fwd_kernel(const float* __restrict__ x, int ldx, const float* __restrict_
 
 // keep-mask from a counter-based hash (splitmix64 of seed + site offset + element index), P(keep) = keep_prob
 __global__ void __launch_bounds__(kT)
-make_mask_kernel(uint8_t* __restrict__ mask, int64_t total, unsigned long long seed, float keep_prob) {
+make_mask_kernel(uint8_t* __restrict__ mask, int64_t total, unsigned long long seed, float keep_prob,
+                 const gn_step_state* __restrict__ state) {
+    seed += state->seed_bump;         // advances on the device every step, so a captured graph draws fresh masks on replay
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         unsigned long long z = seed + (unsigned long long)i * 0x9E3779B97F4A7C15ull;
         z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -502,7 +504,8 @@ conv_bwd_w_kernel(const float* __restrict__ dy, const float* __restrict__ x, int
 // torch.optim.Adam (no weight decay, no amsgrad): p -= lr * mhat / (sqrt(vhat) + eps)
 __global__ void __launch_bounds__(kT)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t total,
-            float grad_scale, float lr, float b1, float b2, float eps, float bc1, float bc2) {
+            float grad_scale, float lr, float b1, float b2, float eps, const gn_step_state* __restrict__ state) {
+    const float bc1 = state->bc1, bc2 = state->bc2;
     for (int64_t i = blockIdx.x * (int64_t)kT + threadIdx.x; i < total; i += (int64_t)gridDim.x * kT) {
         const float gi = g[i] * grad_scale;
         const float mi = b1 * m[i] + (1.f - b1) * gi;
@@ -788,6 +791,7 @@ struct gn_avm_trainer {
     int use_tc;                      // conv2 / conv3 GEMMs on the tensor cores as TF32 (default) or the fp32 SGEMM
     float *d_fin, *d_f[4];
     uint8_t* masks[5];               // keep-masks: linear5 (512), fusion.0/3/6/9 (512, 512, 256, 128)
+    gn_step_state* state;            // device: Adam step count, bias corrections, dropout seed bump (CUDA-graph safe)
     void* arena;
 };
 
@@ -887,6 +891,7 @@ extern "C" int gn_avm_trainer_create(gn_handle* h, gn_avm_trainer** out, const g
         t->lin_part = (float*)take(t->lin_part_elems, 4);
         const int mw[5] = {512, 512, 512, 256, 128};
         for (int i = 0; i < 5; ++i) t->masks[i] = (uint8_t*)take(n * mw[i], 1);
+        t->state = (gn_step_state*)take(sizeof(gn_step_state), 1);      // zeroed with the arena: step 0, no seed bump
         if (pass == 0) {
             bytes = off + 256;
             cudaError_t e = cudaMalloc(&t->arena, bytes);
@@ -1142,7 +1147,7 @@ extern "C" int gn_avm_trainer_forward_backward(gn_avm_trainer* t, const float* d
             if (d_masks && d_masks[i]) mk[i] = d_masks[i];
             else {
                 TL(make_mask_kernel, (int64_t)n * mw[i], t->masks[i], (int64_t)n * mw[i],
-                   seed + 0x632BE59BD9B4E019ull * (unsigned long long)(i + 1), 1.f - dropout_p);
+                   seed + 0x632BE59BD9B4E019ull * (unsigned long long)(i + 1), 1.f - dropout_p, t->state);
                 mk[i] = t->masks[i];
             }
         }
@@ -1268,9 +1273,11 @@ extern "C" int gn_avm_trainer_adam_step(gn_avm_trainer* t, float grad_scale, voi
     if (!t) return GN_E_ARG;
     cudaStream_t st = gn_stream(stream);
     t->step += 1;
-    const float bc1 = 1.f - powf(t->b1, (float)t->step), bc2 = 1.f - powf(t->b2, (float)t->step);
+    // step count and bias corrections advance ON THE DEVICE (a captured graph replays them)
+    int rc0 = gn_launch_step_advance(t->h, t->state, t->b1, t->b2, st);
+    if (rc0) return rc0;
     adam_kernel<<<grid_for(t->n_params, t->h->num_sms * 8), kT, 0, st>>>(t->params, t->grads, t->m, t->v, t->n_params,
-                                                                         grad_scale, t->lr, t->b1, t->b2, t->eps, bc1, bc2);
+                                                                         grad_scale, t->lr, t->b1, t->b2, t->eps, t->state);
     GN_LAUNCHED(t->h);
     return GN_OK;
 }

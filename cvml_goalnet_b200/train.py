@@ -24,6 +24,38 @@ FUSION_LAYERS = ("fusion.0", "fusion.3", "fusion.6", "fusion.9", "fusion.12")
 HIDDEN_WIDTHS = (512, 512, 256, 128)
 
 
+class _GraphedStep:
+    """A whole train step (forward, loss, backward, gradient all-reduce, Adam) captured ONCE in a CUDA graph and replayed:
+    the step is a chain of 30-90 small dependent launches, so issuing it as one graph launch removes the per-launch host
+    cost that bounded it.  What changes from step to step lives on the device (`gn_step_state`: Adam step count, bias
+    corrections, dropout seed bump), so a replay is a new step, not a repetition.  Inputs are copied into static buffers
+    (same addresses every replay); the first `warmup` calls run eagerly (they also set kernel attributes and let NCCL
+    build its communicator outside the capture)."""
+
+    def __init__(self, dev, warmup: int = 2):
+        self.dev, self.warmup, self.calls, self.graphs = dev, warmup, 0, {}
+
+    def run(self, key, eager_fn):
+        """eager_fn() must launch the step on the current stream reading only static buffers."""
+        self.calls += 1
+        if self.calls <= self.warmup:
+            eager_fn()
+            return
+        ent = self.graphs.get(key)
+        if ent is None:
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            l0 = int(_lib.load().gn_launch_count(_lib.handle(self.dev.index)))
+            with torch.cuda.graph(g):
+                eager_fn()
+            captured = int(_lib.load().gn_launch_count(_lib.handle(self.dev.index))) - l0
+            # the capture only RECORDED those launches: take them back out, every replay adds them
+            _lib.add_graph_launches(self.dev.index, -captured)
+            ent = self.graphs[key] = (g, captured)
+        ent[0].replay()
+        _lib.add_graph_launches(self.dev.index, ent[1])
+
+
 class FusionTrainer:
     """Adam training of `model.fusion` (reference defaults: lr 1e-3, betas (0.9, 0.999), eps 1e-8).
 
@@ -37,9 +69,12 @@ class FusionTrainer:
     """
 
     def __init__(self, model: AVM, max_rows: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 fixed_loss: bool = False, dropout_p: float = 0.2, device=None, process_group=None, seed: int = 12344321):
+                 fixed_loss: bool = False, dropout_p: float = 0.2, device=None, process_group=None, seed: int = 12344321,
+                 use_graph: bool = False):
         self.dev = _device(device)
         self.model = model
+        self.use_graph = bool(use_graph)
+        self._graph = _GraphedStep(self.dev)
         self.fin = 640 if model.audio_included else 512
         self.n_cls = int(getattr(model, "OUT_COLS", 1))
         self.fixed_loss = bool(fixed_loss)
@@ -70,6 +105,9 @@ class FusionTrainer:
         self.grads = torch.zeros(self.n_params, dtype=torch.float32, device=self.dev)
         self.scores = torch.empty(self.max_rows * self.n_cls, dtype=torch.float32, device=self.dev)
         self.loss = torch.zeros(1, dtype=torch.float64, device=self.dev)
+        if self.use_graph:
+            self._gx = torch.zeros((self.max_rows, self.fin), dtype=torch.float32, device=self.dev)
+            self._glab = torch.zeros(self.max_rows, dtype=torch.float32, device=self.dev)
 
     def __del__(self):
         try:
@@ -122,6 +160,20 @@ class FusionTrainer:
 
     def step(self, features, labels, masks=None):
         """One train step (main.py:187-193).  Returns (loss tensor float64[1] on the device, predictions (N,1))."""
+        if self.use_graph and masks is None:
+            x = _to_dev(features, torch.float32, self.dev)
+            lab = _to_dev(labels, torch.float32, self.dev).reshape(-1)
+            n = int(x.shape[0])
+            assert x.dim() == 2 and x.shape[1] == self.fin and lab.numel() == n and n <= self.max_rows, \
+                "E: Inconsistency in data loader definition"
+            self._gx[:n].copy_(x, non_blocking=True)
+            self._glab[:n].copy_(lab, non_blocking=True)
+
+            def body():
+                self.forward_backward(self._gx[:n], self._glab[:n])
+                self.optimizer_step()
+            self._graph.run(n, body)
+            return self.loss, self.scores[:n * self.n_cls].reshape(n, self.n_cls)
         n = self.forward_backward(features, labels, masks)
         self.optimizer_step()
         return self.loss, self.scores[:n * self.n_cls].reshape(n, self.n_cls)
@@ -172,9 +224,12 @@ class AVMTrainer:
     """
 
     def __init__(self, model: AVM, max_frames: int = 10, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 fixed_loss: bool = False, dropout_p: float = 0.2, device=None, process_group=None, seed: int = 12344321):
+                 fixed_loss: bool = False, dropout_p: float = 0.2, device=None, process_group=None, seed: int = 12344321,
+                 use_graph: bool = False):
         self.dev = _device(device)
         self.model = model
+        self.use_graph = bool(use_graph)
+        self._graph = _GraphedStep(self.dev)
         self.fixed_loss, self.dropout_p = bool(fixed_loss), float(dropout_p)
         self.group, self.seed, self.steps, self.max_frames = process_group, int(seed), 0, int(max_frames)
         lib = _lib.load()
@@ -194,6 +249,10 @@ class AVMTrainer:
         self._grads_ptr = g.value
         self.scores = torch.empty(self.max_frames, dtype=torch.float32, device=self.dev)
         self.loss = torch.zeros(1, dtype=torch.float64, device=self.dev)
+        if self.use_graph:
+            self._gvis = torch.zeros((self.max_frames, 3, model.S, model.S), dtype=torch.float32, device=self.dev)
+            self._gaud = torch.zeros((self.max_frames, 30, model.B), dtype=torch.float32, device=self.dev)
+            self._glab = torch.zeros(self.max_frames, dtype=torch.float32, device=self.dev)
 
     def __del__(self):
         try:
@@ -266,6 +325,20 @@ class AVMTrainer:
 
     def step(self, audios, frames, labels, masks=None):
         """One train sub-step.  Returns (loss float64[1] on the device, train-mode predictions (n,1))."""
+        if self.use_graph and masks is None:
+            vis = _to_dev(frames, torch.float32, self.dev)
+            n = int(vis.shape[0])
+            assert 1 <= n <= self.max_frames, "E: sub-batch larger than max_frames"
+            self._gvis[:n].copy_(vis, non_blocking=True)
+            if self.model.audio_included:
+                self._gaud[:n].copy_(_to_dev(audios, torch.float32, self.dev), non_blocking=True)
+            self._glab[:n].copy_(_to_dev(labels, torch.float32, self.dev).reshape(-1), non_blocking=True)
+
+            def body():
+                self.forward_backward(self._gaud[:n] if self.model.audio_included else None, self._gvis[:n], self._glab[:n])
+                self.optimizer_step()
+            self._graph.run(n, body)
+            return self.loss, self.scores[:n].reshape(n, 1)
         n = self.forward_backward(audios, frames, labels, masks)
         self.optimizer_step()
         return self.loss, self.scores[:n].reshape(n, 1)
@@ -278,8 +351,21 @@ class AVMTrainer:
         return keep
 
     def sync_model(self):
+        """Write the trained parameters and BatchNorm running buffers back into `model`.  Data parallel: gradients are
+        all-reduced every step, so the parameters agree on every rank, but each rank's running statistics come from its
+        own sub-batches -- they are averaged over the group here so that every rank ends with the same eval model."""
+        import torch.distributed as dist
+        trained = self.state_dict()
+        if self.group is not False and dist.is_available() and dist.is_initialized():
+            group = self.group if self.group is not None else dist.group.WORLD
+            world = dist.get_world_size(group)
+            if world > 1:
+                for k in sorted(trained):
+                    if k.endswith("running_mean") or k.endswith("running_var"):
+                        dist.all_reduce(trained[k], op=dist.ReduceOp.SUM, group=group)
+                        trained[k] /= world
         sd = self.model.state_dict()
-        for k, v in self.state_dict().items():
+        for k, v in trained.items():
             sd[k].copy_(v.to(sd[k].device))
         self.model.invalidate()
 

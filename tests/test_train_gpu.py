@@ -341,3 +341,48 @@ def test_tf32_tcgen05_gemm_vs_torch_fp32(cuda_device, M, K, N):
     torch.backends.cuda.matmul.allow_tf32 = prev
     err = (c.double() - ref).abs().max().item() / ref.abs().max().item()
     assert err <= 2e-3, err
+
+
+def test_graph_replay_equals_eager_steps(cuda_device):
+    """A train step captured once in a CUDA graph and replayed (Adam step count, bias corrections and dropout seed bump
+    live on the device) gives the same parameters as the same steps issued launch by launch -- fusion trainer and
+    full-AVM trainer, dropout off so that both runs are deterministic; with dropout on, replays must still differ from
+    one another (fresh masks every replay)."""
+    from cvml_goalnet_b200.train import AVMTrainer, FusionTrainer
+    rng = np.random.default_rng(31)
+    x = np.abs(rng.standard_normal((512, 640))).astype(np.float32)
+    lab = rng.integers(1, 6, 512).astype(np.float32)
+    outs = []
+    for use_graph in (False, True):
+        m, _ = _model(True)
+        tr = FusionTrainer(m, max_rows=512, dropout_p=0.0, process_group=False, use_graph=use_graph)
+        losses = []
+        for _ in range(6):
+            tr.step(x, lab)
+            losses.append(float(tr.loss.item()))
+        outs.append((tr.flat_params().cpu().numpy(), losses))
+    # (the loss statistics are accumulated with double atomics, so two runs agree to rounding, not bit for bit; Adam turns
+    #  a sign flip of a ~0 gradient into a step of lr, hence the looser bound on single parameters)
+    assert np.allclose(outs[0][1], outs[1][1], rtol=1e-6)
+    d = np.abs(outs[0][0] - outs[1][0])
+    assert d.max() <= 1.3e-2 and d.mean() <= 1e-5, (d.max(), d.mean())
+    assert outs[0][1][-1] < outs[0][1][0]                                   # and it trains
+    m, _ = _model(True)
+    tr = FusionTrainer(m, max_rows=512, dropout_p=0.2, process_group=False, use_graph=True)
+    ls = [float(tr.step(x, lab)[0].item()) for _ in range(6)]
+    assert len(set(ls[2:])) == 4                                             # replays draw fresh dropout masks
+
+    vis = rng.random((10, 3, 40, 40)).astype(np.float32)
+    aud = (25.0 * rng.standard_normal((10, 30, 30))).astype(np.float32)
+    lab10 = rng.integers(1, 6, 10).astype(np.float32)
+    outs = []
+    for use_graph in (False, True):
+        m, _ = _model(True)
+        tr = AVMTrainer(m, max_frames=10, dropout_p=0.0, process_group=False, use_graph=use_graph)
+        for _ in range(5):
+            tr.step(aud, vis, lab10)
+        sd = tr.state_dict()
+        outs.append({k: v.cpu().numpy() for k, v in sd.items()})
+    for k in outs[0]:
+        d = np.abs(outs[0][k] - outs[1][k])
+        assert d.max() <= 1.1e-2 and d.mean() <= 2e-5, (k, d.max(), d.mean())
