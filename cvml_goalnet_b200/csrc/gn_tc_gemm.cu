@@ -15,6 +15,8 @@
 // warps 2..9 = epilogue (TMEM lane quarter = warp_id % 4; the two warps of a quarter split the
 // 32-column chunks).  The conv epilogue is the larger half of a conv tile's work, so it gets two
 // warps per scheduler and 16-byte shared/global accesses throughout.
+#include <stdlib.h>
+
 #include "gn_common.cuh"
 #include "gn_tc_ptx.cuh"
 
@@ -583,6 +585,266 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
 }
 
+// =====================================================================================================================
+// conv block on CTA PAIRS (tcgen05 cta_group::2): the frame-aligned conv tiles of the 40x40 model, two frames per MMA.
+//
+// The cta_group::1 kernel above keeps the tensor pipe "active" 95 % of the time on conv3 yet delivers only ~65 % of the
+// nominal MMA rate: every MMA reads its whole B tile (256 weight rows) from this SM's shared memory, TMA writes the same
+// bytes in, and together with the A tile that saturates the shared-memory port (measured: skipping the pooling pass --
+// 6 % of the shared-memory traffic -- speeds the kernel up 18 %).  A CTA pair halves the B side: the two CTAs of a
+// cluster sit on one TPC, each stages ITS frame's A tile (128 rows) and HALF of the weight rows, and the leader issues
+// one M = 256 MMA whose result rows 0..127 / 128..255 land in the two CTAs' own TMEM.  Per CTA and k-step that is
+// 16 KB + 16 KB instead of 16 KB + 32 KB fetched, and 8 KB instead of 12 KB read per MMA; the shorter stage also buys
+// two more pipeline stages.  Roles per CTA are as above (TMA producer, MMA issuer -- leader only --, 8 epilogue warps);
+// what crosses the pair: the producers count their bytes on the LEADER's full barriers, the MMA commits are multicast to
+// both CTAs' empty / accumulator-ready barriers, and both epilogues release the accumulator on the leader's barrier.
+// =====================================================================================================================
+template <int BN, int STAGES, int OHT, int SUBC>
+struct PairCfg {
+    static constexpr int kABytes = 128 * 128;            // this CTA's frame: 128 rows x 64 k
+    static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the tile's BN weight rows
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStgStride = SUBC * 2 + 16;
+    static constexpr int kStgBytes = ((OHT * OHT * kStgStride) + 127) & ~127;
+    static constexpr int kParamBytes = 3 * kMaxN * 4;
+    static constexpr int kSmemBytes = 1024 + STAGES * kStageBytes + kStgBytes + kParamBytes + 256;
+    static_assert(BN <= kAccCols && BN % 32 == 0 && OHT * OHT <= 128, "one 128-row M tile per CTA, <= 256 columns");
+    static_assert(kSmemBytes <= 232448, "exceeds the 227 KB shared memory of one CTA");
+};
+
+template <int BN, int STAGES, int OHT, int SUBC>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmArgs args) {
+    using C = PairCfg<BN, STAGES, OHT, SUBC>;
+    static_assert(BN % SUBC == 0 && SUBC % 64 == 0, "channel passes are whole pairs of 32-column TMEM chunks");
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    unsigned char* stage_base = smem;
+    unsigned char* stg = smem + STAGES * C::kStageBytes;
+    float* s_par = reinterpret_cast<float*>(stg + C::kStgBytes);      // [3][kMaxN]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stg + C::kStgBytes + C::kParamBytes);
+    uint64_t* full_bar = bars;                    // [STAGES]  (the leader's are the ones in use)
+    uint64_t* empty_bar = bars + STAGES;          // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]       (the leader's are the ones in use)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader
+    const int n_blocks = args.N / BN;
+    const int64_t pairs = (args.M + 1) / 2;
+    const int64_t num_units = pairs * n_blocks;
+    const int64_t cl = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+    const int k_total = args.K / kBK;
+
+    for (int i = threadIdx.x; i < args.N; i += kThreads) {
+        s_par[i] = __ldg(args.bias + i);
+        s_par[kMaxN + i] = __ldg(args.bn_scale + i);
+        s_par[2 * kMaxN + i] = __ldg(args.bn_shift + i);
+    }
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_a);
+        prefetch_tmap(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(smem_u32(&full_bar[s]), 1);             // the leader's arrive.expect_tx (it expects BOTH CTAs' bytes)
+            mbar_init(smem_u32(&empty_bar[s]), 1);            // the multicast MMA commit
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(&tfull_bar[b]), 1);            // the multicast MMA commit
+            mbar_init(smem_u32(&tempty_bar[b]), 2 * kEpiWarps);   // every epilogue warp of both CTAs
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);    // all 512 columns, the same base in both CTAs
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                       // the peer's barriers are initialised before any remote arrive
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t unit = cl; unit < num_units; unit += ncl) {
+                const int64_t pair = unit / n_blocks;
+                const int n_blk = (int)(unit - pair * n_blocks);
+                const int frame = (int)(2 * pair + rank);     // beyond the last frame: the box is zero-filled
+                for (int kt = 0; kt < k_total; ++kt) {
+                    mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+                    const uint32_t fb = mapa(smem_u32(&full_bar[stage]), 0);       // the leader's barrier
+                    const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                    const uint32_t sb = sa + C::kABytes;
+                    const int tap = kt / args.g.cin_blocks;
+                    const int cb = kt - tap * args.g.cin_blocks;
+                    const int ky = tap / 3, kx = tap - ky * 3;
+                    // the leader alone arms its barrier, with the bytes of both CTAs' loads: no remote arrive (a
+                    // cluster-scope release costs the producer a MEMBAR + ERRBAR per k-step: it starved the MMAs).  The
+                    // peer's bytes may land before the leader has armed the phase; the transaction count is signed and
+                    // the phase cannot complete before the leader's arrival.
+                    if (rank == 0) mbar_expect_tx(smem_u32(&full_bar[stage]), 2u * (uint32_t)(OHT * OHT * 128 + C::kBBytes));
+                    tma_load_4d_pair(sa, &tmap_a, fb, cb * kBK, kx, ky, frame);
+                    tma_load_2d_pair(sb, &tmap_b, fb, kt * kBK, n_blk * BN + (int)rank * (BN / 2));
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader only) =====================
+        if (rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(256, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int ab = 0;
+            uint32_t aphase = 0;
+            for (int64_t unit = cl; unit < num_units; unit += ncl) {
+                mbar_wait(smem_u32(&tempty_bar[ab]), aphase ^ 1);                  // both epilogues drained this buffer
+                tc_fence_after();
+                for (int kt = 0; kt < k_total; ++kt) {
+                    mbar_wait(smem_u32(&full_bar[stage]), phase);                  // both CTAs' operands have landed
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                        const uint32_t sb = sa + C::kABytes;
+                        const uint32_t d = tmem_base + (uint32_t)(ab * kAccCols);
+#pragma unroll
+                        for (int k4 = 0; k4 < kBK / 16; ++k4)
+                            umma_bf16_pair(d, make_desc_sw128(sa + k4 * 32), make_desc_sw128(sb + k4 * 32), idesc,
+                                           (kt > 0 || k4 > 0) ? 1u : 0u);
+                        umma_commit_pair(smem_u32(&empty_bar[stage]));             // both CTAs' stage is free
+                        if (kt == k_total - 1) umma_commit_pair(smem_u32(&tfull_bar[ab]));   // both accumulators ready
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                if (++ab == 2) { ab = 0; aphase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..9, both CTAs: each pools and stores ITS frame) =====================
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int row = q * 32 + lane;
+        const int et = (warp - 2) * 32 + lane;
+        const float* s_bias = s_par;
+        int ab = 0;
+        uint32_t aphase = 0;
+        constexpr int npix = OHT * OHT;
+        constexpr int kPasses = BN / SUBC;
+        constexpr int P = OHT - 2;
+        constexpr int CG = SUBC / 8;
+        static_assert(P * CG <= kEpiThreads, "one thread per (pooled column, channel group)");
+        for (int64_t unit = cl; unit < num_units; unit += ncl) {
+            const int64_t pair = unit / n_blocks;
+            const int n_blk = (int)(unit - pair * n_blocks);
+            const int64_t frame = 2 * pair + rank;
+            const bool live = frame < args.M;
+            const int n0 = n_blk * BN;
+            mbar_wait(smem_u32(&tfull_bar[ab]), aphase);
+            tc_fence_after();
+            const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * kAccCols);
+#pragma unroll 1
+            for (int pass = 0; pass < kPasses; ++pass) {
+                const int nsub = n0 + pass * SUBC;
+                // ---- phase 1: TMEM -> bf16 staging tile [pixel][SUBC] (bias + ReLU follow the pool, see above) ----
+                if (q * 32 < npix) {
+#pragma unroll 1
+                    for (int c = half; c < SUBC / 32; c += 2) {
+                        uint32_t r[32];
+                        tmem_ld32(tbase + (uint32_t)(pass * SUBC + c * 32), r);
+                        tmem_ld_wait();
+                        if (row < npix) {
+                            uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)row * C::kStgStride + c * 64);
+#pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                const int i = v * 8;
+                                dst[v] = make_uint4(pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1])),
+                                                    pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])),
+                                                    pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5])),
+                                                    pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7])));
+                            }
+                        }
+                    }
+                }
+                if (pass == kPasses - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(mapa(smem_u32(&tempty_bar[ab]), 0));   // on the leader's barrier
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile complete
+                // ---- phase 2: MaxPool(3, stride 1), bias + ReLU, BatchNorm affine, bf16 store ----
+                const int PW = P + 2 * args.g.out_pad;
+                __nv_bfloat16* obase = args.out + (size_t)frame * PW * PW * args.g.cout + nsub;
+                const int ox = et / CG, cg = et - ox * CG;
+                if (ox < P && live) {
+                    const float4* sc = reinterpret_cast<const float4*>(s_par + kMaxN + nsub + cg * 8);
+                    const float4* sh = reinterpret_cast<const float4*>(s_par + 2 * kMaxN + nsub + cg * 8);
+                    const float4* bb = reinterpret_cast<const float4*>(s_bias + nsub + cg * 8);
+                    const float4 sc0 = sc[0], sc1 = sc[1], sh0 = sh[0], sh1 = sh[1], b0 = bb[0], b1 = bb[1];
+                    const unsigned char* s0 = stg + (size_t)ox * C::kStgStride + cg * 16;
+                    uint4 h0 = make_uint4(0u, 0u, 0u, 0u), h1 = h0;
+                    uint4 t0 = *reinterpret_cast<const uint4*>(s0), t1 = *reinterpret_cast<const uint4*>(s0 + C::kStgStride),
+                          t2 = *reinterpret_cast<const uint4*>(s0 + 2 * C::kStgStride);
+#pragma unroll
+                    for (int r = 0; r < OHT; ++r) {
+                        uint4 n0v = t0, n1v = t1, n2v = t2;
+                        if (r + 1 < OHT) {
+                            const unsigned char* sr = s0 + (size_t)((r + 1) * OHT) * C::kStgStride;
+                            n0v = *reinterpret_cast<const uint4*>(sr);
+                            n1v = *reinterpret_cast<const uint4*>(sr + C::kStgStride);
+                            n2v = *reinterpret_cast<const uint4*>(sr + 2 * C::kStgStride);
+                        }
+                        const uint4 h2 = hmax2_u4(hmax2_u4(t0, t1), t2);
+                        if (r >= 2) {
+                            const uint4 m = hmax2_u4(hmax2_u4(h0, h1), h2);
+                            const float2 f0 = bf2_to_f2(m.x), f1 = bf2_to_f2(m.y), f2 = bf2_to_f2(m.z), f3 = bf2_to_f2(m.w);
+                            const uint4 o = make_uint4(
+                                pack_bf16(fmaf(fmaxf(f0.x + b0.x, 0.f), sc0.x, sh0.x), fmaf(fmaxf(f0.y + b0.y, 0.f), sc0.y, sh0.y)),
+                                pack_bf16(fmaf(fmaxf(f1.x + b0.z, 0.f), sc0.z, sh0.z), fmaf(fmaxf(f1.y + b0.w, 0.f), sc0.w, sh0.w)),
+                                pack_bf16(fmaf(fmaxf(f2.x + b1.x, 0.f), sc1.x, sh1.x), fmaf(fmaxf(f2.y + b1.y, 0.f), sc1.y, sh1.y)),
+                                pack_bf16(fmaf(fmaxf(f3.x + b1.z, 0.f), sc1.z, sh1.z), fmaf(fmaxf(f3.y + b1.w, 0.f), sc1.w, sh1.w)));
+                            const int opix = (r - 2 + args.g.out_pad) * PW + ox + args.g.out_pad;
+                            if (args.g.blocked)
+                                *reinterpret_cast<uint4*>(args.out + gn_a3_off(frame, (int64_t)opix * args.g.cout + nsub + cg * 8,
+                                                                               (int64_t)PW * PW * args.g.cout / 64)) = o;
+                            else
+                                *reinterpret_cast<uint4*>(obase + (size_t)opix * args.g.cout + cg * 8) = o;
+                        }
+                        h0 = h1;
+                        h1 = h2;
+                        t0 = n0v; t1 = n1v; t2 = n2v;
+                    }
+                }
+                if (args.g.out_pad && live) {              // zero border of the next conv's input (padding = 1)
+                    const int nborder = 4 * PW - 4;
+                    for (int item = et; item < nborder * CG; item += kEpiThreads) {
+                        const int bi = item / CG, cgb = item - bi * CG;
+                        int by, bx;
+                        if (bi < PW) { by = 0; bx = bi; }
+                        else if (bi < 2 * PW) { by = PW - 1; bx = bi - PW; }
+                        else { const int tt = bi - 2 * PW; by = 1 + (tt >> 1); bx = (tt & 1) ? PW - 1 : 0; }
+                        *reinterpret_cast<uint4*>(obase + (size_t)(by * PW + bx) * args.g.cout + cgb * 8) =
+                            make_uint4(0u, 0u, 0u, 0u);
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");   // staging tile may be reused
+            }
+            if (++ab == 2) { ab = 0; aphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();        // no CTA leaves while its peer may still arrive on its barriers or the leader's MMAs write its TMEM
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 // ---- host side --------------------------------------------------------------------------------------
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -648,6 +910,50 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __n
     a.g.tiles = 1; a.g.pfull = OH - 2; a.g.blocked = out_pad ? 0 : 1;
     if (OH * OH > MT * 128 || Cin % kBK || Cout % BN) return GN_E_SHAPE;
     return launch<MT, BN, STAGES, kConv, OH, SUBC>(m->h, ta, tb, a, n * (Cout / BN), st);
+}
+
+// conv block on CTA pairs (see tc_conv_pair_kernel): same operands and result as run_conv<1, BN, ...>
+template <int BN, int STAGES, int OH, int SUBC>
+int run_conv_pair(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __nv_bfloat16* wk, int Cout,
+                  const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad, cudaStream_t st) {
+    using C = PairCfg<BN, STAGES, OH, SUBC>;
+    if (Cin % kBK || Cout % BN || Cout > kMaxN) return GN_E_SHAPE;
+    CUtensorMap ta, tb;
+    const int IW = OH + 2;
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)IW, (uint64_t)IW, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)IW * Cin * 2, (uint64_t)IW * IW * Cin * 2};
+    const uint32_t box[4] = {(uint32_t)kBK, (uint32_t)OH, (uint32_t)OH, 1};
+    int rc = make_tmap(m->h, &ta, in, 4, dims, str, box);
+    if (rc) return rc;
+    rc = make_tmap_2d(m->h, &tb, wk, Cout, 9 * Cin, 9 * Cin, BN / 2);      // each CTA of a pair fetches half of the rows
+    if (rc) return rc;
+    GemmArgs a{};
+    a.M = n; a.N = Cout; a.K = 9 * Cin;
+    a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
+    a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
+    a.g.tiles = 1; a.g.pfull = OH - 2; a.g.blocked = out_pad ? 0 : 1;
+    auto kern = tc_conv_pair_kernel<BN, STAGES, OH, SUBC>;
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(kern)))
+        GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    const int64_t units = ((n + 1) / 2) * (Cout / BN);
+    int64_t clusters = m->h->num_sms / 2;
+    if (clusters > units) clusters = units;
+    if (clusters < 1) return GN_OK;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    GN_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, a));
+    GN_LAUNCHED(m->h);
+    return GN_OK;
 }
 
 // zero the one-pixel border of [n][PW][PW][C] bf16 (the padding the next conv reads); 16 bytes per thread
@@ -835,6 +1141,11 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
         // block 3: conv3 (256 -> 512) on 11x11, pool -> 9x9, dense (p, c) rows for linear5
         // (4 operand stages: with 3 the TMA round trip was exposed -- tensor pipe 83 % busy; the pooling stage shrinks
         //  to 64 channels per pass to make room)
+        static const bool pair3 = !getenv("GN_CONV3_SINGLE");      // development switch: the cta_group::1 kernel for A/B runs
+        if (pair3)
+            rc = run_conv_pair<256, 6, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2],
+                                               m->bn_shift[2], ws.a3, 0, st);
+        else
         rc = run_conv<1, 256, 4, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
                                          ws.a3, 0, st);
     } else {
