@@ -530,7 +530,8 @@ def native_arm(args, rank, world, local_rank):
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get("conv3_block_dram_bytes_per_launch")
-    roofline = {"kernel": "tc_gemm_kernel<1,256,4,conv> (conv3 block: implicit GEMM + ReLU + maxpool + BN)",
+    roofline = {"kernel": "tc_conv_pair_kernel<256,6,11,64> (conv3 block on CTA pairs, tcgen05 cta_group::2: implicit GEMM + "
+                          "maxpool + bias + ReLU + BN)",
                 "bound": "tensor", "achieved": achieved, "peak": peaks["tf_burst"], "unit": "TFLOP/s",
                 "frac": achieved / peaks["tf_burst"], "traffic": traffic,
                 # the timed region is tens of ms at full SM clock (see "clocks"); the sustained cuBLAS figure
