@@ -599,24 +599,24 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // what crosses the pair: the producers count their bytes on the LEADER's full barriers, the MMA commits are multicast to
 // both CTAs' empty / accumulator-ready barriers, and both epilogues release the accumulator on the leader's barrier.
 // =====================================================================================================================
-template <int BN, int STAGES, int OHT, int SUBC>
+template <int MT, int BN, int STAGES, int OHT, int SUBC>
 struct PairCfg {
-    static constexpr int kABytes = 128 * 128;            // this CTA's frame: 128 rows x 64 k
+    static constexpr int kABytes = MT * 128 * 128;       // this CTA's frame: MT x 128 rows x 64 k
     static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the tile's BN weight rows
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kStgStride = SUBC * 2 + 16;
     static constexpr int kStgBytes = ((OHT * OHT * kStgStride) + 127) & ~127;
     static constexpr int kParamBytes = 3 * kMaxN * 4;
     static constexpr int kSmemBytes = 1024 + STAGES * kStageBytes + kStgBytes + kParamBytes + 256;
-    static_assert(BN <= kAccCols && BN % 32 == 0 && OHT * OHT <= 128, "one 128-row M tile per CTA, <= 256 columns");
+    static_assert(MT * BN <= kAccCols && BN % 32 == 0 && OHT * OHT <= MT * 128, "MT 128-row M tiles per CTA, <= 256 columns");
     static_assert(kSmemBytes <= 232448, "exceeds the 227 KB shared memory of one CTA");
 };
 
-template <int BN, int STAGES, int OHT, int SUBC>
+template <int MT, int BN, int STAGES, int OHT, int SUBC>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmArgs args) {
-    using C = PairCfg<BN, STAGES, OHT, SUBC>;
+    using C = PairCfg<MT, BN, STAGES, OHT, SUBC>;
     static_assert(BN % SUBC == 0 && SUBC % 64 == 0, "channel passes are whole pairs of 32-column TMEM chunks");
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -709,11 +709,14 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     if (elect_one()) {
                         const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
                         const uint32_t sb = sa + C::kABytes;
-                        const uint32_t d = tmem_base + (uint32_t)(ab * kAccCols);
 #pragma unroll
-                        for (int k4 = 0; k4 < kBK / 16; ++k4)
-                            umma_bf16_pair(d, make_desc_sw128(sa + k4 * 32), make_desc_sw128(sb + k4 * 32), idesc,
-                                           (kt > 0 || k4 > 0) ? 1u : 0u);
+                        for (int mt = 0; mt < MT; ++mt) {
+                            const uint32_t d = tmem_base + (uint32_t)(ab * kAccCols + mt * BN);
+#pragma unroll
+                            for (int k4 = 0; k4 < kBK / 16; ++k4)
+                                umma_bf16_pair(d, make_desc_sw128(sa + mt * (128 * 128) + k4 * 32), make_desc_sw128(sb + k4 * 32),
+                                               idesc, (kt > 0 || k4 > 0) ? 1u : 0u);
+                        }
                         umma_commit_pair(smem_u32(&empty_bar[stage]));             // both CTAs' stage is free
                         if (kt == k_total - 1) umma_commit_pair(smem_u32(&tfull_bar[ab]));   // both accumulators ready
                     }
@@ -750,14 +753,17 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             for (int pass = 0; pass < kPasses; ++pass) {
                 const int nsub = n0 + pass * SUBC;
                 // ---- phase 1: TMEM -> bf16 staging tile [pixel][SUBC] (bias + ReLU follow the pool, see above) ----
-                if (q * 32 < npix) {
+#pragma unroll 1
+                for (int mt = 0; mt < MT; ++mt) {
+                    if (mt * 128 + q * 32 >= npix) continue;      // (warp-uniform) this warp's 32 rows are all padding
+                    const int pix = mt * 128 + row;
 #pragma unroll 1
                     for (int c = half; c < SUBC / 32; c += 2) {
                         uint32_t r[32];
-                        tmem_ld32(tbase + (uint32_t)(pass * SUBC + c * 32), r);
+                        tmem_ld32(tbase + (uint32_t)(mt * BN + pass * SUBC + c * 32), r);
                         tmem_ld_wait();
-                        if (row < npix) {
-                            uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)row * C::kStgStride + c * 64);
+                        if (pix < npix) {
+                            uint4* dst = reinterpret_cast<uint4*>(stg + (size_t)pix * C::kStgStride + c * 64);
 #pragma unroll
                             for (int v = 0; v < 4; ++v) {
                                 const int i = v * 8;
@@ -913,10 +919,10 @@ int run_conv(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __n
 }
 
 // conv block on CTA pairs (see tc_conv_pair_kernel): same operands and result as run_conv<1, BN, ...>
-template <int BN, int STAGES, int OH, int SUBC>
+template <int MT, int BN, int STAGES, int OH, int SUBC>
 int run_conv_pair(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, const __nv_bfloat16* wk, int Cout,
                   const float* bias, const float* sc, const float* sh, __nv_bfloat16* out, int out_pad, cudaStream_t st) {
-    using C = PairCfg<BN, STAGES, OH, SUBC>;
+    using C = PairCfg<MT, BN, STAGES, OH, SUBC>;
     if (Cin % kBK || Cout % BN || Cout > kMaxN) return GN_E_SHAPE;
     CUtensorMap ta, tb;
     const int IW = OH + 2;
@@ -932,7 +938,7 @@ int run_conv_pair(gn_model* m, int64_t n, const __nv_bfloat16* in, int Cin, cons
     a.bias = bias; a.bn_scale = sc; a.bn_shift = sh; a.out = out;
     a.g.OH = OH; a.g.OW = OH; a.g.P = OH - 2; a.g.out_pad = out_pad; a.g.cin_blocks = Cin / kBK; a.g.cout = Cout;
     a.g.tiles = 1; a.g.pfull = OH - 2; a.g.blocked = out_pad ? 0 : 1;
-    auto kern = tc_conv_pair_kernel<BN, STAGES, OH, SUBC>;
+    auto kern = tc_conv_pair_kernel<MT, BN, STAGES, OH, SUBC>;
     if (gn_attr_first(m->h, reinterpret_cast<const void*>(kern)))
         GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     const int64_t units = ((n + 1) / 2) * (Cout / BN);
@@ -1134,6 +1140,11 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
     if (m->P1 == 13 && m->P2 == 11) {
         // the reference's 40x40 frames: one frame per tile
         // block 2: conv2 (64 -> 256) on 13x13, pool -> 11x11, written with a zero border for conv3
+        static const bool pair2 = !getenv("GN_CONV2_SINGLE");      // development switch: the cta_group::1 kernel for A/B runs
+        if (pair2)
+            rc = run_conv_pair<2, 128, 4, 13, 128>(m, n, ws.a1p, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1],
+                                                   m->bn_shift[1], ws.a2p, 1, st);
+        else
         rc = run_conv<2, 128, 3, 13>(m, n, ws.a1p, 64, m->conv2_wk, 256, m->conv2_b, m->bn_scale[1], m->bn_shift[1],
                                      ws.a2p, 1, st);
         if (rc) return rc;
@@ -1143,7 +1154,7 @@ int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scor
         //  to 64 channels per pass to make room)
         static const bool pair3 = !getenv("GN_CONV3_SINGLE");      // development switch: the cta_group::1 kernel for A/B runs
         if (pair3)
-            rc = run_conv_pair<256, 6, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2],
+            rc = run_conv_pair<1, 256, 6, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2],
                                                m->bn_shift[2], ws.a3, 0, st);
         else
         rc = run_conv<1, 256, 4, 11, 64>(m, n, ws.a2p, 256, m->conv3_wk, 512, m->conv3_b, m->bn_scale[2], m->bn_shift[2],
