@@ -12,6 +12,8 @@
 // the tables (twiddles, window, mel weights, DCT rows, W) are read through L1.  HBM traffic is the
 // slot's samples in and 30*B floats out.  Every sum is formed in a fixed order: a slot's features do
 // not depend on the launch it is part of.
+#include <type_traits>
+
 #include "gn_common.cuh"
 #include "gn_fft2.cuh"
 
@@ -60,38 +62,50 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
         const float* seg = y + s0;
         float emax = 0.f;                                      // largest mel energy seen by this thread
         // sample rows of 128: row m of a group holds samples j0*512 - 1024 + 128 m + t; column j0+c starts at row 4c.
-        // Samples outside [0, L) are the centre zero padding; interior groups skip the bounds checks.  The rows of group
-        // g+1 are requested while group g is between its passes (they are only consumed one group later).
+        // Samples outside [0, L) are the centre zero padding; interior groups skip the bounds checks.  Rows 16..27 of a
+        // group are rows 0..11 of the next one (hop 512 = 4 rows), so a group only loads 16 new rows, and those are
+        // requested while the current group is between its passes (they are only consumed one group later).
         float raw[28];
-        auto load_rows = [&](int j0) {
+        auto load_rows = [&](int j0, auto first) {
+            constexpr int kFirst = decltype(first)::value;
             const int base = j0 * kHop - kFFT / 2 + t;
-            if (base - t >= 0 && base - t + 28 * 128 <= L) {
+            if (base - t + kFirst * 128 >= 0 && base - t + 28 * 128 <= L) {
                 const float* p = seg + base;
 #pragma unroll
-                for (int m = 0; m < 28; ++m) raw[m] = __ldg(p + 128 * m);
+                for (int m = kFirst; m < 28; ++m) raw[m] = __ldg(p + 128 * m);
             } else {
 #pragma unroll
-                for (int m = 0; m < 28; ++m) {
+                for (int m = kFirst; m < 28; ++m) {
                     const int i = base + 128 * m;
                     raw[m] = ((unsigned)i < (unsigned)L) ? __ldg(seg + i) : 0.f;
                 }
             }
         };
-        load_rows(0);
+        load_rows(0, std::integral_constant<int, 0>{});
         for (int j0 = 0; j0 < q; j0 += 4) {
             // ---- windowed columns j0..j0+3: transform A = (j0, j0+1), transform B = (j0+2, j0+3) ----
             {
                 C2 z[16];
-                {
-                    const float c1 = (j0 + 1 < q) ? 1.f : 0.f, c2 = (j0 + 2 < q) ? 1.f : 0.f, c3 = (j0 + 3 < q) ? 1.f : 0.f;
+#pragma unroll
+                for (int n1 = 0; n1 < 16; ++n1) {
+                    const V2 h = bc(__ldg(hann + t + 128 * n1));
+                    z[n1].re = mul2(mk(raw[n1], raw[n1 + 8]), h);
+                    z[n1].im = mul2(mk(raw[n1 + 4], raw[n1 + 12]), h);
+                }
+                if (j0 + 3 >= q) {                             // the last group of a slot: columns >= q count as silence
+                    const V2 mre = mk(1.f, (j0 + 2 < q) ? 1.f : 0.f);
+                    const V2 mim = mk((j0 + 1 < q) ? 1.f : 0.f, 0.f);
 #pragma unroll
                     for (int n1 = 0; n1 < 16; ++n1) {
-                        const float h = __ldg(hann + t + 128 * n1);
-                        z[n1].re = mk(raw[n1] * h, raw[n1 + 8] * (h * c2));
-                        z[n1].im = mk(raw[n1 + 4] * (h * c1), raw[n1 + 12] * (h * c3));
+                        z[n1].re = mul2(z[n1].re, mre);
+                        z[n1].im = mul2(z[n1].im, mim);
                     }
                 }
-                if (j0 + 4 < q) load_rows(j0 + 4);
+                if (j0 + 4 < q) {
+#pragma unroll
+                    for (int m = 0; m < 12; ++m) raw[m] = raw[m + 16];
+                    load_rows(j0 + 4, std::integral_constant<int, 12>{});
+                }
                 pass1(t, z, tw1, xb);                          // (the previous group's readers left at the barrier below)
             }
             __syncthreads();
@@ -116,36 +130,12 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             }
             __syncthreads();
             {
-                // pass 3 in place: all reads, barrier, then the spectrum in natural (swizzled) order
+                // pass 3 on a unit and its mirror unit, fused with the split into the four real columns' power spectra:
+                // all reads, barrier, then pw[bin] = {col j0, col j0+2, col j0+1, col j0+3} over the same buffer
                 C2 va[8], vb[8];
-                const int ka = t & 15;                         // k2 of both pairs (p = t and t + 128 share p & 15)
-#pragma unroll
-                for (int n3 = 0; n3 < 8; ++n3) {
-                    va[n3] = unpack4(xb[t * 8 + (n3 ^ (ka & 7))]);
-                    vb[n3] = unpack4(xb[(t + 128) * 8 + (n3 ^ (ka & 7))]);
-                }
+                pass3_load(t, xb, va, vb);
                 __syncthreads();
-                dft8(va);
-                dft8(vb);
-                const int kba = (t >> 4) + 16 * ka, kbb = ((t + 128) >> 4) + 16 * ka;
-#pragma unroll
-                for (int k3 = 0; k3 < 8; ++k3) {
-                    xb[spec_index(kba + 256 * k3)] = pack4(va[k3]);
-                    xb[spec_index(kbb + 256 * k3)] = pack4(vb[k3]);
-                }
-            }
-            __syncthreads();
-            {
-                // power spectra of the four real columns, bins k = t + 128 r (r < 8) and k = 1024 (thread 0):
-                // to registers, barrier, then over the spectrum as pw[k] = {col j0, col j0+2, col j0+1, col j0+3}
-                float4 pw[8], pwn = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int r = 0; r < 8; ++r) pw[r] = split_power(xb, t + 128 * r);
-                if (t == 0) pwn = split_power(xb, 1024);
-                __syncthreads();
-#pragma unroll
-                for (int r = 0; r < 8; ++r) xb[t + 128 * r] = pw[r];
-                if (t == 0) xb[1024] = pwn;
+                pass3_power(t, va, vb, xb);
             }
             __syncthreads();
             {
@@ -154,7 +144,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                 int i = 0;
                 for (; i + 1 < mcn; i += 2) {
                     const float w0 = mw[i], w1 = mw[i + 1];
-                    const float4 p0 = xb[mst + i], p1 = xb[mst + i + 1];
+                    const float4 p0 = xb[pw_index(mst + i)], p1 = xb[pw_index(mst + i + 1)];
                     a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
                     a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
                     b02 = fma2(bc(w1), mk(p1.x, p1.y), b02);
@@ -162,7 +152,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                 }
                 if (i < mcn) {
                     const float w0 = mw[i];
-                    const float4 p0 = xb[mst + i];
+                    const float4 p0 = xb[pw_index(mst + i)];
                     a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
                     a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
                 }
