@@ -7,10 +7,10 @@
 //   pass 1: thread t = 8 n2 + n3 holds x[t + 128 n1] (coalesced loads), DFT-16 over n1, twiddle W_2048^(t k1)
 //   exchange through shared memory, layout [k1][n2][n3]
 //   pass 2: thread t = 8 k1 + n3, DFT-16 over n2, twiddle W_128^(n3 k2)
-//   exchange, layout [k1][k2][n3 ^ (k2 & 7)]
+//   exchange, layout [k1][k2][n3 ^ (k1 & 7)]
 //   pass 3: thread u handles two units p = 16 k1 + k2 (DFT-8 over n3 -> X[k1 + 16 k2 + 256 k3]): a unit and the unit of
 //           its mirror frequencies N - k, so that the power spectra of the packed real columns come straight out of
-//           the registers (no spectrum round trip), stored at bin ^ ((bin >> 4) & 7)
+//           the registers (no spectrum round trip), stored in natural order
 // Every shared-memory element is a float4 {re(A), re(B), im(A), im(B)} of the two transforms A and B, and every access
 // pattern above is conflict-free for 16-byte accesses (8 lanes of a quarter-warp hit 8 different 16-byte bank groups).
 //
@@ -182,7 +182,7 @@ GNF2_HD void pass2(int t, const float2* tw2, float4* xbuf_in, float4* xbuf_out) 
             const float2 w = tw2[(k2 - 1) * 8 + n3];
             v = cmul(v, bc(w.x), bc(w.y));
         }
-        xbuf_out[(k1 * 16 + k2) * 8 + (n3 ^ (k2 & 7))] = pack4(v);
+        xbuf_out[(k1 * 16 + k2) * 8 + (n3 ^ (k1 & 7))] = pack4(v);
     }
 }
 
@@ -192,30 +192,31 @@ GNF2_HD void pass2(int t, const float2* tw2, float4* xbuf_in, float4* xbuf_out) 
 // halves of every pair (Z[k], Z[N-k]) are then in the thread's registers, and the power spectra of the real columns
 //   X1 = (Z[k] + conj Z[N-k]) / 2,  X2 = (Z[k] - conj Z[N-k]) / (2i)
 // are formed without writing the spectrum to shared memory and reading it back.
-//   k1 = 1..7  (u = 16..127): pa = u,        pb = 271 - u      (k1' = 16 - k1, k2' = 15 - k2)
-//   k1 = 8     (u = 0..7)   : pa = 128 + u,  pb = 143 - u      (k2' = 15 - k2, same row)
-//   k1 = 0     (u = 9..15)  : pa = u - 8,    pb = 24 - u       (k2' = 16 - k2)
-//   u = 8: the two self-mirrored units (0, 0) and (0, 8): k = 256 k3 and k = 128 + 256 k3
-// A quarter-warp's eight units have eight different k2 & 7 in either half, so the swizzled reads stay conflict-free.
+// With u = 8 k2 + j the eight lanes of a quarter-warp hold eight different k1 & 7 in either half (so the reads, swizzled
+// by k1 & 7, are conflict-free) and store eight consecutive bins (so the power spectrum needs no swizzle):
+//   j = 1..7          : pa = (k1 = j, k2),       pb = (16 - j, 15 - k2)
+//   j = 0, k2 = 0..7  : pa = (8, k2),            pb = (8, 15 - k2)
+//   j = 0, k2 = 9..15 : pa = (0, k2 - 8),        pb = (0, 24 - k2)
+//   j = 0, k2 = 8     : the two self-mirrored units (0, 0) and (0, 8): k = 256 k3 and k = 128 + 256 k3
+constexpr int kSelfMirrorThread = 64;
 GNF2_HD void pass3_units(int u, int& pa, int& pb) {
-    if (u >= 16) { pa = u; pb = 271 - u; }
-    else if (u < 8) { pa = 128 + u; pb = 143 - u; }
-    else if (u == 8) { pa = 0; pb = 8; }
-    else { pa = u - 8; pb = 24 - u; }
+    const int k2 = u >> 3, j = u & 7;
+    if (j != 0) { pa = 16 * j + k2; pb = 16 * (16 - j) + (15 - k2); }
+    else if (k2 < 8) { pa = 128 + k2; pb = 143 - k2; }
+    else if (k2 == 8) { pa = 0; pb = 8; }
+    else { pa = k2 - 8; pb = 24 - k2; }
 }
 
 GNF2_HD void pass3_load(int u, const float4* xbuf_in, C2 (&va)[8], C2 (&vb)[8]) {
     int pa, pb;
     pass3_units(u, pa, pb);
+    const int sa = (pa >> 4) & 7, sb = (pb >> 4) & 7;
     GNF2_UNROLL
     for (int n3 = 0; n3 < 8; ++n3) {
-        va[n3] = unpack4(xbuf_in[pa * 8 + (n3 ^ (pa & 7))]);
-        vb[n3] = unpack4(xbuf_in[pb * 8 + (n3 ^ (pb & 7))]);
+        va[n3] = unpack4(xbuf_in[pa * 8 + (n3 ^ sa)]);
+        vb[n3] = unpack4(xbuf_in[pb * 8 + (n3 ^ sb)]);
     }
 }
-
-// where power bin k (0..1024) lives: lanes with consecutive k2 store to different 16-byte slots
-GNF2_HD int pw_index(int bin) { return bin ^ ((bin >> 4) & 7); }
 
 // {|X1|^2 (A), |X1|^2 (B), |X2|^2 (A), |X2|^2 (B)} from zk = Z[k], zn = Z[N-k] (symmetric in the two: bin k == bin N-k)
 GNF2_HD float4 power_of(C2 zk, C2 zn) {
@@ -231,22 +232,22 @@ GNF2_HD void pass3_power(int u, C2 (&va)[8], C2 (&vb)[8], float4* pw) {
     dft8(va);
     dft8(vb);
     const int ka = (pa >> 4) + 16 * (pa & 15), kb = (pb >> 4) + 16 * (pb & 15);
-    if (u != 8) {
+    if (u != kSelfMirrorThread) {
         GNF2_UNROLL
         for (int i = 0; i < 8; ++i) {
             const int bin = (i < 4) ? ka + 256 * i : kb + 256 * (7 - i);
-            pw[pw_index(bin)] = power_of(va[i], vb[7 - i]);
+            pw[bin] = power_of(va[i], vb[7 - i]);
         }
     } else {
-        pw[pw_index(0)] = power_of(va[0], va[0]);
-        pw[pw_index(256)] = power_of(va[1], va[7]);
-        pw[pw_index(512)] = power_of(va[2], va[6]);
-        pw[pw_index(768)] = power_of(va[3], va[5]);
-        pw[pw_index(1024)] = power_of(va[4], va[4]);
-        pw[pw_index(128)] = power_of(vb[0], vb[7]);
-        pw[pw_index(384)] = power_of(vb[1], vb[6]);
-        pw[pw_index(640)] = power_of(vb[2], vb[5]);
-        pw[pw_index(896)] = power_of(vb[3], vb[4]);
+        pw[0] = power_of(va[0], va[0]);
+        pw[256] = power_of(va[1], va[7]);
+        pw[512] = power_of(va[2], va[6]);
+        pw[768] = power_of(va[3], va[5]);
+        pw[1024] = power_of(va[4], va[4]);
+        pw[128] = power_of(vb[0], vb[7]);
+        pw[384] = power_of(vb[1], vb[6]);
+        pw[640] = power_of(vb[2], vb[5]);
+        pw[896] = power_of(vb[3], vb[4]);
     }
 }
 

@@ -26,7 +26,17 @@ constexpr int kHop = 512;
 constexpr int kMels = 128;
 constexpr int kMfcc = 30;
 constexpr int kT = 128;                     // threads per CTA == gnfft2::kThreads
-constexpr int kXBytes = kFFT * 16;          // exchange / spectrum / power buffer
+constexpr int kXBytes = kFFT * 16;          // exchange / power buffer (8192 floats); in a slot's tail:
+constexpr int kDctCols = 32;                //   DCT partial sums [4 warps][kDctCols][32] = the first 4096 floats,
+constexpr int kDctPart = 4 * kDctCols * 32; //   then the output rows [30][B] over them,
+constexpr int kWStage = kFFT * 4 - kDctPart;    //   and the staged resampling operator W [B][q] in the other 4096
+
+// a sample is read once: it bypasses L1, which then keeps the tables (twiddles, window, DCT rows, W)
+__device__ __forceinline__ float ld_stream(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
 
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
@@ -52,6 +62,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
     // this thread's mel band: contiguous bins [mst, mst + mcn), weights mw[0..mcn); the weights are staged once per CTA
     const int mst = __ldg(mel_start + t), mcn = __ldg(mel_count + t);
     const float* mw = mws + __ldg(mel_offset + t);
+    const int mrot = (mcn > 0) ? (((t & 7) - mst) & 7) % mcn : 0;
     for (int i = t; i < n_mel_w; i += kT) mws[i] = __ldg(mel_w + i);
     __syncthreads();
 
@@ -72,12 +83,12 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             if (base - t + kFirst * 128 >= 0 && base - t + 28 * 128 <= L) {
                 const float* p = seg + base;
 #pragma unroll
-                for (int m = kFirst; m < 28; ++m) raw[m] = __ldg(p + 128 * m);
+                for (int m = kFirst; m < 28; ++m) raw[m] = ld_stream(p + 128 * m);
             } else {
 #pragma unroll
                 for (int m = kFirst; m < 28; ++m) {
                     const int i = base + 128 * m;
-                    raw[m] = ((unsigned)i < (unsigned)L) ? __ldg(seg + i) : 0.f;
+                    raw[m] = ((unsigned)i < (unsigned)L) ? ld_stream(seg + i) : 0.f;
                 }
             }
         };
@@ -125,7 +136,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                         const float2 w = __ldg(tw2 + (k2 - 1) * 8 + n3);
                         v = cmul(v, bc(w.x), bc(w.y));
                     }
-                    xb[(k1 * 16 + k2) * 8 + (n3 ^ (k2 & 7))] = pack4(v);
+                    xb[(k1 * 16 + k2) * 8 + (n3 ^ (k1 & 7))] = pack4(v);
                 }
             }
             __syncthreads();
@@ -139,20 +150,26 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             }
             __syncthreads();
             {
-                // mel filterbank: thread = band (its bins are contiguous); four independent accumulator pairs
+                // mel filterbank: thread = band (its bins are contiguous); four independent accumulator pairs.  A band is
+                // walked from its bin mrot round to mrot - 1, mrot chosen so that the lanes of a quarter-warp start on
+                // eight different 16-byte slots and move on in step: the 128-bit reads do not collide.
                 V2 a02 = bc(0.f), a13 = bc(0.f), b02 = bc(0.f), b13 = bc(0.f);
-                int i = 0;
+                int i = 0, ix = mrot;
                 for (; i + 1 < mcn; i += 2) {
-                    const float w0 = mw[i], w1 = mw[i + 1];
-                    const float4 p0 = xb[pw_index(mst + i)], p1 = xb[pw_index(mst + i + 1)];
+                    int ix1 = ix + 1;
+                    ix1 = (ix1 >= mcn) ? 0 : ix1;
+                    const float w0 = mw[ix], w1 = mw[ix1];
+                    const float4 p0 = xb[mst + ix], p1 = xb[mst + ix1];
                     a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
                     a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
                     b02 = fma2(bc(w1), mk(p1.x, p1.y), b02);
                     b13 = fma2(bc(w1), mk(p1.z, p1.w), b13);
+                    ix = ix1 + 1;
+                    ix = (ix >= mcn) ? 0 : ix;
                 }
                 if (i < mcn) {
-                    const float w0 = mw[i];
-                    const float4 p0 = xb[pw_index(mst + i)];
+                    const float w0 = mw[ix];
+                    const float4 p0 = xb[mst + ix];
                     a02 = fma2(bc(w0), mk(p0.x, p0.y), a02);
                     a13 = fma2(bc(w0), mk(p0.z, p0.w), a13);
                 }
@@ -166,6 +183,17 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
         }
         emax = warp_max(emax);
         if (lane == 0) red[warp] = emax;
+        // Requested now, so that they arrive while the log stage runs: this warp's 32 rows of the (transposed) DCT table
+        // (the warp takes the mel rows 32 warp .. 32 warp + 31 of every column) and the slot's resampling operator W,
+        // staged behind the DCT partial sums when it fits
+        float dct_r[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) dct_r[i] = __ldg(dctT + (32 * warp + i) * 32 + lane);
+        float* fx = reinterpret_cast<float*>(xb);
+        const float* W = w_all + w_offset[slot];
+        const bool w_staged = B * q <= kWStage && kMfcc * B <= kDctPart;
+        if (w_staged)
+            for (int i = t; i < B * q; i += kT) fx[kDctPart + i] = __ldg(W + i);
         __syncthreads();
         // power_to_db: 10 log10(max(1e-10, S)), floored at (segment max - 80 dB); log10 is monotone, so the
         // segment max of the log is the log of the largest energy
@@ -183,39 +211,51 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             *mp = v;
         }
         __syncthreads();
-        // DCT-II (ortho) over the mel axis: cep[c][j] = sum_m dct[c][m] * logmel[m][j]; lane = row c, warp = column quad.
-        // The table is transposed ([m][32]) so that a warp's 32 coefficients are one 128-byte line.
-        {
-            for (int jq = warp; jq < (qp >> 2); jq += kT / 32) {
+        // DCT-II (ortho) over the mel axis: cep[c][j] = sum_m dct[c][m] * logmel[m][j]; lane = row c.  Each warp sums its
+        // 32 mel rows for every column (table rows in registers, log-mels as broadcast reads); the four partial sums are
+        // added in warp order.  Columns go in chunks of kDctCols.
+        for (int c0 = 0; c0 < qp; c0 += kDctCols) {
+            const int nq = ((qp - c0 < kDctCols) ? qp - c0 : kDctCols) >> 2;
+            for (int jq = 0; jq < nq; ++jq) {
                 V2 a01 = bc(0.f), a23 = bc(0.f);
-                const float* mp = mel + 4 * jq;
-#pragma unroll 8
-                for (int m = 0; m < kMels; ++m) {
-                    const float d = __ldg(dctT + m * 32 + lane);
-                    const float4 v = *reinterpret_cast<const float4*>(mp + m * mq);      // broadcast
-                    a01 = fma2(bc(d), mk(v.x, v.y), a01);
-                    a23 = fma2(bc(d), mk(v.z, v.w), a23);
+                const float* mp = mel + (32 * warp) * mq + c0 + 4 * jq;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float4 v = *reinterpret_cast<const float4*>(mp + i * mq);      // broadcast
+                    a01 = fma2(bc(dct_r[i]), mk(v.x, v.y), a01);
+                    a23 = fma2(bc(dct_r[i]), mk(v.z, v.w), a23);
                 }
-                float* cp = cepT + (4 * jq) * 32 + lane;
-                cp[0] = a01.x; cp[32] = a01.y; cp[64] = a23.x; cp[96] = a23.y;
+                float* pp = fx + (warp * kDctCols + 4 * jq) * 32 + lane;
+                pp[0] = a01.x; pp[32] = a01.y; pp[64] = a23.x; pp[96] = a23.y;
             }
+            __syncthreads();
+            for (int i = t; i < nq * 128; i += kT)
+                cepT[c0 * 32 + i] = ((fx[i] + fx[kDctCols * 32 + i]) + fx[2 * kDctCols * 32 + i]) + fx[3 * kDctCols * 32 + i];
+            __syncthreads();
         }
-        __syncthreads();
         // cubic time resampling (utils.py:336-343) as the linear operator W (B x q): warp = output column b (its W row is
-        // one broadcast line), lane = cepstral row c; results are staged row-major in the exchange buffer and stored as
-        // whole lines
+        // a broadcast read), lane = cepstral row c; results are staged row-major over the (dead) partial sums and stored
+        // as whole lines
         {
-            const float* W = w_all + w_offset[slot];
-            float* stage = reinterpret_cast<float*>(xb);
-            for (int bb = warp; bb < B; bb += kT / 32) {
-                const float* wr = W + bb * q;
-                float acc = 0.f;
-                for (int j = 0; j < q; ++j) acc = fmaf(__ldg(wr + j), cepT[j * 32 + lane], acc);
-                if (lane < kMfcc) stage[lane * B + bb] = acc;
+            if (w_staged) {
+                for (int bb = warp; bb < B; bb += kT / 32) {
+                    const float* wr = fx + kDctPart + bb * q;
+                    float acc = 0.f;
+#pragma unroll 8
+                    for (int j = 0; j < q; ++j) acc = fmaf(wr[j], cepT[j * 32 + lane], acc);
+                    if (lane < kMfcc) fx[lane * B + bb] = acc;
+                }
+            } else {
+                for (int bb = warp; bb < B; bb += kT / 32) {
+                    const float* wr = W + bb * q;
+                    float acc = 0.f;
+                    for (int j = 0; j < q; ++j) acc = fmaf(__ldg(wr + j), cepT[j * 32 + lane], acc);
+                    if (lane < kMfcc) fx[lane * B + bb] = acc;
+                }
             }
             __syncthreads();
             float* o = out + slot * (int64_t)(kMfcc * B);
-            for (int i = t; i < kMfcc * B; i += kT) o[i] = stage[i];
+            for (int i = t; i < kMfcc * B; i += kT) o[i] = fx[i];
         }
         // (the next slot's first pass-1 store is behind that slot's loads; cep / mel are rewritten only after barriers)
         __syncthreads();

@@ -54,7 +54,7 @@ int main() {
             if (memcmp(&before[i], &buf1[i], sizeof(float4)) != 0) ++writes[i];
     }
     int coverage_errors = 0;
-    for (int k = 0; k <= kN / 2; ++k) coverage_errors += writes[pw_index(k)] != 1;
+    for (int k = 0; k <= kN / 2; ++k) coverage_errors += writes[k] != 1;
     int total_writes = 0;
     for (int i = 0; i < kN; ++i) total_writes += writes[i];
     coverage_errors += total_writes != kN / 2 + 1;
@@ -70,7 +70,7 @@ int main() {
             p[2][0] += xa_im[n] * c; p[2][1] += xa_im[n] * s;      // real sequence 2 of A
             p[3][0] += xb_im[n] * c; p[3][1] += xb_im[n] * s;      // real sequence 2 of B
         }
-        const float4 pw = buf1[pw_index(k)];
+        const float4 pw = buf1[k];
         const float got[4] = {pw.x, pw.y, pw.z, pw.w};
         for (int i = 0; i < 4; ++i) {
             const double ref = p[i][0] * p[i][0] + p[i][1] * p[i][1];
@@ -100,14 +100,14 @@ int main() {
         int pa, pb;
         pass3_units(u, pa, pb);
         const int p = (i < 8) ? pa : pb, n3 = i & 7;
-        return p * 8 + (n3 ^ (p & 7));
+        return p * 8 + (n3 ^ ((p >> 4) & 7));
     });
     check("pass3 store", 8, [](int u, int i) {
-        if ((u >> 3) == 1) return -1;                      // the quarter-warp with the self-mirrored units (thread 8)
+        if ((u >> 3) == (kSelfMirrorThread >> 3)) return -1;   // the quarter-warp with the self-mirrored units
         int pa, pb;
         pass3_units(u, pa, pb);
         const int ka = (pa >> 4) + 16 * (pa & 15), kb = (pb >> 4) + 16 * (pb & 15);
-        return pw_index((i < 4) ? ka + 256 * i : kb + 256 * (7 - i));
+        return (i < 4) ? ka + 256 * i : kb + 256 * (7 - i);
     });
     printf("power   : max_abs_err %.3e max_ref %.3e rel %.3e\n", perr, pref, perr / pref);
     printf("coverage errors %d, bank conflicts %d\n", coverage_errors, conflicts);

@@ -90,14 +90,17 @@ def test_audio_golden(U, golden):
         np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
 
 
-@pytest.mark.parametrize("n,spf,sr", [(64, 8000, 16000), (5, 11025, 22050), (3, 2100, 16000), (0, 8000, 16000)])
-def test_audio_vs_oracle(U, n, spf, sr):
+@pytest.mark.parametrize("n,spf,sr,B", [(64, 8000, 16000, 30), (5, 11025, 22050, 30), (3, 2100, 16000, 30),
+                                        (0, 8000, 16000, 30),
+                                        (2, 40000, 16000, 30),      # 79 STFT columns: the DCT goes in three column chunks
+                                        (2, 40000, 16000, 60)])     # B q > 4096: W is read from global memory
+def test_audio_vs_oracle(U, n, spf, sr, B):
     y = syn.make_audio(max(n, 1), spf, sr, seed=n)[: max(n, 1) * spf]
     if n == 0:
-        assert U.extract_audio_features_array(y, sr, 0, 30).shape == (0, 30, 30)
+        assert U.extract_audio_features_array(y, sr, 0, B).shape == (0, 30, B)
         return
-    out = U.extract_audio_features_array(y, sr, n, 30, as_numpy=True)
-    ref = O.extract_audio_features_array(y, sr, n, 30)
+    out = U.extract_audio_features_array(y, sr, n, B, as_numpy=True)
+    ref = O.extract_audio_features_array(y, sr, n, B)
     np.testing.assert_allclose(out, ref, rtol=MFCC_RTOL, atol=MFCC_ATOL)
 
 
