@@ -145,14 +145,44 @@ GNF2_HD void dft8(C2 (&v)[8]) {
 GNF2_HD float4 pack4(C2 v) { return make_float4(v.re.x, v.re.y, v.im.x, v.im.y); }
 GNF2_HD C2 unpack4(float4 f) { C2 v; v.re = mk(f.x, f.y); v.im = mk(f.z, f.w); return v; }
 
-// ---- tables (built on the host in double, see gn_fft2_fill_tables) --------------------------------------------
+// ---- tables (built on the host in double) ------------------------------------------------------------------------
 //   tw1[(k1 - 1) * 128 + t] = {wr, wi} of W_2048^(t k1),  k1 = 1..15
 //   tw2[(k2 - 1) * 8 + n3]  = {wr, wi} of W_128^(n3 k2),  k2 = 1..15
 // (scalars: the packed instructions broadcast a 32-bit operand to both lanes for free)
+// A thread reads only the rows k = 1, 2, 4, 8 (four loads, issued before the butterflies that hide their latency) and
+// forms the other eleven powers as products of two of them, at most three multiplications deep: fifteen dependent table
+// loads per pass were the kernel's largest single stall.
 constexpr int kTw1 = 15 * 128, kTw2 = 15 * 8;
+
+struct TwBase { V2 w1, w2, w4, w8; };      // (re, im) pairs of w^1, w^2, w^4, w^8
+GNF2_HD TwBase tw_load(const float2* tw, int stride, int i) {
+    const float2 a = tw[i], b = tw[stride + i], c = tw[3 * stride + i], d = tw[7 * stride + i];
+    TwBase r;
+    r.w1 = mk(a.x, a.y); r.w2 = mk(b.x, b.y); r.w4 = mk(c.x, c.y); r.w8 = mk(d.x, d.y);
+    return r;
+}
+// a * b for (re, im) pairs; b_rot = (-b.im, b.re)
+GNF2_HD V2 cpair_mul(V2 a, V2 b, V2 b_rot) { return fma2(bc(a.x), b, mul2(bc(a.y), b_rot)); }
+// w^k, k = 1..15 (k is a compile-time constant after unrolling; common sub-products are merged by the compiler)
+GNF2_HD V2 tw_power(const TwBase& b, int k) {
+    const V2 r2 = mk(-b.w2.y, b.w2.x), r4 = mk(-b.w4.y, b.w4.x), r8 = mk(-b.w8.y, b.w8.x);
+    V2 lo;                                  // w^(k & 7)
+    switch (k & 7) {
+        case 1: lo = b.w1; break;
+        case 2: lo = b.w2; break;
+        case 3: lo = cpair_mul(b.w1, b.w2, r2); break;
+        case 4: lo = b.w4; break;
+        case 5: lo = cpair_mul(b.w1, b.w4, r4); break;
+        case 6: lo = cpair_mul(b.w2, b.w4, r4); break;
+        case 7: lo = cpair_mul(cpair_mul(b.w1, b.w2, r2), b.w4, r4); break;
+        default: return b.w8;               // k == 8
+    }
+    return (k & 8) ? cpair_mul(lo, b.w8, r8) : lo;
+}
 
 // pass 1 for thread t: z[n1] = x[t + 128 n1] on entry; results to the exchange buffer
 GNF2_HD void pass1(int t, C2 (&z)[16], const float2* tw1, float4* xbuf) {
+    const TwBase tb = tw_load(tw1, 128, t);
     dft16(z);
     const int n2 = t >> 3, n3 = t & 7;
     GNF2_UNROLL
@@ -160,7 +190,7 @@ GNF2_HD void pass1(int t, C2 (&z)[16], const float2* tw1, float4* xbuf) {
         const int k1 = perm16(p);
         C2 v = z[p];
         if (k1 != 0) {
-            const float2 w = tw1[(k1 - 1) * 128 + t];
+            const V2 w = tw_power(tb, k1);
             v = cmul(v, bc(w.x), bc(w.y));
         }
         xbuf[(k1 * 16 + n2) * 8 + n3] = pack4(v);
@@ -170,6 +200,7 @@ GNF2_HD void pass1(int t, C2 (&z)[16], const float2* tw1, float4* xbuf) {
 // pass 2 for thread t = 8 k1 + n3
 GNF2_HD void pass2(int t, const float2* tw2, float4* xbuf_in, float4* xbuf_out) {
     const int k1 = t >> 3, n3 = t & 7;
+    const TwBase tb = tw_load(tw2, 8, n3);
     C2 z[16];
     GNF2_UNROLL
     for (int n2 = 0; n2 < 16; ++n2) z[n2] = unpack4(xbuf_in[(k1 * 16 + n2) * 8 + n3]);
@@ -179,7 +210,7 @@ GNF2_HD void pass2(int t, const float2* tw2, float4* xbuf_in, float4* xbuf_out) 
         const int k2 = perm16(p);
         C2 v = z[p];
         if (k2 != 0) {
-            const float2 w = tw2[(k2 - 1) * 8 + n3];
+            const V2 w = tw_power(tb, k2);
             v = cmul(v, bc(w.x), bc(w.y));
         }
         xbuf_out[(k1 * 16 + k2) * 8 + (n3 ^ (k1 & 7))] = pack4(v);

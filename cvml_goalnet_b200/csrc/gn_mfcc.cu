@@ -123,6 +123,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
             {
                 // pass 2 in place: a quarter-warp (same k1) reads and writes the same 128 elements
                 const int k1 = t >> 3, n3 = t & 7;
+                const TwBase tb = tw_load(tw2, 8, n3);
                 C2 z[16];
 #pragma unroll
                 for (int n2 = 0; n2 < 16; ++n2) z[n2] = unpack4(xb[(k1 * 16 + n2) * 8 + n3]);
@@ -133,7 +134,7 @@ mfcc_kernel(const float* __restrict__ y, const int64_t* __restrict__ seg_start, 
                     const int k2 = perm16(p);
                     C2 v = z[p];
                     if (k2 != 0) {
-                        const float2 w = __ldg(tw2 + (k2 - 1) * 8 + n3);
+                        const V2 w = tw_power(tb, k2);
                         v = cmul(v, bc(w.x), bc(w.y));
                     }
                     xb[(k1 * 16 + k2) * 8 + (n3 ^ (k1 & 7))] = pack4(v);
