@@ -109,6 +109,7 @@ SIGNATURES = {
     "gn_clip_information": (_I, [_P, _P, _L, _I, _L, _P, _I, _P, _P, _P]),
     "gn_knapsack_workspace_bytes": (_L, [_I, _L]),
     "gn_knapsack": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P, _P, _L, _P]),
+    "gn_knapsack_static": (_I, [_P, _P, _P, _I, _L, _I, _I, _P, _P, _P]),
     "gn_summary_indicator": (_I, [_P, _P, _P, _I, _L, _P, _P]),
     "gn_fscore_counts": (_I, [_P, _P, _P, _I, _L, _P, _P]),
     "gn_fusion_trainer_create": (_I, [_P, C.POINTER(_P), C.POINTER(gn_fusion_state), _I, _L, _P]),

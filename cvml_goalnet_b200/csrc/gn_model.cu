@@ -32,6 +32,7 @@ extern "C" const char* gn_status_string(int s) {
         case GN_E_WORKSPACE: return "workspace too small";
         case GN_E_NODEVICE: return "no usable CUDA device";
         case GN_E_RANGE: return "integer range exceeded";
+        case GN_E_STATIC_LIMIT: return "problem exceeds the static scratch limit of the allocation-free entry point";
         default: break;
     }
     if (s > 0) return cudaGetErrorString((cudaError_t)s);

@@ -3,6 +3,7 @@
 //   gn_knapsack          <- utils.py:466-510 (0/1 DP + backtrack)
 //   gn_summary_indicator <- utils.py:638-641
 //   gn_fscore_counts     <- utils.py:571-573 (the three sums per annotator)
+#include <mutex>
 #include <stdio.h>
 #include <stdlib.h>
 #include "gn_common.cuh"
@@ -618,6 +619,58 @@ extern "C" int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t*
         0);
     GN_LAUNCHED(h);
     return GN_OK;
+}
+
+// ---- gn_knapsack without a caller workspace and without any allocation ----------------------------------------------
+// The scratch (decision bits, fallback table rows, status words) lives in a file-scope device array: every GPU that
+// loads the library holds GN_KNAPSACK_STATIC_MAX_BYTES of it until exit.  In host code `g_knap_scratch` is only a
+// stand-in for the symbol; its device address is looked up once per device with cudaGetSymbolAddress (that device
+// current) and it is that address the kernels receive.
+static __device__ __align__(256) unsigned char g_knap_scratch[GN_KNAPSACK_STATIC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+void* g_knap_scratch_ptr[kMaxStaticDevices];       // device address of g_knap_scratch on each device, 0 = not looked up
+std::mutex g_knap_scratch_mutex;
+
+int knap_scratch_address(int device, void** out) {
+    if (device < 0 || device >= kMaxStaticDevices) return GN_E_ARG;
+    std::lock_guard<std::mutex> lock(g_knap_scratch_mutex);
+    if (!g_knap_scratch_ptr[device]) {
+        int cur = -1;
+        GN_CUDA(cudaGetDevice(&cur));
+        if (cur != device) GN_CUDA(cudaSetDevice(device));
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_knap_scratch);
+        if (cur != device) cudaSetDevice(cur);
+        if (e != cudaSuccess) { cudaGetLastError(); return (int)e; }
+        if (!p) return GN_E_NODEVICE;
+        g_knap_scratch_ptr[device] = p;
+    }
+    *out = g_knap_scratch_ptr[device];
+    return GN_OK;
+}
+}  // namespace
+
+extern "C" int gn_knapsack_static(gn_handle* h, const int32_t* d_values, const int32_t* d_weights, int n_items,
+                                  int64_t capacity, int capacity_rem, int batch, uint8_t* d_selected,
+                                  int32_t* d_best, void* stream) {
+    if (!h || n_items < 0 || capacity < 0 || batch < 0 || capacity_rem < 0) return GN_E_ARG;
+    if (batch == 0) return GN_OK;
+    if (capacity > (1LL << 31) - 64) return GN_E_RANGE;
+    const int64_t per = gn_knapsack_workspace_bytes(n_items, capacity);
+    if (per < 0) return (int)per;
+    if (per > (int64_t)GN_KNAPSACK_STATIC_MAX_BYTES / batch) return GN_E_STATIC_LIMIT;
+    void* scratch = nullptr;
+    const int rc = knap_scratch_address(h->device, &scratch);
+    if (rc != GN_OK) return rc;
+    // Nothing in the scratch has to start at zero: every word a kernel reads (decision bits, table rows, status) is
+    // written earlier in the same call.  The status words are cleared all the same, so that a call never sees the
+    // previous call's "declined" marks.
+    GN_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(scratch) + per * batch - 256 * (int64_t)batch, 0,
+                            256 * (size_t)batch, gn_stream(stream)));
+    return gn_knapsack(h, d_values, d_weights, n_items, capacity, capacity_rem, batch, d_selected, d_best, scratch,
+                       per * batch, stream);
 }
 
 // d_dst[m][r * per + j] = d_src[r][m][j] (see goalnet_b200.h): the layout change after an all-gather of frame shards

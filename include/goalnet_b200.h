@@ -37,6 +37,7 @@ extern "C" {
 #define GN_E_WORKSPACE (-3) /* caller workspace too small */
 #define GN_E_NODEVICE (-4)  /* no usable CUDA device / driver entry point missing */
 #define GN_E_RANGE (-5)     /* integer overflow risk (values do not fit the device integer type) */
+#define GN_E_STATIC_LIMIT (-6) /* gn_knapsack_static: the problem needs more than GN_KNAPSACK_STATIC_MAX_BYTES */
 
 typedef struct gn_handle gn_handle; /* per-device context: SM count, driver entry points, tables */
 typedef struct gn_model gn_model;   /* packed AVM weights on the device */
@@ -199,6 +200,21 @@ int64_t gn_knapsack_workspace_bytes(int n_items, int64_t capacity_columns);
 int gn_knapsack(gn_handle* h, const int32_t* d_values, const int32_t* d_weights, int n_items,
                 int64_t capacity, int capacity_rem, int batch, uint8_t* d_selected, int32_t* d_best,
                 void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* gn_knapsack for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO counterpart in the reference.  Same arguments, results
+ * and kernels as gn_knapsack, minus the workspace: the scratch is a static device array of
+ * GN_KNAPSACK_STATIC_MAX_BYTES inside the library (every GPU that loads the library holds it until exit), and the
+ * call itself allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: batch * gn_knapsack_workspace_bytes(n_items, capacity) <= GN_KNAPSACK_STATIC_MAX_BYTES, else
+ * GN_E_STATIC_LIMIT (config 2's problem -- about 380 clips, 24 300 capacity columns -- needs 1.2 MB).
+ * All calls on one device share the array, and it keeps the previous call's contents (nothing in it has to start at
+ * zero; the status words are cleared per call): two calls that OVERLAP on the GPU (different streams, or concurrent
+ * host threads) RACE -- serialise them on one stream, or use gn_knapsack with separate workspaces. */
+#define GN_KNAPSACK_STATIC_MAX_BYTES (8u << 20)
+int gn_knapsack_static(gn_handle* h, const int32_t* d_values, const int32_t* d_weights, int n_items,
+                       int64_t capacity, int capacity_rem, int batch, uint8_t* d_selected, int32_t* d_best,
+                       void* stream);
 
 /* utils.py:638-641: uint8 indicator over raw frames, 1 on a..b INCLUSIVE of every selected clip. */
 int gn_summary_indicator(gn_handle* h, const int32_t* d_clips, const uint8_t* d_selected, int n_clips,
