@@ -399,7 +399,7 @@ def reference_arm(args, rank):
                              "stages_ms": r["stages_ms"], "config2_knapsack": r["config2_knapsack"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -584,7 +584,7 @@ def native_arm(args, rank, world, local_rank):
         line["config3_share"] = share
     if cpu is not None:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -721,7 +721,7 @@ def config3_arm(args, rank, world, local_rank):
                     "h2d_ceiling_how": "bare pinned cudaMemcpyAsync of this rank's frame shards in 16 chunks on every rank at "
                                        "once, best of 3 (slowest rank quoted)"},
             "gpu_launches": int(launches)}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -786,7 +786,7 @@ def train_arm(args, rank, world, local_rank):
                          "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_burst"], "traffic": None,
                          "note": "whole step over the GEMM FLOPs: 18.5 GFLOP per step is ~12 us of tensor time, the step is "
                                  "bound by its ~30 dependent launches"}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -915,7 +915,7 @@ def stress_arm(args, rank, world, local_rank):
                          "flops_per_launch": conv3_flops, "ms_per_launch": acc["conv3_block"],
                          "note": "algorithmic FLOPs (72x72 outputs); the tiles recompute a 2-pixel halo (81 % useful)"},
             "stages_ms": stages}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -988,7 +988,7 @@ def avm_train_arm(args, rank, world, local_rank):
                                  "(p, m, v read and written): 9 x 4 B per parameter; 11.4 GFLOP per sub-step is negligible"}}
     if cpu is not None:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def h2d_arm(args, rank, world, local_rank):
@@ -1002,8 +1002,31 @@ def h2d_arm(args, rank, world, local_rank):
     db = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     gbs, ranks = h2d_ceiling(hz, hb, db, chunks=16, reps=5)
     if rank == 0:
-        print(json.dumps({"metric": "pinned_h2d_GBps", "n_gpus": world, "per_rank": [round(x, 2) for x in ranks],
-                          "aggregate": round(float(np.sum(ranks)), 1), "bytes_per_rank": nbytes, "chunks": 16}), flush=True)
+        emit({"metric": "pinned_h2d_GBps", "n_gpus": world, "per_rank": [round(x, 2) for x in ranks],
+              "aggregate": round(float(np.sum(ranks)), 1), "bytes_per_rank": nbytes, "chunks": 16})
+
+
+_RESULT_FD = None
+
+
+def guard_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to stdout on
+    some boxes), so file descriptor 1 is pointed at stderr for the whole run and the result line goes to the saved one."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, data)
 
 
 def main():
@@ -1026,6 +1049,7 @@ def main():
     ap.add_argument("--no-share", action="store_true", help="N = 1: skip the config-3 share sub-measurement")
     ap.add_argument("--no-graph", action="store_true", help="training workloads: issue every launch instead of replaying a CUDA graph")
     args = ap.parse_args()
+    guard_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
