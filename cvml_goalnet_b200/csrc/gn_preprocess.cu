@@ -157,17 +157,19 @@ preprocess_l2_kernel(const uint8_t* __restrict__ frames, int64_t n, int H, int W
 
 // ---------------------------------------------------------------------------------------------
 // tap-capturing version.  A host-built plan (one per (H, W, S), cached in the handle) lists, as 32-bit
-// words:  header[20] | ly0[S] ly1[S] fy[S] | cb0[S] cb1[S] fx[S] | rowslot[H] | rank[CL][5]
+// words:  header[24] | ly0[S] ly1[S] fy[S] | cb0[S] cb1[S] fx[S] | rowslot[H] | rank[CL][5]
 //   ly0/ly1  compact index of the two source rows of output row y       rowslot  source row -> compact index or -1
 //   cb0/cb1  byte offset inside a source row of the B byte of the two tap pixels of output column x
 //   rank r   {ya, yb, sa, se, first}: output rows [ya,yb), streamed source rows [sa,se), first compact row
+//   narrow outputs (S <= 64) also carry  tapbefore[H+1] (tap rows above source row r)  and  taprow[nR] (compact
+//   index -> source row): a chunk's tap rows are the compact indices [tapbefore[r0], tapbefore[r0 + nr))
 // A compact tap row holds, per output column, the 6 bytes the resize needs (8-byte slots), so the resize pass reads
 // two conflict-free 8-byte words per pixel and looks the bytes up in a lane-private copy of the normalisation LUT.
 // ---------------------------------------------------------------------------------------------
 constexpr int kTapThreads = 512;
 constexpr int kTapWarps = kTapThreads / 32;
 enum { PP_S = 0, PP_H, PP_W, PP_CL, PP_NWC, PP_ROWSMAX, PP_LY0, PP_LY1, PP_FY, PP_CB0, PP_CB1, PP_FX, PP_K,
-       PP_ROWSLOT, PP_SRCWORD, PP_RANK, PP_TOTAL, PP_NSLOT, PP_SLOTB, PP_HEADER = 20 };
+       PP_ROWSLOT, PP_SRCWORD, PP_RANK, PP_TOTAL, PP_NSLOT, PP_SLOTB, PP_TAPBEFORE, PP_TAPROW, PP_HEADER = 24 };
 
 __device__ __forceinline__ uint32_t pp_cluster_ctarank() {
     uint32_t r;
@@ -252,6 +254,8 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
     const float* fx = reinterpret_cast<const float*>(sp + sp[PP_FX]);
     const int* rowslot = sp + sp[PP_ROWSLOT];
     const int K = sp[PP_K];                                            // rows per chunk
+    const int* tapbefore = sp + sp[PP_TAPBEFORE];                      // (narrow outputs only)
+    const int* taprow = sp + sp[PP_TAPROW];
     float* lut = reinterpret_cast<float*>(sp + total);                 // 256 normalised byte levels
     unsigned int* xch = reinterpret_cast<unsigned int*>(lut + 256);    // [2 parities][8 ranks][min, max]
     float* lutr = reinterpret_cast<float*>(xch + 32);                  // [256][32]: one copy of the LUT per lane = per bank
@@ -311,19 +315,40 @@ preprocess_tap_kernel(const uint8_t* __restrict__ frames, int64_t n, const int32
             for (int j = tid; j < nvc; j += kTapThreads) mm.vec(cv[j]);
             // tap rows of this chunk: gather the 6 source bytes of every output column into the compact tap buffer
             const uint8_t* cbytes = reinterpret_cast<const uint8_t*>(cv);
-            // (narrow outputs: one warp per source row; wide outputs, where a chunk is only a few rows: all threads per row)
-            const int rstep = wide ? 1 : kTapWarps, xstep = wide ? kTapThreads : 32;
-            for (int r = wide ? 0 : warp; r < nr; r += rstep) {
-                const int sl = rowslot[sa + r0 + r];
-                const int l = sl - first;
-                if (sl < 0 || l < 0 || l >= rowsMax) continue;
-                for (int x = wide ? tid : lane; x < S; x += xstep) {
-                    const uint8_t* p0 = cbytes + r * RB + cb0[x];
-                    const uint8_t* p1 = cbytes + r * RB + cb1[x];
+            if (wide) {
+                // wide outputs, where a chunk is only a few rows: all threads per row
+                for (int r = 0; r < nr; ++r) {
+                    const int sl = rowslot[sa + r0 + r];
+                    const int l = sl - first;
+                    if (sl < 0 || l < 0 || l >= rowsMax) continue;
+                    for (int x = tid; x < S; x += kTapThreads) {
+                        const uint8_t* p0 = cbytes + r * RB + cb0[x];
+                        const uint8_t* p1 = cbytes + r * RB + cb1[x];
+                        uint2 v;
+                        v.x = (uint32_t)p0[0] | ((uint32_t)p0[1] << 8) | ((uint32_t)p0[2] << 16) | ((uint32_t)p1[0] << 24);
+                        v.y = (uint32_t)p1[1] | ((uint32_t)p1[2] << 8);
+                        tap[l * S + x] = v;
+                    }
+                }
+            } else {
+                // narrow outputs: the chunk's (tap row, output column) pairs are one flat list over all consumer threads
+                // (at 224 -> 40 a 24-row chunk holds 8-9 tap rows: 340 pairs, less than one pass of the 512 threads)
+                int lo = tapbefore[sa + r0], hi = tapbefore[sa + r0 + nr];
+                lo = lo < first ? first : lo;
+                hi = hi > first + rowsMax ? first + rowsMax : hi;
+                const int items = (hi - lo) * S;
+                int k = yy0, x = x0s;                                   // item tid = (tid / S, tid % S)
+                for (int idx = tid; idx < items; idx += kTapThreads) {
+                    const int l = lo + k;
+                    const uint8_t* rowp = cbytes + (taprow[l] - sa - r0) * RB;
+                    const uint8_t* p0 = rowp + cb0[x];
+                    const uint8_t* p1 = rowp + cb1[x];
                     uint2 v;
                     v.x = (uint32_t)p0[0] | ((uint32_t)p0[1] << 8) | ((uint32_t)p0[2] << 16) | ((uint32_t)p1[0] << 24);
                     v.y = (uint32_t)p1[1] | ((uint32_t)p1[2] << 8);
-                    tap[l * S + x] = v;
+                    tap[(l - first) * S + x] = v;
+                    k += dyy; x += dxs;
+                    if (x >= S) { x -= S; ++k; }
                 }
             }
             __syncwarp();
@@ -476,6 +501,9 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
             const int o_rowslot = off; off += H;
             const int o_srcword = off;
             const int o_rank = off; off += 5 * CL;
+            const bool narrow = S <= 64;
+            const int o_tapbefore = off; off += narrow ? H + 1 : 0;
+            const int o_taprow = off; off += narrow ? nR : 0;
             const int total = (off + 3) & ~3;
             const size_t rest = (size_t)(total + 256 + 32 + (S > 64 ? 256 * 32 : 0)) * 4 + (size_t)rowsMax * nWc * 4;
             const size_t slotB = ((size_t)K * 3 * W + 127) & ~(size_t)127;
@@ -499,6 +527,15 @@ bool build_plan(int H, int W, int S, std::vector<int32_t>& out, int& CL_out, siz
             }
             for (int r = 0; r < H; ++r) out[o_rowslot + r] = rowslot[r];
             for (int i = 0; i < 5 * CL; ++i) out[o_rank + i] = rk[i];
+            out[PP_TAPBEFORE] = o_tapbefore; out[PP_TAPROW] = o_taprow;
+            if (narrow) {
+                int seen = 0;
+                for (int r = 0; r < H; ++r) {
+                    out[o_tapbefore + r] = seen;
+                    if (rowslot[r] >= 0) out[o_taprow + seen++] = r;
+                }
+                out[o_tapbefore + H] = seen;
+            }
             CL_out = CL;
             smem_out = smem;
             return true;
