@@ -851,6 +851,181 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
 }
 
+// =====================================================================================================================
+// linear5 on CTA pairs: the split-K GEMM of run_linear_splitk with one M = 256 MMA per k-step over two 128-row blocks.
+// Each CTA of the pair stages ITS row block's A box and HALF of the tile's BN weight rows (32 KB per stage instead of
+// 48: the single-CTA kernel read 48 KB of operands from its own shared memory per 128-cycle MMA, more than the port
+// delivers).  Same K ranges and the same partial-sum slabs as the single-CTA kernel: the sums a row receives do not
+// change (an accumulator row still adds the same products in the same order), so batch invariance is untouched.
+// =====================================================================================================================
+template <int BN, int STAGES>
+struct PairLinCfg {
+    static constexpr int kABytes = 128 * 128;            // this CTA's 128 rows x 64 k
+    static constexpr int kBBytes = (BN / 2) * 128;       // this CTA's half of the weight rows
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kSmemBytes = 1024 + STAGES * kStageBytes + 256;
+    static_assert(BN <= kAccCols && BN % 64 == 0, "one 128-row tile per CTA, <= 256 columns");
+    static_assert(kSmemBytes <= 232448, "exceeds the 227 KB shared memory of one CTA");
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_splitk_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      const GemmArgs args) {
+    using C = PairLinCfg<BN, STAGES>;
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    unsigned char* stage_base = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::kStageBytes);
+    uint64_t* full_bar = bars;                    // [STAGES]  (the leader's are the ones in use)
+    uint64_t* empty_bar = bars + STAGES;          // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]       (the leader's are the ones in use)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader
+    const int n_blocks = args.N / BN;
+    const int64_t m_blocks = (args.M + 127) / 128;
+    const int64_t m_pairs = (m_blocks + 1) / 2;
+    const int k_splits = args.k_splits > 1 ? args.k_splits : 1;
+    const int64_t num_units = m_pairs * n_blocks * k_splits;
+    const int64_t cl = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+    const int k_total = args.K / kBK;
+    const int k_per = (k_total + k_splits - 1) / k_splits;
+    // unit -> (row-block pair, n_blk, split): split fastest, then n_blk (pairs running side by side share A and W in L2)
+#define GN_PAIR_UNIT_DECODE()                                                             \
+    const int64_t mn_ = unit / k_splits;                                                  \
+    const int ks = (int)(unit - mn_ * k_splits);                                          \
+    const int64_t mp = mn_ / n_blocks;                                                    \
+    const int n_blk = (int)(mn_ - mp * n_blocks);                                         \
+    const int64_t m_blk = 2 * mp + rank;                                                  \
+    const int k_begin = ks * k_per;                                                       \
+    const int k_iters = (k_total - k_begin) < k_per ? (k_total - k_begin) : k_per;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_a);
+        prefetch_tmap(&tmap_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(smem_u32(&full_bar[s]), 1);             // the leader's arrive.expect_tx (it expects BOTH CTAs' bytes)
+            mbar_init(smem_u32(&empty_bar[s]), 1);            // the multicast MMA commit
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(&tfull_bar[b]), 1);            // the multicast MMA commit
+            mbar_init(smem_u32(&tempty_bar[b]), 2 * kEpiWarps);   // every epilogue warp of both CTAs
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                       // the peer's barriers are initialised before any remote arrive
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t unit = cl; unit < num_units; unit += ncl) {
+                GN_PAIR_UNIT_DECODE();
+                for (int it = 0; it < k_iters; ++it) {
+                    const int kt = k_begin + it;
+                    mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+                    const uint32_t fb = mapa(smem_u32(&full_bar[stage]), 0);       // the leader's barrier
+                    const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                    const uint32_t sb = sa + C::kABytes;
+                    // the leader alone arms its barrier, with the bytes of both CTAs' loads (see tc_conv_pair_kernel)
+                    if (rank == 0) mbar_expect_tx(smem_u32(&full_bar[stage]), 2u * (uint32_t)C::kStageBytes);
+                    // K-blocked operands: every box is one contiguous chunk.  A row block beyond the last one (odd number
+                    // of blocks) lies outside the map and is zero-filled.
+                    tma_load_2d_pair(sa, &tmap_a, fb, 0, (int)((m_blk * k_total + kt) * 128));
+                    tma_load_2d_pair(sb, &tmap_b, fb, 0, kt * args.N + n_blk * BN + (int)rank * (BN / 2));
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader only) =====================
+        if (rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(256, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int ab = 0;
+            uint32_t aphase = 0;
+            for (int64_t unit = cl; unit < num_units; unit += ncl) {
+                GN_PAIR_UNIT_DECODE();
+                (void)m_blk; (void)n_blk;
+                mbar_wait(smem_u32(&tempty_bar[ab]), aphase ^ 1);                  // both epilogues drained this buffer
+                tc_fence_after();
+                for (int it = 0; it < k_iters; ++it) {
+                    mbar_wait(smem_u32(&full_bar[stage]), phase);                  // both CTAs' operands have landed
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+                        const uint32_t sb = sa + C::kABytes;
+                        const uint32_t d = tmem_base + (uint32_t)(ab * kAccCols);
+#pragma unroll
+                        for (int k4 = 0; k4 < kBK / 16; ++k4)
+                            umma_bf16_pair(d, make_desc_sw128(sa + k4 * 32), make_desc_sw128(sb + k4 * 32), idesc,
+                                           (it > 0 || k4 > 0) ? 1u : 0u);
+                        umma_commit_pair(smem_u32(&empty_bar[stage]));             // both CTAs' stage is free
+                        if (it == k_iters - 1) umma_commit_pair(smem_u32(&tfull_bar[ab]));   // both accumulators ready
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                if (++ab == 2) { ab = 0; aphase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..9, both CTAs: each stores ITS row block's partial sums) ============
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int row = q * 32 + lane;
+        int ab = 0;
+        uint32_t aphase = 0;
+        for (int64_t unit = cl; unit < num_units; unit += ncl) {
+            GN_PAIR_UNIT_DECODE();
+            (void)k_iters;
+            const int n0 = n_blk * BN;
+            const int64_t grow = m_blk * 128 + row;
+            mbar_wait(smem_u32(&tfull_bar[ab]), aphase);
+            tc_fence_after();
+            const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * kAccCols);
+#pragma unroll 1
+            for (int c = half; c < BN / 32; c += 2) {
+                uint32_t r[32];
+                tmem_ld32(tbase + (uint32_t)(c * 32), r);
+                tmem_ld_wait();
+                if (grow < args.M) {
+                    float4* df = reinterpret_cast<float4*>(args.out_f32 + (size_t)ks * args.split_stride +
+                                                           (size_t)grow * args.N + n0 + c * 32);
+#pragma unroll
+                    for (int v = 0; v < 8; ++v)
+                        df[v] = make_float4(__uint_as_float(r[v * 4]), __uint_as_float(r[v * 4 + 1]),
+                                            __uint_as_float(r[v * 4 + 2]), __uint_as_float(r[v * 4 + 3]));
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa(smem_u32(&tempty_bar[ab]), 0));   // on the leader's barrier
+            if (++ab == 2) { ab = 0; aphase ^= 1; }
+        }
+    }
+#undef GN_PAIR_UNIT_DECODE
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();        // no CTA leaves while its peer may still arrive on its barriers or the leader's MMAs write its TMEM
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+}
+
 // ---- host side --------------------------------------------------------------------------------------
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1056,8 +1231,39 @@ int run_linear_splitk(gn_model* m, int64_t M, const __nv_bfloat16* A, int64_t K,
     if (rc) return rc;
     GemmArgs a{};
     a.M = M; a.N = N; a.K = (int)K; a.out_f32 = part; a.k_splits = splits; a.split_stride = M * N; a.kblocked = 1;
-    rc = launch<1, BN, 4, kSplitK, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN) * splits, st);
-    if (rc) return rc;
+    static const bool single = getenv("GN_LINEAR5_SINGLE") != nullptr;      // the single-CTA kernel, kept for A/B timing
+    if (single) {
+        rc = launch<1, BN, 4, kSplitK, 0>(m->h, ta, tb, a, ((M + 127) / 128) * (N / BN) * splits, st);
+        if (rc) return rc;
+    } else {
+        // CTA pairs: two 128-row blocks per MMA, each CTA fetches half of the weight rows
+        constexpr int kStages = 6;
+        using C = PairLinCfg<BN, kStages>;
+        rc = make_tmaps_kblocked(m->h, &ta, &tb, A, M, K, wk, N, BN / 2);
+        if (rc) return rc;
+        auto kern = tc_splitk_pair_kernel<BN, kStages>;
+        if (gn_attr_first(m->h, reinterpret_cast<const void*>(kern)))
+            GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+        const int64_t units = (((M + 127) / 128 + 1) / 2) * (N / BN) * splits;
+        int64_t clusters = m->h->num_sms / 2;
+        if (clusters > units) clusters = units;
+        if (clusters >= 1) {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)(2 * clusters));
+            cfg.blockDim = dim3(kThreads);
+            cfg.dynamicSmemBytes = C::kSmemBytes;
+            cfg.stream = st;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2;
+            at[0].val.clusterDim.y = 1;
+            at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            GN_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, a));
+            GN_LAUNCHED(m->h);
+        }
+    }
     const int64_t blocks = (M * N / 4 + 255) / 256, cap = (int64_t)m->h->num_sms * 8;
     splitk_reduce_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(part, splits, M, N, bias, out, ld_out,
                                                                              col_off, out_f32);
