@@ -5,6 +5,7 @@
 //   * AudBl: conv1d 30->64 s2, conv1d 64->128 s2, linear -> 128, ReLUs             (utils.py:216-225)
 //     -> TF32 columns [0,128) of the fusion input (audio first, utils.py:266).
 #include "gn_common.cuh"
+#include "gn_fft2.cuh"      // packed fp32 helpers (V2, fma2)
 
 namespace {
 
@@ -294,53 +295,89 @@ audbl_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, int L2, co
 }
 
 // AudBl conv1 (30 -> 64, k3 s2 p1) + ReLU on CUDA cores (fp32: the raw MFCCs span +-600), written as
-// bf16 (position, channel)-major rows with a zero row on each side for the tensor-core conv2.
-// thread = (output channel, position group); its 90 weights live in registers, the inputs of kCF frames
-// are staged transposed ([t][ci], ci padded to 32) so that a tap is 8 broadcast 16-byte loads.
+// TF32 (position, channel)-major rows with a zero row on each side for the tensor-core conv2.
+// thread = (output channel, position group); its 90 weights live in registers.  TWO frames ride in the two lanes of
+// the packed fp32 instructions (a scalar FFMA issues every other cycle): the inputs of kCF frames are staged as
+// [frame pair][t][ci][2], so that one 16-byte load is two input channels of both frames and a tap is 15 broadcast
+// loads; the 16-byte groups of a row are XOR-swizzled with the row so that the transposing stores do not all hit one
+// bank (the plain [t][ci] layout was a 32-way conflict).
 constexpr int kCThreads = 256;
 constexpr int kCF = 4;
 
 __global__ void __launch_bounds__(kCThreads, 2)
 audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, const float* __restrict__ w1,
                    const float* __restrict__ b1, float* __restrict__ ac1) {
-    extern __shared__ __align__(16) float sm[];            // [kCF][B+2][32]
+    using gnfft2::V2;
+    using gnfft2::bc;
+    using gnfft2::mk;
+    using gnfft2::fma2;
+    extern __shared__ __align__(16) float sm_all[];        // 2 x [kCF / 2][B + 2][32 ci][2 frames]
     const int tid = threadIdx.x, co = tid & 63, g = tid >> 6;
     const int rows = B + 2;
+    const int buf_floats = (kCF / 2) * rows * 64;
+    const unsigned b_magic = 0xFFFFFFFFu / (unsigned)B + 1u;      // __umulhi(r, b_magic) == r / B for r < 2^16
     float wr[90];
 #pragma unroll
     for (int i = 0; i < 90; ++i) wr[i] = __ldg(w1 + co * 90 + i);     // [ci][k]
     const float bias = __ldg(b1 + co);
-    for (int i = tid; i < kCF * rows * 32; i += kCThreads) sm[i] = 0.f;   // pad rows / pad channels stay zero
-    for (int64_t f0 = (int64_t)blockIdx.x * kCF; f0 < n; f0 += (int64_t)gridDim.x * kCF) {
+    for (int i = tid; i < 2 * buf_floats; i += kCThreads) sm_all[i] = 0.f;     // pad rows stay zero
+    __syncthreads();
+    // the inputs of pass p+1 travel (cp.async, 4 bytes each: the copy transposes) while pass p is computed
+    auto stage = [&](int64_t f0, int buf) {
         const int nf = (int)((n - f0) < kCF ? (n - f0) : kCF);
-        __syncthreads();
-        for (int i = tid; i < nf * 30 * B; i += kCThreads) {
-            const int f = i / (30 * B), r = i - f * 30 * B, ci = r / B, t = r - ci * B;
-            sm[(f * rows + t + 1) * 32 + ci] = __ldg(aud + f0 * 30 * B + i);
-        }
-        __syncthreads();
-        for (int f = 0; f < nf; ++f) {
-            float* o = ac1 + (f0 + f) * (int64_t)(L1 + 2) * 64;
-            if (g == 0) { o[co] = 0.f; o[(L1 + 1) * 64 + co] = 0.f; }
-            for (int l = g; l < L1; l += kCThreads / 64) {
-                float acc = bias;
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float4* xr = reinterpret_cast<const float4*>(sm + (f * rows + 2 * l + k) * 32);   // t = 2l-1+k
-#pragma unroll
-                    for (int v = 0; v < 8; ++v) {
-                        const float4 x = xr[v];
-                        acc = fmaf(x.x, wr[(4 * v) * 3 + k], acc);
-                        acc = fmaf(x.y, wr[(4 * v + 1) * 3 + k], acc);
-                        if (v < 7) {
-                            acc = fmaf(x.z, wr[(4 * v + 2) * 3 + k], acc);
-                            acc = fmaf(x.w, wr[(4 * v + 3) * 3 + k], acc);
-                        }
-                    }
-                }
-                o[(l + 1) * 64 + co] = gn_round_tf32(fmaxf(acc, 0.f));
+        const uint32_t base = (uint32_t)__cvta_generic_to_shared(sm_all + buf * buf_floats);
+        for (int f = 0; f < kCF; ++f) {
+            const bool live = f < nf;                          // frames beyond the batch: zero fill (src-size 0)
+            const float* src = aud + (live ? (f0 + f) * 30 * B : 0);
+            const uint32_t fbase = base + 4u * (uint32_t)((f >> 1) * rows * 64 + (f & 1));
+            for (int r = tid; r < 30 * B; r += kCThreads) {
+                const int ci = (int)__umulhi((unsigned)r, b_magic), t = r - ci * B;      // r / B, r % B (r < 2^16)
+                const int row = t + 1;
+                const uint32_t dst = fbase + 4u * (uint32_t)(row * 64 + (((ci >> 1) ^ (row & 15)) << 2) + ((ci & 1) << 1));
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src + (live ? r : 0)),
+                             "r"(live ? 4 : 0) : "memory");
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const int64_t fstep = (int64_t)gridDim.x * kCF;
+    int buf = 0;
+    if ((int64_t)blockIdx.x * kCF < n) stage((int64_t)blockIdx.x * kCF, 0);
+    for (int64_t f0 = (int64_t)blockIdx.x * kCF; f0 < n; f0 += fstep, buf ^= 1) {
+        const int nf = (int)((n - f0) < kCF ? (n - f0) : kCF);
+        const bool more = f0 + fstep < n;
+        if (more) stage(f0 + fstep, buf ^ 1);                  // (its previous readers passed the barrier below)
+        if (more) asm volatile("cp.async.wait_group 1;" ::: "memory");
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        const float* sm = sm_all + buf * buf_floats;
+        for (int fp = 0; 2 * fp < nf; ++fp) {
+            float* o0 = ac1 + (f0 + 2 * fp) * (int64_t)(L1 + 2) * 64;
+            float* o1 = o0 + (int64_t)(L1 + 2) * 64;
+            const bool two = 2 * fp + 1 < nf;
+            if (g == 0) {
+                o0[co] = 0.f; o0[(L1 + 1) * 64 + co] = 0.f;
+                if (two) { o1[co] = 0.f; o1[(L1 + 1) * 64 + co] = 0.f; }
+            }
+            for (int l = g; l < L1; l += kCThreads / 64) {
+                V2 acc0 = mk(bias, bias), acc1 = bc(0.f);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const int row = 2 * l + k;                                                   // t = 2l-1+k
+                    const float4* xr = reinterpret_cast<const float4*>(sm + (fp * rows + row) * 64);
+                    const int sw = row & 15;
+#pragma unroll
+                    for (int v = 0; v < 15; ++v) {
+                        const float4 x = xr[v ^ sw];
+                        acc0 = fma2(mk(x.x, x.y), bc(wr[(2 * v) * 3 + k]), acc0);
+                        acc1 = fma2(mk(x.z, x.w), bc(wr[(2 * v + 1) * 3 + k]), acc1);
+                    }
+                }
+                o0[(l + 1) * 64 + co] = gn_round_tf32(fmaxf(acc0.x + acc1.x, 0.f));
+                if (two) o1[(l + 1) * 64 + co] = gn_round_tf32(fmaxf(acc0.y + acc1.y, 0.f));
+            }
+        }
+        __syncthreads();                                       // this buffer is refilled by the next pass's stage()
     }
 }
 
@@ -385,7 +422,7 @@ int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& w
         GN_LAUNCHED(m->h);
         return GN_OK;
     }
-    const size_t smem = sizeof(float) * kCF * (m->B + 2) * 32;
+    const size_t smem = sizeof(float) * 2 * (kCF / 2) * (m->B + 2) * 64;      // two staging buffers
     if (smem > 48 * 1024) return GN_E_SHAPE;
     const int64_t groups = (n + kCF - 1) / kCF;
     const int64_t cap = (int64_t)m->h->num_sms * 2;
