@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GN_LIB_PATH: development override to A/B two builds of the same ABI on one box (never a different backend)
 LIB_PATH = os.environ.get("GN_LIB_PATH") or os.path.join(_HERE, "libgoalnet_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu", "gn_train.cu", "gn_train_avm.cu"]
+SOURCES = ["gn_preprocess.cu", "gn_mfcc.cu", "gn_front.cu", "gn_front_tc.cu", "gn_tc_gemm.cu", "gn_model.cu", "gn_select.cu", "gn_train.cu", "gn_train_avm.cu"]
 NVCC_FLAGS = ["-shared", "-Xcompiler", "-fPIC", "-std=c++17", "-O3", "-lineinfo",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 

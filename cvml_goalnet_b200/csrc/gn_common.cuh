@@ -132,7 +132,8 @@ int gn_launch_zero_border(gn_handle* h, __nv_bfloat16* buf, int64_t n, int PW, i
 int gn_linear5_splits(const gn_model* m);   // gn_tc_gemm.cu: number of K ranges of linear5 (a function of K only: batch-invariant sums)
 
 // ---- stage launchers (defined in the per-stage .cu files) ----------------------------------------
-int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);
+int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt = false);
+int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);   // gn_front_tc.cu
 int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt);
 int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st);   // conv2 + linear3 on tensor cores
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,

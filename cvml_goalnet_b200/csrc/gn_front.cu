@@ -383,7 +383,11 @@ audbl_conv1_kernel(const float* __restrict__ aud, int64_t n, int B, int L1, cons
 
 }  // namespace
 
-int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
+int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt) {
+    // the 40x40 model's block 1 runs on the tensor cores (gn_front_tc.cu); the CUDA-core kernel below stays as the
+    // validation path (gn_dbg_avm_forward_simt) and for A/B timing (GN_BLOCK1_SIMT)
+    static const bool force_simt = getenv("GN_BLOCK1_SIMT") != nullptr;
+    if (m->S == kS && m->C1 == kC1 && !simt && !force_simt) return gn_launch_visbl_block1_tc(m, d_visual, n, ws, st);
     if (m->S != kS || m->C1 != kC1) {
         const size_t smem_t = sizeof(float) * kT1 * kT1 * (64 + kPatch);
         if (gn_attr_first(m->h, reinterpret_cast<const void*>(visbl_block1_tiled_kernel)))

@@ -1,0 +1,202 @@
+// VisBl block 1 of the 40x40 model on the tensor cores: conv1 3->64 k3 s3 p3 + ReLU + MaxPool(3,1) + BatchNorm(eval)
+// (utils.py:174-177) -> bf16 NHWC with a zero border (the padding = 1 input of conv2).
+//
+// conv1 has stride == kernel size, so its im2col is a PERMUTATION of the zero-padded image: pixel (y, x) of channel ci
+// is tap k = ci*9 + (y%3)*3 + x%3 of conv pixel (y/3+1, x/3+1).  The CUDA-core kernel (gn_front.cu) spent its time
+// feeding 27 taps x 64 channels through the LSU (72 % of the shared-memory pipe) and half-rate scalar FFMAs; here the
+// frame is scattered once into a K-major, 128-byte-swizzled patch matrix (one 128-byte row = the 27 taps of a conv
+// pixel, padded to 32) and the convolution is one tcgen05 GEMM per frame:
+//     D[channel][pixel] = sum_k W[channel][k] * patch[pixel][k]        M = 128, N = 240, K = 32, kind::tf32
+//   * rows (TMEM lanes) = channels -- the 64 channels twice, so that all four warps of the CTA have lanes to read;
+//     columns = conv pixels at 16 y + x (a conv row starts on a 16-column boundary): a thread owns one channel and
+//     walks down the conv rows of its half of the image, so the separable 3x3/s1 max pool, bias + ReLU (monotone:
+//     they commute with the max) and the BatchNorm affine all happen in registers -- no staging tile in shared memory;
+//   * fp32 accuracy from TF32 tensor cores: both operands are split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and
+//     three MMAs accumulate hi*hi + lo*hi + hi*lo (the dropped lo*lo term is 2^-22 relative): the inputs of this layer
+//     are normalised pixels whose fp32 precision the CUDA-core kernel kept, and the parity budget is spent elsewhere.
+// One CTA = 128 threads, 256 TMEM columns, ~105 KB of shared memory -> two CTAs per SM overlap each other's phases
+// (scatter / MMA / epilogue); the next frame's pixels travel to registers during the MMA and the epilogue.
+#include "gn_common.cuh"
+#include "gn_tc_ptx.cuh"
+
+namespace {
+
+using namespace tcx;
+
+constexpr int kS = 40;               // frame side (reference utils.py:285)
+constexpr int kC1 = 15;              // conv1 output side: (40 + 2*3 - 3)/3 + 1
+constexpr int kP = kC1 - 2;          // pooled side
+constexpr int kNPix = 16 * kC1;      // GEMM N: conv pixel (y, x) is column 16 y + x
+constexpr int kBT = 128;             // threads
+constexpr int kBBytes = kNPix * 128; // one patch matrix (hi or lo)
+constexpr int kABytes = 128 * 128;   // one weight matrix (hi or lo): 128 rows = the 64 channels twice
+constexpr int kTmemColsB1 = 256;
+constexpr int kVec = 3 * kS * kS / 4, kPre = (kVec + kBT - 1) / kBT;
+constexpr size_t kB1Smem = 1024 + 2 * kBBytes + 2 * kABytes + sizeof(unsigned short) * 3 * kS * kS + 64;
+
+// float index of element (row r, k) in a K-major tile with 128-byte rows and the 128-byte swizzle
+__device__ __forceinline__ int sw_index(int r, int k) { return r * 32 + ((((k >> 2) ^ (r & 7))) << 2) + (k & 3); }
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kBT, 2)
+visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __restrict__ w /*[27][64], k=(ky*3+kx)*3+ci*/,
+                       const float* __restrict__ b, const float* __restrict__ sc, const float* __restrict__ sh,
+                       __nv_bfloat16* __restrict__ a1p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* Bhi = reinterpret_cast<float*>(smem);                               // [240][32] patch matrix, hi parts
+    float* Blo = reinterpret_cast<float*>(smem + kBBytes);                     //           lo parts
+    float* Ahi = reinterpret_cast<float*>(smem + 2 * kBBytes);                 // [128][32] weights (64 channels twice)
+    float* Alo = reinterpret_cast<float*>(smem + 2 * kBBytes + kABytes);
+    unsigned short* dsto = reinterpret_cast<unsigned short*>(smem + 2 * kBBytes + 2 * kABytes);   // [4800] scatter offsets
+    uint64_t* bar = reinterpret_cast<uint64_t*>(dsto + 3 * kS * kS);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- once per CTA: zero patch matrices (padding pixels, pad column 15, k = 27..31 stay zero), weights, offsets ----
+    for (int i = tid; i < 2 * kNPix * 32; i += kBT) Bhi[i] = 0.f;              // Bhi | Blo are contiguous
+    for (int i = tid; i < 128 * 32; i += kBT) {
+        const int m = i >> 5, k = i & 31, ch = m & 63;
+        const float v = (k < 27) ? __ldg(w + ((k % 9) * 3 + k / 9) * 64 + ch) : 0.f;      // k = ci*9 + tap
+        const float hi = gn_round_tf32(v);
+        Ahi[sw_index(m, k)] = hi;
+        Alo[sw_index(m, k)] = gn_round_tf32(v - hi);
+    }
+    for (int e = tid; e < 3 * kS * kS; e += kBT) {
+        const int ci = e / (kS * kS), r = e - ci * kS * kS, y = r / kS, x = r - y * kS;
+        dsto[e] = (unsigned short)sw_index(16 * (y / 3 + 1) + (x / 3 + 1), ci * 9 + (y % 3) * 3 + (x % 3));
+    }
+    if (tid == 0) {
+        mbar_init(smem_u32(bar), 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), kTmemColsB1);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int ch = tid & 63, half = tid >> 6;                   // channel of this thread's TMEM lane; image half
+    const float bias = __ldg(b + ch), scale = __ldg(sc + ch), shift = __ldg(sh + ch);
+    const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16);
+    const int y_begin = half == 0 ? 0 : 7;                      // pooled rows [y_begin, y_end) of this half
+    const int y_end = half == 0 ? 7 : kP;
+
+    // the next frame's pixels travel to registers while this frame is multiplied and pooled
+    float4 pre[kPre];
+    auto prefetch = [&](int64_t f) {
+        const float4* src = reinterpret_cast<const float4*>(vis + f * 3 * kS * kS);
+#pragma unroll
+        for (int v = 0; v < kPre; ++v) {
+            const int i = tid + v * kBT;
+            if (i < kVec) pre[v] = __ldg(src + i);
+        }
+    };
+    if ((int64_t)blockIdx.x < n) prefetch(blockIdx.x);
+    uint32_t phase = 0;
+    for (int64_t f = blockIdx.x; f < n; f += gridDim.x) {
+        // ---- scatter the frame into the patch matrices (the previous frame's MMAs have completed: every thread waited) ----
+#pragma unroll
+        for (int v = 0; v < kPre; ++v) {
+            const int i = tid + v * kBT;
+            if (i < kVec) {
+                const uint2 o = *reinterpret_cast<const uint2*>(dsto + 4 * i);
+                const float x4[4] = {pre[v].x, pre[v].y, pre[v].z, pre[v].w};
+                const uint32_t o4[4] = {o.x & 0xffffu, o.x >> 16, o.y & 0xffffu, o.y >> 16};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float hi = gn_round_tf32(x4[j]);
+                    Bhi[o4[j]] = hi;
+                    Blo[o4[j]] = gn_round_tf32(x4[j] - hi);
+                }
+            }
+        }
+        fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async-proxy reads
+        tc_fence_before();            // (and this thread's TMEM reads of the previous frame are ordered before the barrier)
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            constexpr uint32_t idesc = make_idesc_tf32(128, kNPix);
+            const uint32_t ahi = smem_u32(Ahi), alo = smem_u32(Alo), bhi = smem_u32(Bhi), blo = smem_u32(Blo);
+            // hi*hi + lo*hi + hi*lo
+#pragma unroll
+            for (int p = 0; p < 3; ++p) {
+                const uint32_t aa = (p == 1) ? alo : ahi, bb = (p == 2) ? blo : bhi;
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4)
+                    umma_tf32(tmem_base, make_desc_sw128(aa + k4 * 32), make_desc_sw128(bb + k4 * 32), idesc,
+                              (p > 0 || k4 > 0) ? 1u : 0u);
+            }
+            umma_commit(smem_u32(bar));
+        }
+        if (f + gridDim.x < n) prefetch(f + gridDim.x);
+        uint32_t* o32 = reinterpret_cast<uint32_t*>(a1p + f * (int64_t)kC1 * kC1 * 64);
+        // zero border = conv2's padding
+        for (int bi = warp; bi < 4 * kC1 - 4; bi += kBT / 32) {
+            int y, x;
+            if (bi < kC1) { y = 0; x = bi; }
+            else if (bi < 2 * kC1) { y = kC1 - 1; x = bi - kC1; }
+            else { const int t = bi - 2 * kC1; y = 1 + (t >> 1); x = (t & 1) ? kC1 - 1 : 0; }
+            o32[(y * kC1 + x) * 32 + lane] = 0u;
+        }
+        mbar_wait(smem_u32(bar), phase);
+        phase ^= 1;
+        tc_fence_after();
+        // ---- epilogue: this thread's channel, conv rows y_begin .. y_end + 1 of D: separable max pool in registers ----
+        __nv_bfloat16* ob = a1p + f * (int64_t)kC1 * kC1 * 64 + ch;
+        float h0[kP], h1[kP];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+            const int y = y_begin + i;                           // conv row (warp-uniform)
+            if (y < y_end + 2) {
+                uint32_t r[16];
+                tmem_ld16(taddr + (uint32_t)(16 * y), r);
+                tmem_ld_wait();
+                float h2[kP];
+#pragma unroll
+                for (int x = 0; x < kP; ++x)
+                    h2[x] = fmaxf(fmaxf(__uint_as_float(r[x]), __uint_as_float(r[x + 1])), __uint_as_float(r[x + 2]));
+                if (i >= 2) {
+                    __nv_bfloat16* orow = ob + ((y - 1) * kC1 + 1) * 64;       // pooled row y - 2 -> padded row y - 1
+#pragma unroll
+                    for (int x = 0; x < kP; ++x) {
+                        const float m = fmaxf(fmaxf(h0[x], h1[x]), h2[x]);
+                        orow[x * 64] = __float2bfloat16(fmaf(fmaxf(m + bias, 0.f), scale, shift));
+                    }
+                }
+#pragma unroll
+                for (int x = 0; x < kP; ++x) { h0[x] = h1[x]; h1[x] = h2[x]; }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemColsB1);
+    }
+}
+
+}  // namespace
+
+int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
+    if (m->S != kS || m->C1 != kC1) return GN_E_SHAPE;
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(visbl_block1_tc_kernel)))
+        GN_CUDA(cudaFuncSetAttribute(visbl_block1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kB1Smem));
+    const int64_t cap = (int64_t)m->h->num_sms * 2;
+    const int grid = (int)(n < cap ? n : cap);
+    if (grid <= 0) return GN_OK;
+    visbl_block1_tc_kernel<<<grid, kBT, kB1Smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0], m->bn_shift[0],
+                                                        ws.a1p);
+    GN_LAUNCHED(m->h);
+    return GN_OK;
+}

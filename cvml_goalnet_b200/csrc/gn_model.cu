@@ -380,7 +380,7 @@ static int avm_forward_impl(gn_model* m, const float* d_visual, const float* d_a
     if (ws.bytes > ws_bytes) return GN_E_WORKSPACE;
     cudaStream_t st = gn_stream(stream);
     GN_STAGE_MARK(m, 0, st);
-    int rc = gn_launch_visbl_front(m, d_visual, n, ws, st);
+    int rc = gn_launch_visbl_front(m, d_visual, n, ws, st, simt);
     if (rc) return rc;
     GN_STAGE_MARK(m, 1, st);
     rc = gn_launch_audbl(m, d_audio, n, ws, st, simt);
