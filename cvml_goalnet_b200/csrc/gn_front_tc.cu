@@ -7,14 +7,14 @@
 // frame is scattered once into a K-major, 128-byte-swizzled patch matrix (one 128-byte row = the 27 taps of a conv
 // pixel, padded to 32) and the convolution is one tcgen05 GEMM per frame:
 //     D[channel][pixel] = sum_k W[channel][k] * patch[pixel][k]        M = 128, N = 240, K = 32, kind::tf32
-//   * rows (TMEM lanes) = channels -- the 64 channels twice, so that all four warps of the CTA have lanes to read;
+//   * rows (TMEM lanes) = channels -- the 64 channels twice, so that every lane quarter has rows to read;
 //     columns = conv pixels at 16 y + x (a conv row starts on a 16-column boundary): a thread owns one channel and
-//     walks down the conv rows of its half of the image, so the separable 3x3/s1 max pool, bias + ReLU (monotone:
+//     walks down the conv rows of its quarter of the image, so the separable 3x3/s1 max pool, bias + ReLU (monotone:
 //     they commute with the max) and the BatchNorm affine all happen in registers -- no staging tile in shared memory;
 //   * fp32 accuracy from TF32 tensor cores: both operands are split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and
 //     three MMAs accumulate hi*hi + lo*hi + hi*lo (the dropped lo*lo term is 2^-22 relative): the inputs of this layer
 //     are normalised pixels whose fp32 precision the CUDA-core kernel kept, and the parity budget is spent elsewhere.
-// One CTA = 128 threads, 256 TMEM columns, ~105 KB of shared memory -> two CTAs per SM overlap each other's phases
+// One CTA = 256 threads, 256 TMEM columns, ~105 KB of shared memory -> two CTAs per SM overlap each other's phases
 // (scatter / MMA / epilogue); the next frame's pixels travel to registers during the MMA and the epilogue.
 #include "gn_common.cuh"
 #include "gn_tc_ptx.cuh"
@@ -27,15 +27,22 @@ constexpr int kS = 40;               // frame side (reference utils.py:285)
 constexpr int kC1 = 15;              // conv1 output side: (40 + 2*3 - 3)/3 + 1
 constexpr int kP = kC1 - 2;          // pooled side
 constexpr int kNPix = 16 * kC1;      // GEMM N: conv pixel (y, x) is column 16 y + x
-constexpr int kBT = 128;             // threads
+constexpr int kBT = 256;             // threads: 8 warps (warp w reads TMEM lanes 32 (w & 3) ..)
 constexpr int kBBytes = kNPix * 128; // one patch matrix (hi or lo)
 constexpr int kABytes = 128 * 128;   // one weight matrix (hi or lo): 128 rows = the 64 channels twice
 constexpr int kTmemColsB1 = 256;
-constexpr int kVec = 3 * kS * kS / 4, kPre = (kVec + kBT - 1) / kBT;
+constexpr int kRowVec = kS / 4;                     // float4 per image row
+constexpr int kGroups = 3 * kS / 3;                 // scatter groups of 3 image rows (30 float4: one warp pass)
+constexpr int kPre = kGroups / (kBT / 32);          // passes per warp and frame
+static_assert(kGroups % (kBT / 32) == 0 && 3 * kRowVec <= 32, "a warp pass = three image rows");
 constexpr size_t kB1Smem = 1024 + 2 * kBBytes + 2 * kABytes + sizeof(unsigned short) * 3 * kS * kS + 64;
 
 // float index of element (row r, k) in a K-major tile with 128-byte rows and the 128-byte swizzle
 __device__ __forceinline__ int sw_index(int r, int k) { return r * 32 + ((((k >> 2) ^ (r & 7))) << 2) + (k & 3); }
+// column of conv pixel px inside its row's 16-column block.  The hardware swizzle only sees row & 7, so pixels 8 apart
+// would share a bank pattern -- and they are exactly the ones two lanes of a scatter store hit together (lanes 6 apart
+// hold pixels 24 = 8 conv columns apart with the same tap): the upper eight columns are rotated by one.
+__host__ __device__ constexpr int px_col(int px) { return px < 8 ? px : 8 + ((px + 1) & 7); }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
@@ -73,7 +80,7 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
     }
     for (int e = tid; e < 3 * kS * kS; e += kBT) {
         const int ci = e / (kS * kS), r = e - ci * kS * kS, y = r / kS, x = r - y * kS;
-        dsto[e] = (unsigned short)sw_index(16 * (y / 3 + 1) + (x / 3 + 1), ci * 9 + (y % 3) * 3 + (x % 3));
+        dsto[e] = (unsigned short)sw_index(16 * (y / 3 + 1) + px_col(x / 3 + 1), ci * 9 + (y % 3) * 3 + (x % 3));
     }
     if (tid == 0) {
         mbar_init(smem_u32(bar), 1);
@@ -85,21 +92,24 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int ch = tid & 63, half = tid >> 6;                   // channel of this thread's TMEM lane; image half
+    // TMEM lane of this thread = 32 (warp & 3) + lane -> channel (lanes 64..127 repeat the channels); the four warps that
+    // share a channel set take a quarter of the pooled rows each
+    const int tl = 32 * (warp & 3) + lane, ch = tl & 63, rq = (tl >> 6) + 2 * (warp >> 2);
     const float bias = __ldg(b + ch), scale = __ldg(sc + ch), shift = __ldg(sh + ch);
-    const uint32_t taddr = tmem_base + ((uint32_t)(32 * warp) << 16);
-    const int y_begin = half == 0 ? 0 : 7;                      // pooled rows [y_begin, y_end) of this half
-    const int y_end = half == 0 ? 7 : kP;
+    const uint32_t taddr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+    const int y_begin = rq == 0 ? 0 : 1 + 3 * rq;               // pooled rows [y_begin, y_end): 0-3, 4-6, 7-9, 10-12
+    const int y_end = 4 + 3 * rq;
 
     // the next frame's pixels travel to registers while this frame is multiplied and pooled
+    // a warp pass covers three image rows (30 float4, lanes 30 and 31 idle): their taps differ in ky, so the stores of
+    // different rows do not systematically share banks
     float4 pre[kPre];
+    const bool lane_on = lane < 3 * kRowVec;
     auto prefetch = [&](int64_t f) {
         const float4* src = reinterpret_cast<const float4*>(vis + f * 3 * kS * kS);
 #pragma unroll
-        for (int v = 0; v < kPre; ++v) {
-            const int i = tid + v * kBT;
-            if (i < kVec) pre[v] = __ldg(src + i);
-        }
+        for (int v = 0; v < kPre; ++v)
+            if (lane_on) pre[v] = __ldg(src + (warp + v * (kBT / 32)) * (3 * kRowVec) + lane);
     };
     if ((int64_t)blockIdx.x < n) prefetch(blockIdx.x);
     uint32_t phase = 0;
@@ -107,8 +117,8 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
         // ---- scatter the frame into the patch matrices (the previous frame's MMAs have completed: every thread waited) ----
 #pragma unroll
         for (int v = 0; v < kPre; ++v) {
-            const int i = tid + v * kBT;
-            if (i < kVec) {
+            const int i = (warp + v * (kBT / 32)) * (3 * kRowVec) + lane;
+            if (lane_on) {
                 const uint2 o = *reinterpret_cast<const uint2*>(dsto + 4 * i);
                 const float x4[4] = {pre[v].x, pre[v].y, pre[v].z, pre[v].w};
                 const uint32_t o4[4] = {o.x & 0xffffu, o.x >> 16, o.y & 0xffffu, o.y >> 16};
@@ -155,7 +165,7 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
         __nv_bfloat16* ob = a1p + f * (int64_t)kC1 * kC1 * 64 + ch;
         float h0[kP], h1[kP];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) {
+        for (int i = 0; i < 6; ++i) {
             const int y = y_begin + i;                           // conv row (warp-uniform)
             if (y < y_end + 2) {
                 uint32_t r[16];
@@ -164,7 +174,8 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
                 float h2[kP];
 #pragma unroll
                 for (int x = 0; x < kP; ++x)
-                    h2[x] = fmaxf(fmaxf(__uint_as_float(r[x]), __uint_as_float(r[x + 1])), __uint_as_float(r[x + 2]));
+                    h2[x] = fmaxf(fmaxf(__uint_as_float(r[px_col(x)]), __uint_as_float(r[px_col(x + 1)])),
+                                  __uint_as_float(r[px_col(x + 2)]));
                 if (i >= 2) {
                     __nv_bfloat16* orow = ob + ((y - 1) * kC1 + 1) * 64;       // pooled row y - 2 -> padded row y - 1
 #pragma unroll
