@@ -11,9 +11,10 @@
 //     columns = conv pixels at 16 y + x (a conv row starts on a 16-column boundary): a thread owns one channel and
 //     walks down the conv rows of its quarter of the image, so the separable 3x3/s1 max pool, bias + ReLU (monotone:
 //     they commute with the max) and the BatchNorm affine all happen in registers -- no staging tile in shared memory;
-//   * fp32 accuracy from TF32 tensor cores: both operands are split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and
-//     three MMAs accumulate hi*hi + lo*hi + hi*lo (the dropped lo*lo term is 2^-22 relative): the inputs of this layer
-//     are normalised pixels whose fp32 precision the CUDA-core kernel kept, and the parity budget is spent elsewhere.
+//   * precision: operands are rounded to TF32 (cvt.rna).  On the oracle, rounding conv1's pixels and weights to TF32
+//     moves the scores by at most 1.3e-5 relative (512 frames, spread weights; the layer's output is rounded to bf16 for
+//     conv2 anyway) against the 1e-3 parity tolerance, so one MMA group is the default.  kSplit (GN_BLOCK1_SPLIT) keeps
+//     the fp32-accurate variant: x = hi + lo (hi = tf32(x), lo = tf32(x - hi)), three MMA groups hi*hi + lo*hi + hi*lo.
 // One CTA = 256 threads, 256 TMEM columns, ~105 KB of shared memory -> two CTAs per SM overlap each other's phases
 // (scatter / MMA / epilogue); the next frame's pixels travel to registers during the MMA and the epilogue.
 #include "gn_common.cuh"
@@ -35,7 +36,9 @@ constexpr int kRowVec = kS / 4;                     // float4 per image row
 constexpr int kGroups = 3 * kS / 3;                 // scatter groups of 3 image rows (30 float4: one warp pass)
 constexpr int kPre = kGroups / (kBT / 32);          // passes per warp and frame
 static_assert(kGroups % (kBT / 32) == 0 && 3 * kRowVec <= 32, "a warp pass = three image rows");
-constexpr size_t kB1Smem = 1024 + 2 * kBBytes + 2 * kABytes + sizeof(unsigned short) * 3 * kS * kS + 64;
+constexpr size_t b1_smem(bool split) {
+    return 1024 + (split ? 2 : 1) * (size_t)(kBBytes + kABytes) + sizeof(unsigned short) * 3 * kS * kS + 64;
+}
 
 // float index of element (row r, k) in a K-major tile with 128-byte rows and the 128-byte swizzle
 __device__ __forceinline__ int sw_index(int r, int k) { return r * 32 + ((((k >> 2) ^ (r & 7))) << 2) + (k & 3); }
@@ -54,29 +57,31 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+template <bool kSplit>
 __global__ void __launch_bounds__(kBT, 2)
 visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __restrict__ w /*[27][64], k=(ky*3+kx)*3+ci*/,
                        const float* __restrict__ b, const float* __restrict__ sc, const float* __restrict__ sh,
                        __nv_bfloat16* __restrict__ a1p) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    float* Bhi = reinterpret_cast<float*>(smem);                               // [240][32] patch matrix, hi parts
-    float* Blo = reinterpret_cast<float*>(smem + kBBytes);                     //           lo parts
-    float* Ahi = reinterpret_cast<float*>(smem + 2 * kBBytes);                 // [128][32] weights (64 channels twice)
-    float* Alo = reinterpret_cast<float*>(smem + 2 * kBBytes + kABytes);
-    unsigned short* dsto = reinterpret_cast<unsigned short*>(smem + 2 * kBBytes + 2 * kABytes);   // [4800] scatter offsets
+    constexpr int kParts = kSplit ? 2 : 1;
+    float* Bhi = reinterpret_cast<float*>(smem);                               // [240][32] patch matrix (hi parts)
+    float* Blo = reinterpret_cast<float*>(smem + kBBytes);                     //           lo parts (kSplit)
+    float* Ahi = reinterpret_cast<float*>(smem + kParts * kBBytes);            // [128][32] weights (64 channels twice)
+    float* Alo = reinterpret_cast<float*>(smem + kParts * kBBytes + kABytes);  //           lo parts (kSplit)
+    unsigned short* dsto = reinterpret_cast<unsigned short*>(smem + kParts * (kBBytes + kABytes));   // [4800] scatter offsets
     uint64_t* bar = reinterpret_cast<uint64_t*>(dsto + 3 * kS * kS);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // ---- once per CTA: zero patch matrices (padding pixels, pad column 15, k = 27..31 stay zero), weights, offsets ----
-    for (int i = tid; i < 2 * kNPix * 32; i += kBT) Bhi[i] = 0.f;              // Bhi | Blo are contiguous
+    for (int i = tid; i < kParts * kNPix * 32; i += kBT) Bhi[i] = 0.f;         // Bhi | Blo are contiguous
     for (int i = tid; i < 128 * 32; i += kBT) {
         const int m = i >> 5, k = i & 31, ch = m & 63;
         const float v = (k < 27) ? __ldg(w + ((k % 9) * 3 + k / 9) * 64 + ch) : 0.f;      // k = ci*9 + tap
         const float hi = gn_round_tf32(v);
         Ahi[sw_index(m, k)] = hi;
-        Alo[sw_index(m, k)] = gn_round_tf32(v - hi);
+        if (kSplit) Alo[sw_index(m, k)] = gn_round_tf32(v - hi);
     }
     for (int e = tid; e < 3 * kS * kS; e += kBT) {
         const int ci = e / (kS * kS), r = e - ci * kS * kS, y = r / kS, x = r - y * kS;
@@ -126,7 +131,7 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
                 for (int j = 0; j < 4; ++j) {
                     const float hi = gn_round_tf32(x4[j]);
                     Bhi[o4[j]] = hi;
-                    Blo[o4[j]] = gn_round_tf32(x4[j] - hi);
+                    if (kSplit) Blo[o4[j]] = gn_round_tf32(x4[j] - hi);
                 }
             }
         }
@@ -137,9 +142,9 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
             tc_fence_after();
             constexpr uint32_t idesc = make_idesc_tf32(128, kNPix);
             const uint32_t ahi = smem_u32(Ahi), alo = smem_u32(Alo), bhi = smem_u32(Bhi), blo = smem_u32(Blo);
-            // hi*hi + lo*hi + hi*lo
+            // hi*hi (+ lo*hi + hi*lo)
 #pragma unroll
-            for (int p = 0; p < 3; ++p) {
+            for (int p = 0; p < (kSplit ? 3 : 1); ++p) {
                 const uint32_t aa = (p == 1) ? alo : ahi, bb = (p == 2) ? blo : bhi;
 #pragma unroll
                 for (int k4 = 0; k4 < 4; ++k4)
@@ -201,13 +206,15 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
 
 int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
     if (m->S != kS || m->C1 != kC1) return GN_E_SHAPE;
-    if (gn_attr_first(m->h, reinterpret_cast<const void*>(visbl_block1_tc_kernel)))
-        GN_CUDA(cudaFuncSetAttribute(visbl_block1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kB1Smem));
+    static const bool split = getenv("GN_BLOCK1_SPLIT") != nullptr;
+    auto kern = split ? visbl_block1_tc_kernel<true> : visbl_block1_tc_kernel<false>;
+    const size_t smem = b1_smem(split);
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(kern)))
+        GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t cap = (int64_t)m->h->num_sms * 2;
     const int grid = (int)(n < cap ? n : cap);
     if (grid <= 0) return GN_OK;
-    visbl_block1_tc_kernel<<<grid, kBT, kB1Smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0], m->bn_shift[0],
-                                                        ws.a1p);
+    kern<<<grid, kBT, smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0], m->bn_shift[0], ws.a1p);
     GN_LAUNCHED(m->h);
     return GN_OK;
 }
