@@ -226,6 +226,32 @@ def test_model_vs_oracle_and_simt(U, weights, n):
     assert np.abs(h0_tc[:, :128] - ra).max() <= 2e-3 * max(np.abs(ra).max(), 1e-3)   # TF32 AudBl GEMMs, TF32-rounded store
 
 
+def test_block1_tensor_core_kernel_vs_cuda_core_kernel_and_oracle(U, weights):
+    """VisBl block 1 (utils.py:174-177) of the 40x40 model runs as one tcgen05 TF32 GEMM per frame (gn_front_tc.cu); the
+    CUDA-core kernel (fp32 operands) is the validation path.  Both against the oracle's block-1 output, and against each
+    other, on a frame count that is neither a multiple of the grid nor of two; all-black and all-white frames included
+    (min == max: the normalisation's 1e-7 guard, utils.py:284)."""
+    n = 601
+    frames = syn.make_frames(n, 48, 48, seed=5)
+    frames[7] = 0
+    frames[8] = 255
+    vis = O.extract_condensed_frame_tensor_array(frames, 40)
+    aud = np.zeros((n, 30, 30), np.float32)
+    m = _model(U, weights)
+    m(aud, vis)
+    a_tc = m.read_activation(1, n).cpu().numpy()
+    m(aud, vis, _simt=True)
+    a_simt = m.read_activation(1, n).cpu().numpy()
+    _, feats = O.avm_forward(weights, aud, vis, return_features=True)
+    assert a_tc.shape == a_simt.shape == (n, 64, 13, 13)
+    scale = np.abs(a_simt).max()
+    # the stored activations are bf16: TF32 operand rounding can move a value across a bf16 rounding boundary (2^-8)
+    assert np.abs(a_tc - a_simt).max() <= 2.0 ** -7 * scale
+    r = feats["vis1"].numpy()
+    for a in (a_tc, a_simt):                   # one bf16 rounding of the output (2^-9 relative) + the operand rounding
+        assert np.abs(a - r).max() <= 2.0 ** -8 * np.abs(r).max()
+
+
 @pytest.mark.parametrize("S,n", [(64, 5), (100, 3), (46, 130), (224, 2)])
 def test_model_other_frame_sizes_tiled_conv_and_splitk(U, S, n):
     """Frame sizes other than the reference's 40 (R224 = BASELINE config 5; legal because every layer of the
