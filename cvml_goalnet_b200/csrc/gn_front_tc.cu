@@ -15,7 +15,7 @@
 //     moves the scores by at most 1.3e-5 relative (512 frames, spread weights; the layer's output is rounded to bf16 for
 //     conv2 anyway) against the 1e-3 parity tolerance, so one MMA group is the default.  kSplit (GN_BLOCK1_SPLIT) keeps
 //     the fp32-accurate variant: x = hi + lo (hi = tf32(x), lo = tf32(x - hi)), three MMA groups hi*hi + lo*hi + hi*lo.
-// One CTA = 256 threads, 256 TMEM columns, ~105 KB of shared memory -> two CTAs per SM overlap each other's phases
+// One CTA = 256 threads, 256 TMEM columns, 56 KB of shared memory (105 KB with kSplit) -> two CTAs per SM (TMEM-limited) overlap each other's phases
 // (scatter / MMA / epilogue); the next frame's pixels travel to registers during the MMA and the epilogue.
 #include "gn_common.cuh"
 #include "gn_tc_ptx.cuh"
