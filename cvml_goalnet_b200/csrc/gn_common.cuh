@@ -135,6 +135,7 @@ int gn_linear5_splits(const gn_model* m);   // gn_tc_gemm.cu: number of K ranges
 int gn_launch_visbl_front(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt = false);
 int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st);   // gn_front_tc.cu
 int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st, bool simt);
+int gn_launch_audbl_conv1_tc(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st);   // gn_front_tc.cu
 int gn_launch_tc_audbl(gn_model* m, int64_t n, const gn_ws& ws, cudaStream_t st);   // conv2 + linear3 on tensor cores
 int gn_launch_tc_backbone(gn_model* m, int64_t n, const gn_ws& ws, float* d_scores, float* d_visfeat,
                           cudaStream_t st, const gn_score_sink* sink = nullptr);

@@ -1,5 +1,7 @@
 // CUDA-core front layers of the AVM forward (fp32 math; they are <0.5 % of the FLOPs and their inputs
-// need fp32 range/precision: normalised pixels and raw MFCCs).
+// need fp32 range/precision: normalised pixels and raw MFCCs).  For the reference's shapes (40x40 frames, 30 time bins)
+// the default path runs both layers on the tensor cores instead (gn_front_tc.cu); these kernels serve other shapes, the
+// validation path (gn_dbg_avm_forward_simt) and the GN_BLOCK1_SIMT / GN_AUDBL_SIMT switches.
 //   * VisBl block 1: conv1 3->64 k3 s3 p3 + ReLU + MaxPool(3,1) + BatchNorm(eval)  (utils.py:174-177)
 //     -> bf16 NHWC with a zero border (the padding=1 input of conv2);
 //   * AudBl: conv1d 30->64 s2, conv1d 64->128 s2, linear -> 128, ReLUs             (utils.py:216-225)
@@ -425,6 +427,13 @@ int gn_launch_audbl(gn_model* m, const float* d_audio, int64_t n, const gn_ws& w
                                                     m->aconv2_w, m->aconv2_b, m->alinear3_w, m->alinear3_b, ws.h0, m->fin);
         GN_LAUNCHED(m->h);
         return GN_OK;
+    }
+    // the reference's 30 time bins: conv1 on the tensor cores too (gn_front_tc.cu); GN_AUDBL_SIMT keeps the CUDA-core kernel
+    static const bool conv1_simt = getenv("GN_AUDBL_SIMT") != nullptr;
+    if (m->B == 30 && m->L1 == 15 && !conv1_simt) {
+        const int rc = gn_launch_audbl_conv1_tc(m, d_audio, n, ws, st);
+        if (rc) return rc;
+        return gn_launch_tc_audbl(m, n, ws, st);
     }
     const size_t smem = sizeof(float) * 2 * (kCF / 2) * (m->B + 2) * 64;      // two staging buffers
     if (smem > 48 * 1024) return GN_E_SHAPE;

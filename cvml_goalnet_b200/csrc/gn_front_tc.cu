@@ -202,6 +202,170 @@ visbl_block1_tc_kernel(const float* __restrict__ vis, int64_t n, const float* __
     }
 }
 
+
+// =====================================================================================================================
+// AudBl conv1 (conv1d 30 -> 64, k3 s2 p1) + ReLU on the tensor cores (utils.py:216-217), for the reference's 30 time
+// bins (15 output positions).  The CUDA-core kernel (gn_front.cu) is bound by the LSU: every (frame pair, position)
+// task of a warp reads its 90 inputs as 45 broadcast 16-byte loads, two wavefronts each (ncu: LSU data pipe 67 %).
+// Here 8 frames are scattered into an im2col matrix (row = 16 frame + position, K = ci*3 + k padded 90 -> 96: three
+// 128-byte-swizzled k-blocks; an input lands in one or two rows because the windows overlap) and multiplied by the
+// weights in one tcgen05 kind::tf32 GEMM group, M = 128, N = 64, K = 96.
+// Precision: the raw MFCCs span +-600 and plain TF32 operands would cost 1.5e-4 of the 1e-3 score tolerance (oracle
+// experiment), so BOTH operands are split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and three groups accumulate
+// hi*hi + lo*hi + hi*lo (the dropped lo*lo term is 2^-22 relative): fp32-equivalent, as the CUDA-core kernel.
+// Epilogue: lane = (frame, position) row of D, 32 channels per warp: + bias, ReLU, TF32 rounding (the next GEMM's operand
+// format), written as (position, channel) rows with the zero row on each side that the tensor-core conv2 reads.
+// =====================================================================================================================
+constexpr int kAB = 30;                    // time bins (utils.py:313: bin_length)
+constexpr int kAL1 = 15;                   // conv1 output positions
+constexpr int kAFr = 8;                    // frames per M tile: 8 x 16 rows
+constexpr int kAIn = 30 * kAB;             // inputs per frame
+constexpr int kAT = 256;                   // threads
+constexpr int kAPre = (kAFr * kAIn + kAT - 1) / kAT;
+constexpr int kAMat = 3 * 128 * 32;        // floats of one im2col matrix (3 k-blocks x 128 rows x 32)
+constexpr int kAWMat = 3 * 64 * 32;        // floats of one weight matrix
+constexpr size_t kAudSmem = 1024 + sizeof(float) * (2 * kAMat + 2 * kAWMat) + sizeof(uint32_t) * kAIn + sizeof(float) * 64 + 64;
+
+__global__ void __launch_bounds__(kAT, 1)
+audbl_conv1_tc_kernel(const float* __restrict__ aud, int64_t n, const float* __restrict__ w1 /*[64][30][3]*/,
+                      const float* __restrict__ b1, float* __restrict__ ac1 /*[n][17][64]*/) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* Ahi = reinterpret_cast<float*>(smem);               // [3][128][32] im2col, hi parts
+    float* Alo = Ahi + kAMat;
+    float* Whi = Alo + kAMat;                                  // [3][64][32] weights
+    float* Wlo = Whi + kAWMat;
+    uint32_t* dst2 = reinterpret_cast<uint32_t*>(Wlo + kAWMat);    // [900] two 16-bit im2col offsets per input (0xffff = none)
+    float* sbias = reinterpret_cast<float*>(dst2 + kAIn);      // [64]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sbias + 64);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- once per CTA ----
+    for (int i = tid; i < 2 * kAMat; i += kAT) Ahi[i] = 0.f;   // padding (t = -1), pad rows (position 15) and k = 90..95 stay zero
+    for (int i = tid; i < 64 * 96; i += kAT) {
+        const int co = i / 96, kk = i - co * 96;
+        const float v = kk < 90 ? __ldg(w1 + co * 90 + kk) : 0.f;
+        const float hi = gn_round_tf32(v);
+        const int o = (kk >> 5) * (64 * 32) + sw_index(co, kk & 31);
+        Whi[o] = hi;
+        Wlo[o] = gn_round_tf32(v - hi);
+    }
+    for (int e = tid; e < kAIn; e += kAT) {
+        // input (ci, t) is tap k of position l where t = 2 l - 1 + k: t even -> (t/2, 1); t odd -> ((t+1)/2, 0) and ((t-1)/2, 2)
+        const int ci = e / kAB, t = e - ci * kAB;
+        auto off = [&](int l, int k) -> uint32_t {
+            if (l < 0 || l >= kAL1) return 0xffffu;
+            const int kk = ci * 3 + k;
+            return (uint32_t)((kk >> 5) * (128 * 32) + sw_index(l, kk & 31));
+        };
+        const uint32_t d0 = (t & 1) ? off((t + 1) >> 1, 0) : off(t >> 1, 1);
+        const uint32_t d1 = (t & 1) ? off((t - 1) >> 1, 2) : 0xffffu;
+        dst2[e] = d0 | (d1 << 16);
+    }
+    if (tid < 64) sbias[tid] = __ldg(b1 + tid);
+    if (tid == 0) {
+        mbar_init(smem_u32(bar), 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // the next tile's inputs travel to registers while this tile is multiplied and written out
+    float pre[kAPre];
+    auto prefetch = [&](int64_t f0) {
+        const int64_t lim = (n - f0) * kAIn;                   // inputs of frames beyond the batch read as silence
+        const float* src = aud + f0 * kAIn;
+#pragma unroll
+        for (int v = 0; v < kAPre; ++v) {
+            const int i = tid + v * kAT;
+            pre[v] = (i < kAFr * kAIn && i < lim) ? __ldg(src + i) : 0.f;
+        }
+    };
+    const int64_t tiles = (n + kAFr - 1) / kAFr;
+    if ((int64_t)blockIdx.x < tiles) prefetch((int64_t)blockIdx.x * kAFr);
+    uint32_t phase = 0;
+    for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int64_t f0 = tile * kAFr;
+        // ---- scatter (the previous tile's MMAs have completed: every thread waited on the barrier) ----
+#pragma unroll
+        for (int v = 0; v < kAPre; ++v) {
+            const int i = tid + v * kAT;
+            if (i < kAFr * kAIn) {
+                const int j = i / kAIn, e = i - j * kAIn;
+                const uint32_t d = dst2[e];
+                const float x = pre[v], hi = gn_round_tf32(x), lo = gn_round_tf32(x - hi);
+                const int fo = j * (16 * 32);                  // 16 rows per frame (16 j = 0 mod 8: the swizzle phase is unchanged)
+                const uint32_t d0 = d & 0xffffu, d1 = d >> 16;
+                if (d0 != 0xffffu) { Ahi[fo + d0] = hi; Alo[fo + d0] = lo; }
+                if (d1 != 0xffffu) { Ahi[fo + d1] = hi; Alo[fo + d1] = lo; }
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            constexpr uint32_t idesc = make_idesc_tf32(128, 64);
+            const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo), w_hi = smem_u32(Whi), w_lo = smem_u32(Wlo);
+#pragma unroll
+            for (int p = 0; p < 3; ++p) {                       // hi*hi + lo*hi + hi*lo
+                const uint32_t aa = (p == 1) ? a_lo : a_hi, ww = (p == 2) ? w_lo : w_hi;
+#pragma unroll
+                for (int kb = 0; kb < 3; ++kb)
+#pragma unroll
+                    for (int k8 = 0; k8 < 4; ++k8)
+                        umma_tf32(tmem_base, make_desc_sw128(aa + kb * (128 * 128) + k8 * 32),
+                                  make_desc_sw128(ww + kb * (64 * 128) + k8 * 32), idesc, (p > 0 || kb > 0 || k8 > 0) ? 1u : 0u);
+            }
+            umma_commit(smem_u32(bar));
+        }
+        if (tile + gridDim.x < tiles) prefetch((tile + gridDim.x) * kAFr);
+        mbar_wait(smem_u32(bar), phase);
+        phase ^= 1;
+        tc_fence_after();
+        // ---- epilogue: lane = row (frame j, position l) of D; the two warps of a lane quarter take 32 channels each ----
+        {
+            const int q = warp & 3, ch0 = 32 * (warp >> 2);
+            const int r = 32 * q + lane, j = r >> 4, l = r & 15;
+            uint32_t acc[32];
+            tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)ch0, acc);
+            tmem_ld_wait();
+            const int64_t f = f0 + j;
+            if (f < n) {
+                float* o = ac1 + f * (int64_t)(kAL1 + 2) * 64 + ch0;
+                if (l < kAL1) {
+                    float4* orow = reinterpret_cast<float4*>(o + (l + 1) * 64);
+                    const float4* bb = reinterpret_cast<const float4*>(sbias + ch0);
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) {
+                        const float4 bv = bb[v];
+                        orow[v] = make_float4(gn_round_tf32(fmaxf(__uint_as_float(acc[4 * v]) + bv.x, 0.f)),
+                                              gn_round_tf32(fmaxf(__uint_as_float(acc[4 * v + 1]) + bv.y, 0.f)),
+                                              gn_round_tf32(fmaxf(__uint_as_float(acc[4 * v + 2]) + bv.z, 0.f)),
+                                              gn_round_tf32(fmaxf(__uint_as_float(acc[4 * v + 3]) + bv.w, 0.f)));
+                    }
+                } else {
+                    // the pad row's lane writes the zero rows on either side of the frame's positions
+                    float4* z0 = reinterpret_cast<float4*>(o);
+                    float4* z1 = reinterpret_cast<float4*>(o + (kAL1 + 1) * 64);
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) { z0[v] = make_float4(0.f, 0.f, 0.f, 0.f); z1[v] = make_float4(0.f, 0.f, 0.f, 0.f); }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 64);
+    }
+}
+
 }  // namespace
 
 int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, const gn_ws& ws, cudaStream_t st) {
@@ -215,6 +379,18 @@ int gn_launch_visbl_block1_tc(gn_model* m, const float* d_visual, int64_t n, con
     const int grid = (int)(n < cap ? n : cap);
     if (grid <= 0) return GN_OK;
     kern<<<grid, kBT, smem, st>>>(d_visual, n, m->conv1_w, m->conv1_b, m->bn_scale[0], m->bn_shift[0], ws.a1p);
+    GN_LAUNCHED(m->h);
+    return GN_OK;
+}
+
+int gn_launch_audbl_conv1_tc(gn_model* m, const float* d_audio, int64_t n, const gn_ws& ws, cudaStream_t st) {
+    if (m->B != kAB || m->L1 != kAL1) return GN_E_SHAPE;
+    if (gn_attr_first(m->h, reinterpret_cast<const void*>(audbl_conv1_tc_kernel)))
+        GN_CUDA(cudaFuncSetAttribute(audbl_conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kAudSmem));
+    const int64_t tiles = (n + kAFr - 1) / kAFr;
+    const int grid = (int)(tiles < m->h->num_sms ? tiles : m->h->num_sms);
+    if (grid <= 0) return GN_OK;
+    audbl_conv1_tc_kernel<<<grid, kAT, kAudSmem, st>>>(d_audio, n, m->aconv1_w, m->aconv1_b, ws.ac1);
     GN_LAUNCHED(m->h);
     return GN_OK;
 }
